@@ -1,0 +1,263 @@
+/*
+ * gsb200.h — C-ABI of libgsb200.so, the B200 (sm_100a) Gaussian-splatting training hot path.
+ *
+ * The reference (uc-vision/splat-trainer) is pure Python and has no FFI of its own: every
+ * kernel on its hot path lives in the un-vendored dependency `taichi-splatting >= 0.31.0`
+ * (reference pyproject.toml:14).  The entry points below are therefore what a binding for
+ * that dependency's *call sites* needs; each one cites the reference call site it serves.
+ * SURVEY.md §8(b) is the contract this header implements.
+ *
+ * Conventions
+ *   - every pointer is a raw DEVICE pointer unless the name starts with `h_`;
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, nothing
+ *     synchronises the host unless the comment says so;
+ *   - the library allocates nothing persistent and keeps no global state: the caller
+ *     (PyTorch's caching allocator) owns every buffer incl. workspaces (size query first);
+ *   - every function returns 0 on success or a negative gs_status; the text of the last
+ *     error on the calling thread is returned by gs_last_error();
+ *   - all floating point is fp32; quaternions are xyzw (reference scene/io.py:45,104);
+ *   - images are H×W×C row-major, pixel centres at (+0.5,+0.5);
+ *   - "rows": the tile mapper / rasteriser work on M rows of projected splats.  In the
+ *     fused scene path M = N (row i = Gaussian i, culled rows carry opacity 0); in the
+ *     operator path (project_to_image → render_projected) M = V compacted rows.
+ */
+#ifndef GSB200_H
+#define GSB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSB200_VERSION 100          /* 0.1.0 */
+#define GS_TILE 16                  /* tile edge in pixels (only supported value) */
+#define GS_G2D_STRIDE 6             /* floats per projected row: mean.x mean.y conic.a conic.b conic.c opacity */
+
+typedef enum gs_status {
+  GS_OK = 0,
+  GS_ERR_INVALID = -1,              /* bad argument                                   */
+  GS_ERR_CUDA = -2,                 /* a CUDA call / launch failed (see gs_last_error) */
+  GS_ERR_WORKSPACE = -3,            /* workspace too small                            */
+  GS_ERR_UNSUPPORTED = -4           /* e.g. channel count not instantiated            */
+} gs_status;
+
+/* CameraParams of the reference (trainer/trainer.py:291-301, camera_table/camera_table.py:167-175). */
+typedef struct gs_camera {
+  float T_camera_world[16];         /* row-major 4×4, x_cam = R x_world + t            */
+  float fx, fy, cx, cy;             /* CameraParams.projection                        */
+  int32_t width, height;            /* CameraParams.image_size = (W, H)               */
+  float near_plane, far_plane;      /* config/trainer/default.yaml:83-84              */
+} gs_camera;
+
+/* RasterConfig: the four names the reference passes (trainer/trainer.py:308-310,
+ * scene/mlp_scene.py:373) plus the constants SURVEY Appendix A lists. */
+typedef struct gs_raster_config {
+  int32_t tile_size;                /* 16                                             */
+  float alpha_threshold;            /* 1/255: contributions below are skipped         */
+  float clamp_max_alpha;            /* 0.99                                           */
+  float saturate_threshold;         /* 0.9999: stop a pixel once T < 1 - this         */
+  float blur_cov;                   /* 0.3 px² added to the 2-D covariance diagonal   */
+  int32_t antialias;                /* opacity *= sqrt(det Σ / det(Σ+blur))           */
+  int32_t compute_visibility;       /* forward accumulates Σ α·T per row              */
+  int32_t compute_point_heuristic;  /* backward writes prune_cost / split_score       */
+  int32_t render_median_depth;      /* forward writes depth of first splat with T<½   */
+  float frustum_clamp;              /* 1.3: |x/z| clamp (× half-FOV tangent) in the Jacobian */
+} gs_raster_config;
+
+void gs_default_raster_config(gs_raster_config *cfg);
+int gs_version(void);
+const char *gs_last_error(void);
+
+/* ---------------------------------------------------------------------------------------
+ * (1) 3D→2D projection + SH colour.   Serves taichi_splatting.project_to_image
+ *     (reference scene/mlp_scene.py:415, :375) and evaluate_sh_at (scene/transfer_sh.py:49).
+ *     Row i of the outputs belongs to Gaussian i.  Culled Gaussians (outside near/far,
+ *     degenerate covariance, opacity <= alpha_threshold, or no tile touched) get
+ *     g2d = {0,0,1,0,1,0}, depth = +inf, rgb = 0.
+ *     sh: (n,3,K) with K=(deg+1)^2, basis order/sign = rsh_cart_3 (scene/mlp/rsh.py:110-157),
+ *     colour = 0.5 + Σ_k Y_k(dir) sh[c][k] (util/misc.py:41-49). sh may be NULL (rgb untouched).
+ *     acc (nullable): the raster-backward accumulator (n × acc_stride); rows of in-view
+ *     Gaussians are zeroed here so no separate memset is needed.
+ * ------------------------------------------------------------------------------------- */
+int gs_project_fwd(const gs_camera *h_cam, const gs_raster_config *h_cfg, int64_t n,
+                   const float *position, const float *log_scaling, const float *rotation,
+                   const float *alpha_logit, const float *sh, int sh_degree,
+                   float *g2d, float *depth, float *rgb,
+                   float *acc, int acc_stride, void *stream);
+
+/* Backward of gs_project_fwd.  d_g2d (row stride d_g2d_stride floats, 6 used),
+ * d_rgb (stride d_rgb_stride, 3 used), d_depth (nullable, n) are dL/d(outputs).
+ * Gradients are ADDED into g_* when accumulate != 0 (batch = sum, reference
+ * trainer/trainer.py:500-514), else written for in-view rows only (culled rows untouched). */
+int gs_project_bwd(const gs_camera *h_cam, const gs_raster_config *h_cfg, int64_t n,
+                   const float *position, const float *log_scaling, const float *rotation,
+                   const float *alpha_logit, const float *sh, int sh_degree,
+                   const float *g2d,
+                   const float *d_g2d, int d_g2d_stride,
+                   const float *d_rgb, int d_rgb_stride,
+                   const float *d_depth,
+                   float *g_position, float *g_log_scaling, float *g_rotation,
+                   float *g_alpha_logit, float *g_sh, int accumulate, void *stream);
+
+/* evaluate_sh_at(sh (n,3,K), positions (n,3), indexes (v), cam_pos (3)) -> (v,3)
+ * (reference scene/transfer_sh.py:49).  indexes are int64 (torch default); NULL = arange. */
+int gs_sh_eval_fwd(int64_t v, const int64_t *indexes, const float *sh, int sh_degree,
+                   const float *position, const float *h_cam_pos, float *rgb, void *stream);
+int gs_sh_eval_bwd(int64_t v, const int64_t *indexes, const float *sh, int sh_degree,
+                   const float *position, const float *h_cam_pos, const float *d_rgb,
+                   float *g_sh, float *g_position, void *stream);
+
+/* ---------------------------------------------------------------------------------------
+ * (2) Tile-overlap mapping: (tile, depth) key sort + tile ranges.  Serves the mapper inside
+ *     taichi_splatting.render_projected (reference scene/mlp_scene.py:418, :377).
+ *     The result equals a stable sort of all (row, tile) overlaps by the 64-bit key
+ *     (tile_id << 32 | float_bits(depth)), ties broken by row index.  It is computed as a
+ *     stable 32-bit LSD radix sort of rows by depth followed by a stable radix sort of the
+ *     emitted overlaps by tile id, which moves 4–5× fewer bytes.
+ *       overlap_to_point[o]  row index of the o-th sorted overlap        (max_overlaps)
+ *       tile_ranges[2t,2t+1] [begin,end) of tile t in overlap_to_point   (tiles_x*tiles_y*2)
+ *       counters[0] = total overlaps O (may exceed max_overlaps: then counters[1] = 1 and
+ *                     only the ranges/lists of the first max_overlaps emitted pairs are valid)
+ * ------------------------------------------------------------------------------------- */
+size_t gs_tile_map_workspace_bytes(int64_t m, int64_t max_overlaps, int width, int height);
+int gs_tile_map(const gs_raster_config *h_cfg, int64_t m, const float *g2d, const float *depth,
+                int width, int height, int64_t max_overlaps,
+                void *workspace, size_t workspace_bytes,
+                int32_t *overlap_to_point, int32_t *tile_ranges, int32_t *counters,
+                void *stream);
+/* Count only: tiles touched per row (m) and their total (counters[0]); used by the
+ * drop-in path to size overlap buffers exactly (the reference reads the total back too). */
+int gs_tile_count(const gs_raster_config *h_cfg, int64_t m, const float *g2d, const float *depth,
+                  int width, int height, int32_t *counts, int32_t *counters, void *stream);
+
+/* Stable LSD radix sort of (key,value) u32 pairs on bits [begin_bit,end_bit).  n may be given
+ * on the host (n_dev == NULL) or as a device scalar bounded by n (grid sizing uses n).
+ * keys_out/vals_out receive the result; keys_in/vals_in are clobbered (ping-pong). */
+size_t gs_radix_sort_workspace_bytes(int64_t n);
+int gs_radix_sort_pairs(uint32_t *keys_in, uint32_t *vals_in, uint32_t *keys_out, uint32_t *vals_out,
+                        int64_t n, const int32_t *n_dev, int begin_bit, int end_bit,
+                        void *workspace, size_t workspace_bytes, void *stream);
+
+/* ---------------------------------------------------------------------------------------
+ * (3) Forward rasterisation: front-to-back alpha compositing per 16×16 tile, splat records
+ *     staged in shared memory, block-level early termination.  (render_projected,
+ *     reference scene/mlp_scene.py:418; flags trainer/trainer.py:308-310,319.)
+ *       image (H,W,C), final_T (H,W) transmittance left, n_contrib (H,W) 1+index (within
+ *       the tile list) of the last blended splat, visibility (m, nullable) += Σ α·T,
+ *       median_depth (H,W, nullable) depth of the splat that takes T below ½ (0 if none).
+ *     channels ∈ {1,3,4}.
+ * ------------------------------------------------------------------------------------- */
+int gs_raster_fwd(const gs_raster_config *h_cfg, int channels, int64_t m,
+                  const float *g2d, const float *features, const float *depth,
+                  const int32_t *overlap_to_point, const int32_t *tile_ranges,
+                  int width, int height,
+                  float *image, float *final_T, int32_t *n_contrib,
+                  float *visibility, float *median_depth, void *stream);
+
+/* (4) Backward rasterisation: back-to-front re-composite, per-thread 2×2 pixels, warp
+ *     transpose-reduction, one vector of atomics per (warp, splat).  acc row layout
+ *     (acc_stride = gs_raster_acc_stride(channels) floats, must be zeroed by the caller or by
+ *     gs_project_fwd):  [0..5] dL/dg2d, [6..6+C) dL/dfeature, [6+C] prune_cost,
+ *     [7+C] split_score, [8+C] visibility (Σ α·T, same value the forward flag produces). */
+int gs_raster_acc_stride(int channels);
+int gs_raster_bwd(const gs_raster_config *h_cfg, int channels, int64_t m,
+                  const float *g2d, const float *features,
+                  const int32_t *overlap_to_point, const int32_t *tile_ranges,
+                  int width, int height,
+                  const float *final_T, const int32_t *n_contrib, const float *d_image,
+                  float *acc, int acc_stride, void *stream);
+
+/* L1 + MSE photometric loss against a target, fused with the reference's post-activation
+ * clamp(image,0,1) (scene/color_model.py:154-160; trainer/trainer.py:465-476):
+ *   loss = w_l1·mean|c−t| + w_mse·mean(c−t)², c = clamp(pred,0,1)
+ * d_pred receives dloss/dpred (0 where pred is outside [0,1]); sums[0] += Σ|c−t|,
+ * sums[1] += Σ(c−t)² (caller zeroes; divide by n for the means).  target is float [0,1] or,
+ * if target_u8 != NULL, uint8 scaled by 1/255 (trainer/trainer.py:548-553). */
+int gs_loss_l1_mse(int64_t n, const float *pred, const float *target, const uint8_t *target_u8,
+                   float w_l1, float w_mse, float *d_pred, float *sums, void *stream);
+
+/* ---------------------------------------------------------------------------------------
+ * (5) Optimiser, statistics, densification.
+ * ------------------------------------------------------------------------------------- */
+typedef struct gs_optim_config {
+  int32_t mode;                     /* 0 = Adam, 1 = LaProp (VisibilityAwareLaProp, scene/mlp_scene.py:58-60) */
+  float beta1, beta2, eps;
+  float vis_beta, vis_smooth;       /* config/scene/mlp.yaml:25-29                      */
+  float grad_clip;                  /* <= 0 disables                                    */
+  int32_t bias_correction;
+} gs_optim_config;
+
+enum { GS_GROUP_SCALAR = 0, GS_GROUP_VECTOR = 1, GS_GROUP_LOCAL_VECTOR = 2 };  /* config/scene/mlp.yaml:8-14 */
+enum { GS_POST_NONE = 0, GS_POST_NORMALIZE = 1, GS_POST_CLAMP = 2 };          /* scene/mlp_scene.py:236-237 */
+
+/* Per-point visibility state, once per optimiser step and before the group steps:
+ * for rows with visible[i] > 0: step[i] += 1; running_vis[i] = lerp(vis_beta). */
+int gs_optim_vis_update(const gs_optim_config *h_cfg, int64_t n, const float *visible,
+                        float *running_vis, float *step, void *stream);
+
+/* One parameter group (ParameterClass.step(visibility, indexes, basis), reference
+ * scene/mlp_scene.py:214-230).  Rows with visible[i] <= 0 are skipped (the reference's
+ * `indexes = visible.nonzero()` done in-kernel, no host sync).  exp_avg is n×dim;
+ * exp_avg_sq is n×dim for SCALAR, n for VECTOR / LOCAL_VECTOR.  LOCAL_VECTOR (dim 3)
+ * expresses gradient and update in the basis R(q)·diag(max(exp(s),1e-4)) (point_basis,
+ * gaussians/split.py:15-19) built from basis_log_scaling / basis_rotation.
+ * post: GS_POST_NORMALIZE renormalises each row, GS_POST_CLAMP clamps to [post_lo,post_hi].
+ * zero_grad != 0 clears the consumed gradient rows (reference zero_grad, :155-161). */
+int gs_optim_step(const gs_optim_config *h_cfg, int kind, int64_t n, int dim, float lr,
+                  float *param, float *grad, float *exp_avg, float *exp_avg_sq,
+                  const float *visible, const float *running_vis, const float *step,
+                  const float *basis_log_scaling, const float *basis_rotation,
+                  int post, float post_lo, float post_hi, int zero_grad, void *stream);
+
+/* PointState.add_rendering (reference controller/point_state.py:34-50) + MLPScene.add_rendering
+ * (scene/mlp_scene.py:242-244) for one rendering whose rows are Gaussians (fused path, idx=NULL)
+ * or listed by idx (m rows -> Gaussian idx[i]).  In-view rows: opacity (g2d[5]) > 0.
+ * screen scale = larger std-dev in px of the 2-D Gaussian (from the conic).
+ *   max_scale_px = max(.), points_in_view += (vis>0), visibility += vis, scene_visible += vis,
+ *   split_score = exp_lerp(split_alpha, old, new), prune_cost = exp_lerp(prune_alpha, old, new)
+ *   with exp_lerp(t,a,b) = m + log(lerp(e^(a-m), e^(b-m), t)), m = max(a,b) (util/misc.py:56-59).
+ * heur points at (prune_cost, split_score) pairs with row stride heur_stride; vis has stride vis_stride. */
+int gs_accumulate_stats(int64_t m, const int64_t *idx, const float *g2d,
+                        const float *vis, int vis_stride, const float *heur, int heur_stride,
+                        float split_alpha, float prune_alpha,
+                        float *prune_cost, float *split_score, float *max_scale_px,
+                        int16_t *points_in_view, float *visibility, float *scene_visible,
+                        void *stream);
+
+/* take_n (reference controller/target_controller.py:150-160): mask of the k smallest
+ * (descending=0) or largest values; ties at the threshold broken by lowest index, so exactly
+ * min(k,n) entries are set.  NaNs order last.  Radix select, no full sort. */
+size_t gs_select_topk_workspace_bytes(int64_t n);
+int gs_select_topk_mask(const float *values, int64_t n, int64_t k, int descending,
+                        uint8_t *mask, void *workspace, size_t workspace_bytes, void *stream);
+
+/* Stream compaction of rows (points[keep_mask], reference scene/mlp_scene.py:308): step 1 turns a
+ * byte mask into destination slots (slots[i] = rank among kept, or -1) and the kept count
+ * (count_dev[0]); step 2 moves any number of row arrays with those slots. */
+size_t gs_compact_workspace_bytes(int64_t n);
+int gs_compact_slots(const uint8_t *keep_mask, int64_t n, int32_t *slots, int32_t *count_dev,
+                     void *workspace, size_t workspace_bytes, void *stream);
+int gs_compact_rows(const void *src, void *dst, int64_t n, int row_bytes, const int32_t *slots,
+                    void *stream);
+
+/* split_gaussians_uniform(points[split_idx], k=2, random_axis=True) (reference
+ * gaussians/split.py:87-113) written to rows [out_offset, out_offset+2S) of the destination
+ * arrays: children at ∓sep along the sampled axis in the R·S basis, log_scaling[axis] +=
+ * log(1/sqrt 2).  axis ~ Multinomial(∝ max(exp(s),eps)) drawn by inverse CDF from uniform[s]
+ * (caller-supplied U[0,1) so every rank and the oracle draw the same axis); uniform == NULL
+ * selects argmax (random_axis=False).  The caller copies the remaining attributes
+ * (rotation, alpha_logit, feature) with gs_gather_rows(repeat=2). */
+int gs_split_positions(int64_t s, const int64_t *split_idx, const float *position,
+                       const float *log_scaling, const float *rotation, const float *uniform,
+                       float sep, float *out_position, float *out_log_scaling, int64_t out_offset,
+                       void *stream);
+/* dst[out_offset + i*repeat + r] = src[idx[i]] for r < repeat (repeat_interleave, gaussians/split.py:42-44) */
+int gs_gather_rows(const void *src, void *dst, int64_t s, const int64_t *idx, int row_bytes,
+                   int repeat, int64_t out_offset, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSB200_H */
