@@ -1,0 +1,88 @@
+// common.cuh — shared helpers for libgsb200 (sm_100a).  No torch types anywhere in csrc/.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/gsb200.h"
+
+#define GS_FULL 0xffffffffu
+
+void gs_set_error(const char *fmt, ...);
+
+#define GS_REQUIRE(cond, msg)                 \
+  do {                                        \
+    if (!(cond)) {                            \
+      gs_set_error("%s: %s", __func__, msg);  \
+      return GS_ERR_INVALID;                  \
+    }                                         \
+  } while (0)
+
+#define GS_LAUNCH_CHECK()                                                             \
+  do {                                                                                \
+    cudaError_t e__ = cudaGetLastError();                                             \
+    if (e__ != cudaSuccess) {                                                         \
+      gs_set_error("%s: CUDA error %s (%s:%d)", __func__, cudaGetErrorString(e__), __FILE__, __LINE__); \
+      return GS_ERR_CUDA;                                                             \
+    }                                                                                 \
+  } while (0)
+
+#define GS_CUDA(call)                                                                 \
+  do {                                                                                \
+    cudaError_t e__ = (call);                                                         \
+    if (e__ != cudaSuccess) {                                                         \
+      gs_set_error("%s: %s failed: %s", __func__, #call, cudaGetErrorString(e__));    \
+      return GS_ERR_CUDA;                                                             \
+    }                                                                                 \
+  } while (0)
+
+static inline int gs_div_up(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+static inline size_t gs_align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+// camera in kernel-parameter form
+struct CamDev {
+  float T[12];  // rows 0..2 of T_camera_world
+  float fx, fy, cx, cy;
+  int W, H;
+  float near_plane, far_plane;
+  float limx, limy;  // frustum clamp on x/z, y/z
+  float cam_pos[3];
+};
+
+struct CfgDev {
+  float thr, amax, tmin, blur;
+  int antialias;
+};
+
+static inline CamDev gs_make_cam(const gs_camera *c, const gs_raster_config *cfg) {
+  CamDev d;
+  for (int i = 0; i < 12; ++i) d.T[i] = c->T_camera_world[i];
+  d.fx = c->fx; d.fy = c->fy; d.cx = c->cx; d.cy = c->cy;
+  d.W = c->width; d.H = c->height;
+  d.near_plane = c->near_plane; d.far_plane = c->far_plane;
+  d.limx = cfg->frustum_clamp * 0.5f * (float)c->width / c->fx;
+  d.limy = cfg->frustum_clamp * 0.5f * (float)c->height / c->fy;
+  const float *T = c->T_camera_world;
+  for (int k = 0; k < 3; ++k) d.cam_pos[k] = -(T[k] * T[3] + T[4 + k] * T[7] + T[8 + k] * T[11]);
+  return d;
+}
+
+static inline CfgDev gs_make_cfg(const gs_raster_config *c) {
+  CfgDev d;
+  d.thr = c->alpha_threshold; d.amax = c->clamp_max_alpha;
+  d.tmin = 1.0f - c->saturate_threshold; d.blur = c->blur_cov; d.antialias = c->antialias;
+  return d;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(GS_FULL, v, o);
+  return v;
+}
+
+// ---- exclusive scan of int32 (scan.cu) -------------------------------------------------------
+// out[i] = sum_{j<i} in[idx ? idx[j] : j]; total (nullable) receives the full sum.
+// n_dev (nullable) bounds the element count on the device (<= n).  partials: >= gs_scan_partials(n) ints.
+int64_t gs_scan_partials(int64_t n);
+int gs_exclusive_scan_i32(const int32_t *in, const int32_t *idx, int32_t *out, int64_t n, const int32_t *n_dev,
+                          int32_t *partials, int32_t *total, cudaStream_t st);

@@ -1,0 +1,107 @@
+// footprint.cuh — tile footprint of one projected splat row ("Spec T" in DESIGN.md).
+//
+// Every operation is an explicit round-to-nearest IEEE intrinsic (no FMA contraction, IEEE
+// division and square root), so the tile lists are BIT-EXACT against the CPU oracle, which
+// evaluates the same sequence with gcc -ffp-contract=off.  The support of a splat is the set of
+// pixel centres where opacity·exp(-q/2) >= alpha_threshold, i.e. q <= k2 = 2·ln(opacity/thr):
+// an opacity-aware bound that is exact for the rasteriser's own alpha cut, so tile culling never
+// changes the image.  ln is evaluated by a fixed polynomial (det_logf) for the same reason.
+#pragma once
+#include "common.cuh"
+
+__device__ __forceinline__ float det_logf(float x) {
+  uint32_t b = __float_as_uint(x);
+  int e = (int)(b >> 23) - 127;
+  float m = __uint_as_float((b & 0x007fffffu) | 0x3f800000u);
+  if (m > 1.41421356f) { m = __fmul_rn(m, 0.5f); e += 1; }
+  float f = __fsub_rn(m, 1.0f);
+  float s = __fdiv_rn(f, __fadd_rn(2.0f, f));
+  float s2 = __fmul_rn(s, s);
+  float p = 0.11111111f;
+  p = __fadd_rn(__fmul_rn(p, s2), 0.14285715f);
+  p = __fadd_rn(__fmul_rn(p, s2), 0.2f);
+  p = __fadd_rn(__fmul_rn(p, s2), 0.33333334f);
+  p = __fadd_rn(__fmul_rn(p, s2), 1.0f);
+  float t = __fmul_rn(__fmul_rn(2.0f, s), p);
+  float el = __fmul_rn((float)e, 0.69314718f);
+  return __fadd_rn(el, t);
+}
+
+struct Footprint {
+  int tx0, tx1, ty0, ty1;
+  float mx, my, ca, cb, cc, k2;
+  bool valid;
+};
+
+__device__ __forceinline__ Footprint row_footprint(float mx, float my, float ca, float cb, float cc, float op,
+                                                   float depth, float thr, int W, int H) {
+  Footprint fp;
+  fp.valid = false;
+  fp.tx0 = fp.ty0 = 0; fp.tx1 = fp.ty1 = -1;
+  fp.mx = mx; fp.my = my; fp.ca = ca; fp.cb = cb; fp.cc = cc; fp.k2 = 0.f;
+  if (!(op > thr)) return fp;
+  if (!(depth > 0.0f) || !(depth < 3.0e38f)) return fp;
+  if (!(fabsf(mx) < 1.0e6f) || !(fabsf(my) < 1.0e6f)) return fp;
+  float detc = __fsub_rn(__fmul_rn(ca, cc), __fmul_rn(cb, cb));
+  if (!(detc > 0.0f) || !(ca > 0.0f) || !(cc > 0.0f)) return fp;
+  float k2 = __fmul_rn(2.0f, det_logf(__fdiv_rn(op, thr)));
+  k2 = __fadd_rn(__fmul_rn(k2, 1.0001f), 1.0e-5f);
+  float ex = __fsqrt_rn(__fdiv_rn(__fmul_rn(k2, cc), detc));
+  float ey = __fsqrt_rn(__fdiv_rn(__fmul_rn(k2, ca), detc));
+  if (!(ex < 1.0e6f) || !(ey < 1.0e6f)) return fp;
+  float x_lo = __fsub_rn(mx, ex), x_hi = __fadd_rn(mx, ex);
+  float y_lo = __fsub_rn(my, ey), y_hi = __fadd_rn(my, ey);
+  int TX = (W + GS_TILE - 1) / GS_TILE, TY = (H + GS_TILE - 1) / GS_TILE;
+  int tx0 = (int)ceilf(__fdiv_rn(__fsub_rn(x_lo, 15.5f), 16.0f));
+  int tx1 = (int)floorf(__fdiv_rn(__fsub_rn(x_hi, 0.5f), 16.0f));
+  int ty0 = (int)ceilf(__fdiv_rn(__fsub_rn(y_lo, 15.5f), 16.0f));
+  int ty1 = (int)floorf(__fdiv_rn(__fsub_rn(y_hi, 0.5f), 16.0f));
+  tx0 = max(tx0, 0); ty0 = max(ty0, 0);
+  tx1 = min(tx1, TX - 1); ty1 = min(ty1, TY - 1);
+  if (tx0 > tx1 || ty0 > ty1) return fp;
+  fp.tx0 = tx0; fp.tx1 = tx1; fp.ty0 = ty0; fp.ty1 = ty1;
+  fp.k2 = k2;
+  fp.valid = true;
+  return fp;
+}
+
+__device__ __forceinline__ float clampf_(float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+// exact test: does the k2-ellipse reach any pixel centre of tile (tx,ty)?
+__device__ __forceinline__ bool tile_hit(const Footprint &fp, int tx, int ty, int W, int H) {
+  int px1 = min(tx * GS_TILE + GS_TILE - 1, W - 1);
+  int py1 = min(ty * GS_TILE + GS_TILE - 1, H - 1);
+  float dxl = __fsub_rn(__fadd_rn((float)(tx * GS_TILE), 0.5f), fp.mx);
+  float dxr = __fsub_rn(__fadd_rn((float)px1, 0.5f), fp.mx);
+  float dyl = __fsub_rn(__fadd_rn((float)(ty * GS_TILE), 0.5f), fp.my);
+  float dyr = __fsub_rn(__fadd_rn((float)py1, 0.5f), fp.my);
+  bool in_x = (dxl <= 0.0f) && (dxr >= 0.0f), in_y = (dyl <= 0.0f) && (dyr >= 0.0f);
+  if (in_x && in_y) return true;
+  float qmin = 3.0e38f;
+  float cb2 = __fmul_rn(2.0f, fp.cb);
+  if (!in_x) {
+    float dx = (dxl > 0.0f) ? dxl : dxr;
+    float dy = clampf_(__fdiv_rn(-__fmul_rn(fp.cb, dx), fp.cc), dyl, dyr);
+    float q0 = __fmul_rn(__fmul_rn(fp.ca, dx), dx), q1 = __fmul_rn(__fmul_rn(cb2, dx), dy),
+          q2 = __fmul_rn(__fmul_rn(fp.cc, dy), dy);
+    float q = __fadd_rn(__fadd_rn(q0, q1), q2);
+    if (q < qmin) qmin = q;
+  }
+  if (!in_y) {
+    float dy = (dyl > 0.0f) ? dyl : dyr;
+    float dx = clampf_(__fdiv_rn(-__fmul_rn(fp.cb, dy), fp.ca), dxl, dxr);
+    float q0 = __fmul_rn(__fmul_rn(fp.ca, dx), dx), q1 = __fmul_rn(__fmul_rn(cb2, dx), dy),
+          q2 = __fmul_rn(__fmul_rn(fp.cc, dy), dy);
+    float q = __fadd_rn(__fadd_rn(q0, q1), q2);
+    if (q < qmin) qmin = q;
+  }
+  return qmin <= fp.k2;
+}
+
+__device__ __forceinline__ int footprint_count(const Footprint &fp, int W, int H) {
+  if (!fp.valid) return 0;
+  int c = 0;
+  for (int ty = fp.ty0; ty <= fp.ty1; ++ty)
+    for (int tx = fp.tx0; tx <= fp.tx1; ++tx) c += tile_hit(fp, tx, ty, W, H) ? 1 : 0;
+  return c;
+}

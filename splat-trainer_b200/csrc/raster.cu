@@ -1,0 +1,381 @@
+// raster.cu — tile rasteriser forward / backward (render_projected at reference
+// scene/mlp_scene.py:418 and its autograd backward via trainer/trainer.py:512).
+//
+// Design (B200): one CTA of 64 threads per 16x16 tile, every thread owns a 2x2 pixel quad, so a
+// warp covers 16x8 pixels.  The tile's sorted splat records are staged through shared memory in
+// batches of 64 (one gathered 36-B record per thread, conic pre-scaled by -log2(e)/2 so the inner
+// loop is 3 FMA + one ex2.approx per pixel, and a per-splat log2(thr/opacity) bound that rejects a
+// pixel before the SFU is touched).  Forward: front-to-back, block vote (__syncthreads_and) ends
+// the tile when all 256 pixels are saturated.  Backward: back-to-front, the 4 pixels of a thread
+// are summed in registers, then a 13-shuffle transpose-reduction leaves the 12 per-splat sums on
+// 12 lanes, which issue one coalesced vector of fp32 reductions (RED) per (warp, splat) — instead
+// of 12 x 5 butterfly shuffles and 12 separate atomics.  No tensor cores: FMA/SFU/LSU bound.
+#include "common.cuh"
+
+constexpr int RT = 64;  // threads per tile
+constexpr float LOG2E = 1.4426950408889634f;
+constexpr float LN2 = 0.6931471805599453f;
+
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+struct TileCtx {
+  int begin, n;
+  float fx0, fy0;
+  bool in[4];
+};
+
+__device__ __forceinline__ TileCtx tile_ctx(const int32_t *__restrict__ ranges, int W, int H, int TX) {
+  TileCtx c;
+  int tile = blockIdx.x;
+  int tx = tile % TX, ty = tile / TX;
+  int lx = threadIdx.x & 7, ly = threadIdx.x >> 3;
+  int px0 = tx * GS_TILE + 2 * lx, py0 = ty * GS_TILE + 2 * ly;
+  c.fx0 = (float)px0 + 0.5f;
+  c.fy0 = (float)py0 + 0.5f;
+  c.in[0] = px0 < W && py0 < H;
+  c.in[1] = px0 + 1 < W && py0 < H;
+  c.in[2] = px0 < W && py0 + 1 < H;
+  c.in[3] = px0 + 1 < W && py0 + 1 < H;
+  c.begin = ranges[2 * tile];
+  c.n = ranges[2 * tile + 1] - c.begin;
+  return c;
+}
+
+__device__ __forceinline__ int64_t pixel_index(int p, int W, int TX) {
+  int tile = blockIdx.x;
+  int tx = tile % TX, ty = tile / TX;
+  int lx = threadIdx.x & 7, ly = threadIdx.x >> 3;
+  int px = tx * GS_TILE + 2 * lx + (p & 1), py = ty * GS_TILE + 2 * ly + (p >> 1);
+  return (int64_t)py * W + px;
+}
+
+// stage one splat record into shared memory (conic pre-scaled for exp2)
+template <int C>
+__device__ __forceinline__ void stage_splat(int slot, int id, const float *__restrict__ g2d, const float *__restrict__ feat,
+                                            float thr, float4 *sA, float4 *sB, float (*sF)[RT]) {
+  const float2 *g = reinterpret_cast<const float2 *>(g2d + (int64_t)GS_G2D_STRIDE * id);
+  float2 a = __ldg(g), b = __ldg(g + 1), c = __ldg(g + 2);
+  float op = c.y;
+  // alpha >= thr  <=>  p' >= log2(thr/op); loosen slightly so the exact alpha test below decides
+  float pmin = (op > 0.f) ? (log2f(thr / op) - 1.0e-3f) : 1.0f;
+  sA[slot] = make_float4(a.x, a.y, -0.5f * LOG2E * b.x, -LOG2E * b.y);
+  sB[slot] = make_float4(-0.5f * LOG2E * c.x, op, pmin, __int_as_float(id));
+  const float *f = feat + (int64_t)C * id;
+#pragma unroll
+  for (int ch = 0; ch < C; ++ch) sF[ch][slot] = __ldg(f + ch);
+}
+
+template <int C, bool VIS, bool MEDIAN>
+__global__ void __launch_bounds__(RT) k_raster_fwd(CfgDev cfg, const float *__restrict__ g2d, const float *__restrict__ feat,
+                                                   const float *__restrict__ depth, const int32_t *__restrict__ o2p,
+                                                   const int32_t *__restrict__ ranges, int W, int H, int TX,
+                                                   float *__restrict__ image, float *__restrict__ final_T,
+                                                   int32_t *__restrict__ n_contrib, float *__restrict__ vis,
+                                                   float *__restrict__ median) {
+  __shared__ float4 sA[RT];
+  __shared__ float4 sB[RT];
+  __shared__ float sF[C][RT];
+  __shared__ float sD[MEDIAN ? RT : 1];
+  TileCtx tc = tile_ctx(ranges, W, H, TX);
+  float T[4] = {1.f, 1.f, 1.f, 1.f};
+  float col[4][C];
+  float med[4] = {0.f, 0.f, 0.f, 0.f};
+  int last[4] = {0, 0, 0, 0};
+  bool done[4];
+#pragma unroll
+  for (int p = 0; p < 4; ++p) {
+    done[p] = !tc.in[p];
+#pragma unroll
+    for (int ch = 0; ch < C; ++ch) col[p][ch] = 0.f;
+  }
+  const float fx[2] = {tc.fx0, tc.fx0 + 1.0f}, fy[2] = {tc.fy0, tc.fy0 + 1.0f};
+
+  for (int base = 0; base < tc.n; base += RT) {
+    bool all_done = done[0] && done[1] && done[2] && done[3];
+    if (__syncthreads_and(all_done)) break;  // also orders the previous batch's reads before the new writes
+    int j = base + threadIdx.x;
+    if (j < tc.n) {
+      int id = o2p[tc.begin + j];
+      stage_splat<C>(threadIdx.x, id, g2d, feat, cfg.thr, sA, sB, sF);
+      if (MEDIAN) sD[threadIdx.x] = depth[id];
+    }
+    __syncthreads();
+    int cnt = min(RT, tc.n - base);
+    for (int k = 0; k < cnt; ++k) {
+      if (!VIS && all_done) break;
+      float4 A = sA[k], B = sB[k];
+      float dx[2] = {fx[0] - A.x, fx[1] - A.x}, dy[2] = {fy[0] - A.y, fy[1] - A.y};
+      float ax[2] = {A.z * dx[0] * dx[0], A.z * dx[1] * dx[1]};
+      float cy[2] = {B.x * dy[0] * dy[0], B.x * dy[1] * dy[1]};
+      float bx[2] = {A.w * dx[0], A.w * dx[1]};
+      float vsum = 0.f;
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        float pw = ax[p & 1] + cy[p >> 1] + bx[p & 1] * dy[p >> 1];
+        if (!done[p] && pw <= 0.f && pw >= B.z) {
+          float a = fminf(cfg.amax, B.y * ex2_approx(pw));
+          if (a >= cfg.thr) {
+            float w = a * T[p];
+#pragma unroll
+            for (int ch = 0; ch < C; ++ch) col[p][ch] += w * sF[ch][k];
+            float Tn = T[p] * (1.0f - a);
+            if (MEDIAN && T[p] >= 0.5f && Tn < 0.5f) med[p] = sD[k];
+            T[p] = Tn;
+            last[p] = base + k + 1;
+            if (Tn < cfg.tmin) done[p] = true;
+            vsum += w;
+          }
+        }
+      }
+      if (VIS) {
+        if (__any_sync(GS_FULL, vsum > 0.f)) {
+          float s = warp_sum(vsum);
+          if ((threadIdx.x & 31) == 0) atomicAdd(vis + __float_as_int(B.w), s);
+        }
+      } else {
+        all_done = done[0] && done[1] && done[2] && done[3];
+      }
+    }
+  }
+#pragma unroll
+  for (int p = 0; p < 4; ++p) {
+    if (!tc.in[p]) continue;
+    int64_t pix = pixel_index(p, W, TX);
+#pragma unroll
+    for (int ch = 0; ch < C; ++ch) image[pix * C + ch] = col[p][ch];
+    final_T[pix] = T[p];
+    n_contrib[pix] = last[p];
+    if (MEDIAN) median[pix] = med[p];
+  }
+}
+
+// ---- warp transpose-reductions: NV per-lane values -> NV totals spread over lanes --------------------
+// 12 values, 13 shuffles.  On return lane L (even, !(b2&&b1)) holds the total of value `index`.
+__device__ __forceinline__ float multi_reduce12(const float *v, int lane, int &index, bool &valid) {
+  bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
+  float a[6];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) {
+    float keep = b4 ? v[6 + i] : v[i], send = b4 ? v[i] : v[6 + i];
+    a[i] = keep + __shfl_xor_sync(GS_FULL, send, 16);
+  }
+  float b[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    float keep = b3 ? a[3 + i] : a[i], send = b3 ? a[i] : a[3 + i];
+    b[i] = keep + __shfl_xor_sync(GS_FULL, send, 8);
+  }
+  float c0, c1;
+  {
+    float keep = b2 ? b[2] : b[0], send = b2 ? b[0] : b[2];
+    c0 = keep + __shfl_xor_sync(GS_FULL, send, 4);
+    float keep1 = b2 ? 0.f : b[1], send1 = b2 ? b[1] : 0.f;
+    c1 = keep1 + __shfl_xor_sync(GS_FULL, send1, 4);
+  }
+  float keep = b1 ? c1 : c0, send = b1 ? c0 : c1;
+  float d = keep + __shfl_xor_sync(GS_FULL, send, 2);
+  d += __shfl_xor_sync(GS_FULL, d, 1);
+  index = (b4 ? 6 : 0) + (b3 ? 3 : 0) + (b2 ? 2 : (b1 ? 1 : 0));
+  valid = !(b2 && b1) && !(lane & 1);
+  return d;
+}
+
+// 16 values, 16 shuffles; lane L (even) holds the total of value index = lane >> 1.
+__device__ __forceinline__ float multi_reduce16(const float *v, int lane, int &index, bool &valid) {
+  bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
+  float a[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    float keep = b4 ? v[8 + i] : v[i], send = b4 ? v[i] : v[8 + i];
+    a[i] = keep + __shfl_xor_sync(GS_FULL, send, 16);
+  }
+  float b[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float keep = b3 ? a[4 + i] : a[i], send = b3 ? a[i] : a[4 + i];
+    b[i] = keep + __shfl_xor_sync(GS_FULL, send, 8);
+  }
+  float c[2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    float keep = b2 ? b[2 + i] : b[i], send = b2 ? b[i] : b[2 + i];
+    c[i] = keep + __shfl_xor_sync(GS_FULL, send, 4);
+  }
+  float keep = b1 ? c[1] : c[0], send = b1 ? c[0] : c[1];
+  float d = keep + __shfl_xor_sync(GS_FULL, send, 2);
+  d += __shfl_xor_sync(GS_FULL, d, 1);
+  index = (b4 ? 8 : 0) + (b3 ? 4 : 0) + (b2 ? 2 : 0) + (b1 ? 1 : 0);
+  valid = !(lane & 1);
+  return d;
+}
+
+template <int C>
+__global__ void __launch_bounds__(RT) k_raster_bwd(CfgDev cfg, const float *__restrict__ g2d, const float *__restrict__ feat,
+                                                   const int32_t *__restrict__ o2p, const int32_t *__restrict__ ranges,
+                                                   int W, int H, int TX, const float *__restrict__ final_T,
+                                                   const int32_t *__restrict__ n_contrib, const float *__restrict__ d_image,
+                                                   float *__restrict__ acc, int acc_stride) {
+  constexpr int NV = (9 + C <= 12) ? 12 : 16;
+  __shared__ float4 sA[RT];
+  __shared__ float4 sB[RT];
+  __shared__ float sF[C][RT];
+  __shared__ int s_max[RT / 32];
+  TileCtx tc = tile_ctx(ranges, W, H, TX);
+  float T[4], last_a[4] = {0.f, 0.f, 0.f, 0.f};
+  float dC[4][C], rec[4][C], lastc[4][C];
+  int nc[4];
+  int mynmax = 0;
+#pragma unroll
+  for (int p = 0; p < 4; ++p) {
+    T[p] = 1.f; nc[p] = 0;
+#pragma unroll
+    for (int ch = 0; ch < C; ++ch) { dC[p][ch] = 0.f; rec[p][ch] = 0.f; lastc[p][ch] = 0.f; }
+    if (tc.in[p]) {
+      int64_t pix = pixel_index(p, W, TX);
+      T[p] = final_T[pix];
+      nc[p] = n_contrib[pix];
+#pragma unroll
+      for (int ch = 0; ch < C; ++ch) dC[p][ch] = d_image[pix * C + ch];
+    }
+    mynmax = max(mynmax, nc[p]);
+  }
+  int wmax = __reduce_max_sync(GS_FULL, mynmax);
+  if ((threadIdx.x & 31) == 0) s_max[threadIdx.x >> 5] = wmax;
+  __syncthreads();
+  int top = 0;
+#pragma unroll
+  for (int i = 0; i < RT / 32; ++i) top = max(top, s_max[i]);
+  top = min(top, tc.n);
+  const float fx[2] = {tc.fx0, tc.fx0 + 1.0f}, fy[2] = {tc.fy0, tc.fy0 + 1.0f};
+  const int lane = threadIdx.x & 31;
+
+  for (; top > 0; top -= RT) {
+    int lo = max(0, top - RT), cnt = top - lo;
+    __syncthreads();
+    if ((int)threadIdx.x < cnt) {
+      int id = o2p[tc.begin + lo + threadIdx.x];
+      stage_splat<C>(threadIdx.x, id, g2d, feat, cfg.thr, sA, sB, sF);
+    }
+    __syncthreads();
+    for (int k = cnt - 1; k >= 0; --k) {
+      int pos = lo + k;
+      float4 A = sA[k], B = sB[k];
+      float dx[2] = {fx[0] - A.x, fx[1] - A.x}, dy[2] = {fy[0] - A.y, fy[1] - A.y};
+      float ax[2] = {A.z * dx[0] * dx[0], A.z * dx[1] * dx[1]};
+      float cy[2] = {B.x * dy[0] * dy[0], B.x * dy[1] * dy[1]};
+      float bx[2] = {A.w * dx[0], A.w * dx[1]};
+      float v[NV];
+#pragma unroll
+      for (int i = 0; i < NV; ++i) v[i] = 0.f;
+      bool touched = false;
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        float pw = ax[p & 1] + cy[p >> 1] + bx[p & 1] * dy[p >> 1];
+        if (pos < nc[p] && pw <= 0.f && pw >= B.z) {
+          float G = ex2_approx(pw);
+          float a = B.y * G;
+          bool clamped = a > cfg.amax;
+          a = fminf(a, cfg.amax);
+          if (a >= cfg.thr) {
+            touched = true;
+            float Tp = __fdividef(T[p], 1.0f - a);
+            T[p] = Tp;
+            float w = a * Tp;
+            float dLda = 0.f;
+#pragma unroll
+            for (int ch = 0; ch < C; ++ch) {
+              float f = sF[ch][k];
+              rec[p][ch] = last_a[p] * lastc[p][ch] + (1.0f - last_a[p]) * rec[p][ch];
+              lastc[p][ch] = f;
+              dLda += (f - rec[p][ch]) * dC[p][ch];
+              v[6 + ch] += w * dC[p][ch];
+            }
+            dLda *= Tp;
+            last_a[p] = a;
+            v[8 + C] += w;
+            v[6 + C] += fabsf(a * dLda);
+            if (!clamped) {
+              float ddx = dx[p & 1], ddy = dy[p >> 1];
+              float dp = B.y * dLda * G * LN2;  // dL/dp', p' = log2(e)·power
+              float gx = -dp * (2.0f * A.z * ddx + A.w * ddy);
+              float gy = -dp * (2.0f * B.x * ddy + A.w * ddx);
+              v[0] += gx; v[1] += gy;
+              v[2] += dp * ddx * ddx; v[3] += dp * ddx * ddy; v[4] += dp * ddy * ddy;
+              v[5] += G * dLda;
+              v[7 + C] += fabsf(gx) + fabsf(gy);
+            }
+          }
+        }
+      }
+      if (__any_sync(GS_FULL, touched)) {
+        v[2] *= -0.5f * LOG2E; v[3] *= -LOG2E; v[4] *= -0.5f * LOG2E;
+        int index; bool valid;
+        float tot = (NV == 12) ? multi_reduce12(v, lane, index, valid) : multi_reduce16(v, lane, index, valid);
+        if (valid && index < 9 + C && tot != 0.f)
+          atomicAdd(acc + (int64_t)acc_stride * __float_as_int(B.w) + index, tot);
+      }
+    }
+  }
+}
+
+extern "C" int gs_raster_acc_stride(int channels) { return (9 + channels + 3) / 4 * 4; }
+
+template <int C>
+static int launch_fwd(const gs_raster_config *h_cfg, const float *g2d, const float *features, const float *depth,
+                      const int32_t *o2p, const int32_t *ranges, int W, int H, float *image, float *final_T,
+                      int32_t *n_contrib, float *visibility, float *median, cudaStream_t st) {
+  CfgDev cfg = gs_make_cfg(h_cfg);
+  int TX = (W + GS_TILE - 1) / GS_TILE, TY = (H + GS_TILE - 1) / GS_TILE;
+  int tiles = TX * TY;
+  bool vis = visibility != nullptr, med = median != nullptr;
+#define GS_FWD(V, M) k_raster_fwd<C, V, M><<<tiles, RT, 0, st>>>(cfg, g2d, features, depth, o2p, ranges, W, H, TX, image, final_T, n_contrib, visibility, median)
+  if (vis && med) GS_FWD(true, true);
+  else if (vis) GS_FWD(true, false);
+  else if (med) GS_FWD(false, true);
+  else GS_FWD(false, false);
+#undef GS_FWD
+  GS_LAUNCH_CHECK();
+  return GS_OK;
+}
+
+extern "C" int gs_raster_fwd(const gs_raster_config *h_cfg, int channels, int64_t m, const float *g2d, const float *features,
+                             const float *depth, const int32_t *overlap_to_point, const int32_t *tile_ranges, int width,
+                             int height, float *image, float *final_T, int32_t *n_contrib, float *visibility,
+                             float *median_depth, void *stream) {
+  (void)m;
+  GS_REQUIRE(h_cfg && h_cfg->tile_size == GS_TILE, "tile_size must be 16");
+  GS_REQUIRE(width > 0 && height > 0, "bad image size");
+  GS_REQUIRE(median_depth == nullptr || depth != nullptr, "median depth needs depth");
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (channels) {
+    case 1: return launch_fwd<1>(h_cfg, g2d, features, depth, overlap_to_point, tile_ranges, width, height, image, final_T, n_contrib, visibility, median_depth, st);
+    case 3: return launch_fwd<3>(h_cfg, g2d, features, depth, overlap_to_point, tile_ranges, width, height, image, final_T, n_contrib, visibility, median_depth, st);
+    case 4: return launch_fwd<4>(h_cfg, g2d, features, depth, overlap_to_point, tile_ranges, width, height, image, final_T, n_contrib, visibility, median_depth, st);
+    default: gs_set_error("gs_raster_fwd: channels must be 1, 3 or 4"); return GS_ERR_UNSUPPORTED;
+  }
+}
+
+extern "C" int gs_raster_bwd(const gs_raster_config *h_cfg, int channels, int64_t m, const float *g2d, const float *features,
+                             const int32_t *overlap_to_point, const int32_t *tile_ranges, int width, int height,
+                             const float *final_T, const int32_t *n_contrib, const float *d_image, float *acc,
+                             int acc_stride, void *stream) {
+  (void)m;
+  GS_REQUIRE(h_cfg && h_cfg->tile_size == GS_TILE, "tile_size must be 16");
+  GS_REQUIRE(acc_stride >= 9 + channels, "acc_stride too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  CfgDev cfg = gs_make_cfg(h_cfg);
+  int TX = (width + GS_TILE - 1) / GS_TILE, TY = (height + GS_TILE - 1) / GS_TILE;
+  int tiles = TX * TY;
+  switch (channels) {
+    case 1: k_raster_bwd<1><<<tiles, RT, 0, st>>>(cfg, g2d, features, overlap_to_point, tile_ranges, width, height, TX, final_T, n_contrib, d_image, acc, acc_stride); break;
+    case 3: k_raster_bwd<3><<<tiles, RT, 0, st>>>(cfg, g2d, features, overlap_to_point, tile_ranges, width, height, TX, final_T, n_contrib, d_image, acc, acc_stride); break;
+    case 4: k_raster_bwd<4><<<tiles, RT, 0, st>>>(cfg, g2d, features, overlap_to_point, tile_ranges, width, height, TX, final_T, n_contrib, d_image, acc, acc_stride); break;
+    default: gs_set_error("gs_raster_bwd: channels must be 1, 3 or 4"); return GS_ERR_UNSUPPORTED;
+  }
+  GS_LAUNCH_CHECK();
+  return GS_OK;
+}
