@@ -89,6 +89,9 @@ int gs_project_fwd(const gs_camera *h_cam, const gs_raster_config *h_cfg, int64_
 
 /* Backward of gs_project_fwd.  d_g2d (row stride d_g2d_stride floats, 6 used),
  * d_rgb (stride d_rgb_stride, 3 used), d_depth (nullable, n) are dL/d(outputs).
+ * row_vis (nullable, stride row_vis_stride): rows with row_vis <= 0 are skipped — a splat no pixel
+ * blended has an exactly-zero image gradient, so the fused path neither reads its SH row nor
+ * touches its gradient row (keeps the gradient buffer all-zero outside the visible set).
  * Gradients are ADDED into g_* when accumulate != 0 (batch = sum, reference
  * trainer/trainer.py:500-514), else written for in-view rows only (culled rows untouched). */
 int gs_project_bwd(const gs_camera *h_cam, const gs_raster_config *h_cfg, int64_t n,
@@ -97,7 +100,7 @@ int gs_project_bwd(const gs_camera *h_cam, const gs_raster_config *h_cfg, int64_
                    const float *g2d,
                    const float *d_g2d, int d_g2d_stride,
                    const float *d_rgb, int d_rgb_stride,
-                   const float *d_depth,
+                   const float *d_depth, const float *row_vis, int row_vis_stride,
                    float *g_position, float *g_log_scaling, float *g_rotation,
                    float *g_alpha_logit, float *g_sh, int accumulate, void *stream);
 

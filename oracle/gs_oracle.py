@@ -105,12 +105,13 @@ class Oracle:
     return g2d, depth, rgb
 
   def project_bwd(self, cam, cfg, position, log_scaling, rotation, alpha_logit, sh, sh_degree, g2d,
-                  d_g2d, d_rgb, d_depth=None, grads=None):
+                  d_g2d, d_rgb, d_depth=None, grads=None, row_vis=None):
     n = position.shape[0]
     position, log_scaling, rotation, alpha_logit, g2d = map(self.r, (position, log_scaling, rotation, alpha_logit, g2d))
     sh = None if sh is None else self.r(sh)
     d_g2d = self.r(d_g2d); d_rgb = None if d_rgb is None else self.r(d_rgb)
     d_depth = None if d_depth is None else self.r(d_depth)
+    row_vis = None if row_vis is None else self.r(row_vis)
     accumulate = grads is not None
     if grads is None:
       grads = dict(position=np.zeros((n, 3), self.real), log_scaling=np.zeros((n, 3), self.real),
@@ -120,7 +121,7 @@ class Oracle:
                              self.p(rotation), self.p(alpha_logit), self.p(sh), C.c_int(sh_degree), self.p(g2d),
                              self.p(d_g2d), C.c_int(d_g2d.shape[1]), self.p(d_rgb),
                              C.c_int(0 if d_rgb is None else d_rgb.shape[1]), self.p(d_depth),
-                             self.p(grads["position"]), self.p(grads["log_scaling"]), self.p(grads["rotation"]),
+                             self.p(row_vis), C.c_int(1), self.p(grads["position"]), self.p(grads["log_scaling"]), self.p(grads["rotation"]),
                              self.p(grads["alpha_logit"]), self.p(grads["sh"]), C.c_int(int(accumulate)))
     return grads
 

@@ -1,0 +1,290 @@
+// optim.cu — photometric loss, visibility-aware per-point Adam/LaProp, and the controller's running
+// statistics (reference trainer/trainer.py:465-476, scene/mlp_scene.py:214-239,
+// controller/point_state.py:34-50).
+//
+// All three are streaming, HBM-bound kernels.  The optimiser handles one parameter group per launch;
+// a row is owned by LANES consecutive lanes (LANES = 1 for dim <= 4, 16 for the SH feature rows) so
+// that a warp's loads of a wide row are contiguous 64-B segments, rows the step does not touch
+// (visible <= 0) are never read, and the consumed gradient row is cleared in the same pass (the
+// reference's dense zero_grad, scene/mlp_scene.py:155-161, costs 4·D·N bytes of writes per step).
+#include "common.cuh"
+
+// ---- loss ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_loss_l1_mse(int64_t n, const float *__restrict__ pred, const float *__restrict__ target,
+                                                     const uint8_t *__restrict__ target_u8, float w_l1, float w_mse,
+                                                     float inv_n, float *__restrict__ d_pred, float *__restrict__ sums) {
+  float s1 = 0.f, s2 = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float p = pred[i];
+    bool inside = (p >= 0.f) && (p <= 1.f);
+    float c = fminf(fmaxf(p, 0.f), 1.f);
+    float t = target_u8 ? (float)target_u8[i] / 255.0f : target[i];
+    float d = c - t;
+    s1 += fabsf(d);
+    s2 += d * d;
+    float sg = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);
+    if (d_pred) d_pred[i] = inside ? (w_l1 * sg + w_mse * 2.0f * d) * inv_n : 0.f;
+  }
+  s1 = warp_sum(s1);
+  s2 = warp_sum(s2);
+  __shared__ float sh[2][8];
+  int w = threadIdx.x >> 5;
+  if ((threadIdx.x & 31) == 0) { sh[0][w] = s1; sh[1][w] = s2; }
+  __syncthreads();
+  if (threadIdx.x < 2) {
+    float t = 0.f;
+    for (int k = 0; k < 8; ++k) t += sh[threadIdx.x][k];
+    atomicAdd(sums + threadIdx.x, t);
+  }
+}
+
+extern "C" int gs_loss_l1_mse(int64_t n, const float *pred, const float *target, const uint8_t *target_u8, float w_l1,
+                              float w_mse, float *d_pred, float *sums, void *stream) {
+  GS_REQUIRE(pred && sums && (target || target_u8), "null argument");
+  if (n <= 0) return GS_OK;
+  int blocks = (int)((n + 255) / 256);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  k_loss_l1_mse<<<blocks, 256, 0, (cudaStream_t)stream>>>(n, pred, target, target_u8, w_l1, w_mse, 1.0f / (float)n, d_pred, sums);
+  GS_LAUNCH_CHECK();
+  return GS_OK;
+}
+
+// ---- optimiser -------------------------------------------------------------------------------------
+struct OptDev {
+  int mode;
+  float beta1, beta2, eps, vis_beta, vis_smooth, grad_clip;
+  int bias_correction;
+};
+
+__global__ void __launch_bounds__(256) k_vis_update(int64_t n, float vis_beta, const float *__restrict__ visible,
+                                                    float *__restrict__ running_vis, float *__restrict__ step) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float v = visible[i];
+  if (!(v > 0.f)) return;
+  step[i] += 1.0f;
+  running_vis[i] = vis_beta * running_vis[i] + (1.0f - vis_beta) * v;
+}
+
+extern "C" int gs_optim_vis_update(const gs_optim_config *c, int64_t n, const float *visible, float *running_vis,
+                                   float *step, void *stream) {
+  GS_REQUIRE(c && visible && running_vis && step, "null argument");
+  if (n <= 0) return GS_OK;
+  k_vis_update<<<gs_div_up(n, 256), 256, 0, (cudaStream_t)stream>>>(n, c->vis_beta, visible, running_vis, step);
+  GS_LAUNCH_CHECK();
+  return GS_OK;
+}
+
+// point_basis (reference gaussians/split.py:15-19): B[3*j+k] = R[j][k] * max(exp(s_k), eps)
+__device__ __forceinline__ void point_basis(const float *__restrict__ ls, const float *__restrict__ q, float eps, float *B) {
+  float x = q[0], y = q[1], z = q[2], w = q[3];
+  float ql = sqrtf(x * x + y * y + z * z + w * w);
+  float d = fmaxf(ql, 1e-12f);
+  x /= d; y /= d; z /= d; w /= d;
+  float R[9];
+  R[0] = 1.f - 2.f * (y * y + z * z); R[1] = 2.f * (x * y - w * z); R[2] = 2.f * (x * z + w * y);
+  R[3] = 2.f * (x * y + w * z); R[4] = 1.f - 2.f * (x * x + z * z); R[5] = 2.f * (y * z - w * x);
+  R[6] = 2.f * (x * z - w * y); R[7] = 2.f * (y * z + w * x); R[8] = 1.f - 2.f * (x * x + y * y);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    float s = fmaxf(expf(ls[k]), eps);
+#pragma unroll
+    for (int j = 0; j < 3; ++j) B[3 * j + k] = R[3 * j + k] * s;
+  }
+}
+
+// KIND: 0 scalar, 1 vector, 2 local_vector.  LANES lanes share a row; lane l owns elements l, l+LANES, ...
+// EPL = elements per lane (ceil(dim / LANES)).
+template <int KIND, int LANES, int EPL>
+__global__ void __launch_bounds__(256) k_optim_step(OptDev c, int64_t n, int dim, float lr, float *__restrict__ param,
+                                                    float *__restrict__ grad, float *__restrict__ exp_avg,
+                                                    float *__restrict__ exp_avg_sq, const float *__restrict__ visible,
+                                                    const float *__restrict__ running_vis, const float *__restrict__ step,
+                                                    const float *__restrict__ basis_ls, const float *__restrict__ basis_q,
+                                                    int post, float post_lo, float post_hi, int zero_grad) {
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t i = t / LANES;
+  int l = (int)(t % LANES);
+  bool row_ok = i < n;
+  float w = row_ok ? visible[i] : 0.f;
+  bool active = row_ok && (w > 0.f);
+  // all lanes of a row agree on `active`; sub-warp shuffles below use the full mask, inactive rows just idle
+  if (LANES == 1 && !active) return;
+  float bc1 = 1.f, bc2 = 1.f, lam = 0.f, inv_w = 0.f;
+  if (active) {
+    float ts = step[i];
+    float rv = running_vis[i];
+    if (c.bias_correction) {
+      rv = rv / (1.0f - powf(c.vis_beta, ts));
+      bc1 = 1.0f - powf(c.beta1, ts);
+      bc2 = 1.0f - powf(c.beta2, ts);
+    }
+    lam = w / (rv + c.vis_smooth);
+    inv_w = 1.0f / (w + c.vis_smooth);
+  }
+  float g[EPL], gt[EPL], p[EPL], m1[EPL];
+  float B[9];
+  int64_t row = i * dim;
+#pragma unroll
+  for (int j = 0; j < EPL; ++j) {
+    int k = l + j * LANES;
+    bool ok = active && k < dim;
+    g[j] = ok ? grad[row + k] : 0.f;
+    p[j] = ok ? param[row + k] : 0.f;
+    m1[j] = ok ? exp_avg[row + k] : 0.f;
+  }
+  if (KIND == 2) {  // LANES == 1, dim == 3
+    point_basis(basis_ls + 3 * i, basis_q + 4 * i, 1e-4f, B);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) gt[k] = (B[k] * g[0] + B[3 + k] * g[1] + B[6 + k] * g[2]) * inv_w;
+  } else {
+#pragma unroll
+    for (int j = 0; j < EPL; ++j) gt[j] = g[j] * inv_w;
+  }
+  if (c.grad_clip > 0.f) {
+#pragma unroll
+    for (int j = 0; j < EPL; ++j) gt[j] = fminf(fmaxf(gt[j], -c.grad_clip), c.grad_clip);
+  }
+  float vshared = 0.f;
+  if (KIND != 0) {
+    float ms = 0.f;
+#pragma unroll
+    for (int j = 0; j < EPL; ++j) ms += gt[j] * gt[j];  // lanes past dim hold 0
+#pragma unroll
+    for (int o = LANES / 2; o > 0; o >>= 1) ms += __shfl_xor_sync(GS_FULL, ms, o);
+    ms /= (float)dim;
+    if (active) {
+      vshared = c.beta2 * exp_avg_sq[i] + (1.0f - c.beta2) * ms;
+      if (l == 0) exp_avg_sq[i] = vshared;
+    }
+  }
+  float upd[EPL];
+#pragma unroll
+  for (int j = 0; j < EPL; ++j) {
+    int k = l + j * LANES;
+    bool ok = active && k < dim;
+    float v2 = vshared;
+    if (KIND == 0 && ok) {
+      v2 = c.beta2 * exp_avg_sq[row + k] + (1.0f - c.beta2) * gt[j] * gt[j];
+      exp_avg_sq[row + k] = v2;
+    }
+    float denom = sqrtf(v2 / bc2) + c.eps;
+    if (c.mode == 0) {
+      m1[j] = c.beta1 * m1[j] + (1.0f - c.beta1) * gt[j];
+      upd[j] = (m1[j] / bc1) / denom;
+    } else {
+      m1[j] = c.beta1 * m1[j] + (1.0f - c.beta1) * gt[j] / denom;
+      upd[j] = m1[j] / bc1;
+    }
+    if (ok) exp_avg[row + k] = m1[j];
+  }
+  float sc = lr * lam;
+  if (KIND == 2) {
+#pragma unroll
+    for (int j = 0; j < 3; ++j) p[j] -= sc * (B[3 * j] * upd[0] + B[3 * j + 1] * upd[1] + B[3 * j + 2] * upd[2]);
+  } else {
+#pragma unroll
+    for (int j = 0; j < EPL; ++j) p[j] -= sc * upd[j];
+  }
+  if (post == GS_POST_NORMALIZE) {
+    float ss = 0.f;
+#pragma unroll
+    for (int j = 0; j < EPL; ++j) ss += (l + j * LANES < dim) ? p[j] * p[j] : 0.f;
+#pragma unroll
+    for (int o = LANES / 2; o > 0; o >>= 1) ss += __shfl_xor_sync(GS_FULL, ss, o);
+    float len = fmaxf(sqrtf(ss), 1e-12f);
+#pragma unroll
+    for (int j = 0; j < EPL; ++j) p[j] /= len;
+  } else if (post == GS_POST_CLAMP) {
+#pragma unroll
+    for (int j = 0; j < EPL; ++j) p[j] = fminf(fmaxf(p[j], post_lo), post_hi);
+  }
+#pragma unroll
+  for (int j = 0; j < EPL; ++j) {
+    int k = l + j * LANES;
+    if (active && k < dim) {
+      param[row + k] = p[j];
+      if (zero_grad) grad[row + k] = 0.f;
+    }
+  }
+}
+
+extern "C" int gs_optim_step(const gs_optim_config *h, int kind, int64_t n, int dim, float lr, float *param, float *grad,
+                             float *exp_avg, float *exp_avg_sq, const float *visible, const float *running_vis,
+                             const float *step, const float *basis_ls, const float *basis_q, int post, float post_lo,
+                             float post_hi, int zero_grad, void *stream) {
+  GS_REQUIRE(h && param && grad && exp_avg && exp_avg_sq && visible && running_vis && step, "null argument");
+  GS_REQUIRE(dim >= 1 && dim <= 64, "dim must be 1..64");
+  GS_REQUIRE(kind >= 0 && kind <= 2, "bad group kind");
+  GS_REQUIRE(kind != GS_GROUP_LOCAL_VECTOR || (dim == 3 && basis_ls && basis_q), "local_vector needs dim 3 and a basis");
+  if (n <= 0) return GS_OK;
+  OptDev c = {h->mode, h->beta1, h->beta2, h->eps, h->vis_beta, h->vis_smooth, h->grad_clip, h->bias_correction};
+  cudaStream_t st = (cudaStream_t)stream;
+#define GS_OPT(KIND, LANES, EPL)                                                                                   \
+  k_optim_step<KIND, LANES, EPL><<<gs_div_up(n * LANES, 256), 256, 0, st>>>(c, n, dim, lr, param, grad, exp_avg,   \
+                                                                            exp_avg_sq, visible, running_vis, step, \
+                                                                            basis_ls, basis_q, post, post_lo, post_hi, zero_grad)
+  if (kind == GS_GROUP_LOCAL_VECTOR) GS_OPT(2, 1, 3);
+  else if (kind == GS_GROUP_SCALAR) {
+    if (dim <= 4) GS_OPT(0, 1, 4);
+    else if (dim <= 16) GS_OPT(0, 4, 4);
+    else GS_OPT(0, 16, 4);
+  } else {
+    if (dim <= 4) GS_OPT(1, 1, 4);
+    else if (dim <= 16) GS_OPT(1, 4, 4);
+    else GS_OPT(1, 16, 4);
+  }
+#undef GS_OPT
+  GS_LAUNCH_CHECK();
+  return GS_OK;
+}
+
+// ---- statistics --------------------------------------------------------------------------------------
+__device__ __forceinline__ float exp_lerp(float t, float a, float b) {  // reference util/misc.py:56-59
+  float m = fmaxf(a, b);
+  float ea = expf(a - m), eb = expf(b - m);
+  return m + logf(ea + t * (eb - ea));
+}
+
+__global__ void __launch_bounds__(256) k_accumulate_stats(int64_t m, const int64_t *__restrict__ idx, const float *__restrict__ g2d,
+                                                          const float *__restrict__ vis, int vis_stride,
+                                                          const float *__restrict__ heur, int heur_stride, float split_alpha,
+                                                          float prune_alpha, float *__restrict__ prune_cost,
+                                                          float *__restrict__ split_score, float *__restrict__ max_scale_px,
+                                                          int16_t *__restrict__ points_in_view, float *__restrict__ visibility,
+                                                          float *__restrict__ scene_visible) {
+  int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= m) return;
+  const float2 *g = reinterpret_cast<const float2 *>(g2d + GS_G2D_STRIDE * r);
+  float2 cc_op = g[2];
+  if (!(cc_op.y > 0.f)) return;  // not in view
+  float2 ca_cb = g[1];
+  int64_t i = idx ? idx[r] : r;
+  float ca = ca_cb.x, cb = ca_cb.y, cc = cc_op.x;
+  float detc = ca * cc - cb * cb;
+  float cxx = cc / detc, cyy = ca / detc, cxy = -cb / detc;
+  float mid = 0.5f * (cxx + cyy);
+  float disc = mid * mid - (cxx * cyy - cxy * cxy);
+  float lam = mid + sqrtf(fmaxf(disc, 0.f));
+  float scale_px = sqrtf(fmaxf(lam, 0.f));
+  if (scale_px > max_scale_px[i]) max_scale_px[i] = scale_px;
+  float v = vis[(int64_t)vis_stride * r];
+  if (v > 0.f) points_in_view[i] += 1;
+  visibility[i] += v;
+  if (scene_visible) scene_visible[i] += v;
+  split_score[i] = exp_lerp(split_alpha, split_score[i], heur[(int64_t)heur_stride * r + 1]);
+  prune_cost[i] = exp_lerp(prune_alpha, prune_cost[i], heur[(int64_t)heur_stride * r]);
+}
+
+extern "C" int gs_accumulate_stats(int64_t m, const int64_t *idx, const float *g2d, const float *vis, int vis_stride,
+                                   const float *heur, int heur_stride, float split_alpha, float prune_alpha,
+                                   float *prune_cost, float *split_score, float *max_scale_px, int16_t *points_in_view,
+                                   float *visibility, float *scene_visible, void *stream) {
+  GS_REQUIRE(g2d && vis && heur && prune_cost && split_score && max_scale_px && points_in_view && visibility, "null argument");
+  if (m <= 0) return GS_OK;
+  k_accumulate_stats<<<gs_div_up(m, 256), 256, 0, (cudaStream_t)stream>>>(m, idx, g2d, vis, vis_stride, heur, heur_stride,
+                                                                          split_alpha, prune_alpha, prune_cost, split_score,
+                                                                          max_scale_px, points_in_view, visibility, scene_visible);
+  GS_LAUNCH_CHECK();
+  return GS_OK;
+}

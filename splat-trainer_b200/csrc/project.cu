@@ -210,12 +210,14 @@ __global__ void __launch_bounds__(128) k_project_bwd(CamDev cam, CfgDev cfg, int
                                                      const float *__restrict__ alpha_logit, const float *__restrict__ sh,
                                                      const float *__restrict__ g2d, const float *__restrict__ d_g2d,
                                                      int d_g2d_stride, const float *__restrict__ d_rgb, int d_rgb_stride,
-                                                     const float *__restrict__ d_depth, float *__restrict__ g_position,
+                                                     const float *__restrict__ d_depth, const float *__restrict__ row_vis,
+                                                     int row_vis_stride, float *__restrict__ g_position,
                                                      float *__restrict__ g_log_scaling, float *__restrict__ g_rotation,
                                                      float *__restrict__ g_alpha_logit, float *__restrict__ g_sh, int accumulate) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   if (!(g2d[GS_G2D_STRIDE * i + 5] > 0.f)) return;  // culled in forward
+  if (row_vis && !(row_vis[(int64_t)row_vis_stride * i] > 0.f)) return;  // blended by no pixel
   float px = position[3 * i], py = position[3 * i + 1], pz = position[3 * i + 2];
   Proj t;
   float4 q = reinterpret_cast<const float4 *>(rotation)[i];
@@ -432,8 +434,8 @@ extern "C" int gs_project_fwd(const gs_camera *h_cam, const gs_raster_config *h_
 extern "C" int gs_project_bwd(const gs_camera *h_cam, const gs_raster_config *h_cfg, int64_t n, const float *position,
                               const float *log_scaling, const float *rotation, const float *alpha_logit, const float *sh,
                               int sh_degree, const float *g2d, const float *d_g2d, int d_g2d_stride, const float *d_rgb,
-                              int d_rgb_stride, const float *d_depth, float *g_position, float *g_log_scaling,
-                              float *g_rotation, float *g_alpha_logit, float *g_sh, int accumulate, void *stream) {
+                              int d_rgb_stride, const float *d_depth, const float *row_vis, int row_vis_stride,
+                              float *g_position, float *g_log_scaling, float *g_rotation, float *g_alpha_logit, float *g_sh, int accumulate, void *stream) {
   GS_REQUIRE(h_cam && h_cfg, "null camera/config");
   GS_REQUIRE(d_g2d && d_g2d_stride >= 6, "d_g2d stride must be >= 6");
   if (n <= 0) return GS_OK;
@@ -443,8 +445,8 @@ extern "C" int gs_project_bwd(const gs_camera *h_cam, const gs_raster_config *h_
   int blocks = gs_div_up(n, 128);
   GS_DISPATCH_DEG(sh_degree, (k_project_bwd<D><<<blocks, 128, 0, st>>>(cam, cfg, n, position, log_scaling, rotation,
                                                                         alpha_logit, sh, g2d, d_g2d, d_g2d_stride, d_rgb,
-                                                                        d_rgb_stride, d_depth, g_position, g_log_scaling,
-                                                                        g_rotation, g_alpha_logit, g_sh, accumulate)));
+                                                                        d_rgb_stride, d_depth, row_vis, row_vis_stride,
+                                                                        g_position, g_log_scaling, g_rotation, g_alpha_logit, g_sh, accumulate)));
   GS_LAUNCH_CHECK();
   return GS_OK;
 }
