@@ -1,0 +1,277 @@
+"""Tensor-level wrappers over the C-ABI, one per entry point of include/gsb200.h.
+
+Each function enqueues work on torch's current CUDA stream and returns torch tensors that own the
+outputs.  Nothing here computes on the host; nothing falls back to torch ops.
+"""
+import ctypes as C
+
+import torch
+
+from . import lib as L
+
+
+def _f32(t):
+  assert t.dtype == torch.float32, f"expected float32, got {t.dtype}"
+  return t
+
+
+def tiles_of(width, height):
+  return (width + 15) // 16, (height + 15) // 16
+
+
+# ---- (1) projection + SH ---------------------------------------------------------------------------
+def project_fwd(cam, cfg, position, log_scaling, rotation, alpha_logit, sh=None, sh_degree=0, acc=None,
+                out=None):
+  """gs_project_fwd.  Returns (g2d (n,6), depth (n), rgb (n,3)); row i belongs to Gaussian i."""
+  n = position.shape[0]
+  dev = position.device
+  if out is None:
+    g2d = torch.empty((n, 6), device=dev, dtype=torch.float32)
+    depth = torch.empty((n,), device=dev, dtype=torch.float32)
+    rgb = torch.empty((n, 3), device=dev, dtype=torch.float32)
+  else:
+    g2d, depth, rgb = out
+  L.check(L.load().gs_project_fwd(C.byref(cam), C.byref(cfg), n, L.ptr(_f32(position)), L.ptr(_f32(log_scaling)),
+                                  L.ptr(_f32(rotation)), L.ptr(_f32(alpha_logit)), L.ptr(sh), sh_degree,
+                                  L.ptr(g2d), L.ptr(depth), L.ptr(rgb), L.ptr(acc),
+                                  0 if acc is None else acc.shape[1], L.stream()))
+  return g2d, depth, rgb
+
+
+def project_bwd(cam, cfg, position, log_scaling, rotation, alpha_logit, sh, sh_degree, g2d, d_g2d, d_rgb,
+                d_depth=None, row_vis=None, grads=None, accumulate=False):
+  """gs_project_bwd.  d_g2d / d_rgb / row_vis may be column views of one (n, stride) accumulator.
+  grads: dict(position, log_scaling, rotation, alpha_logit, sh) to write/accumulate into (allocated if None)."""
+  n = position.shape[0]
+  dev = position.device
+  if grads is None:
+    grads = dict(position=torch.zeros((n, 3), device=dev), log_scaling=torch.zeros((n, 3), device=dev),
+                 rotation=torch.zeros((n, 4), device=dev), alpha_logit=torch.zeros((n,), device=dev),
+                 sh=None if sh is None else torch.zeros_like(sh))
+
+  def strided(t):
+    if t is None:
+      return None, 0
+    assert t.dtype == torch.float32 and t.is_cuda
+    if t.dim() == 1:
+      return t.data_ptr(), t.stride(0)
+    assert t.stride(1) == 1
+    return t.data_ptr(), t.stride(0)
+
+  p_dg, s_dg = strided(d_g2d)
+  p_dr, s_dr = strided(d_rgb)
+  p_rv, s_rv = strided(row_vis)
+  L.check(L.load().gs_project_bwd(C.byref(cam), C.byref(cfg), n, L.ptr(position), L.ptr(log_scaling), L.ptr(rotation),
+                                  L.ptr(alpha_logit), L.ptr(sh), sh_degree, L.ptr(g2d), p_dg, s_dg, p_dr, s_dr,
+                                  L.ptr(d_depth), p_rv, s_rv, L.ptr(grads["position"]), L.ptr(grads["log_scaling"]),
+                                  L.ptr(grads["rotation"]), L.ptr(grads["alpha_logit"]), L.ptr(grads.get("sh")),
+                                  int(accumulate), L.stream()))
+  return grads
+
+
+def _cam_pos3(cam_pos):
+  v = [float(x) for x in torch.as_tensor(cam_pos).reshape(-1).tolist()]
+  assert len(v) == 3
+  return (C.c_float * 3)(*v)
+
+
+def sh_eval_fwd(indexes, sh, sh_degree, position, cam_pos):
+  v = position.shape[0] if indexes is None else indexes.shape[0]
+  rgb = torch.empty((v, 3), device=position.device, dtype=torch.float32)
+  if indexes is not None:
+    assert indexes.dtype == torch.int64
+  L.check(L.load().gs_sh_eval_fwd(v, L.ptr(indexes), L.ptr(_f32(sh)), sh_degree, L.ptr(_f32(position)),
+                                  _cam_pos3(cam_pos), L.ptr(rgb), L.stream()))
+  return rgb
+
+
+def sh_eval_bwd(indexes, sh, sh_degree, position, cam_pos, d_rgb):
+  v = position.shape[0] if indexes is None else indexes.shape[0]
+  g_sh = torch.zeros_like(sh)
+  g_pos = torch.zeros_like(position)
+  L.check(L.load().gs_sh_eval_bwd(v, L.ptr(indexes), L.ptr(sh), sh_degree, L.ptr(position), _cam_pos3(cam_pos),
+                                  L.ptr(_f32(d_rgb.contiguous())), L.ptr(g_sh), L.ptr(g_pos), L.stream()))
+  return g_sh, g_pos
+
+
+# ---- (2) tile mapping --------------------------------------------------------------------------------
+def tile_count(cfg, g2d, depth, width, height):
+  m = g2d.shape[0]
+  counts = torch.empty((max(m, 1),), device=g2d.device, dtype=torch.int32)
+  counters = torch.empty((4,), device=g2d.device, dtype=torch.int32)
+  L.check(L.load().gs_tile_count(C.byref(cfg), m, L.ptr(g2d), L.ptr(depth), width, height, L.ptr(counts),
+                                 L.ptr(counters), L.stream()))
+  return counts[:m], counters
+
+
+class TileMapBuffers:
+  """Caller-owned buffers of gs_tile_map for (m rows, max_overlaps, image size); reusable across calls."""
+
+  def __init__(self, m, max_overlaps, width, height, device):
+    self.m, self.max_overlaps, self.width, self.height = m, int(max_overlaps), width, height
+    tx, ty = tiles_of(width, height)
+    nbytes = L.load().gs_tile_map_workspace_bytes(m, self.max_overlaps, width, height)
+    self.workspace = torch.empty((nbytes,), device=device, dtype=torch.uint8)
+    self.overlap_to_point = torch.empty((max(self.max_overlaps, 1),), device=device, dtype=torch.int32)
+    self.tile_ranges = torch.empty((tx * ty, 2), device=device, dtype=torch.int32)
+    self.counters = torch.zeros((4,), device=device, dtype=torch.int32)
+
+
+def tile_map(cfg, g2d, depth, width, height, max_overlaps=None, buffers=None):
+  """gs_tile_map.  With max_overlaps=None the exact total is read back first (one host sync, like the
+  reference's mapper); the training path passes reusable `buffers` and never syncs.
+  Returns (overlap_to_point[max_overlaps], tile_ranges (T,2), counters[4], buffers)."""
+  m = g2d.shape[0]
+  if buffers is None:
+    if max_overlaps is None:
+      _, counters = tile_count(cfg, g2d, depth, width, height)
+      max_overlaps = int(counters[0].item())
+    buffers = TileMapBuffers(m, max_overlaps, width, height, g2d.device)
+  b = buffers
+  assert b.m >= m and b.width == width and b.height == height
+  L.check(L.load().gs_tile_map(C.byref(cfg), m, L.ptr(g2d), L.ptr(depth), width, height, b.max_overlaps,
+                               L.ptr(b.workspace), b.workspace.numel(), L.ptr(b.overlap_to_point),
+                               L.ptr(b.tile_ranges), L.ptr(b.counters), L.stream()))
+  return b.overlap_to_point, b.tile_ranges, b.counters, b
+
+
+def radix_sort_pairs(keys, vals, begin_bit=0, end_bit=32, n_dev=None):
+  n = keys.shape[0]
+  assert keys.dtype == torch.int32 and vals.dtype == torch.int32  # bit patterns of u32
+  kin, vin = keys.clone(), vals.clone()
+  kout, vout = torch.empty_like(keys), torch.empty_like(vals)
+  nbytes = L.load().gs_radix_sort_workspace_bytes(n)
+  ws = torch.empty((nbytes,), device=keys.device, dtype=torch.uint8)
+  L.check(L.load().gs_radix_sort_pairs(L.ptr(kin), L.ptr(vin), L.ptr(kout), L.ptr(vout), n, L.ptr(n_dev), begin_bit,
+                                       end_bit, L.ptr(ws), nbytes, L.stream()))
+  return kout, vout
+
+
+# ---- (3)/(4) rasterisation -------------------------------------------------------------------------
+def acc_stride(channels):
+  return L.load().gs_raster_acc_stride(channels)
+
+
+def raster_fwd(cfg, g2d, features, depth, overlap_to_point, tile_ranges, width, height, visibility=False,
+               median=False, out=None):
+  m, ch = g2d.shape[0], features.shape[1]
+  dev = g2d.device
+  if out is None:
+    image = torch.empty((height, width, ch), device=dev, dtype=torch.float32)
+    final_T = torch.empty((height, width), device=dev, dtype=torch.float32)
+    n_contrib = torch.empty((height, width), device=dev, dtype=torch.int32)
+  else:
+    image, final_T, n_contrib = out
+  if visibility is True:
+    vis = torch.zeros((m,), device=dev, dtype=torch.float32)
+  elif visibility is False or visibility is None:
+    vis = None
+  else:
+    vis = visibility  # caller's accumulator (+=)
+  med = torch.empty((height, width), device=dev, dtype=torch.float32) if median else None
+  L.check(L.load().gs_raster_fwd(C.byref(cfg), ch, m, L.ptr(g2d), L.ptr(_f32(features)), L.ptr(depth),
+                                 L.ptr(overlap_to_point), L.ptr(tile_ranges), width, height, L.ptr(image),
+                                 L.ptr(final_T), L.ptr(n_contrib), L.ptr(vis), L.ptr(med), L.stream()))
+  return image, final_T, n_contrib, vis, med
+
+
+def raster_bwd(cfg, g2d, features, overlap_to_point, tile_ranges, width, height, final_T, n_contrib, d_image,
+               acc=None):
+  """gs_raster_bwd; acc (m, acc_stride) must be zero on entry (allocated zeroed if None)."""
+  m, ch = g2d.shape[0], features.shape[1]
+  if acc is None:
+    acc = torch.zeros((m, acc_stride(ch)), device=g2d.device, dtype=torch.float32)
+  L.check(L.load().gs_raster_bwd(C.byref(cfg), ch, m, L.ptr(g2d), L.ptr(features), L.ptr(overlap_to_point),
+                                 L.ptr(tile_ranges), width, height, L.ptr(final_T), L.ptr(n_contrib),
+                                 L.ptr(_f32(d_image)), L.ptr(acc), acc.shape[1], L.stream()))
+  return acc
+
+
+def loss_l1_mse(pred, target, w_l1, w_mse, d_pred=None, sums=None):
+  """target: float32 in [0,1] or uint8.  Returns (d_pred, sums[2] = (Σ|c−t|, Σ(c−t)²))."""
+  n = pred.numel()
+  assert target.numel() == n
+  if d_pred is None:
+    d_pred = torch.empty_like(pred)
+  if sums is None:
+    sums = torch.zeros((2,), device=pred.device, dtype=torch.float32)
+  tf = target if target.dtype == torch.float32 else None
+  tu = target if target.dtype == torch.uint8 else None
+  assert tf is not None or tu is not None
+  L.check(L.load().gs_loss_l1_mse(n, L.ptr(_f32(pred)), L.ptr(tf), L.ptr(tu), w_l1, w_mse, L.ptr(d_pred), L.ptr(sums),
+                                  L.stream()))
+  return d_pred, sums
+
+
+# ---- (5) optimiser / statistics / densification ----------------------------------------------------
+def optim_vis_update(ocfg, visible, running_vis, step):
+  L.check(L.load().gs_optim_vis_update(C.byref(ocfg), visible.shape[0], L.ptr(_f32(visible)), L.ptr(running_vis),
+                                       L.ptr(step), L.stream()))
+
+
+def optim_step(ocfg, kind, lr, param, grad, exp_avg, exp_avg_sq, visible, running_vis, step, basis_ls=None,
+               basis_q=None, post=L.GS_POST_NONE, post_lo=0.0, post_hi=0.0, zero_grad=True):
+  n = param.shape[0]
+  dim = param.numel() // max(n, 1) if n > 0 else 1
+  L.check(L.load().gs_optim_step(C.byref(ocfg), kind, n, dim, lr, L.ptr(_f32(param)), L.ptr(_f32(grad)), L.ptr(exp_avg),
+                                 L.ptr(exp_avg_sq), L.ptr(visible), L.ptr(running_vis), L.ptr(step), L.ptr(basis_ls),
+                                 L.ptr(basis_q), post, post_lo, post_hi, int(zero_grad), L.stream()))
+
+
+def accumulate_stats(idx, g2d, vis, heur, split_alpha, prune_alpha, state, scene_visible=None):
+  """vis: (m,) or a column view; heur: (m,2)-like view whose row stride is heur.stride(0) with
+  [.,0]=prune_cost, [.,1]=split_score.  state: dict of the PointState tensors (updated in place)."""
+  m = g2d.shape[0]
+  assert state["points_in_view"].dtype == torch.int16
+  L.check(L.load().gs_accumulate_stats(m, L.ptr(idx), L.ptr(g2d), vis.data_ptr(), vis.stride(0), heur.data_ptr(),
+                                       heur.stride(0), split_alpha, prune_alpha, L.ptr(state["prune_cost"]),
+                                       L.ptr(state["split_score"]), L.ptr(state["max_scale_px"]),
+                                       L.ptr(state["points_in_view"]), L.ptr(state["visibility"]),
+                                       L.ptr(scene_visible), L.stream()))
+
+
+def select_topk_mask(values, k, descending):
+  """take_n: bool mask with exactly min(k,n) True entries (k smallest, or largest if descending)."""
+  n = values.shape[0]
+  mask = torch.zeros((n,), device=values.device, dtype=torch.uint8)
+  nbytes = L.load().gs_select_topk_workspace_bytes(n)
+  ws = torch.empty((nbytes,), device=values.device, dtype=torch.uint8)
+  L.check(L.load().gs_select_topk_mask(L.ptr(_f32(values)), n, int(k), int(descending), L.ptr(mask), L.ptr(ws), nbytes,
+                                       L.stream()))
+  return mask.view(torch.bool) if hasattr(mask, "view") else mask.bool()
+
+
+def compact_slots(keep_mask):
+  n = keep_mask.shape[0]
+  km = keep_mask.view(torch.uint8) if keep_mask.dtype == torch.bool else keep_mask
+  assert km.dtype == torch.uint8
+  slots = torch.empty((max(n, 1),), device=km.device, dtype=torch.int32)
+  count = torch.zeros((1,), device=km.device, dtype=torch.int32)
+  nbytes = L.load().gs_compact_workspace_bytes(n)
+  ws = torch.empty((nbytes,), device=km.device, dtype=torch.uint8)
+  L.check(L.load().gs_compact_slots(L.ptr(km), n, L.ptr(slots), L.ptr(count), L.ptr(ws), nbytes, L.stream()))
+  return slots[:n], count
+
+
+def compact_rows(src, slots, dst):
+  n = src.shape[0]
+  row_bytes = src.element_size() * (src.numel() // max(n, 1)) if n > 0 else src.element_size()
+  L.check(L.load().gs_compact_rows(L.ptr(src), L.ptr(dst), n, row_bytes, L.ptr(slots), L.stream()))
+  return dst
+
+
+def split_positions(split_idx, position, log_scaling, rotation, uniform, sep, out_position, out_log_scaling,
+                    out_offset=0):
+  s = split_idx.shape[0]
+  assert split_idx.dtype == torch.int64
+  L.check(L.load().gs_split_positions(s, L.ptr(split_idx), L.ptr(position), L.ptr(log_scaling), L.ptr(rotation),
+                                      L.ptr(uniform), sep, L.ptr(out_position), L.ptr(out_log_scaling), out_offset,
+                                      L.stream()))
+
+
+def gather_rows(src, dst, idx, repeat=1, out_offset=0):
+  s = idx.shape[0]
+  n = src.shape[0]
+  row_bytes = src.element_size() * (src.numel() // max(n, 1)) if n > 0 else src.element_size()
+  L.check(L.load().gs_gather_rows(L.ptr(src), L.ptr(dst), s, L.ptr(idx), row_bytes, repeat, out_offset, L.stream()))
+  return dst

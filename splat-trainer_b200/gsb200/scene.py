@@ -1,0 +1,311 @@
+"""SplatScene — the fused training hot path over packed splat parameters (host side).
+
+Mirrors the reference scene interface for this path (reference scene/scene.py:17-83; the MLPScene
+implementation scene/mlp_scene.py:214-313,411-427): render(), add_rendering (statistics), step(),
+zero_grad(), split_and_prune(), num_points — with an SH colour model instead of the colour MLP.
+
+HBM layout (one allocation each, attribute planes 256-B aligned):
+  params / grads / exp_avg : [position 3N | log_scaling 3N | rotation 4N | alpha_logit N | sh 3K·N] (+ `visible` N at
+  the tail of grads, so ONE all-reduce moves gradients and visibility under camera-batch data parallelism)
+  exp_avg_sq               : [position N | log_scaling 3N | rotation N | alpha_logit N | sh N]
+Per-image work buffers (g2d, depth, rgb, acc, image, final_T, n_contrib, d_image, tile-map workspace) are
+allocated once and reused; no stage reads a count back to the host.
+"""
+import dataclasses
+import math
+
+import torch
+
+from . import lib as L
+from . import ops
+
+ATTRS = ("position", "log_scaling", "rotation", "alpha_logit", "sh")
+
+
+@dataclasses.dataclass
+class SceneConfig:
+  sh_degree: int = 3
+  # per-group learning rates and kinds (reference config/scene/mlp.yaml:8-14 names the groups/kinds; the values
+  # here are ours — the reference's optimiser arithmetic is unpinned, DESIGN.md "Spec O")
+  lr_position: float = 0.05      # local_vector: in units of the splat's own R·S basis
+  lr_log_scaling: float = 0.02   # scalar
+  lr_rotation: float = 0.01      # vector
+  lr_alpha_logit: float = 0.05   # scalar
+  lr_sh: float = 0.01            # vector
+  optim: dict = dataclasses.field(default_factory=dict)  # overrides of make_optim_config (LaProp, .8/.95, ...)
+  w_l1: float = 0.0              # reference trainer/config.py:67-70, config/trainer/default.yaml:52-55
+  w_mse: float = 10.0
+  split_alpha: float = 0.01      # reference controller/point_state.py:49-50
+  prune_alpha: float = 0.1
+  antialias: bool = False        # reference trainer/trainer.py:308-310: blur_cov = 0.0 if antialias else 0.3
+  blur_cov: float = 0.3
+  max_overlaps: int = 0          # capacity of the tile-overlap list; 0 = calibrate on first use
+
+
+def _plane_offsets(n, dims):
+  offs, o = [], 0
+  for d in dims:
+    offs.append(o)
+    o += (n * d + 63) // 64 * 64  # 256-B aligned planes
+  return offs, o
+
+
+class SplatScene:
+  def __init__(self, gaussians, config=None, device="cuda"):
+    """gaussians: dict position (N,3), log_scaling (N,3), rotation (N,4) xyzw, alpha_logit (N,), sh (N,3,K)."""
+    self.config = config or SceneConfig()
+    self.device = torch.device(device)
+    if self.device.type != "cuda":
+      raise L.GsError("SplatScene needs a CUDA device (no CPU fallback)")
+    L.load()
+    self.K = (self.config.sh_degree + 1) ** 2
+    self.ocfg = L.make_optim_config(**self.config.optim)
+    self._alloc(int(gaussians["position"].shape[0]))
+    for name in ATTRS:
+      src = gaussians[name]
+      if name == "sh":
+        src = src[:, :, :self.K]
+      self.p[name].copy_(torch.as_tensor(src, dtype=torch.float32).reshape(self.p[name].shape))
+    self._work = None
+    self.timer = None  # optional StageTimer (bench.py): records a CUDA event after every stage
+    self.raster_cfg = L.default_raster_config(antialias=int(self.config.antialias),
+                                              blur_cov=0.0 if self.config.antialias else self.config.blur_cov,
+                                              compute_visibility=1, compute_point_heuristic=1)
+
+  # ---- storage ---------------------------------------------------------------------------------------
+  def _dims(self):
+    return (3, 3, 4, 1, 3 * self.K)
+
+  def _alloc(self, n):
+    dev = self.device
+    self.n = n
+    dims = self._dims()
+    offs, total = _plane_offsets(n, dims)
+    self._offs, self._total = offs, total
+    self.params = torch.zeros((total,), device=dev)
+    self.grads = torch.zeros((total + (n + 63) // 64 * 64,), device=dev)  # + visible at the tail
+    self.exp_avg = torch.zeros((total,), device=dev)
+    sq_dims = (1, 3, 1, 1, 1)
+    sq_offs, sq_total = _plane_offsets(n, sq_dims)
+    self.exp_avg_sq_flat = torch.zeros((sq_total,), device=dev)
+    shapes = dict(position=(n, 3), log_scaling=(n, 3), rotation=(n, 4), alpha_logit=(n,), sh=(n, 3, self.K))
+
+    def views(flat, offsets, dims_, shp):
+      return {name: flat[o:o + n * d].view(shp[name]) for name, o, d in zip(ATTRS, offsets, dims_)}
+
+    self.p = views(self.params, offs, dims, shapes)
+    self.g = views(self.grads, offs, dims, shapes)
+    self.m1 = views(self.exp_avg, offs, dims, shapes)
+    sq_shapes = dict(position=(n,), log_scaling=(n, 3), rotation=(n,), alpha_logit=(n,), sh=(n,))
+    self.m2 = views(self.exp_avg_sq_flat, sq_offs, sq_dims, sq_shapes)
+    self.visible = self.grads[total:total + n]
+    self.running_vis = torch.zeros((n,), device=dev)
+    self.opt_step = torch.zeros((n,), device=dev)
+    self.stats = self.new_point_state(n)
+    self._work = None
+
+  def new_point_state(self, n):
+    """PointState.new_zeros (reference controller/point_state.py:19-32)."""
+    dev = self.device
+    return dict(prune_cost=torch.zeros((n,), device=dev), split_score=torch.zeros((n,), device=dev),
+                max_scale_px=torch.zeros((n,), device=dev), points_in_view=torch.zeros((n,), device=dev, dtype=torch.int16),
+                visibility=torch.zeros((n,), device=dev))
+
+  @property
+  def num_points(self):
+    return self.n
+
+  def gaussians(self):
+    return {k: v.clone() for k, v in self.p.items()}
+
+  # ---- per-image work buffers --------------------------------------------------------------------------
+  def _buffers(self, cam):
+    W, H = cam.width, cam.height
+    w = self._work
+    if w is not None and w["W"] == W and w["H"] == H and w["n"] == self.n:
+      return w
+    dev, n = self.device, self.n
+    stride = ops.acc_stride(3)
+    w = dict(W=W, H=H, n=n,
+             g2d=torch.empty((n, 6), device=dev), depth=torch.empty((n,), device=dev), rgb=torch.empty((n, 3), device=dev),
+             acc=torch.zeros((n, stride), device=dev),
+             image=torch.empty((H, W, 3), device=dev), final_T=torch.empty((H, W), device=dev),
+             n_contrib=torch.empty((H, W), device=dev, dtype=torch.int32), d_image=torch.empty((H, W, 3), device=dev),
+             loss_sums=torch.zeros((2,), device=dev), tile=None)
+    self._work = w
+    return w
+
+  def _tile_buffers(self, w, cam):
+    """Overlap-list capacity: config.max_overlaps, else calibrated once from this camera's exact count × 1.5
+    (one host read at start-up; the steady-state path never reads a count back)."""
+    if w["tile"] is None:
+      cap = self.config.max_overlaps
+      if cap <= 0:
+        _, counters = ops.tile_count(self.raster_cfg, w["g2d"], w["depth"], cam.width, cam.height)
+        cap = int(int(counters[0].item()) * 1.5) + 65536
+      w["tile"] = ops.TileMapBuffers(self.n, cap, cam.width, cam.height, self.device)
+    return w["tile"]
+
+  def overflowed(self):
+    """True if the last tile map exceeded the overlap capacity (host sync; call off the hot path)."""
+    w = self._work
+    return bool(w and w["tile"] is not None and int(w["tile"].counters[1].item()) != 0)
+
+  def grow_overlaps(self, factor=2.0):
+    w = self._work
+    if w and w["tile"] is not None:
+      cap = int(w["tile"].max_overlaps * factor)
+      w["tile"] = ops.TileMapBuffers(self.n, cap, w["W"], w["H"], self.device)
+
+  def _mark(self, name):
+    if self.timer is not None:
+      self.timer.mark(name)
+
+  # ---- forward ---------------------------------------------------------------------------------------
+  def _forward(self, cam, median=False, visibility=None):
+    w = self._buffers(cam)
+    p = self.p
+    self._mark("begin")
+    ops.project_fwd(cam, self.raster_cfg, p["position"], p["log_scaling"], p["rotation"], p["alpha_logit"], p["sh"],
+                    self.config.sh_degree, acc=w["acc"], out=(w["g2d"], w["depth"], w["rgb"]))
+    self._mark("project_fwd")
+    tb = self._tile_buffers(w, cam)
+    ops.tile_map(self.raster_cfg, w["g2d"], w["depth"], cam.width, cam.height, buffers=tb)
+    self._mark("tile_map")
+    _, _, _, vis, med = ops.raster_fwd(self.raster_cfg, w["g2d"], w["rgb"], w["depth"], tb.overlap_to_point,
+                                       tb.tile_ranges, cam.width, cam.height, visibility=visibility, median=median,
+                                       out=(w["image"], w["final_T"], w["n_contrib"]))
+    self._mark("raster_fwd")
+    return w, tb, vis, med
+
+  def render(self, cam, median_depth=False, compute_visibility=False):
+    """Forward only (reference scene/mlp_scene.py:411-427): returns dict(image (H,W,3) clamped to [0,1] like the
+    reference's post_activation scene/color_model.py:154-160, raw, weight, visibility, median_depth)."""
+    w, tb, vis, med = self._forward(cam, median=median_depth, visibility=True if compute_visibility else None)
+    return dict(image=w["image"].clamp(0, 1), raw=w["image"], weight=1.0 - w["final_T"], visibility=vis,
+                median_depth=med, g2d=w["g2d"], depth=w["depth"])
+
+  # ---- one training image: forward + loss + backward + statistics ------------------------------------------
+  def forward_backward(self, cam, target):
+    """Reference trainer/trainer.py:500-514 for one image (render → loss → backward → add_rendering), fused:
+    gradients are ADDED into self.g (batch = sum), statistics into self.stats / self.visible.
+    target: (H,W,3) float32 in [0,1] or uint8 on the device.  Returns loss_sums (device, 2): Σ|d|, Σd²."""
+    w, tb, _, _ = self._forward(cam)
+    c = self.config
+    w["loss_sums"].zero_()
+    ops.loss_l1_mse(w["image"], target, c.w_l1, c.w_mse, d_pred=w["d_image"], sums=w["loss_sums"])
+    self._mark("loss")
+    acc = w["acc"]
+    ops.raster_bwd(self.raster_cfg, w["g2d"], w["rgb"], tb.overlap_to_point, tb.tile_ranges, cam.width, cam.height,
+                   w["final_T"], w["n_contrib"], w["d_image"], acc=acc)
+    self._mark("raster_bwd")
+    p = self.p
+    ops.project_bwd(cam, self.raster_cfg, p["position"], p["log_scaling"], p["rotation"], p["alpha_logit"], p["sh"],
+                    c.sh_degree, w["g2d"], acc[:, 0:6], acc[:, 6:9], None, row_vis=acc[:, 11], grads=self.g,
+                    accumulate=True)
+    self._mark("project_bwd")
+    ops.accumulate_stats(None, w["g2d"], acc[:, 11], acc[:, 9:11], c.split_alpha, c.prune_alpha, self.stats,
+                         scene_visible=self.visible)
+    self._mark("stats")
+    return w["loss_sums"]
+
+  # ---- optimiser step (reference scene/mlp_scene.py:214-239) -----------------------------------------------------
+  def step(self):
+    c, o = self.config, self.ocfg
+    vis, rv, st = self.visible, self.running_vis, self.opt_step
+    self._mark("optim_begin")
+    ops.optim_vis_update(o, vis, rv, st)
+    p, g, m1, m2 = self.p, self.g, self.m1, self.m2
+    # position first: its local basis is built from log_scaling / rotation BEFORE their update (mlp_scene.py:219)
+    ops.optim_step(o, L.GS_GROUP_LOCAL_VECTOR, c.lr_position, p["position"], g["position"], m1["position"],
+                   m2["position"], vis, rv, st, basis_ls=p["log_scaling"], basis_q=p["rotation"])
+    ops.optim_step(o, L.GS_GROUP_SCALAR, c.lr_log_scaling, p["log_scaling"], g["log_scaling"], m1["log_scaling"],
+                   m2["log_scaling"], vis, rv, st, post=L.GS_POST_CLAMP, post_lo=-8.0, post_hi=8.0)
+    ops.optim_step(o, L.GS_GROUP_VECTOR, c.lr_rotation, p["rotation"], g["rotation"], m1["rotation"], m2["rotation"],
+                   vis, rv, st, post=L.GS_POST_NORMALIZE)
+    ops.optim_step(o, L.GS_GROUP_SCALAR, c.lr_alpha_logit, p["alpha_logit"], g["alpha_logit"], m1["alpha_logit"],
+                   m2["alpha_logit"], vis, rv, st)
+    ops.optim_step(o, L.GS_GROUP_VECTOR, c.lr_sh, p["sh"], g["sh"], m1["sh"], m2["sh"], vis, rv, st)
+    self._mark("optim")
+    vis.zero_()  # zero_grad(): gradient rows were cleared by the optimiser kernels (mlp_scene.py:155-161)
+
+  def zero_grad(self):
+    self.grads.zero_()
+
+  # ---- densification (reference scene/mlp_scene.py:301-313, gaussians/split.py:87-113) ---------------------------
+  def split_and_prune(self, keep_mask, split_idx=None, uniform=None, sep=0.7):
+    """points = points[keep_mask] (parameters AND optimiser state) then append 2 children per split_idx row with
+    zero optimiser state.  keep_mask: (N,) bool; split_idx: (S,) int64 rows of the OLD numbering.
+    uniform: (S,) U[0,1) draws for the split axis (random_axis=True); None draws them from torch's CUDA generator.
+    The number of kept rows is read back once (densification is off the per-iteration path; the reference
+    reads four scalars here, controller/point_state.py:83-91)."""
+    old_n = self.n
+    s = 0 if split_idx is None else int(split_idx.shape[0])
+    slots, count = ops.compact_slots(keep_mask)
+    kept = int(count.item())
+    new_n = kept + 2 * s
+    old = dict(p=self.p, m1=self.m1, m2=self.m2, running_vis=self.running_vis, opt_step=self.opt_step, stats=self.stats,
+               flats=(self.params, self.grads, self.exp_avg, self.exp_avg_sq_flat))
+    self._alloc(new_n)  # zero-initialised: children get zero state, PointState rows of children are zero
+    for name in ATTRS:
+      ops.compact_rows(old["p"][name], slots, self.p[name])
+      ops.compact_rows(old["m1"][name], slots, self.m1[name])
+      ops.compact_rows(old["m2"][name], slots, self.m2[name])
+    ops.compact_rows(old["running_vis"], slots, self.running_vis)
+    ops.compact_rows(old["opt_step"], slots, self.opt_step)
+    for k, v in old["stats"].items():
+      ops.compact_rows(v, slots, self.stats[k])
+    if s > 0:
+      if uniform is None:
+        uniform = torch.rand((s,), device=self.device)
+      op = old["p"]
+      ops.split_positions(split_idx, op["position"], op["log_scaling"], op["rotation"], uniform, sep,
+                          self.p["position"], self.p["log_scaling"], out_offset=kept)
+      for name in ("rotation", "alpha_logit", "sh"):
+        ops.gather_rows(op[name], self.p[name], split_idx, repeat=2, out_offset=kept)
+    return old_n, new_n
+
+  def find_split_prune(self, t, target_points, prune_rate=0.025, min_views=5, max_scale_px=200.0, min_split_px=0.0):
+    """TargetController.find_split_prune_indexes (reference controller/target_controller.py:73-96) with the two
+    full argsorts replaced by radix selects.  Returns (split_mask, prune_mask)."""
+    st = self.stats
+    n = self.n
+    exceeds = st["max_scale_px"] > max_scale_px
+    n_prune = int(math.ceil(prune_rate * n * (1 - t)))
+    seen = st["points_in_view"] >= min_views
+    prune_cost = torch.where(seen, st["prune_cost"], torch.full_like(st["prune_cost"], float("inf")))
+    prune_mask = ops.select_topk_mask(prune_cost, n_prune, descending=0) | exceeds
+    target_split = (target_points - n) + int(prune_mask.sum().item())
+    split_score = st["split_score"]
+    split_score[prune_mask] = 0.0
+    if min_split_px > 0:
+      split_score[st["max_scale_px"] < min_split_px] = 0.0
+    split_mask = ops.select_topk_mask(split_score, max(target_split, 0), descending=1)
+    both = split_mask & prune_mask
+    return split_mask ^ both, prune_mask ^ both
+
+  def densify(self, t, target_points, uniform=None, **kw):
+    """densify_and_prune (reference controller/point_state.py:76-110) + new PointState (target_controller.py:122)."""
+    split_mask, prune_mask = self.find_split_prune(t, target_points, **kw)
+    split_idx = split_mask.nonzero().squeeze(1)
+    keep = ~(split_mask | prune_mask)
+    out = self.split_and_prune(keep, split_idx, uniform=uniform)
+    self.stats = self.new_point_state(self.n)
+    return out
+
+  def state_dict(self):
+    """plain tensors / scalars only (reference checkpoints load with weights_only=True, trainer/checkpoint.py:38)."""
+    sd = {f"p.{k}": v.clone() for k, v in self.p.items()}
+    sd.update({f"m1.{k}": v.clone() for k, v in self.m1.items()})
+    sd.update({f"m2.{k}": v.clone() for k, v in self.m2.items()})
+    sd.update(running_vis=self.running_vis.clone(), opt_step=self.opt_step.clone(), sh_degree=self.config.sh_degree)
+    return sd
+
+  @staticmethod
+  def from_state_dict(sd, config=None, device="cuda"):
+    config = config or SceneConfig(sh_degree=int(sd["sh_degree"]))
+    scene = SplatScene({k: sd[f"p.{k}"] for k in ATTRS}, config, device)
+    for k in ATTRS:
+      scene.m1[k].copy_(sd[f"m1.{k}"]); scene.m2[k].copy_(sd[f"m2.{k}"])
+    scene.running_vis.copy_(sd["running_vis"]); scene.opt_step.copy_(sd["opt_step"])
+    return scene
