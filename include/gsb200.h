@@ -80,12 +80,14 @@ const char *gs_last_error(void);
  *     colour = 0.5 + Σ_k Y_k(dir) sh[c][k] (util/misc.py:41-49). sh may be NULL (rgb untouched).
  *     acc (nullable): the raster-backward accumulator (n × acc_stride); rows of in-view
  *     Gaussians are zeroed here so no separate memset is needed.
+ *     tile_counts (nullable, n): tiles touched by each row (0 for culled rows) — the cull already computes
+ *     them, and gs_tile_map(counts_in = tile_counts) then skips its own counting pass.
  * ------------------------------------------------------------------------------------- */
 int gs_project_fwd(const gs_camera *h_cam, const gs_raster_config *h_cfg, int64_t n,
                    const float *position, const float *log_scaling, const float *rotation,
                    const float *alpha_logit, const float *sh, int sh_degree,
                    float *g2d, float *depth, float *rgb,
-                   float *acc, int acc_stride, void *stream);
+                   float *acc, int acc_stride, int32_t *tile_counts, void *stream);
 
 /* Backward of gs_project_fwd.  d_g2d (row stride d_g2d_stride floats, 6 used),
  * d_rgb (stride d_rgb_stride, 3 used), d_depth (nullable, n) are dL/d(outputs).
@@ -123,10 +125,13 @@ int gs_sh_eval_bwd(int64_t v, const int64_t *indexes, const float *sh, int sh_de
  *       tile_ranges[2t,2t+1] [begin,end) of tile t in overlap_to_point   (tiles_x*tiles_y*2)
  *       counters[0] = total overlaps O (may exceed max_overlaps: then counters[1] = 1 and
  *                     only the ranges/lists of the first max_overlaps emitted pairs are valid)
+ *       counters[2] = min(O, max_overlaps), counters[3] = rows touching at least one tile
+ *     counts_in (nullable, m): per-row tile counts from gs_project_fwd / gs_tile_count (must come from
+ *     the same g2d/depth); NULL = counted here.
  * ------------------------------------------------------------------------------------- */
 size_t gs_tile_map_workspace_bytes(int64_t m, int64_t max_overlaps, int width, int height);
 int gs_tile_map(const gs_raster_config *h_cfg, int64_t m, const float *g2d, const float *depth,
-                int width, int height, int64_t max_overlaps,
+                const int32_t *counts_in, int width, int height, int64_t max_overlaps,
                 void *workspace, size_t workspace_bytes,
                 int32_t *overlap_to_point, int32_t *tile_ranges, int32_t *counters,
                 void *stream);
@@ -200,6 +205,12 @@ enum { GS_POST_NONE = 0, GS_POST_NORMALIZE = 1, GS_POST_CLAMP = 2 };          /*
 int gs_optim_vis_update(const gs_optim_config *h_cfg, int64_t n, const float *visible,
                         float *running_vis, float *step, void *stream);
 
+/* `indexes = points.visible.nonzero()` (reference scene/mlp_scene.py:217) without the host sync: ascending row
+ * indexes with visible > 0 into indexes[0..count), count -> count_dev[0]. */
+size_t gs_visible_indexes_workspace_bytes(int64_t n);
+int gs_visible_indexes(int64_t n, const float *visible, int32_t *indexes, int32_t *count_dev,
+                       void *workspace, size_t workspace_bytes, void *stream);
+
 /* One parameter group (ParameterClass.step(visibility, indexes, basis), reference
  * scene/mlp_scene.py:214-230).  Rows with visible[i] <= 0 are skipped (the reference's
  * `indexes = visible.nonzero()` done in-kernel, no host sync).  exp_avg is n×dim;
@@ -207,8 +218,11 @@ int gs_optim_vis_update(const gs_optim_config *h_cfg, int64_t n, const float *vi
  * expresses gradient and update in the basis R(q)·diag(max(exp(s),1e-4)) (point_basis,
  * gaussians/split.py:15-19) built from basis_log_scaling / basis_rotation.
  * post: GS_POST_NORMALIZE renormalises each row, GS_POST_CLAMP clamps to [post_lo,post_hi].
- * zero_grad != 0 clears the consumed gradient rows (reference zero_grad, :155-161). */
-int gs_optim_step(const gs_optim_config *h_cfg, int kind, int64_t n, int dim, float lr,
+ * zero_grad != 0 clears the consumed gradient rows (reference zero_grad, :155-161).
+ * indexes/count_dev (both or neither): the ascending list of rows with visible > 0 and its device-side
+ * length from gs_visible_indexes — the kernel then touches only those rows (grid-stride over the list). */
+int gs_optim_step(const gs_optim_config *h_cfg, int kind, int64_t n,
+                  const int32_t *indexes, const int32_t *count_dev, int dim, float lr,
                   float *param, float *grad, float *exp_avg, float *exp_avg_sq,
                   const float *visible, const float *running_vis, const float *step,
                   const float *basis_log_scaling, const float *basis_rotation,

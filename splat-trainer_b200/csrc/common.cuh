@@ -83,6 +83,7 @@ __device__ __forceinline__ float warp_sum(float v) {
 // ---- exclusive scan of int32 (scan.cu) -------------------------------------------------------
 // out[i] = sum_{j<i} in[idx ? idx[j] : j]; total (nullable) receives the full sum.
 // n_dev (nullable) bounds the element count on the device (<= n).  partials: >= gs_scan_partials(n) ints.
+// as_flag != 0 scans the predicate (value > 0) instead of the value (stream-compaction ranks).
 int64_t gs_scan_partials(int64_t n);
 int gs_exclusive_scan_i32(const int32_t *in, const int32_t *idx, int32_t *out, int64_t n, const int32_t *n_dev,
-                          int32_t *partials, int32_t *total, cudaStream_t st);
+                          int32_t *partials, int32_t *total, cudaStream_t st, int as_flag = 0);

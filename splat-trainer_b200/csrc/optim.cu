@@ -66,6 +66,43 @@ __global__ void __launch_bounds__(256) k_vis_update(int64_t n, float vis_beta, c
   running_vis[i] = vis_beta * running_vis[i] + (1.0f - vis_beta) * v;
 }
 
+// indexes of rows with visible > 0 (ascending) + their count, all on the device
+__global__ void __launch_bounds__(256) k_vis_flags(int64_t n, const float *__restrict__ visible, int32_t *__restrict__ flags) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) flags[i] = visible[i] > 0.f ? 1 : 0;
+}
+__global__ void __launch_bounds__(256) k_vis_indexes(int64_t n, const float *__restrict__ visible,
+                                                     const int32_t *__restrict__ rank, int32_t *__restrict__ indexes) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && visible[i] > 0.f) indexes[rank[i]] = (int32_t)i;
+}
+
+extern "C" size_t gs_visible_indexes_workspace_bytes(int64_t n) {
+  size_t nn = (size_t)(n > 0 ? n : 1);
+  return 2 * gs_align256(nn * 4) + gs_align256((size_t)gs_scan_partials(nn) * 4) + 256;
+}
+
+extern "C" int gs_visible_indexes(int64_t n, const float *visible, int32_t *indexes, int32_t *count_dev, void *workspace,
+                                  size_t workspace_bytes, void *stream) {
+  GS_REQUIRE(n >= 0 && n < ((int64_t)1 << 31), "n must fit int32");
+  GS_REQUIRE(count_dev, "null count");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n == 0) { GS_CUDA(cudaMemsetAsync(count_dev, 0, 4, st)); return GS_OK; }
+  GS_REQUIRE(visible && indexes && workspace, "null argument");
+  if (workspace_bytes < gs_visible_indexes_workspace_bytes(n)) { gs_set_error("gs_visible_indexes: workspace too small"); return GS_ERR_WORKSPACE; }
+  uintptr_t a = ((uintptr_t)workspace + 255) & ~(uintptr_t)255;
+  int32_t *flags = (int32_t *)a;
+  int32_t *rank = (int32_t *)(a + gs_align256((size_t)n * 4));
+  int32_t *partials = (int32_t *)(a + 2 * gs_align256((size_t)n * 4));
+  int blocks = gs_div_up(n, 256);
+  k_vis_flags<<<blocks, 256, 0, st>>>(n, visible, flags);
+  int rc = gs_exclusive_scan_i32(flags, nullptr, rank, n, nullptr, partials, count_dev, st);
+  if (rc != GS_OK) return rc;
+  k_vis_indexes<<<blocks, 256, 0, st>>>(n, visible, rank, indexes);
+  GS_LAUNCH_CHECK();
+  return GS_OK;
+}
+
 extern "C" int gs_optim_vis_update(const gs_optim_config *c, int64_t n, const float *visible, float *running_vis,
                                    float *step, void *stream) {
   GS_REQUIRE(c && visible && running_vis && step, "null argument");
@@ -96,20 +133,16 @@ __device__ __forceinline__ void point_basis(const float *__restrict__ ls, const 
 // KIND: 0 scalar, 1 vector, 2 local_vector.  LANES lanes share a row; lane l owns elements l, l+LANES, ...
 // EPL = elements per lane (ceil(dim / LANES)).
 template <int KIND, int LANES, int EPL>
-__global__ void __launch_bounds__(256) k_optim_step(OptDev c, int64_t n, int dim, float lr, float *__restrict__ param,
-                                                    float *__restrict__ grad, float *__restrict__ exp_avg,
-                                                    float *__restrict__ exp_avg_sq, const float *__restrict__ visible,
-                                                    const float *__restrict__ running_vis, const float *__restrict__ step,
-                                                    const float *__restrict__ basis_ls, const float *__restrict__ basis_q,
-                                                    int post, float post_lo, float post_hi, int zero_grad) {
-  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int64_t i = t / LANES;
-  int l = (int)(t % LANES);
-  bool row_ok = i < n;
+__device__ __forceinline__ void optim_row(const OptDev &c, int64_t i, int l, bool row_ok, int dim, float lr,
+                                          float *__restrict__ param, float *__restrict__ grad, float *__restrict__ exp_avg,
+                                          float *__restrict__ exp_avg_sq, const float *__restrict__ visible,
+                                          const float *__restrict__ running_vis, const float *__restrict__ step,
+                                          const float *__restrict__ basis_ls, const float *__restrict__ basis_q,
+                                          int post, float post_lo, float post_hi, int zero_grad) {
   float w = row_ok ? visible[i] : 0.f;
   bool active = row_ok && (w > 0.f);
   // all lanes of a row agree on `active`; sub-warp shuffles below use the full mask, inactive rows just idle
-  if (LANES == 1 && !active) return;
+  if (LANES == 1 && !active) return;  // (returns from optim_row only)
   float bc1 = 1.f, bc2 = 1.f, lam = 0.f, inv_w = 0.f;
   if (active) {
     float ts = step[i];
@@ -209,7 +242,33 @@ __global__ void __launch_bounds__(256) k_optim_step(OptDev c, int64_t n, int dim
   }
 }
 
-extern "C" int gs_optim_step(const gs_optim_config *h, int kind, int64_t n, int dim, float lr, float *param, float *grad,
+// Grid-stride over rows.  Dense mode (indexes == NULL): row r is Gaussian r, rows with visible <= 0 idle.
+// Indexed mode: row r is Gaussian indexes[r], r < *count_dev (the device-side `visible.nonzero()` of the
+// reference, scene/mlp_scene.py:217, with no host read-back) — only the rows the step touches are ever read.
+template <int KIND, int LANES, int EPL>
+__global__ void __launch_bounds__(256) k_optim_step(OptDev c, int64_t n, const int32_t *__restrict__ indexes,
+                                                    const int32_t *__restrict__ count_dev, int dim, float lr,
+                                                    float *__restrict__ param, float *__restrict__ grad,
+                                                    float *__restrict__ exp_avg, float *__restrict__ exp_avg_sq,
+                                                    const float *__restrict__ visible, const float *__restrict__ running_vis,
+                                                    const float *__restrict__ step, const float *__restrict__ basis_ls,
+                                                    const float *__restrict__ basis_q, int post, float post_lo, float post_hi,
+                                                    int zero_grad) {
+  int64_t rows = indexes ? min((int64_t)*count_dev, n) : n;
+  int64_t total = rows * LANES;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  int lane = threadIdx.x & 31;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t - lane < total; t += stride) {  // warp-uniform trip count
+    int64_t r = t / LANES;
+    bool row_ok = r < rows;
+    int64_t i = row_ok ? (indexes ? (int64_t)indexes[r] : r) : 0;
+    optim_row<KIND, LANES, EPL>(c, i, (int)(t % LANES), row_ok, dim, lr, param, grad, exp_avg, exp_avg_sq, visible, running_vis,
+                                step, basis_ls, basis_q, post, post_lo, post_hi, zero_grad);
+  }
+}
+
+extern "C" int gs_optim_step(const gs_optim_config *h, int kind, int64_t n, const int32_t *indexes, const int32_t *count_dev,
+                             int dim, float lr, float *param, float *grad,
                              float *exp_avg, float *exp_avg_sq, const float *visible, const float *running_vis,
                              const float *step, const float *basis_ls, const float *basis_q, int post, float post_lo,
                              float post_hi, int zero_grad, void *stream) {
@@ -217,13 +276,19 @@ extern "C" int gs_optim_step(const gs_optim_config *h, int kind, int64_t n, int 
   GS_REQUIRE(dim >= 1 && dim <= 64, "dim must be 1..64");
   GS_REQUIRE(kind >= 0 && kind <= 2, "bad group kind");
   GS_REQUIRE(kind != GS_GROUP_LOCAL_VECTOR || (dim == 3 && basis_ls && basis_q), "local_vector needs dim 3 and a basis");
+  GS_REQUIRE((indexes == nullptr) == (count_dev == nullptr), "indexes and count_dev go together");
   if (n <= 0) return GS_OK;
   OptDev c = {h->mode, h->beta1, h->beta2, h->eps, h->vis_beta, h->vis_smooth, h->grad_clip, h->bias_correction};
   cudaStream_t st = (cudaStream_t)stream;
-#define GS_OPT(KIND, LANES, EPL)                                                                                   \
-  k_optim_step<KIND, LANES, EPL><<<gs_div_up(n * LANES, 256), 256, 0, st>>>(c, n, dim, lr, param, grad, exp_avg,   \
-                                                                            exp_avg_sq, visible, running_vis, step, \
-                                                                            basis_ls, basis_q, post, post_lo, post_hi, zero_grad)
+  // grid: enough CTAs to fill the machine (148 SMs x 8 resident CTAs of 256 threads), never more than the work
+#define GS_OPT(KIND, LANES, EPL)                                                                                    \
+  do {                                                                                                               \
+    int64_t want = (n * LANES + 255) / 256;                                                                          \
+    int grid = (int)(want < 148 * 8 ? want : 148 * 8);                                                               \
+    k_optim_step<KIND, LANES, EPL><<<grid, 256, 0, st>>>(c, n, indexes, count_dev, dim, lr, param, grad, exp_avg,    \
+                                                         exp_avg_sq, visible, running_vis, step, basis_ls, basis_q, \
+                                                         post, post_lo, post_hi, zero_grad);                        \
+  } while (0)
   if (kind == GS_GROUP_LOCAL_VECTOR) GS_OPT(2, 1, 3);
   else if (kind == GS_GROUP_SCALAR) {
     if (dim <= 4) GS_OPT(0, 1, 4);

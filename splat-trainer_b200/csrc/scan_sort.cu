@@ -70,7 +70,7 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int *s_warp, int &blo
 
 __global__ void __launch_bounds__(SC_THREADS) k_scan_reduce(const int32_t *__restrict__ in, const int32_t *__restrict__ idx,
                                                             int64_t n_cap, const int32_t *__restrict__ n_dev,
-                                                            int32_t *__restrict__ partials) {
+                                                            int32_t *__restrict__ partials, int as_flag) {
   __shared__ int s_warp[33];
   int64_t n = n_dev ? min((int64_t)*n_dev, n_cap) : n_cap;
   int64_t base = (int64_t)blockIdx.x * SC_TILE;
@@ -78,7 +78,10 @@ __global__ void __launch_bounds__(SC_THREADS) k_scan_reduce(const int32_t *__res
 #pragma unroll
   for (int i = 0; i < SC_ITEMS; ++i) {
     int64_t j = base + i * SC_THREADS + threadIdx.x;
-    if (j < n) sum += idx ? in[idx[j]] : in[j];
+    if (j < n) {
+      int v = idx ? in[idx[j]] : in[j];
+      sum += as_flag ? (v > 0) : v;
+    }
   }
   int tot;
   block_exclusive_scan(sum, s_warp, tot);
@@ -108,7 +111,7 @@ __global__ void __launch_bounds__(1024) k_scan_partials(int32_t *__restrict__ pa
 __global__ void __launch_bounds__(SC_THREADS) k_scan_apply(const int32_t *__restrict__ in, const int32_t *__restrict__ idx,
                                                            int32_t *__restrict__ out, int64_t n_cap,
                                                            const int32_t *__restrict__ n_dev,
-                                                           const int32_t *__restrict__ partials) {
+                                                           const int32_t *__restrict__ partials, int as_flag) {
   __shared__ int s_warp[33];
   int64_t n = n_dev ? min((int64_t)*n_dev, n_cap) : n_cap;
   int64_t base = (int64_t)blockIdx.x * SC_TILE + (int64_t)threadIdx.x * SC_ITEMS;
@@ -118,6 +121,7 @@ __global__ void __launch_bounds__(SC_THREADS) k_scan_apply(const int32_t *__rest
   for (int i = 0; i < SC_ITEMS; ++i) {
     int64_t j = base + i;
     v[i] = (j < n) ? (idx ? in[idx[j]] : in[j]) : 0;
+    if (as_flag) v[i] = v[i] > 0;
     sum += v[i];
   }
   int tot;
@@ -131,15 +135,15 @@ __global__ void __launch_bounds__(SC_THREADS) k_scan_apply(const int32_t *__rest
 }
 
 int gs_exclusive_scan_i32(const int32_t *in, const int32_t *idx, int32_t *out, int64_t n, const int32_t *n_dev,
-                          int32_t *partials, int32_t *total, cudaStream_t st) {
+                          int32_t *partials, int32_t *total, cudaStream_t st, int as_flag) {
   if (n <= 0) {
     if (total) cudaMemsetAsync(total, 0, sizeof(int32_t), st);
     return GS_OK;
   }
   int nblk = gs_div_up(n, SC_TILE);
-  k_scan_reduce<<<nblk, SC_THREADS, 0, st>>>(in, idx, n, n_dev, partials);
+  k_scan_reduce<<<nblk, SC_THREADS, 0, st>>>(in, idx, n, n_dev, partials, as_flag);
   k_scan_partials<<<1, 1024, 0, st>>>(partials, nblk, total);
-  k_scan_apply<<<nblk, SC_THREADS, 0, st>>>(in, idx, out, n, n_dev, partials);
+  k_scan_apply<<<nblk, SC_THREADS, 0, st>>>(in, idx, out, n, n_dev, partials, as_flag);
   GS_LAUNCH_CHECK();
   return GS_OK;
 }

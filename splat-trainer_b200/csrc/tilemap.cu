@@ -15,19 +15,24 @@ __device__ __forceinline__ Footprint load_footprint(const float *__restrict__ g2
   return row_footprint(a.x, a.y, b.x, b.y, c.x, c.y, depth[i], thr, W, H);
 }
 
-// per row: tiles touched + depth sort key (0xffffffff for rows that touch nothing)
+// per row: tiles touched
 __global__ void __launch_bounds__(256) k_tile_count(const float *__restrict__ g2d, const float *__restrict__ depth,
-                                                    int64_t m, float thr, int W, int H, int32_t *__restrict__ counts,
-                                                    uint32_t *__restrict__ depth_keys, uint32_t *__restrict__ rows) {
+                                                    int64_t m, float thr, int W, int H, int32_t *__restrict__ counts) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= m) return;
   Footprint fp = load_footprint(g2d, depth, i, thr, W, H);
-  int c = footprint_count(fp, W, H);
-  counts[i] = c;
-  if (depth_keys) {
-    depth_keys[i] = c > 0 ? __float_as_uint(depth[i]) : 0xffffffffu;
-    rows[i] = (uint32_t)i;
-  }
+  counts[i] = footprint_count(fp, W, H);
+}
+
+// rows that touch at least one tile, compacted in row order: (depth bits, row) at rank[i]
+__global__ void __launch_bounds__(256) k_compact_live(const int32_t *__restrict__ counts, const float *__restrict__ depth,
+                                                      int64_t m, const int32_t *__restrict__ rank,
+                                                      uint32_t *__restrict__ depth_keys, uint32_t *__restrict__ rows) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m || counts[i] <= 0) return;
+  int r = rank[i];
+  depth_keys[r] = __float_as_uint(depth[i]);
+  rows[r] = (uint32_t)i;
 }
 
 __global__ void __launch_bounds__(256) k_sum_i32(const int32_t *__restrict__ v, int64_t n, int32_t *__restrict__ out) {
@@ -44,22 +49,21 @@ __global__ void __launch_bounds__(256) k_sum_i32(const int32_t *__restrict__ v, 
   }
 }
 
+// counters: [0] total overlaps, [1] overflow flag, [2] min(total, capacity), [3] rows touching >= 1 tile
 __global__ void k_finish_counters(int32_t *counters, int64_t max_overlaps) {
   int o = counters[0];
   counters[1] = (o > max_overlaps) ? 1 : 0;
   counters[2] = (int32_t)min((int64_t)o, max_overlaps);
 }
 
-// thread j = j-th row in depth order; writes its (tile, row) pairs at offsets[j]...
+// thread j = j-th live row in depth order; writes its (tile, row) pairs at offsets[j]...
 __global__ void __launch_bounds__(256) k_tile_emit(const float *__restrict__ g2d, const float *__restrict__ depth,
-                                                   int64_t m, float thr, int W, int H,
+                                                   const int32_t *__restrict__ live_dev, int64_t m, float thr, int W, int H,
                                                    const uint32_t *__restrict__ sorted_rows,
-                                                   const uint32_t *__restrict__ sorted_keys,
                                                    const int32_t *__restrict__ offsets, int64_t max_overlaps,
                                                    uint32_t *__restrict__ tile_keys, uint32_t *__restrict__ tile_vals) {
   int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= m) return;
-  if (sorted_keys[j] == 0xffffffffu) return;  // touches no tile (sorted to the tail)
+  if (j >= min((int64_t)*live_dev, m)) return;
   int64_t i = sorted_rows[j];
   Footprint fp = load_footprint(g2d, depth, i, thr, W, H);
   if (!fp.valid) return;
@@ -128,15 +132,15 @@ extern "C" int gs_tile_count(const gs_raster_config *h_cfg, int64_t m, const flo
   cudaStream_t st = (cudaStream_t)stream;
   GS_CUDA(cudaMemsetAsync(counters, 0, 4 * sizeof(int32_t), st));
   if (m <= 0) return GS_OK;
-  k_tile_count<<<gs_div_up(m, 256), 256, 0, st>>>(g2d, depth, m, h_cfg->alpha_threshold, width, height, counts,
-                                                 nullptr, nullptr);
+  k_tile_count<<<gs_div_up(m, 256), 256, 0, st>>>(g2d, depth, m, h_cfg->alpha_threshold, width, height, counts);
   GS_LAUNCH_CHECK();
   k_sum_i32<<<gs_div_up(m, 256), 256, 0, st>>>(counts, m, counters);
   GS_LAUNCH_CHECK();
   return GS_OK;
 }
 
-extern "C" int gs_tile_map(const gs_raster_config *h_cfg, int64_t m, const float *g2d, const float *depth, int width,
+extern "C" int gs_tile_map(const gs_raster_config *h_cfg, int64_t m, const float *g2d, const float *depth,
+                           const int32_t *counts_in, int width,
                            int height, int64_t max_overlaps, void *workspace, size_t workspace_bytes,
                            int32_t *overlap_to_point, int32_t *tile_ranges, int32_t *counters, void *stream) {
   GS_REQUIRE(h_cfg && h_cfg->tile_size == GS_TILE, "tile_size must be 16");
@@ -156,15 +160,25 @@ extern "C" int gs_tile_map(const gs_raster_config *h_cfg, int64_t m, const float
   if (m == 0) return GS_OK;
   float thr = h_cfg->alpha_threshold;
   int blocks = gs_div_up(m, 256);
-  k_tile_count<<<blocks, 256, 0, st>>>(g2d, depth, m, thr, width, height, w.counts, w.dk[0], w.dv[0]);
-  GS_LAUNCH_CHECK();
-  // (a) rows by depth: stable 32-bit LSD sort, ties keep row order
-  int in_b = 0;
-  int rc = gs_radix_sort_pingpong(w.dk[0], w.dv[0], w.dk[1], w.dv[1], m, nullptr, 0, 32, w.sort_ws, &in_b, st);
+  const int32_t *counts = counts_in;  // the fused path gets them from gs_project_fwd (same footprint code)
+  if (!counts) {
+    k_tile_count<<<blocks, 256, 0, st>>>(g2d, depth, m, thr, width, height, w.counts);
+    GS_LAUNCH_CHECK();
+    counts = w.counts;
+  }
+  // (a) compact the live rows (>= 1 tile) in row order, then sort them by depth: stable 32-bit LSD sort, ties keep
+  //     row order.  Culled / off-screen rows never enter the sort.
+  int32_t *live = counters + 3;
+  int rc = gs_exclusive_scan_i32(counts, nullptr, w.offsets, m, nullptr, w.partials, live, st, /*as_flag=*/1);
   if (rc != GS_OK) return rc;
-  uint32_t *skeys = w.dk[in_b], *srows = w.dv[in_b];
+  k_compact_live<<<blocks, 256, 0, st>>>(counts, depth, m, w.offsets, w.dk[0], w.dv[0]);
+  GS_LAUNCH_CHECK();
+  int in_b = 0;
+  rc = gs_radix_sort_pingpong(w.dk[0], w.dv[0], w.dk[1], w.dv[1], m, live, 0, 32, w.sort_ws, &in_b, st);
+  if (rc != GS_OK) return rc;
+  uint32_t *srows = w.dv[in_b];
   // (b) offsets of each depth-ordered row's overlaps; total -> counters[0]
-  rc = gs_exclusive_scan_i32(w.counts, (const int32_t *)srows, w.offsets, m, nullptr, w.partials, counters, st);
+  rc = gs_exclusive_scan_i32(counts, (const int32_t *)srows, w.offsets, m, live, w.partials, counters, st);
   if (rc != GS_OK) return rc;
   k_finish_counters<<<1, 1, 0, st>>>(counters, max_overlaps);
   if (max_overlaps == 0) return GS_OK;
@@ -176,7 +190,7 @@ extern "C" int gs_tile_map(const gs_raster_config *h_cfg, int64_t m, const float
   uint32_t *ka = w.tk[0], *kb = w.tk[1];
   uint32_t *va = (passes % 2) ? w.tv : (uint32_t *)overlap_to_point;
   uint32_t *vb = (passes % 2) ? (uint32_t *)overlap_to_point : w.tv;
-  k_tile_emit<<<blocks, 256, 0, st>>>(g2d, depth, m, thr, width, height, srows, skeys, w.offsets, max_overlaps, ka, va);
+  k_tile_emit<<<blocks, 256, 0, st>>>(g2d, depth, live, m, thr, width, height, srows, w.offsets, max_overlaps, ka, va);
   GS_LAUNCH_CHECK();
   rc = gs_radix_sort_pingpong(ka, va, kb, vb, max_overlaps, counters + 2, 0, bits, w.sort_ws, &in_b, st);
   if (rc != GS_OK) return rc;

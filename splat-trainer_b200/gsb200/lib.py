@@ -41,13 +41,13 @@ SIGNATURES = {
   "gs_default_raster_config": (None, [_CFG]),
   "gs_version": (_I, []),
   "gs_last_error": (C.c_char_p, []),
-  "gs_project_fwd": (_I, [_CAM, _CFG, _L, _P, _P, _P, _P, _P, _I, _P, _P, _P, _P, _I, _P]),
+  "gs_project_fwd": (_I, [_CAM, _CFG, _L, _P, _P, _P, _P, _P, _I, _P, _P, _P, _P, _I, _P, _P]),
   "gs_project_bwd": (_I, [_CAM, _CFG, _L, _P, _P, _P, _P, _P, _I, _P, _P, _I, _P, _I, _P, _P, _I,
                           _P, _P, _P, _P, _P, _I, _P]),
   "gs_sh_eval_fwd": (_I, [_L, _P, _P, _I, _P, C.POINTER(C.c_float), _P, _P]),
   "gs_sh_eval_bwd": (_I, [_L, _P, _P, _I, _P, C.POINTER(C.c_float), _P, _P, _P, _P]),
   "gs_tile_map_workspace_bytes": (_Z, [_L, _L, _I, _I]),
-  "gs_tile_map": (_I, [_CFG, _L, _P, _P, _I, _I, _L, _P, _Z, _P, _P, _P, _P]),
+  "gs_tile_map": (_I, [_CFG, _L, _P, _P, _P, _I, _I, _L, _P, _Z, _P, _P, _P, _P]),
   "gs_tile_count": (_I, [_CFG, _L, _P, _P, _I, _I, _P, _P, _P]),
   "gs_radix_sort_workspace_bytes": (_Z, [_L]),
   "gs_radix_sort_pairs": (_I, [_P, _P, _P, _P, _L, _P, _I, _I, _P, _Z, _P]),
@@ -56,7 +56,9 @@ SIGNATURES = {
   "gs_raster_bwd": (_I, [_CFG, _I, _L, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, _I, _P]),
   "gs_loss_l1_mse": (_I, [_L, _P, _P, _P, _F, _F, _P, _P, _P]),
   "gs_optim_vis_update": (_I, [_OPT, _L, _P, _P, _P, _P]),
-  "gs_optim_step": (_I, [_OPT, _I, _L, _I, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _F, _F, _I, _P]),
+  "gs_visible_indexes_workspace_bytes": (_Z, [_L]),
+  "gs_visible_indexes": (_I, [_L, _P, _P, _P, _P, _Z, _P]),
+  "gs_optim_step": (_I, [_OPT, _I, _L, _P, _P, _I, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _F, _F, _I, _P]),
   "gs_accumulate_stats": (_I, [_L, _P, _P, _P, _I, _P, _I, _F, _F, _P, _P, _P, _P, _P, _P, _P]),
   "gs_select_topk_workspace_bytes": (_Z, [_L]),
   "gs_select_topk_mask": (_I, [_P, _L, _L, _I, _P, _P, _Z, _P]),

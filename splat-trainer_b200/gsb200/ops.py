@@ -21,7 +21,7 @@ def tiles_of(width, height):
 
 # ---- (1) projection + SH ---------------------------------------------------------------------------
 def project_fwd(cam, cfg, position, log_scaling, rotation, alpha_logit, sh=None, sh_degree=0, acc=None,
-                out=None):
+                out=None, tile_counts=None):
   """gs_project_fwd.  Returns (g2d (n,6), depth (n), rgb (n,3)); row i belongs to Gaussian i."""
   n = position.shape[0]
   dev = position.device
@@ -34,7 +34,7 @@ def project_fwd(cam, cfg, position, log_scaling, rotation, alpha_logit, sh=None,
   L.check(L.load().gs_project_fwd(C.byref(cam), C.byref(cfg), n, L.ptr(_f32(position)), L.ptr(_f32(log_scaling)),
                                   L.ptr(_f32(rotation)), L.ptr(_f32(alpha_logit)), L.ptr(sh), sh_degree,
                                   L.ptr(g2d), L.ptr(depth), L.ptr(rgb), L.ptr(acc),
-                                  0 if acc is None else acc.shape[1], L.stream()))
+                                  0 if acc is None else acc.shape[1], L.ptr(tile_counts), L.stream()))
   return g2d, depth, rgb
 
 
@@ -117,7 +117,7 @@ class TileMapBuffers:
     self.counters = torch.zeros((4,), device=device, dtype=torch.int32)
 
 
-def tile_map(cfg, g2d, depth, width, height, max_overlaps=None, buffers=None):
+def tile_map(cfg, g2d, depth, width, height, max_overlaps=None, buffers=None, counts=None):
   """gs_tile_map.  With max_overlaps=None the exact total is read back first (one host sync, like the
   reference's mapper); the training path passes reusable `buffers` and never syncs.
   Returns (overlap_to_point[max_overlaps], tile_ranges (T,2), counters[4], buffers)."""
@@ -129,7 +129,7 @@ def tile_map(cfg, g2d, depth, width, height, max_overlaps=None, buffers=None):
     buffers = TileMapBuffers(m, max_overlaps, width, height, g2d.device)
   b = buffers
   assert b.m >= m and b.width == width and b.height == height
-  L.check(L.load().gs_tile_map(C.byref(cfg), m, L.ptr(g2d), L.ptr(depth), width, height, b.max_overlaps,
+  L.check(L.load().gs_tile_map(C.byref(cfg), m, L.ptr(g2d), L.ptr(depth), L.ptr(counts), width, height, b.max_overlaps,
                                L.ptr(b.workspace), b.workspace.numel(), L.ptr(b.overlap_to_point),
                                L.ptr(b.tile_ranges), L.ptr(b.counters), L.stream()))
   return b.overlap_to_point, b.tile_ranges, b.counters, b
@@ -209,11 +209,30 @@ def optim_vis_update(ocfg, visible, running_vis, step):
                                        L.ptr(step), L.stream()))
 
 
+class VisibleIndexes:
+  """Device-side `visible.nonzero()`: indexes (n,) int32 (first count[0] entries valid) + reusable workspace."""
+
+  def __init__(self, n, device):
+    self.n = n
+    self.indexes = torch.empty((max(n, 1),), device=device, dtype=torch.int32)
+    self.count = torch.zeros((1,), device=device, dtype=torch.int32)
+    self.nbytes = L.load().gs_visible_indexes_workspace_bytes(n)
+    self.workspace = torch.empty((self.nbytes,), device=device, dtype=torch.uint8)
+
+  def update(self, visible):
+    assert visible.shape[0] == self.n
+    L.check(L.load().gs_visible_indexes(self.n, L.ptr(_f32(visible)), L.ptr(self.indexes), L.ptr(self.count),
+                                        L.ptr(self.workspace), self.nbytes, L.stream()))
+    return self
+
+
 def optim_step(ocfg, kind, lr, param, grad, exp_avg, exp_avg_sq, visible, running_vis, step, basis_ls=None,
-               basis_q=None, post=L.GS_POST_NONE, post_lo=0.0, post_hi=0.0, zero_grad=True):
+               basis_q=None, post=L.GS_POST_NONE, post_lo=0.0, post_hi=0.0, zero_grad=True, indexes=None):
+  """indexes: a VisibleIndexes (updated from the same `visible`) -> only those rows are touched; None = dense."""
   n = param.shape[0]
   dim = param.numel() // max(n, 1) if n > 0 else 1
-  L.check(L.load().gs_optim_step(C.byref(ocfg), kind, n, dim, lr, L.ptr(_f32(param)), L.ptr(_f32(grad)), L.ptr(exp_avg),
+  L.check(L.load().gs_optim_step(C.byref(ocfg), kind, n, None if indexes is None else L.ptr(indexes.indexes),
+                                 None if indexes is None else L.ptr(indexes.count), dim, lr, L.ptr(_f32(param)), L.ptr(_f32(grad)), L.ptr(exp_avg),
                                  L.ptr(exp_avg_sq), L.ptr(visible), L.ptr(running_vis), L.ptr(step), L.ptr(basis_ls),
                                  L.ptr(basis_q), post, post_lo, post_hi, int(zero_grad), L.stream()))
 

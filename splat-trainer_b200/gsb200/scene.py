@@ -103,6 +103,7 @@ class SplatScene:
     self.opt_step = torch.zeros((n,), device=dev)
     self.stats = self.new_point_state(n)
     self._work = None
+    self._vis_idx = None
 
   def new_point_state(self, n):
     """PointState.new_zeros (reference controller/point_state.py:19-32)."""
@@ -128,7 +129,7 @@ class SplatScene:
     stride = ops.acc_stride(3)
     w = dict(W=W, H=H, n=n,
              g2d=torch.empty((n, 6), device=dev), depth=torch.empty((n,), device=dev), rgb=torch.empty((n, 3), device=dev),
-             acc=torch.zeros((n, stride), device=dev),
+             acc=torch.zeros((n, stride), device=dev), counts=torch.zeros((n,), device=dev, dtype=torch.int32),
              image=torch.empty((H, W, 3), device=dev), final_T=torch.empty((H, W), device=dev),
              n_contrib=torch.empty((H, W), device=dev, dtype=torch.int32), d_image=torch.empty((H, W, 3), device=dev),
              loss_sums=torch.zeros((2,), device=dev), tile=None)
@@ -141,8 +142,7 @@ class SplatScene:
     if w["tile"] is None:
       cap = self.config.max_overlaps
       if cap <= 0:
-        _, counters = ops.tile_count(self.raster_cfg, w["g2d"], w["depth"], cam.width, cam.height)
-        cap = int(int(counters[0].item()) * 1.5) + 65536
+        cap = int(int(w["counts"].sum(dtype=torch.int64).item()) * 1.5) + 65536
       w["tile"] = ops.TileMapBuffers(self.n, cap, cam.width, cam.height, self.device)
     return w["tile"]
 
@@ -167,10 +167,10 @@ class SplatScene:
     p = self.p
     self._mark("begin")
     ops.project_fwd(cam, self.raster_cfg, p["position"], p["log_scaling"], p["rotation"], p["alpha_logit"], p["sh"],
-                    self.config.sh_degree, acc=w["acc"], out=(w["g2d"], w["depth"], w["rgb"]))
+                    self.config.sh_degree, acc=w["acc"], out=(w["g2d"], w["depth"], w["rgb"]), tile_counts=w["counts"])
     self._mark("project_fwd")
     tb = self._tile_buffers(w, cam)
-    ops.tile_map(self.raster_cfg, w["g2d"], w["depth"], cam.width, cam.height, buffers=tb)
+    ops.tile_map(self.raster_cfg, w["g2d"], w["depth"], cam.width, cam.height, buffers=tb, counts=w["counts"])
     self._mark("tile_map")
     _, _, _, vis, med = ops.raster_fwd(self.raster_cfg, w["g2d"], w["rgb"], w["depth"], tb.overlap_to_point,
                                        tb.tile_ranges, cam.width, cam.height, visibility=visibility, median=median,
@@ -215,17 +215,20 @@ class SplatScene:
     vis, rv, st = self.visible, self.running_vis, self.opt_step
     self._mark("optim_begin")
     ops.optim_vis_update(o, vis, rv, st)
+    if self._vis_idx is None or self._vis_idx.n != self.n:
+      self._vis_idx = ops.VisibleIndexes(self.n, self.device)
+    ix = self._vis_idx.update(vis)  # device-side visible.nonzero() (reference mlp_scene.py:217), no host sync
     p, g, m1, m2 = self.p, self.g, self.m1, self.m2
     # position first: its local basis is built from log_scaling / rotation BEFORE their update (mlp_scene.py:219)
     ops.optim_step(o, L.GS_GROUP_LOCAL_VECTOR, c.lr_position, p["position"], g["position"], m1["position"],
-                   m2["position"], vis, rv, st, basis_ls=p["log_scaling"], basis_q=p["rotation"])
+                   m2["position"], vis, rv, st, basis_ls=p["log_scaling"], basis_q=p["rotation"], indexes=ix)
     ops.optim_step(o, L.GS_GROUP_SCALAR, c.lr_log_scaling, p["log_scaling"], g["log_scaling"], m1["log_scaling"],
-                   m2["log_scaling"], vis, rv, st, post=L.GS_POST_CLAMP, post_lo=-8.0, post_hi=8.0)
+                   m2["log_scaling"], vis, rv, st, post=L.GS_POST_CLAMP, post_lo=-8.0, post_hi=8.0, indexes=ix)
     ops.optim_step(o, L.GS_GROUP_VECTOR, c.lr_rotation, p["rotation"], g["rotation"], m1["rotation"], m2["rotation"],
-                   vis, rv, st, post=L.GS_POST_NORMALIZE)
+                   vis, rv, st, post=L.GS_POST_NORMALIZE, indexes=ix)
     ops.optim_step(o, L.GS_GROUP_SCALAR, c.lr_alpha_logit, p["alpha_logit"], g["alpha_logit"], m1["alpha_logit"],
-                   m2["alpha_logit"], vis, rv, st)
-    ops.optim_step(o, L.GS_GROUP_VECTOR, c.lr_sh, p["sh"], g["sh"], m1["sh"], m2["sh"], vis, rv, st)
+                   m2["alpha_logit"], vis, rv, st, indexes=ix)
+    ops.optim_step(o, L.GS_GROUP_VECTOR, c.lr_sh, p["sh"], g["sh"], m1["sh"], m2["sh"], vis, rv, st, indexes=ix)
     self._mark("optim")
     vis.zero_()  # zero_grad(): gradient rows were cleared by the optimiser kernels (mlp_scene.py:155-161)
 

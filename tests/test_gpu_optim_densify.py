@@ -16,9 +16,10 @@ def _quat(rng, n):
   return q
 
 
+@pytest.mark.parametrize("indexed", [False, True])
 @pytest.mark.parametrize("mode", [0, 1])
 @pytest.mark.parametrize("kind,dim,post", [(0, 1, 0), (0, 3, 2), (1, 4, 1), (1, 48, 0), (1, 16, 0), (2, 3, 0), (0, 48, 0)])
-def test_optim_step_matches_oracle(mode, kind, dim, post):
+def test_optim_step_matches_oracle(mode, kind, dim, post, indexed):
   orc = oracle()
   rng = np.random.default_rng(100 + 10 * kind + dim)
   n = 3001
@@ -42,8 +43,12 @@ def test_optim_step_matches_oracle(mode, kind, dim, post):
                    ref["step"], bls, bq, post, -0.5, 0.5, 1)
     locfg = to_lib_optim(ocfg)
     ops.optim_vis_update(locfg, vis_c, dev["running"], dev["step"])
+    ix = ops.VisibleIndexes(n, "cuda").update(vis_c) if indexed else None
+    if indexed:
+      assert int(ix.count.item()) == (visible > 0).sum()
+      assert np.array_equal(npy(ix.indexes)[:int(ix.count.item())], np.nonzero(visible > 0)[0])
     ops.optim_step(locfg, kind, 0.05, dev["param"], dgrad, dev["exp_avg"], dev["exp_avg_sq"], vis_c, dev["running"],
-                   dev["step"], cu(bls), cu(bq), post, -0.5, 0.5, True)
+                   dev["step"], cu(bls), cu(bq), post, -0.5, 0.5, True, indexes=ix)
     for k in state:
       np.testing.assert_allclose(npy(dev[k]), ref[k], rtol=2e-4, atol=2e-6, err_msg=f"{k} it{it}")
     # consumed gradient rows are cleared, untouched rows keep theirs
