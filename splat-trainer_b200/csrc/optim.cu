@@ -308,7 +308,8 @@ extern "C" int gs_optim_step(const gs_optim_config *h, int kind, int64_t n, cons
 __device__ __forceinline__ float exp_lerp(float t, float a, float b) {  // reference util/misc.py:56-59
   float m = fmaxf(a, b);
   float ea = expf(a - m), eb = expf(b - m);
-  return m + logf(ea + t * (eb - ea));
+  float l = t < 0.5f ? ea + t * (eb - ea) : eb - (eb - ea) * (1.0f - t);  // torch.lerp's two branches
+  return m + logf(l);
 }
 
 __global__ void __launch_bounds__(256) k_accumulate_stats(int64_t m, const int64_t *__restrict__ idx, const float *__restrict__ g2d,
