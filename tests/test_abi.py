@@ -53,7 +53,8 @@ def test_no_torch_in_the_abi(built):
   exported = [l.split()[-1] for l in out.splitlines() if " T " in l]
   assert exported and all(not re.search(r"torch|at::|c10", s) for s in exported)
   deps = subprocess.run(["ldd", built], capture_output=True, text=True).stdout
-  assert "torch" not in deps and "c10" not in deps
+  libs = [l.split()[0] for l in deps.splitlines() if l.strip()]  # names only: load addresses are random hex
+  assert not any(re.search(r"torch|c10", l) for l in libs)
   code = re.sub(r"/\*.*?\*/", "", open(HEADER).read(), flags=re.S)  # declarations only
   assert not re.search(r"torch|at::|Tensor", code)
 
