@@ -87,3 +87,31 @@ __device__ __forceinline__ float warp_sum(float v) {
 int64_t gs_scan_partials(int64_t n);
 int gs_exclusive_scan_i32(const int32_t *in, const int32_t *idx, int32_t *out, int64_t n, const int32_t *n_dev,
                           int32_t *partials, int32_t *total, cudaStream_t st, int as_flag = 0);
+
+// ---- decoupled look-back (single-pass chained scan) ------------------------------------------------------
+// A status word carries a 30-bit count and a 2-bit flag in ONE 32-bit store, so no fence is needed:
+// 0 = not yet published, LOCAL = this tile's own aggregate, INCL = inclusive prefix up to and including the tile.
+// Tiles take their index from an atomic ticket, so every predecessor of a running tile has already started.
+constexpr uint32_t GS_LB_LOCAL = 1u << 30, GS_LB_INCL = 2u << 30, GS_LB_VAL = (1u << 30) - 1u;
+
+__device__ __forceinline__ uint32_t gs_ld_status(const uint32_t *p) { return *(const volatile uint32_t *)p; }
+__device__ __forceinline__ void gs_st_status(uint32_t *p, uint32_t v) { *(volatile uint32_t *)p = v; }
+
+// Whole-warp look-back over a scalar status array: returns the exclusive prefix of `tile` (all lanes).
+__device__ __forceinline__ uint32_t gs_lookback_warp(const uint32_t *status, int tile) {
+  int lane = threadIdx.x & 31;
+  uint32_t prefix = 0;
+  for (int base = tile - 1; base >= 0; base -= 32) {
+    int idx = base - lane;
+    uint32_t s = GS_LB_INCL;  // lanes before tile 0 act as an inclusive zero
+    if (idx >= 0) {
+      do { s = gs_ld_status(status + idx); } while ((s >> 30) == 0);
+    }
+    unsigned incl = __ballot_sync(GS_FULL, (s >> 30) == 2u);
+    int first = incl ? (__ffs(incl) - 1) : 32;
+    uint32_t c = (lane <= first) ? (s & GS_LB_VAL) : 0u;
+    prefix += __reduce_add_sync(GS_FULL, c);
+    if (incl) break;
+  }
+  return prefix;
+}

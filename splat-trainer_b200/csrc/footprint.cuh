@@ -105,3 +105,91 @@ __device__ __forceinline__ int footprint_count(const Footprint &fp, int W, int H
     for (int tx = fp.tx0; tx <= fp.tx1; ++tx) c += tile_hit(fp, tx, ty, W, H) ? 1 : 0;
   return c;
 }
+
+// ---- per-row tile record (16 B) -------------------------------------------------------------------------
+// The cull already visits every tile of a row's rect; it keeps the outcome so that the mapper never repeats the
+// float tests: rect origin/shape plus, for rects of <= 64 tiles, the exact hit bitmask (bit r*w+c = tile
+// (tx0+c, ty0+r)).  Rows with larger rects ("big") are re-tested per 8x8-tile super-tile by the mapper.
+//   x = tx0 | ty0 << 16      y = w | h << 8 | nsuper << 16 (bit 31: big)      z,w = mask lo/hi
+constexpr int GS_SUPER = 8;  // super-tile edge in tiles (8x8 tiles = 64 sub-tiles = one 64-bit mask)
+constexpr uint32_t GS_REC_BIG = 0x80000000u;
+
+struct RecView {
+  int tx0, ty0, w, h, nsuper;
+  bool big;
+  unsigned long long mask;
+};
+
+__device__ __forceinline__ RecView rec_view(const uint4 &r) {
+  RecView v;
+  v.tx0 = (int)(r.x & 0xffffu); v.ty0 = (int)(r.x >> 16);
+  v.w = (int)(r.y & 0xffu); v.h = (int)((r.y >> 8) & 0xffu);
+  v.nsuper = (int)((r.y >> 16) & 0x7fffu);
+  v.big = (r.y & GS_REC_BIG) != 0;
+  v.mask = ((unsigned long long)r.w << 32) | r.z;
+  return v;
+}
+
+// hit mask of a SMALL row restricted to super-tile (sx, sy): bit (ty&7)*8 + (tx&7)
+__device__ __forceinline__ unsigned long long rec_submask(const RecView &v, int sx, int sy) {
+  unsigned long long sub = 0ull;
+  int rel = v.tx0 - GS_SUPER * sx;
+  unsigned long long rowsel = (v.w >= 64) ? ~0ull : ((1ull << v.w) - 1ull);
+  int r0 = max(0, GS_SUPER * sy - v.ty0), r1 = min(v.h - 1, GS_SUPER * sy + GS_SUPER - 1 - v.ty0);
+  for (int r = r0; r <= r1; ++r) {
+    unsigned long long bits = (v.mask >> (r * v.w)) & rowsel;
+    unsigned long long seg = rel >= 0 ? (rel < 64 ? bits << rel : 0ull) : (-rel < 64 ? bits >> (-rel) : 0ull);
+    sub |= (seg & 0xffull) << (GS_SUPER * ((v.ty0 + r) & (GS_SUPER - 1)));
+  }
+  return sub;
+}
+
+// exact hit mask of ANY valid footprint restricted to super-tile (sx, sy) (used for big rows)
+__device__ __forceinline__ unsigned long long footprint_submask(const Footprint &fp, int sx, int sy, int W, int H) {
+  unsigned long long sub = 0ull;
+  int ty_lo = max(fp.ty0, GS_SUPER * sy), ty_hi = min(fp.ty1, GS_SUPER * sy + GS_SUPER - 1);
+  int tx_lo = max(fp.tx0, GS_SUPER * sx), tx_hi = min(fp.tx1, GS_SUPER * sx + GS_SUPER - 1);
+  for (int ty = ty_lo; ty <= ty_hi; ++ty)
+    for (int tx = tx_lo; tx <= tx_hi; ++tx)
+      if (tile_hit(fp, tx, ty, W, H)) sub |= 1ull << (GS_SUPER * (ty & (GS_SUPER - 1)) + (tx & (GS_SUPER - 1)));
+  return sub;
+}
+
+// Builds the record, returns the tile count, and (totals != NULL) adds 1 to totals[tile] for every hit tile.
+__device__ __forceinline__ int footprint_record(const Footprint &fp, int W, int H, int32_t *__restrict__ totals, uint4 &rec) {
+  rec = make_uint4(0u, 0u, 0u, 0u);
+  if (!fp.valid) return 0;
+  int TX = (W + GS_TILE - 1) / GS_TILE;
+  int w = fp.tx1 - fp.tx0 + 1, h = fp.ty1 - fp.ty0 + 1;
+  int count = 0;
+  if (w * h <= 64) {
+    unsigned long long mask = 0ull;
+    int bit = 0;
+    for (int ty = fp.ty0; ty <= fp.ty1; ++ty)
+      for (int tx = fp.tx0; tx <= fp.tx1; ++tx, ++bit)
+        if (tile_hit(fp, tx, ty, W, H)) {
+          mask |= 1ull << bit;
+          if (totals) atomicAdd(totals + ty * TX + tx, 1);
+        }
+    count = __popcll(mask);
+    if (count == 0) return 0;
+    RecView v;
+    v.tx0 = fp.tx0; v.ty0 = fp.ty0; v.w = w; v.h = h; v.mask = mask; v.big = false; v.nsuper = 0;
+    int ns = 0;
+    for (int sy = fp.ty0 / GS_SUPER; sy <= fp.ty1 / GS_SUPER; ++sy)
+      for (int sx = fp.tx0 / GS_SUPER; sx <= fp.tx1 / GS_SUPER; ++sx) ns += rec_submask(v, sx, sy) != 0ull;
+    rec = make_uint4((uint32_t)fp.tx0 | ((uint32_t)fp.ty0 << 16), (uint32_t)w | ((uint32_t)h << 8) | ((uint32_t)ns << 16),
+                     (uint32_t)mask, (uint32_t)(mask >> 32));
+  } else {
+    for (int ty = fp.ty0; ty <= fp.ty1; ++ty)
+      for (int tx = fp.tx0; tx <= fp.tx1; ++tx)
+        if (tile_hit(fp, tx, ty, W, H)) {
+          ++count;
+          if (totals) atomicAdd(totals + ty * TX + tx, 1);
+        }
+    if (count == 0) return 0;
+    int ns = (fp.tx1 / GS_SUPER - fp.tx0 / GS_SUPER + 1) * (fp.ty1 / GS_SUPER - fp.ty0 / GS_SUPER + 1);
+    rec = make_uint4((uint32_t)fp.tx0 | ((uint32_t)fp.ty0 << 16), ((uint32_t)ns << 16) | GS_REC_BIG, 0u, 0u);
+  }
+  return count;
+}

@@ -1,7 +1,7 @@
 // scan_sort.cu — exclusive scan and stable LSD radix sort of (u32 key, u32 value) pairs.
 //
-// Both are deterministic three-kernel schemes (tile reduce -> scan of tile totals -> tile apply):
-// HBM-bound integer work, coalesced 128-B warp accesses, no atomics on the data path.  The sort
+// The scan is a deterministic three-kernel scheme (tile reduce -> scan of tile totals -> tile apply); the sort is
+// an onesweep LSD radix sort (one histogram read + one chained-scan kernel per 8-bit pass).  HBM-bound integer work.  The sort
 // serves SURVEY §8 a8 (the (tile, depth) key sort inside render_projected, reference
 // scene/mlp_scene.py:418): rows are sorted by the 32 depth bits (4 passes over M rows), overlaps
 // are emitted in that order and stably sorted by tile id (1–2 passes over O pairs), which equals
@@ -148,100 +148,215 @@ int gs_exclusive_scan_i32(const int32_t *in, const int32_t *idx, int32_t *out, i
   return GS_OK;
 }
 
-// ---- radix sort -------------------------------------------------------------------------------
-constexpr int RS_THREADS = 256;
-constexpr int RS_ITEMS = 16;
-constexpr int RS_TILE = RS_THREADS * RS_ITEMS;  // 4096 pairs per CTA
-constexpr int RS_WARPS = RS_THREADS / 32;
+// ---- radix sort (onesweep) ------------------------------------------------------------------------
+// One read of the keys builds the digit histograms of ALL passes (k_os_hist); each pass is then ONE
+// kernel: a tile of 4096 pairs is ranked in registers (ballot-based digit matching, stable), its 256
+// digit counts are chained to the previous tiles by decoupled look-back, the pairs are re-ordered by
+// digit in shared memory and written out as contiguous runs.  Per pass each pair is read once and
+// written once (16 B) — the HBM floor of an LSD pass — with 1 launch instead of 5.
+constexpr int OS_THREADS = 256;
+constexpr int OS_ITEMS = 16;
+constexpr int OS_TILE = OS_THREADS * OS_ITEMS;  // 4096 pairs per CTA
+constexpr int OS_WARPS = OS_THREADS / 32;
+constexpr int OS_MAX_PASSES = 4;
 
-// digit histogram of each 4096-pair tile, stored digit-major: hist[d * nblk + blk]
-__global__ void __launch_bounds__(RS_THREADS) k_rs_hist(const uint32_t *__restrict__ keys, int64_t n_cap,
-                                                        const int32_t *__restrict__ n_dev, int shift, uint32_t mask,
-                                                        int32_t *__restrict__ hist, int nblk) {
-  __shared__ int h[256];
-  h[threadIdx.x] = 0;
-  __syncthreads();
-  int64_t n = n_dev ? min((int64_t)*n_dev, n_cap) : n_cap;
-  int64_t base = (int64_t)blockIdx.x * RS_TILE;
-  int lane = threadIdx.x & 31;
-#pragma unroll 4
-  for (int i = 0; i < RS_ITEMS; ++i) {
-    int64_t j = base + i * RS_THREADS + threadIdx.x;
-    bool valid = j < n;
-    int d = valid ? (int)((keys[j] >> shift) & mask) : 256 + lane;
-    unsigned peers = __match_any_sync(GS_FULL, d);
-    if (valid && lane == __ffs(peers) - 1) atomicAdd(&h[d], __popc(peers));
+// lanes of the warp holding the same digit as this lane: NB ballots, no match.any (FULL = every lane valid)
+template <int NB, bool FULL>
+__device__ __forceinline__ unsigned os_match(uint32_t d, bool valid) {
+  unsigned peers = 0xffffffffu;
+  if (!FULL) {
+    unsigned vm = __ballot_sync(GS_FULL, valid);
+    peers = valid ? vm : ~vm;
   }
-  __syncthreads();
-  hist[(int64_t)threadIdx.x * nblk + blockIdx.x] = h[threadIdx.x];
+#pragma unroll
+  for (int b = 0; b < NB; ++b) {
+    bool bit = (d >> b) & 1u;
+    unsigned m = __ballot_sync(GS_FULL, bit);
+    peers &= bit ? m : ~m;
+  }
+  return peers;
 }
 
-// stable scatter: rank of a pair = global base of (digit, tile) + pairs of the same digit in earlier
-// warps of the tile + earlier pairs of the same digit in this warp (match_any ballots, no atomics)
-__global__ void __launch_bounds__(RS_THREADS) k_rs_scatter(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
-                                                           uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out,
-                                                           int64_t n_cap, const int32_t *__restrict__ n_dev, int shift,
-                                                           uint32_t mask, const int32_t *__restrict__ hist_scanned, int nblk) {
-  __shared__ int wcnt[RS_WARPS][256];
+// Digit histograms of all NP passes in one read of the keys.  No atomics and no warp matching on the data path
+// (smem atomics cost 2 cycles per lane): every LANE keeps private 8-bit counters, laid out so that the 32 lanes of
+// a warp hit 32 different bytes ((warp, pass, digit) row = 32 bytes), and a lane counts at most 255 keys per block.
+constexpr int OH_THREADS = 128;
+constexpr int OH_WARPS = OH_THREADS / 32;
+constexpr int OH_PER_LANE = 192;                       // <= 255 keys per lane per block
+constexpr int OH_BLOCK_ITEMS = OH_THREADS * OH_PER_LANE;
+
+template <int NP>
+__global__ void __launch_bounds__(OH_THREADS) k_os_hist(const uint32_t *__restrict__ keys, int64_t n_cap,
+                                                        const int32_t *__restrict__ n_dev, int begin_bit, int end_bit,
+                                                        uint32_t *__restrict__ ghist) {
+  extern __shared__ uint32_t oh_smem[];                // [OH_WARPS][NP][256][8 words]
+  uint8_t *cnt = reinterpret_cast<uint8_t *>(oh_smem);
   int64_t n = n_dev ? min((int64_t)*n_dev, n_cap) : n_cap;
-  int64_t base = (int64_t)blockIdx.x * RS_TILE;
+  int64_t base = (int64_t)blockIdx.x * OH_BLOCK_ITEMS;
   if (base >= n) return;
-  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-#pragma unroll
-  for (int i = 0; i < RS_WARPS; ++i) wcnt[i][threadIdx.x] = 0;
+  for (int i = threadIdx.x; i < OH_WARPS * NP * 256 * 8; i += OH_THREADS) oh_smem[i] = 0;
   __syncthreads();
-  uint32_t k[RS_ITEMS], v[RS_ITEMS];
-  int rank[RS_ITEMS];
-  int64_t wbase = base + (int64_t)w * (RS_ITEMS * 32);
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  uint8_t *mine = cnt + (size_t)w * NP * 256 * 32 + lane;
+  int64_t wbase = base + (int64_t)w * (32 * OH_PER_LANE);
+  constexpr int U = 8;
+#pragma unroll 1
+  for (int r0 = 0; r0 < OH_PER_LANE; r0 += U) {
+    uint32_t k[U];
+    bool ok[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      int64_t j = wbase + (int64_t)(r0 + u) * 32 + lane;
+      ok[u] = j < n;
+      k[u] = ok[u] ? keys[j] : 0u;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (!ok[u]) continue;
+#pragma unroll
+      for (int p = 0; p < NP; ++p) {
+        int shift = begin_bit + 8 * p;
+        int bits = min(8, end_bit - shift);
+        uint32_t d = (k[u] >> shift) & ((1u << bits) - 1u);
+        uint8_t *c = mine + (p * 256 + d) * 32;
+        *c = (uint8_t)(*c + 1);
+      }
+    }
+  }
+  __syncthreads();
+  // reduce: thread t sums the 32 byte counters of (warp, pass, digit) rows t, t+128, ...
+  for (int row = threadIdx.x; row < NP * 256; row += OH_THREADS) {
+    uint32_t tot = 0;
+#pragma unroll
+    for (int ww = 0; ww < OH_WARPS; ++ww) {
+      const uint32_t *r = oh_smem + ((size_t)ww * NP * 256 + row) * 8;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) tot = __dp4a(r[q], 0x01010101u, tot);
+    }
+    if (tot) atomicAdd(ghist + row, tot);
+  }
+}
+
+// stable in-warp ranks of the tile's pairs (warp-striped: warp w owns items [w*512, w*512+512), round r = 32 items)
+template <int NB, bool FULL>
+__device__ __forceinline__ void os_rank(const uint32_t *k, uint16_t *rank, uint32_t (*wcnt)[256], int w, int lane,
+                                        int shift, uint32_t mask, int valid_in_warp) {
   unsigned lt = (1u << lane) - 1u;
 #pragma unroll
-  for (int r = 0; r < RS_ITEMS; ++r) {
-    int64_t j = wbase + r * 32 + lane;
-    bool valid = j < n;
-    k[r] = valid ? keys_in[j] : 0xffffffffu;
-    v[r] = valid ? vals_in[j] : 0u;
-    int d = valid ? (int)((k[r] >> shift) & mask) : 256 + lane;
-    unsigned peers = __match_any_sync(GS_FULL, d);
+  for (int r = 0; r < OS_ITEMS; ++r) {
+    bool valid = FULL || (r * 32 + lane < valid_in_warp);
+    uint32_t d = (k[r] >> shift) & mask;
+    unsigned peers = os_match<NB, FULL>(d, valid);
     int leader = __ffs(peers) - 1;
-    int pre = 0;
+    uint32_t pre = 0;
     if (valid && lane == leader) {
       pre = wcnt[w][d];
       wcnt[w][d] = pre + __popc(peers);
     }
     pre = __shfl_sync(GS_FULL, pre, leader);
-    rank[r] = pre + __popc(peers & lt);
+    rank[r] = (uint16_t)(pre + __popc(peers & lt));
     __syncwarp();
   }
-  __syncthreads();
-  {
-    int d = threadIdx.x;
-    int run = hist_scanned[(int64_t)d * nblk + blockIdx.x];
+}
+
+template <int NB>
+__global__ void __launch_bounds__(OS_THREADS, 3) k_os_pass(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
+                                                           uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out,
+                                                           int n_cap, const int32_t *__restrict__ n_dev, int shift,
+                                                           const uint32_t *__restrict__ ghist, uint32_t *__restrict__ status,
+                                                           uint32_t *__restrict__ ticket) {
+  constexpr uint32_t mask = (1u << NB) - 1u;
+  __shared__ uint32_t s_keys[OS_TILE];
+  __shared__ uint32_t s_vals[OS_TILE];
+  __shared__ uint32_t wcnt[OS_WARPS][256];
+  __shared__ uint32_t s_binoff[256];
+  __shared__ uint32_t s_gbase[256];  // global position of local slot 0 of the digit's run (mod 2^32)
+  __shared__ int s_warp[33];
+  __shared__ int s_tile;
+  if (threadIdx.x == 0) s_tile = (int)atomicAdd(ticket, 1u);
 #pragma unroll
-    for (int i = 0; i < RS_WARPS; ++i) {
-      int c = wcnt[i][d];
-      wcnt[i][d] = run;
-      run += c;
+  for (int i = 0; i < OS_WARPS; ++i) wcnt[i][threadIdx.x] = 0;
+  __syncthreads();
+  const int tile = s_tile;
+  const int n = n_dev ? min(*n_dev, n_cap) : n_cap;
+  const int base = tile * OS_TILE;
+  if (base >= n) return;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int cnt = min(OS_TILE, n - base);
+  uint32_t k[OS_ITEMS], v[OS_ITEMS];
+  uint16_t rank[OS_ITEMS];
+  const int wbase = base + w * (OS_ITEMS * 32);
+  const int valid_in_warp = cnt - w * (OS_ITEMS * 32);
+  if (cnt == OS_TILE) {
+#pragma unroll
+    for (int r = 0; r < OS_ITEMS; ++r) { k[r] = keys_in[wbase + r * 32 + lane]; v[r] = vals_in[wbase + r * 32 + lane]; }
+    os_rank<NB, true>(k, rank, wcnt, w, lane, shift, mask, valid_in_warp);
+  } else {
+#pragma unroll
+    for (int r = 0; r < OS_ITEMS; ++r) {
+      bool valid = r * 32 + lane < valid_in_warp;
+      k[r] = valid ? keys_in[wbase + r * 32 + lane] : 0xffffffffu;
+      v[r] = valid ? vals_in[wbase + r * 32 + lane] : 0u;
+    }
+    os_rank<NB, false>(k, rank, wcnt, w, lane, shift, mask, valid_in_warp);
+  }
+  __syncthreads();
+  // thread d owns digit d: per-warp exclusive offsets, tile count, chained prefix over the earlier tiles
+  const int d = threadIdx.x;
+  uint32_t run = 0;
+#pragma unroll
+  for (int i = 0; i < OS_WARPS; ++i) {
+    uint32_t c = wcnt[i][d];
+    wcnt[i][d] = run;
+    run += c;
+  }
+  uint32_t *my_status = status + (size_t)tile * 256 + d;
+  gs_st_status(my_status, run | (tile == 0 ? GS_LB_INCL : GS_LB_LOCAL));
+  int tot;
+  uint32_t binoff = (uint32_t)block_exclusive_scan((int)run, s_warp, tot);
+  __syncthreads();  // s_warp reused below
+  int gtot;
+  uint32_t gex = (uint32_t)block_exclusive_scan((int)ghist[d], s_warp, gtot);
+  uint32_t prefix = 0;
+  for (int p = tile - 1; p >= 0; --p) {
+    uint32_t s;
+    const uint32_t *ps = status + (size_t)p * 256 + d;
+    do { s = gs_ld_status(ps); } while ((s >> 30) == 0);
+    prefix += s & GS_LB_VAL;
+    if ((s >> 30) == 2u) break;
+  }
+  if (tile > 0) gs_st_status(my_status, (prefix + run) | GS_LB_INCL);
+  s_binoff[d] = binoff;
+  s_gbase[d] = gex + prefix - binoff;
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < OS_ITEMS; ++r) {
+    if (r * 32 + lane < valid_in_warp) {
+      uint32_t dd = (k[r] >> shift) & mask;
+      uint32_t pos = s_binoff[dd] + wcnt[w][dd] + rank[r];
+      s_keys[pos] = k[r];
+      s_vals[pos] = v[r];
     }
   }
   __syncthreads();
 #pragma unroll
-  for (int r = 0; r < RS_ITEMS; ++r) {
-    int64_t j = wbase + r * 32 + lane;
-    if (j < n) {
-      int d = (int)((k[r] >> shift) & mask);
-      int pos = wcnt[w][d] + rank[r];
-      keys_out[pos] = k[r];
-      vals_out[pos] = v[r];
+  for (int r = 0; r < OS_ITEMS; ++r) {
+    int i = r * OS_THREADS + threadIdx.x;
+    if (i < cnt) {
+      uint32_t key = s_keys[i];
+      uint32_t pos = s_gbase[(key >> shift) & mask] + (uint32_t)i;
+      keys_out[pos] = key;
+      vals_out[pos] = s_vals[i];
     }
   }
 }
 
+static size_t os_header_bytes() { return gs_align256((size_t)(OS_MAX_PASSES * 256 + 64) * sizeof(uint32_t)); }
+
 extern "C" size_t gs_radix_sort_workspace_bytes(int64_t n) {
-  int64_t nblk = (n + RS_TILE - 1) / RS_TILE;
+  int64_t nblk = (n + OS_TILE - 1) / OS_TILE;
   if (nblk < 1) nblk = 1;
-  size_t hist = gs_align256((size_t)256 * nblk * sizeof(int32_t));
-  size_t part = gs_align256((size_t)gs_scan_partials(256 * nblk) * sizeof(int32_t));
-  return hist + part;
+  return os_header_bytes() + gs_align256((size_t)OS_MAX_PASSES * nblk * 256 * sizeof(uint32_t));
 }
 
 // internal: ping-pong sort; returns (via *result_in_b) which buffer pair holds the result
@@ -249,17 +364,44 @@ int gs_radix_sort_pingpong(uint32_t *ka, uint32_t *va, uint32_t *kb, uint32_t *v
                            int begin_bit, int end_bit, void *workspace, int *result_in_b, cudaStream_t st) {
   *result_in_b = 0;
   if (n <= 0 || end_bit <= begin_bit) return GS_OK;
-  int nblk = gs_div_up(n, RS_TILE);
-  int32_t *hist = (int32_t *)workspace;
-  int32_t *partials = (int32_t *)((char *)workspace + gs_align256((size_t)256 * nblk * sizeof(int32_t)));
+  if (n >= ((int64_t)1 << 30)) { gs_set_error("radix sort: n must be < 2^30"); return GS_ERR_INVALID; }
+  int nblk = gs_div_up(n, OS_TILE);
+  int passes = (end_bit - begin_bit + 7) / 8;
+  uint32_t *ghist = (uint32_t *)workspace;
+  uint32_t *tickets = ghist + OS_MAX_PASSES * 256;
+  uint32_t *status = (uint32_t *)((char *)workspace + os_header_bytes());
+  GS_CUDA(cudaMemsetAsync(workspace, 0, os_header_bytes() + (size_t)passes * nblk * 256 * sizeof(uint32_t), st));
+  int hgrid = gs_div_up(n, OH_BLOCK_ITEMS);
+  size_t hsm = (size_t)OH_WARPS * passes * 256 * 32;
+#define GS_HIST(NP)                                                                                            \
+  do {                                                                                                         \
+    GS_CUDA(cudaFuncSetAttribute(k_os_hist<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hsm));       \
+    k_os_hist<NP><<<hgrid, OH_THREADS, hsm, st>>>(ka, n, n_dev, begin_bit, end_bit, ghist);                     \
+  } while (0)
+  switch (passes) {
+    case 1: GS_HIST(1); break;
+    case 2: GS_HIST(2); break;
+    case 3: GS_HIST(3); break;
+    default: GS_HIST(4); break;
+  }
+#undef GS_HIST
   uint32_t *ks = ka, *vs = va, *kd = kb, *vd = vb;
-  for (int bit = begin_bit; bit < end_bit; bit += 8) {
+  for (int p = 0; p < passes; ++p) {
+    int bit = begin_bit + 8 * p;
     int bits = min(8, end_bit - bit);
-    uint32_t mask = (1u << bits) - 1u;
-    k_rs_hist<<<nblk, RS_THREADS, 0, st>>>(ks, n, n_dev, bit, mask, hist, nblk);
-    int rc = gs_exclusive_scan_i32(hist, nullptr, hist, (int64_t)256 * nblk, nullptr, partials, nullptr, st);
-    if (rc != GS_OK) return rc;
-    k_rs_scatter<<<nblk, RS_THREADS, 0, st>>>(ks, vs, kd, vd, n, n_dev, bit, mask, hist, nblk);
+    uint32_t *stp = status + (size_t)p * nblk * 256;
+#define GS_PASS(NB) k_os_pass<NB><<<nblk, OS_THREADS, 0, st>>>(ks, vs, kd, vd, (int)n, n_dev, bit, ghist + p * 256, stp, tickets + p)
+    switch (bits) {
+      case 1: GS_PASS(1); break;
+      case 2: GS_PASS(2); break;
+      case 3: GS_PASS(3); break;
+      case 4: GS_PASS(4); break;
+      case 5: GS_PASS(5); break;
+      case 6: GS_PASS(6); break;
+      case 7: GS_PASS(7); break;
+      default: GS_PASS(8); break;
+    }
+#undef GS_PASS
     uint32_t *t;
     t = ks; ks = kd; kd = t;
     t = vs; vs = vd; vd = t;
