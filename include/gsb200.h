@@ -80,14 +80,16 @@ const char *gs_last_error(void);
  *     colour = 0.5 + Σ_k Y_k(dir) sh[c][k] (util/misc.py:41-49). sh may be NULL (rgb untouched).
  *     acc (nullable): the raster-backward accumulator (n × acc_stride); rows of in-view
  *     Gaussians are zeroed here so no separate memset is needed.
- *     tile_counts (nullable, n): tiles touched by each row (0 for culled rows) — the cull already computes
- *     them, and gs_tile_map(counts_in = tile_counts) then skips its own counting pass.
+ *     tile_info (nullable, gs_tile_info_bytes(n, W, H) bytes, 256-B aligned): what the cull learns about each row's
+ *     tile footprint (16-B record with the exact hit mask, tile count, per-tile totals); gs_tile_map(tile_info_in =
+ *     tile_info) then skips its own footprint pass.  Opaque to the caller.
  * ------------------------------------------------------------------------------------- */
 int gs_project_fwd(const gs_camera *h_cam, const gs_raster_config *h_cfg, int64_t n,
                    const float *position, const float *log_scaling, const float *rotation,
                    const float *alpha_logit, const float *sh, int sh_degree,
                    float *g2d, float *depth, float *rgb,
-                   float *acc, int acc_stride, int32_t *tile_counts, void *stream);
+                   float *acc, int acc_stride, void *tile_info, void *stream);
+size_t gs_tile_info_bytes(int64_t n, int width, int height);
 
 /* Backward of gs_project_fwd.  d_g2d (row stride d_g2d_stride floats, 6 used),
  * d_rgb (stride d_rgb_stride, 3 used), d_depth (nullable, n) are dL/d(outputs).
@@ -118,20 +120,21 @@ int gs_sh_eval_bwd(int64_t v, const int64_t *indexes, const float *sh, int sh_de
  * (2) Tile-overlap mapping: (tile, depth) key sort + tile ranges.  Serves the mapper inside
  *     taichi_splatting.render_projected (reference scene/mlp_scene.py:418, :377).
  *     The result equals a stable sort of all (row, tile) overlaps by the 64-bit key
- *     (tile_id << 32 | float_bits(depth)), ties broken by row index.  It is computed as a
- *     stable 32-bit LSD radix sort of rows by depth followed by a stable radix sort of the
- *     emitted overlaps by tile id, which moves 4–5× fewer bytes.
+ *     (tile_id << 32 | float_bits(depth)), ties broken by row index.  It is computed without
+ *     sorting any O-sized list: rows are sorted by depth (32-bit keys), binned per 8x8-tile
+ *     super-tile (one short sort of ~O/6 pairs) and expanded in place into the per-tile lists,
+ *     whose ranges come from per-tile totals.
  *       overlap_to_point[o]  row index of the o-th sorted overlap        (max_overlaps)
  *       tile_ranges[2t,2t+1] [begin,end) of tile t in overlap_to_point   (tiles_x*tiles_y*2)
- *       counters[0] = total overlaps O (may exceed max_overlaps: then counters[1] = 1 and
- *                     only the ranges/lists of the first max_overlaps emitted pairs are valid)
+ *       counters[0] = total overlaps O (may exceed max_overlaps: then counters[1] = 1, ranges are
+ *                     clamped to max_overlaps and the lists are truncated — re-run with more room)
  *       counters[2] = min(O, max_overlaps), counters[3] = rows touching at least one tile
- *     counts_in (nullable, m): per-row tile counts from gs_project_fwd / gs_tile_count (must come from
- *     the same g2d/depth); NULL = counted here.
+ *     tile_info_in (nullable): the tile info gs_project_fwd wrote for the same m rows / image size
+ *     (must come from the same g2d/depth); NULL = computed here.
  * ------------------------------------------------------------------------------------- */
 size_t gs_tile_map_workspace_bytes(int64_t m, int64_t max_overlaps, int width, int height);
 int gs_tile_map(const gs_raster_config *h_cfg, int64_t m, const float *g2d, const float *depth,
-                const int32_t *counts_in, int width, int height, int64_t max_overlaps,
+                const void *tile_info_in, int width, int height, int64_t max_overlaps,
                 void *workspace, size_t workspace_bytes,
                 int32_t *overlap_to_point, int32_t *tile_ranges, int32_t *counters,
                 void *stream);

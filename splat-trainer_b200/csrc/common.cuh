@@ -115,3 +115,11 @@ __device__ __forceinline__ uint32_t gs_lookback_warp(const uint32_t *status, int
   }
   return prefix;
 }
+
+// ---- tile info (tilemap.cu): per-row tile record (16 B) and per-row tile count ---------------------
+struct TileInfo {
+  uint4 *recs;       // n
+  int32_t *counts;   // n
+  size_t bytes;
+};
+TileInfo gs_tile_info_carve(void *base, int64_t n, int width, int height);

@@ -155,11 +155,10 @@ __device__ __forceinline__ unsigned long long footprint_submask(const Footprint 
   return sub;
 }
 
-// Builds the record, returns the tile count, and (totals != NULL) adds 1 to totals[tile] for every hit tile.
-__device__ __forceinline__ int footprint_record(const Footprint &fp, int W, int H, int32_t *__restrict__ totals, uint4 &rec) {
+// Builds the record and returns the tile count.
+__device__ __forceinline__ int footprint_record(const Footprint &fp, int W, int H, uint4 &rec) {
   rec = make_uint4(0u, 0u, 0u, 0u);
   if (!fp.valid) return 0;
-  int TX = (W + GS_TILE - 1) / GS_TILE;
   int w = fp.tx1 - fp.tx0 + 1, h = fp.ty1 - fp.ty0 + 1;
   int count = 0;
   if (w * h <= 64) {
@@ -167,10 +166,7 @@ __device__ __forceinline__ int footprint_record(const Footprint &fp, int W, int 
     int bit = 0;
     for (int ty = fp.ty0; ty <= fp.ty1; ++ty)
       for (int tx = fp.tx0; tx <= fp.tx1; ++tx, ++bit)
-        if (tile_hit(fp, tx, ty, W, H)) {
-          mask |= 1ull << bit;
-          if (totals) atomicAdd(totals + ty * TX + tx, 1);
-        }
+        if (tile_hit(fp, tx, ty, W, H)) mask |= 1ull << bit;
     count = __popcll(mask);
     if (count == 0) return 0;
     RecView v;
@@ -183,10 +179,7 @@ __device__ __forceinline__ int footprint_record(const Footprint &fp, int W, int 
   } else {
     for (int ty = fp.ty0; ty <= fp.ty1; ++ty)
       for (int tx = fp.tx0; tx <= fp.tx1; ++tx)
-        if (tile_hit(fp, tx, ty, W, H)) {
-          ++count;
-          if (totals) atomicAdd(totals + ty * TX + tx, 1);
-        }
+        count += tile_hit(fp, tx, ty, W, H) ? 1 : 0;
     if (count == 0) return 0;
     int ns = (fp.tx1 / GS_SUPER - fp.tx0 / GS_SUPER + 1) * (fp.ty1 / GS_SUPER - fp.ty0 / GS_SUPER + 1);
     rec = make_uint4((uint32_t)fp.tx0 | ((uint32_t)fp.ty0 << 16), ((uint32_t)ns << 16) | GS_REC_BIG, 0u, 0u);

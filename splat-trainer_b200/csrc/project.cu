@@ -172,7 +172,7 @@ __global__ void __launch_bounds__(128) k_project_fwd(CamDev cam, CfgDev cfg, int
                                                      const float *__restrict__ alpha_logit, const float *__restrict__ sh,
                                                      float *__restrict__ g2d, float *__restrict__ depth,
                                                      float *__restrict__ rgb, float *__restrict__ acc, int acc_stride,
-                                                     int32_t *__restrict__ tile_counts) {
+                                                     uint4 *__restrict__ tile_recs, int32_t *__restrict__ tile_counts) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   float px = position[3 * i], py = position[3 * i + 1], pz = position[3 * i + 2];
@@ -183,10 +183,16 @@ __global__ void __launch_bounds__(128) k_project_fwd(CamDev cam, CfgDev cfg, int
   int ntiles = 0;
   if (ok) {
     Footprint fp = row_footprint(t.u, t.v, t.ca, t.cb, t.cc, t.op, t.z, cfg.thr, cam.W, cam.H);
-    ntiles = footprint_count(fp, cam.W, cam.H);
+    if (tile_recs) {  // same footprint code as the mapper: gs_tile_map(tile_info_in) reuses the outcome
+      uint4 rec;
+      ntiles = footprint_record(fp, cam.W, cam.H, rec);
+      if (ntiles > 0) tile_recs[i] = rec;
+    } else {
+      ntiles = footprint_count(fp, cam.W, cam.H);
+    }
     ok = ntiles > 0;
   }
-  if (tile_counts) tile_counts[i] = ntiles;  // same footprint code as the mapper: gs_tile_map(counts_in) reuses it
+  if (tile_counts) tile_counts[i] = ntiles;
   float2 *g = reinterpret_cast<float2 *>(g2d + GS_G2D_STRIDE * i);
   if (!ok) {
     g[0] = make_float2(0.f, 0.f); g[1] = make_float2(1.f, 0.f); g[2] = make_float2(1.f, 0.f);
@@ -421,7 +427,7 @@ __global__ void __launch_bounds__(128) k_sh_eval_bwd(int64_t nv, const int64_t *
 extern "C" int gs_project_fwd(const gs_camera *h_cam, const gs_raster_config *h_cfg, int64_t n, const float *position,
                               const float *log_scaling, const float *rotation, const float *alpha_logit, const float *sh,
                               int sh_degree, float *g2d, float *depth, float *rgb, float *acc, int acc_stride,
-                              int32_t *tile_counts, void *stream) {
+                              void *tile_info, void *stream) {
   GS_REQUIRE(h_cam && h_cfg, "null camera/config");
   GS_REQUIRE(h_cfg->tile_size == GS_TILE, "tile_size must be 16");
   GS_REQUIRE(acc == nullptr || (acc_stride > 0 && acc_stride % 4 == 0), "acc_stride must be a multiple of 4");
@@ -430,8 +436,11 @@ extern "C" int gs_project_fwd(const gs_camera *h_cam, const gs_raster_config *h_
   CfgDev cfg = gs_make_cfg(h_cfg);
   cudaStream_t st = (cudaStream_t)stream;
   int blocks = gs_div_up(n, 128);
+  TileInfo ti = {nullptr, nullptr, 0};
+  if (tile_info) ti = gs_tile_info_carve(tile_info, n, h_cam->width, h_cam->height);
   GS_DISPATCH_DEG(sh_degree, (k_project_fwd<D><<<blocks, 128, 0, st>>>(cam, cfg, n, position, log_scaling, rotation,
-                                                                        alpha_logit, sh, g2d, depth, rgb, acc, acc_stride, tile_counts)));
+                                                                        alpha_logit, sh, g2d, depth, rgb, acc, acc_stride,
+                                                                        ti.recs, ti.counts)));
   GS_LAUNCH_CHECK();
   return GS_OK;
 }

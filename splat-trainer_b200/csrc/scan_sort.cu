@@ -317,13 +317,23 @@ __global__ void __launch_bounds__(OS_THREADS, 3) k_os_pass(const uint32_t *__res
   __syncthreads();  // s_warp reused below
   int gtot;
   uint32_t gex = (uint32_t)block_exclusive_scan((int)ghist[d], s_warp, gtot);
+  // look-back, 8 predecessors per round trip (all tiles of a small sort run in one wave, so a one-at-a-time walk
+  // would cost O(sqrt(tiles)) dependent L2 latencies)
   uint32_t prefix = 0;
-  for (int p = tile - 1; p >= 0; --p) {
-    uint32_t s;
-    const uint32_t *ps = status + (size_t)p * 256 + d;
-    do { s = gs_ld_status(ps); } while ((s >> 30) == 0);
-    prefix += s & GS_LB_VAL;
-    if ((s >> 30) == 2u) break;
+  constexpr int LBW = 8;
+  for (int p = tile - 1; p >= 0; p -= LBW) {
+    uint32_t sv[LBW];
+#pragma unroll
+    for (int i = 0; i < LBW; ++i) sv[i] = (p - i >= 0) ? gs_ld_status(status + (size_t)(p - i) * 256 + d) : GS_LB_INCL;
+    bool done = false;
+#pragma unroll
+    for (int i = 0; i < LBW; ++i) {
+      if (done) break;
+      while ((sv[i] >> 30) == 0) sv[i] = gs_ld_status(status + (size_t)(p - i) * 256 + d);
+      prefix += sv[i] & GS_LB_VAL;
+      done = (sv[i] >> 30) == 2u;
+    }
+    if (done) break;
   }
   if (tile > 0) gs_st_status(my_status, (prefix + run) | GS_LB_INCL);
   s_binoff[d] = binoff;

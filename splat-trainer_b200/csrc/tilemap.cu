@@ -1,12 +1,37 @@
 // tilemap.cu — tile-overlap mapping (mapper inside render_projected, reference
-// scene/mlp_scene.py:418,377).  count -> depth sort of rows -> scan -> emit (tile,row) in depth
-// order -> stable sort by tile -> ranges.  Everything stays on the device: the overlap total is a
-// device counter, buffers are sized by the caller's max_overlaps (no host read-back).
+// scene/mlp_scene.py:418,377).  The result equals a stable sort of all (row, tile) overlaps by the key
+// (tile << 32 | float_bits(depth)), ties by row — but no O-sized pair list is ever sorted:
+//   1. per row: a 16-B tile record (rect + exact hit mask), the tile count and per-tile totals (REDs) — produced by
+//      the cull in gs_project_fwd, or by k_tile_info here;
+//   2. live rows are compacted (one chained-scan kernel) and sorted by depth (onesweep, 32-bit keys);
+//   3. in depth order every row emits one pair per 8x8-tile SUPER-tile it hits (O_s ~ O/6) — sorted by super-tile id;
+//   4. per-tile totals are scanned into tile_ranges (so the ranges need no pass over the list);
+//   5. k_expand: 256·I super-items per CTA, each thread turns its record into the 64-bit mask of sub-tiles hit, a
+//      32x64 bit-matrix transpose across the warp (10 shuffles) yields for every sub-tile the lanes hitting it —
+//      counts and stable ranks by popc — chunks of one super-tile chain by decoupled look-back, and row ids
+//      go straight to their final slot (4 B per overlap written once).
+// Everything stays on the device: totals are device counters, buffers are sized by the caller's max_overlaps.
 #include "common.cuh"
 #include "footprint.cuh"
 
 int gs_radix_sort_pingpong(uint32_t *ka, uint32_t *va, uint32_t *kb, uint32_t *vb, int64_t n, const int32_t *n_dev,
                            int begin_bit, int end_bit, void *workspace, int *result_in_b, cudaStream_t st);
+
+// ---- tile info: what the cull knows about every row ------------------------------------------------------
+TileInfo gs_tile_info_carve(void *base, int64_t n, int width, int height) {
+  TileInfo t;
+  char *p = (char *)base;
+  size_t nn = (size_t)(n > 0 ? n : 1);
+  (void)width; (void)height;
+  t.recs = (uint4 *)p; p += gs_align256(nn * 16);
+  t.counts = (int32_t *)p; p += gs_align256(nn * 4);
+  t.bytes = (size_t)(p - (char *)base);
+  return t;
+}
+
+extern "C" size_t gs_tile_info_bytes(int64_t n, int width, int height) {
+  return gs_tile_info_carve(nullptr, n, width, height).bytes;
+}
 
 __device__ __forceinline__ Footprint load_footprint(const float *__restrict__ g2d, const float *__restrict__ depth,
                                                     int64_t i, float thr, int W, int H) {
@@ -24,11 +49,32 @@ __global__ void __launch_bounds__(256) k_tile_count(const float *__restrict__ g2
   counts[i] = footprint_count(fp, W, H);
 }
 
-// ---- live-row compaction (single pass, decoupled look-back) -------------------------------------------
-// rows that touch at least one tile, compacted in row order: (depth bits, row) at their rank; live count -> *live_out
-constexpr int LC_THREADS = 256;
-constexpr int LC_ITEMS = 8;
-constexpr int LC_TILE = LC_THREADS * LC_ITEMS;
+// per row: record + count (operator path; the fused path gets them from gs_project_fwd)
+__global__ void __launch_bounds__(256) k_tile_info(const float *__restrict__ g2d, const float *__restrict__ depth,
+                                                   int64_t m, float thr, int W, int H, uint4 *__restrict__ recs,
+                                                   int32_t *__restrict__ counts) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  Footprint fp = load_footprint(g2d, depth, i, thr, W, H);
+  uint4 rec;
+  int c = footprint_record(fp, W, H, rec);
+  counts[i] = c;
+  if (c > 0) recs[i] = rec;
+}
+
+__global__ void __launch_bounds__(256) k_sum_i32(const int32_t *__restrict__ v, int64_t n, int32_t *__restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int x = i < n ? v[i] : 0;
+  x = __reduce_add_sync(GS_FULL, x);
+  __shared__ int s[8];
+  if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = x;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int k = 0; k < 8; ++k) t += s[k];
+    if (t) atomicAdd(out, t);
+  }
+}
 
 __device__ __forceinline__ int block_scan_256(int v, int *s_warp, int &block_total) {  // exclusive, 256 threads
   int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -50,6 +96,12 @@ __device__ __forceinline__ int block_scan_256(int v, int *s_warp, int &block_tot
   block_total = tot;
   return wo + inc - v;
 }
+
+// ---- live-row compaction (single pass, decoupled look-back) -------------------------------------------
+// rows that touch at least one tile, compacted in row order: (depth bits, row) at their rank; live count -> *live_out
+constexpr int LC_THREADS = 256;
+constexpr int LC_ITEMS = 8;
+constexpr int LC_TILE = LC_THREADS * LC_ITEMS;
 
 __global__ void __launch_bounds__(LC_THREADS) k_live_compact(const int32_t *__restrict__ counts, const float *__restrict__ depth,
                                                              int64_t m, uint32_t *__restrict__ status, uint32_t *__restrict__ ticket,
@@ -97,20 +149,19 @@ __global__ void __launch_bounds__(LC_THREADS) k_live_compact(const int32_t *__re
   }
 }
 
-// ---- emission (single pass: chained scan of the per-row tile counts in depth order + the pairs) --------
-// thread handles EM_ITEMS consecutive live rows of the depth order; writes (tile, row) pairs at their offsets.
-// The last live tile publishes the counters: [0] total overlaps, [1] overflow flag, [2] min(total, capacity).
+// ---- super-tile pairs (single pass: chained scan of the per-row super-tile counts in depth order + the pairs) ------
+// Thread j = j-th live row of the depth order; it writes one (super-tile id, row) pair per 8x8-tile super-tile the row
+// hits, at its scanned offset.
+// The last live tile publishes scounters: [0] total pairs, [1] overflow flag, [2] min(total, capacity).
 constexpr int EM_THREADS = 256;
-constexpr int EM_ITEMS = 1;
-constexpr int EM_TILE = EM_THREADS * EM_ITEMS;
 
-__global__ void __launch_bounds__(EM_THREADS) k_tile_emit(const float *__restrict__ g2d, const float *__restrict__ depth,
-                                                          const int32_t *__restrict__ counts, const int32_t *__restrict__ live_dev,
-                                                          int64_t m, float thr, int W, int H,
-                                                          const uint32_t *__restrict__ sorted_rows, int64_t max_overlaps,
-                                                          uint32_t *__restrict__ status, uint32_t *__restrict__ ticket,
-                                                          uint32_t *__restrict__ tile_keys, uint32_t *__restrict__ tile_vals,
-                                                          int32_t *__restrict__ counters) {
+__global__ void __launch_bounds__(EM_THREADS) k_super_emit(const float *__restrict__ g2d, const float *__restrict__ depth,
+                                                           const uint4 *__restrict__ recs, const int32_t *__restrict__ live_dev,
+                                                           int64_t m, float thr, int W, int H, int SXN,
+                                                           const uint32_t *__restrict__ sorted_rows, int64_t cap,
+                                                           uint32_t *__restrict__ status, uint32_t *__restrict__ ticket,
+                                                           uint32_t *__restrict__ skeys, uint32_t *__restrict__ svals,
+                                                           int32_t *__restrict__ scounters) {
   __shared__ int s_warp[8];
   __shared__ int s_tile;
   __shared__ uint32_t s_prefix;
@@ -118,118 +169,350 @@ __global__ void __launch_bounds__(EM_THREADS) k_tile_emit(const float *__restric
   __syncthreads();
   const int tile = s_tile;
   int64_t live = min((int64_t)*live_dev, m);
-  int64_t tbase = (int64_t)tile * EM_TILE;
+  int64_t tbase = (int64_t)tile * EM_THREADS;
   if (tbase >= live) return;
-  int64_t j0 = tbase + (int64_t)threadIdx.x * EM_ITEMS;
-  int64_t row[EM_ITEMS];
-  int c[EM_ITEMS];
-  int sum = 0;
-#pragma unroll
-  for (int i = 0; i < EM_ITEMS; ++i) {
-    row[i] = (j0 + i < live) ? (int64_t)sorted_rows[j0 + i] : -1;
-    c[i] = row[i] >= 0 ? counts[row[i]] : 0;
-    sum += c[i];
+  int64_t j = tbase + threadIdx.x;
+  int64_t row = -1;
+  uint4 rec = make_uint4(0u, 0u, 0u, 0u);
+  if (j < live) {
+    row = (int64_t)sorted_rows[j];
+    rec = recs[row];
   }
+  RecView v = rec_view(rec);
+  int ns = row >= 0 ? v.nsuper : 0;
   int tot;
-  int ex = block_scan_256(sum, s_warp, tot);
+  int ex = block_scan_256(ns, s_warp, tot);
   if (threadIdx.x == 0) gs_st_status(status + tile, (uint32_t)tot | (tile == 0 ? GS_LB_INCL : GS_LB_LOCAL));
   if (threadIdx.x < 32) {
     uint32_t prefix = gs_lookback_warp(status, tile);
     if (threadIdx.x == 0) {
       if (tile > 0) gs_st_status(status + tile, (prefix + (uint32_t)tot) | GS_LB_INCL);
       s_prefix = prefix;
-      if (tbase + EM_TILE >= live) {  // last live tile
+      if (tbase + EM_THREADS >= live) {  // last live tile
         int64_t o = (int64_t)prefix + tot;
-        counters[0] = (int32_t)o;
-        counters[1] = (o > max_overlaps) ? 1 : 0;
-        counters[2] = (int32_t)min(o, max_overlaps);
+        scounters[0] = (int32_t)o;
+        scounters[1] = (o > cap) ? 1 : 0;
+        scounters[2] = (int32_t)min(o, cap);
       }
     }
   }
   __syncthreads();
-  int TX = (W + GS_TILE - 1) / GS_TILE;
+  if (ns <= 0) return;
   int64_t o = (int64_t)s_prefix + ex;
-#pragma unroll 1
-  for (int i = 0; i < EM_ITEMS; ++i) {
-    if (c[i] <= 0) continue;
-    Footprint fp = load_footprint(g2d, depth, row[i], thr, W, H);
-    for (int ty = fp.ty0; ty <= fp.ty1; ++ty)
-      for (int tx = fp.tx0; tx <= fp.tx1; ++tx)
-        if (tile_hit(fp, tx, ty, W, H)) {
-          if (o < max_overlaps) {
-            tile_keys[o] = (uint32_t)(ty * TX + tx);
-            tile_vals[o] = (uint32_t)row[i];
-          }
-          ++o;
-        }
-  }
-}
-
-// 4 keys per thread (one 16-B load) + the two neighbours
-__global__ void __launch_bounds__(256) k_tile_ranges(const uint32_t *__restrict__ keys, const int32_t *__restrict__ n_dev,
-                                                     int64_t n_cap, int32_t *__restrict__ ranges) {
-  int64_t n = min((int64_t)*n_dev, n_cap);
-  int64_t o = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
-  if (o >= n) return;
-  uint32_t k[6];
-  if (o + 4 <= n) {
-    uint4 q = *reinterpret_cast<const uint4 *>(keys + o);
-    k[1] = q.x; k[2] = q.y; k[3] = q.z; k[4] = q.w;
+  int sx0, sx1, sy0, sy1;
+  if (v.big) {
+    Footprint fp = load_footprint(g2d, depth, row, thr, W, H);
+    sx0 = fp.tx0 / GS_SUPER; sx1 = fp.tx1 / GS_SUPER; sy0 = fp.ty0 / GS_SUPER; sy1 = fp.ty1 / GS_SUPER;
   } else {
-#pragma unroll
-    for (int i = 0; i < 4; ++i) k[1 + i] = (o + i < n) ? keys[o + i] : 0xffffffffu;
+    sx0 = v.tx0 / GS_SUPER; sx1 = (v.tx0 + v.w - 1) / GS_SUPER; sy0 = v.ty0 / GS_SUPER; sy1 = (v.ty0 + v.h - 1) / GS_SUPER;
   }
-  k[0] = o > 0 ? keys[o - 1] : 0xffffffffu;
-  k[5] = (o + 4 < n) ? keys[o + 4] : 0xffffffffu;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    if (o + i >= n) break;
-    uint32_t t = k[1 + i];
-    if (o + i == 0 || k[i] != t) ranges[2 * t] = (int32_t)(o + i);
-    if (o + i == n - 1 || k[2 + i] != t) ranges[2 * t + 1] = (int32_t)(o + i + 1);
-  }
+  for (int sy = sy0; sy <= sy1; ++sy)
+    for (int sx = sx0; sx <= sx1; ++sx) {
+      if (!v.big && rec_submask(v, sx, sy) == 0ull) continue;
+      int sid = sy * SXN + sx;
+      if (o < cap) {
+        skeys[o] = (uint32_t)sid;
+        svals[o] = (uint32_t)row;
+      }
+      ++o;
+    }
 }
 
-__global__ void __launch_bounds__(256) k_sum_i32(const int32_t *__restrict__ v, int64_t n, int32_t *__restrict__ out) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int x = i < n ? v[i] : 0;
-  x = __reduce_add_sync(GS_FULL, x);
-  __shared__ int s[8];
-  if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = x;
+
+// ---- expansion: super-tile items -> final per-tile lists ---------------------------------------------------
+constexpr int EX_THREADS = 256;
+constexpr int EX_WARPS = EX_THREADS / 32;
+constexpr int EX_ITEMS = 2;                       // super-items per thread
+constexpr int EX_CHUNK = EX_THREADS * EX_ITEMS;   // super-items per CTA
+constexpr int EX_MAX_SUPER = 4096;                // super-tiles whose tables fit shared memory (image up to ~8K x 8K)
+
+// Segment tables of the sorted super-tile list (one block): stab[0..NS] = seg_begin (first index whose key >= s, by
+// binary search over the sorted keys — no atomics), stab[NS+1 .. 2NS+1] = chunk_begin (exclusive scan of
+// ceil(segment / chunk)); both end with their grand total.
+__global__ void __launch_bounds__(1024) k_seg_tables(const uint32_t *__restrict__ skeys, const int32_t *__restrict__ scounters,
+                                                     int NS, int32_t *__restrict__ stab) {
+  __shared__ int s_warp[33];
+  __shared__ int s_carry;
+  const int n = scounters[2];
+  for (int s = threadIdx.x; s <= NS; s += 1024) {
+    int lo = 0, hi = n;  // first index with key >= s
+    while (lo < hi) {
+      int mid = (lo + hi) >> 1;
+      if (skeys[mid] < (uint32_t)s) lo = mid + 1; else hi = mid;
+    }
+    stab[s] = lo;
+  }
+  if (threadIdx.x == 0) s_carry = 0;
   __syncthreads();
-  if (threadIdx.x == 0) {
-    int t = 0;
-    for (int k = 0; k < 8; ++k) t += s[k];
-    if (t) atomicAdd(out, t);
+  for (int base = 0; base < NS; base += 1024) {
+    int s = base + threadIdx.x;
+    int v = s < NS ? (stab[s + 1] - stab[s] + EX_CHUNK - 1) / EX_CHUNK : 0;
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int t = __shfl_up_sync(GS_FULL, inc, o);
+      if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_warp[w] = inc;
+    __syncthreads();
+    if (w == 0) {
+      int x = s_warp[lane], xi = x;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(GS_FULL, xi, o);
+        if (lane >= o) xi += t;
+      }
+      s_warp[lane] = xi - x;
+      if (lane == 31) s_warp[32] = xi;
+    }
+    __syncthreads();
+    if (s < NS) stab[NS + 1 + s] = s_carry + s_warp[w] + inc - v;
+    __syncthreads();
+    if (threadIdx.x == 0) s_carry += s_warp[32];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) stab[2 * NS + 1] = s_carry;
+}
+
+// 32x32 bit-matrix transpose across the warp: on return bit i of lane L = bit L of lane i on entry (5 shuffles)
+__device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, int lane) {
+#pragma unroll
+  for (int j = 16; j >= 1; j >>= 1) {
+    uint32_t lowm = (j == 16) ? 0x0000ffffu : (j == 8) ? 0x00ff00ffu : (j == 4) ? 0x0f0f0f0fu : (j == 2) ? 0x33333333u : 0x55555555u;
+    uint32_t y = __shfl_xor_sync(GS_FULL, x, j);
+    x = (lane & j) ? ((x & ~lowm) | ((y >> j) & lowm)) : ((x & lowm) | ((y << j) & ~lowm));
+  }
+  return x;
+}
+
+struct ChunkCtx {
+  int chunk, sid, sx, sy, item0, seg_end;
+};
+
+// which super-tile segment a chunk belongs to: last s with chunk_begin[s] <= chunk (table staged in shared memory)
+__device__ __forceinline__ bool chunk_ctx(const int32_t *__restrict__ stab, int NS, int SXN, int32_t *cb_smem, ChunkCtx &c) {
+  for (int i = threadIdx.x; i <= NS; i += EX_THREADS) cb_smem[i] = stab[NS + 1 + i];
+  __syncthreads();
+  c.chunk = blockIdx.x;
+  if (c.chunk >= cb_smem[NS]) return false;
+  int lo = 0, hi = NS;
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (cb_smem[mid] <= c.chunk) lo = mid; else hi = mid;
+  }
+  c.sid = lo;
+  c.sx = lo % SXN; c.sy = lo / SXN;
+  c.seg_end = stab[lo + 1];
+  c.item0 = stab[lo] + (c.chunk - cb_smem[lo]) * EX_CHUNK + (threadIdx.x >> 5) * (32 * EX_ITEMS);
+  return true;
+}
+
+// COUNT pass (WRITE = false): each thread turns its super-items into 64-bit masks of sub-tiles hit (stored for the
+// write pass) and the CTA counts the hits per sub-tile -> chunk_counts[chunk][64].
+// WRITE pass: chunk_counts now holds each chunk's exclusive prefix within its super-tile; every hit goes to
+// ranges[tile].begin + prefix + (hits of the sub-tile by earlier warps / rounds / lanes of the chunk).
+template <bool WRITE>
+__global__ void __launch_bounds__(EX_THREADS) k_expand(const float *__restrict__ g2d, const float *__restrict__ depth,
+                                                       const uint4 *__restrict__ recs, float thr, int W, int H, int SXN, int NS,
+                                                       const uint32_t *__restrict__ svals, const int32_t *__restrict__ stab,
+                                                       unsigned long long *__restrict__ masks, int32_t *__restrict__ chunk_counts,
+                                                       const int32_t *__restrict__ tile_begin, int64_t max_overlaps,
+                                                       int32_t *__restrict__ out) {
+  extern __shared__ int32_t ex_smem[];               // chunk_begin table: NS + 1 ints
+  __shared__ uint32_t sT[EX_WARPS][EX_ITEMS][64];    // transposed hit words: [s] = lanes of the warp hitting sub-tile s
+  __shared__ uint32_t sPos[EX_WARPS][EX_ITEMS][64];  // hits of (warp, sub-tile) in earlier rounds
+  __shared__ uint32_t sCnt[EX_WARPS][64];
+  ChunkCtx cc;
+  if (!chunk_ctx(stab, NS, SXN, ex_smem, cc)) return;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  unsigned long long m[EX_ITEMS];
+  uint32_t row[EX_ITEMS];
+  uint32_t c0 = 0, c1 = 0;
+#pragma unroll
+  for (int r = 0; r < EX_ITEMS; ++r) {
+    int idx = cc.item0 + r * 32 + lane;
+    m[r] = 0ull;
+    row[r] = 0u;
+    if (idx < cc.seg_end) {
+      row[r] = svals[idx];
+      if (WRITE) {
+        m[r] = masks[idx];
+      } else {
+        RecView v = rec_view(recs[row[r]]);
+        if (v.big) {
+          const float2 *g = reinterpret_cast<const float2 *>(g2d + GS_G2D_STRIDE * (int64_t)row[r]);
+          float2 a = g[0], b = g[1], c = g[2];
+          Footprint fp = row_footprint(a.x, a.y, b.x, b.y, c.x, c.y, depth[row[r]], thr, W, H);
+          m[r] = fp.valid ? footprint_submask(fp, cc.sx, cc.sy, W, H) : 0ull;
+        } else {
+          m[r] = rec_submask(v, cc.sx, cc.sy);
+        }
+        masks[idx] = m[r];
+      }
+    }
+    uint32_t tl = warp_transpose32((uint32_t)m[r], lane), th = warp_transpose32((uint32_t)(m[r] >> 32), lane);
+    if (WRITE) {
+      sT[w][r][lane] = tl;
+      sT[w][r][32 + lane] = th;
+      sPos[w][r][lane] = c0;
+      sPos[w][r][32 + lane] = c1;
+    }
+    c0 += __popc(tl);
+    c1 += __popc(th);
+  }
+  sCnt[w][lane] = c0;
+  sCnt[w][32 + lane] = c1;
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    const int s = threadIdx.x;
+    uint32_t run = 0, wo[EX_WARPS];
+#pragma unroll
+    for (int i = 0; i < EX_WARPS; ++i) { wo[i] = run; run += sCnt[i][s]; }
+    if (!WRITE) {
+      chunk_counts[(size_t)cc.chunk * 64 + s] = (int32_t)run;
+    } else {
+      int TX = (W + GS_TILE - 1) / GS_TILE, TY = (H + GS_TILE - 1) / GS_TILE;
+      int tx = GS_SUPER * cc.sx + (s & (GS_SUPER - 1)), ty = GS_SUPER * cc.sy + (s >> 3);
+      uint32_t tbegin = (tx < TX && ty < TY) ? (uint32_t)tile_begin[ty * TX + tx] : 0u;
+      uint32_t base = tbegin + (uint32_t)chunk_counts[(size_t)cc.chunk * 64 + s];
+#pragma unroll
+      for (int i = 0; i < EX_WARPS; ++i) sCnt[i][s] = base + wo[i];
+    }
+  }
+  if (!WRITE) return;
+  __syncthreads();
+  const unsigned lt = (1u << lane) - 1u;
+#pragma unroll
+  for (int r = 0; r < EX_ITEMS; ++r) {
+    unsigned long long mm = m[r];
+    while (mm) {
+      int s = __ffsll((long long)mm) - 1;
+      mm &= mm - 1ull;
+      uint32_t pos = sCnt[w][s] + sPos[w][r][s] + __popc(sT[w][r][s] & lt);
+      if ((int64_t)pos < max_overlaps) out[pos] = (int32_t)row[r];
+    }
   }
 }
 
+// One block per super-tile, one thread per sub-tile: turns the chunk counts of the super-tile into exclusive
+// prefixes (in place) and the column totals into per-tile totals.  The last block to finish scans the totals into
+// tile_ranges and the counters: [0] total overlaps O, [1] overflow flag, [2] min(O, capacity).
+__global__ void __launch_bounds__(64) k_chunk_prefix(const int32_t *__restrict__ stab, int NS, int SXN, int TX, int TY,
+                                                     int32_t *__restrict__ chunk_counts, int32_t *__restrict__ totals,
+                                                     uint32_t *__restrict__ done, int64_t max_overlaps,
+                                                     const int32_t *__restrict__ scounters, int32_t *__restrict__ ranges,
+                                                     int32_t *__restrict__ counters) {
+  const int sid = blockIdx.x, s = threadIdx.x;
+  const int c0 = stab[NS + 1 + sid], c1 = stab[NS + 2 + sid];
+  int run = 0;
+  int c = c0;
+  for (; c + 4 <= c1; c += 4) {
+    int v[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = chunk_counts[(size_t)(c + i) * 64 + s];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { chunk_counts[(size_t)(c + i) * 64 + s] = run; run += v[i]; }
+  }
+  for (; c < c1; ++c) {
+    int v = chunk_counts[(size_t)c * 64 + s];
+    chunk_counts[(size_t)c * 64 + s] = run;
+    run += v;
+  }
+  int tx = GS_SUPER * (sid % SXN) + (s & (GS_SUPER - 1)), ty = GS_SUPER * (sid / SXN) + (s >> 3);
+  if (tx < TX && ty < TY) totals[ty * TX + tx] = run;
+  __threadfence();
+  __shared__ bool s_last;
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(done, 1u) == (uint32_t)(NS - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  // last block: exclusive scan of the T tile totals (64 threads, 8 tiles per thread per round)
+  __shared__ int s_w[2];
+  __shared__ long long s_carry;
+  if (threadIdx.x == 0) s_carry = 0;
+  __syncthreads();
+  const int T = TX * TY;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int base = 0; base < T; base += 64 * 8) {
+    int t0 = base + threadIdx.x * 8;
+    int v[8], sum = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { v[i] = (t0 + i < T) ? __ldcg(totals + t0 + i) : 0; sum += v[i]; }
+    int inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int t = __shfl_up_sync(GS_FULL, inc, o);
+      if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_w[w] = inc;
+    __syncthreads();
+    long long b = s_carry + (w ? s_w[0] : 0) + inc - sum;
+    int tot = s_w[0] + s_w[1];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (t0 + i < T) {
+        long long lo = min(b, (long long)max_overlaps), hi = min(b + v[i], (long long)max_overlaps);
+        ranges[2 * (t0 + i)] = hi > lo ? (int32_t)lo : 0;  // empty tiles read [0,0)
+        ranges[2 * (t0 + i) + 1] = hi > lo ? (int32_t)hi : 0;
+        totals[t0 + i] = (int32_t)lo;  // from here on: the tile's first slot (clamped to the capacity)
+      }
+      b += v[i];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) s_carry += tot;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    long long o = s_carry;
+    counters[0] = (int32_t)min(o, (long long)0x7fffffff);
+    counters[1] = (o > max_overlaps || scounters[1] != 0) ? 1 : 0;
+    counters[2] = (int32_t)min(o, (long long)max_overlaps);
+  }
+}
+
+// ---- host side ---------------------------------------------------------------------------------------------
 // workspace layout (all 256-B aligned)
 struct TileWs {
-  int32_t *counts;      // m
+  TileInfo info;        // used when the caller passes no tile info
   uint32_t *dk[2];      // m each: depth keys ping/pong
   uint32_t *dv[2];      // m each: rows ping/pong
-  uint32_t *tk[2];      // max_overlaps each
-  uint32_t *tv;         // max_overlaps: the other value buffer is the caller's overlap_to_point
-  uint32_t *scan_status;  // [0] ticket(compact) [1] ticket(emit) ... then LC tiles + EM tiles status words
-  size_t scan_status_bytes;
+  uint32_t *sk[2];      // cap each: super-tile ids ping/pong
+  uint32_t *sv[2];      // cap each: rows ping/pong
+  unsigned long long *masks;  // cap: sub-tile hit mask of every super-item
+  int32_t *chunk_counts;      // ex_chunks * 64
+  int32_t *totals;            // T: per-tile totals, then per-tile first slots
+  int32_t *stab;              // 2 NS + 2
+  uint32_t *zero;       // zeroed every call: tickets[64] | scounters[4] | compaction / emission status words
+  size_t zero_bytes;
+  int ns, lc_tiles, em_tiles, ex_chunks;
   void *sort_ws;
   size_t total;
 };
 
-static TileWs carve(void *base, int64_t m, int64_t maxo) {
+static TileWs carve(void *base, int64_t m, int64_t maxo, int width, int height) {
   TileWs w;
   char *p = (char *)base;
   auto take = [&](size_t bytes) { char *r = p; p += gs_align256(bytes); return r; };
   size_t mm = (size_t)(m > 0 ? m : 1), oo = (size_t)(maxo > 0 ? maxo : 1);
-  w.counts = (int32_t *)take(mm * 4);
+  w.info = gs_tile_info_carve(p, m, width, height);
+  p += w.info.bytes;
   w.dk[0] = (uint32_t *)take(mm * 4); w.dk[1] = (uint32_t *)take(mm * 4);
   w.dv[0] = (uint32_t *)take(mm * 4); w.dv[1] = (uint32_t *)take(mm * 4);
-  w.tk[0] = (uint32_t *)take(oo * 4); w.tk[1] = (uint32_t *)take(oo * 4);
-  w.tv = (uint32_t *)take(oo * 4);
-  size_t lc = (mm + LC_TILE - 1) / LC_TILE, em = (mm + EM_TILE - 1) / EM_TILE;
-  w.scan_status_bytes = (64 + lc + em) * 4;
-  w.scan_status = (uint32_t *)take(w.scan_status_bytes);
+  w.sk[0] = (uint32_t *)take(oo * 4); w.sk[1] = (uint32_t *)take(oo * 4);
+  w.sv[0] = (uint32_t *)take(oo * 4); w.sv[1] = (uint32_t *)take(oo * 4);
+  w.masks = (unsigned long long *)take(oo * 8);
+  int TX = (width + GS_TILE - 1) / GS_TILE, TY = (height + GS_TILE - 1) / GS_TILE;
+  w.ns = ((TX + GS_SUPER - 1) / GS_SUPER) * ((TY + GS_SUPER - 1) / GS_SUPER);
+  w.lc_tiles = (int)((mm + LC_TILE - 1) / LC_TILE);
+  w.em_tiles = (int)((mm + EM_THREADS - 1) / EM_THREADS);
+  w.ex_chunks = (int)((oo + EX_CHUNK - 1) / EX_CHUNK) + w.ns;
+  w.chunk_counts = (int32_t *)take((size_t)w.ex_chunks * 64 * 4);
+  w.totals = (int32_t *)take((size_t)TX * TY * 4);
+  w.stab = (int32_t *)take((size_t)(2 * w.ns + 2) * 4);
+  w.zero_bytes = ((size_t)64 + 4 + w.lc_tiles + w.em_tiles) * 4;
+  w.zero = (uint32_t *)take(w.zero_bytes);
   int64_t big = m > maxo ? m : maxo;
   w.sort_ws = take(gs_radix_sort_workspace_bytes(big));
   w.total = (size_t)(p - (char *)base);
@@ -237,8 +520,7 @@ static TileWs carve(void *base, int64_t m, int64_t maxo) {
 }
 
 extern "C" size_t gs_tile_map_workspace_bytes(int64_t m, int64_t max_overlaps, int width, int height) {
-  (void)width; (void)height;
-  return carve(nullptr, m, max_overlaps).total + 256;
+  return carve(nullptr, m, max_overlaps, width, height).total + 256;
 }
 
 extern "C" int gs_tile_count(const gs_raster_config *h_cfg, int64_t m, const float *g2d, const float *depth, int width,
@@ -255,61 +537,73 @@ extern "C" int gs_tile_count(const gs_raster_config *h_cfg, int64_t m, const flo
 }
 
 extern "C" int gs_tile_map(const gs_raster_config *h_cfg, int64_t m, const float *g2d, const float *depth,
-                           const int32_t *counts_in, int width,
-                           int height, int64_t max_overlaps, void *workspace, size_t workspace_bytes,
-                           int32_t *overlap_to_point, int32_t *tile_ranges, int32_t *counters, void *stream) {
+                           const void *tile_info_in, int width, int height, int64_t max_overlaps, void *workspace,
+                           size_t workspace_bytes, int32_t *overlap_to_point, int32_t *tile_ranges, int32_t *counters,
+                           void *stream) {
   GS_REQUIRE(h_cfg && h_cfg->tile_size == GS_TILE, "tile_size must be 16");
   GS_REQUIRE(m >= 0 && m < ((int64_t)1 << 30) && max_overlaps >= 0 && max_overlaps < ((int64_t)1 << 30), "m and max_overlaps must be < 2^30");
   GS_REQUIRE(width > 0 && height > 0, "bad image size");
   cudaStream_t st = (cudaStream_t)stream;
   int TX = (width + GS_TILE - 1) / GS_TILE, TY = (height + GS_TILE - 1) / GS_TILE;
   int64_t T = (int64_t)TX * TY;
+  GS_REQUIRE(TX < 65536 && TY < 65536, "image too large");
   uintptr_t aligned = ((uintptr_t)workspace + 255) & ~(uintptr_t)255;
-  TileWs w = carve((void *)aligned, m, max_overlaps);
+  TileWs w = carve((void *)aligned, m, max_overlaps, width, height);
   if (workspace_bytes < w.total + (aligned - (uintptr_t)workspace)) {
     gs_set_error("gs_tile_map: workspace too small (%zu < %zu)", workspace_bytes, w.total + 256);
     return GS_ERR_WORKSPACE;
   }
+  if (w.ns > EX_MAX_SUPER) { gs_set_error("gs_tile_map: more than %d super-tiles", EX_MAX_SUPER); return GS_ERR_UNSUPPORTED; }
   GS_CUDA(cudaMemsetAsync(counters, 0, 4 * sizeof(int32_t), st));
-  GS_CUDA(cudaMemsetAsync(tile_ranges, 0, (size_t)T * 2 * sizeof(int32_t), st));
-  if (m == 0) return GS_OK;
-  float thr = h_cfg->alpha_threshold;
-  int blocks = gs_div_up(m, 256);
-  const int32_t *counts = counts_in;  // the fused path gets them from gs_project_fwd (same footprint code)
-  if (!counts) {
-    k_tile_count<<<blocks, 256, 0, st>>>(g2d, depth, m, thr, width, height, w.counts);
-    GS_LAUNCH_CHECK();
-    counts = w.counts;
+  if (m == 0) {
+    GS_CUDA(cudaMemsetAsync(tile_ranges, 0, (size_t)T * 2 * sizeof(int32_t), st));
+    return GS_OK;
   }
-  // (a) compact the live rows (>= 1 tile) in row order (one chained-scan kernel), then sort them by depth: stable
-  //     32-bit LSD sort, ties keep row order.  Culled / off-screen rows never enter the sort.
+  float thr = h_cfg->alpha_threshold;
+  TileInfo info = w.info;
+  if (tile_info_in) {
+    info = gs_tile_info_carve((void *)tile_info_in, m, width, height);  // the fused path: filled by gs_project_fwd
+  } else {
+    k_tile_info<<<gs_div_up(m, 256), 256, 0, st>>>(g2d, depth, m, thr, width, height, info.recs, info.counts);
+    GS_LAUNCH_CHECK();
+  }
+  GS_CUDA(cudaMemsetAsync(w.zero, 0, w.zero_bytes, st));
+  uint32_t *tickets = w.zero;
+  int32_t *scounters = (int32_t *)(w.zero + 64);
+  uint32_t *lc_status = w.zero + 68;
+  uint32_t *em_status = lc_status + w.lc_tiles;
+  // (a) compact the live rows (>= 1 tile) in row order, then sort them by depth: stable 32-bit LSD sort, ties keep
+  //     row order.  Culled / off-screen rows never enter the sort.
   int32_t *live = counters + 3;
-  GS_CUDA(cudaMemsetAsync(w.scan_status, 0, w.scan_status_bytes, st));
-  int lc_tiles = gs_div_up(m, LC_TILE), em_tiles = gs_div_up(m, EM_TILE);
-  uint32_t *lc_status = w.scan_status + 64, *em_status = lc_status + lc_tiles;
-  k_live_compact<<<lc_tiles, LC_THREADS, 0, st>>>(counts, depth, m, lc_status, w.scan_status, w.dk[0], w.dv[0], live);
+  k_live_compact<<<w.lc_tiles, LC_THREADS, 0, st>>>(info.counts, depth, m, lc_status, tickets + 0, w.dk[0], w.dv[0], live);
   GS_LAUNCH_CHECK();
   int in_b = 0;
   int rc = gs_radix_sort_pingpong(w.dk[0], w.dv[0], w.dk[1], w.dv[1], m, live, 0, 32, w.sort_ws, &in_b, st);
   if (rc != GS_OK) return rc;
   uint32_t *srows = w.dv[in_b];
-  // (b)+(c) offsets of each depth-ordered row's overlaps (chained scan) and the (tile, row) pairs, one kernel;
-  // the value buffers are chosen so that the last sort pass writes overlap_to_point directly (no copy).
+  // (b) one (super-tile, row) pair per super-tile a row hits, in depth order; stable sort by super-tile id
+  int SXN = (TX + GS_SUPER - 1) / GS_SUPER;
+  k_super_emit<<<w.em_tiles, EM_THREADS, 0, st>>>(g2d, depth, info.recs, live, m, thr, width, height, SXN, srows,
+                                                  max_overlaps, em_status, tickets + 1, w.sk[0], w.sv[0], scounters);
+  GS_LAUNCH_CHECK();
   int bits = 1;
-  while (((int64_t)1 << bits) < T) ++bits;
-  int passes = (bits + 7) / 8;
-  uint32_t *ka = w.tk[0], *kb = w.tk[1];
-  uint32_t *va = (passes % 2) ? w.tv : (uint32_t *)overlap_to_point;
-  uint32_t *vb = (passes % 2) ? (uint32_t *)overlap_to_point : w.tv;
-  k_tile_emit<<<em_tiles, EM_THREADS, 0, st>>>(g2d, depth, counts, live, m, thr, width, height, srows, max_overlaps,
-                                               em_status, w.scan_status + 1, ka, va, counters);
+  while ((1 << bits) < w.ns) ++bits;
+  rc = gs_radix_sort_pingpong(w.sk[0], w.sv[0], w.sk[1], w.sv[1], max_overlaps, scounters + 2, 0, bits, w.sort_ws, &in_b, st);
+  if (rc != GS_OK) return rc;
+  // (c) segment / chunk tables, per-chunk sub-tile counts, their prefixes + tile ranges, then the final lists
+  k_seg_tables<<<1, 1024, 0, st>>>(w.sk[in_b], scounters, w.ns, w.stab);
+  GS_LAUNCH_CHECK();
+  size_t ex_smem = (size_t)(w.ns + 1) * sizeof(int32_t);
+  k_expand<false><<<w.ex_chunks, EX_THREADS, ex_smem, st>>>(g2d, depth, info.recs, thr, width, height, SXN, w.ns, w.sv[in_b],
+                                                            w.stab, w.masks, w.chunk_counts, nullptr, max_overlaps, nullptr);
+  GS_LAUNCH_CHECK();
+  k_chunk_prefix<<<w.ns, 64, 0, st>>>(w.stab, w.ns, SXN, TX, TY, w.chunk_counts, w.totals, tickets + 2, max_overlaps,
+                                      scounters, tile_ranges, counters);
   GS_LAUNCH_CHECK();
   if (max_overlaps == 0) return GS_OK;
-  // (d) stable sort by tile id
-  rc = gs_radix_sort_pingpong(ka, va, kb, vb, max_overlaps, counters + 2, 0, bits, w.sort_ws, &in_b, st);
-  if (rc != GS_OK) return rc;
-  uint32_t *tkeys = in_b ? kb : ka;
-  k_tile_ranges<<<gs_div_up(max_overlaps, 1024), 256, 0, st>>>(tkeys, counters + 2, max_overlaps, tile_ranges);
+  k_expand<true><<<w.ex_chunks, EX_THREADS, ex_smem, st>>>(g2d, depth, info.recs, thr, width, height, SXN, w.ns, w.sv[in_b],
+                                                           w.stab, w.masks, w.chunk_counts, w.totals, max_overlaps,
+                                                           overlap_to_point);
   GS_LAUNCH_CHECK();
   return GS_OK;
 }

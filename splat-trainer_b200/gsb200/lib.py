@@ -46,6 +46,7 @@ SIGNATURES = {
                           _P, _P, _P, _P, _P, _I, _P]),
   "gs_sh_eval_fwd": (_I, [_L, _P, _P, _I, _P, C.POINTER(C.c_float), _P, _P]),
   "gs_sh_eval_bwd": (_I, [_L, _P, _P, _I, _P, C.POINTER(C.c_float), _P, _P, _P, _P]),
+  "gs_tile_info_bytes": (_Z, [_L, _I, _I]),
   "gs_tile_map_workspace_bytes": (_Z, [_L, _L, _I, _I]),
   "gs_tile_map": (_I, [_CFG, _L, _P, _P, _P, _I, _I, _L, _P, _Z, _P, _P, _P, _P]),
   "gs_tile_count": (_I, [_CFG, _L, _P, _P, _I, _I, _P, _P, _P]),

@@ -21,8 +21,9 @@ def tiles_of(width, height):
 
 # ---- (1) projection + SH ---------------------------------------------------------------------------
 def project_fwd(cam, cfg, position, log_scaling, rotation, alpha_logit, sh=None, sh_degree=0, acc=None,
-                out=None, tile_counts=None):
-  """gs_project_fwd.  Returns (g2d (n,6), depth (n), rgb (n,3)); row i belongs to Gaussian i."""
+                out=None, tile_info=None):
+  """gs_project_fwd.  Returns (g2d (n,6), depth (n), rgb (n,3)); row i belongs to Gaussian i.
+  tile_info: a TileInfo (filled for gs_tile_map(tile_info=...))."""
   n = position.shape[0]
   dev = position.device
   if out is None:
@@ -34,8 +35,23 @@ def project_fwd(cam, cfg, position, log_scaling, rotation, alpha_logit, sh=None,
   L.check(L.load().gs_project_fwd(C.byref(cam), C.byref(cfg), n, L.ptr(_f32(position)), L.ptr(_f32(log_scaling)),
                                   L.ptr(_f32(rotation)), L.ptr(_f32(alpha_logit)), L.ptr(sh), sh_degree,
                                   L.ptr(g2d), L.ptr(depth), L.ptr(rgb), L.ptr(acc),
-                                  0 if acc is None else acc.shape[1], L.ptr(tile_counts), L.stream()))
+                                  0 if acc is None else acc.shape[1], None if tile_info is None else L.ptr(tile_info.buffer), L.stream()))
   return g2d, depth, rgb
+
+
+class TileInfo:
+  """Opaque per-row tile-footprint buffer written by gs_project_fwd and consumed by gs_tile_map."""
+
+  def __init__(self, n, width, height, device):
+    self.n, self.width, self.height = n, width, height
+    nbytes = L.load().gs_tile_info_bytes(n, width, height)
+    self.buffer = torch.empty((nbytes,), device=device, dtype=torch.uint8)
+
+  @property
+  def counts(self):
+    """per-row tile counts (int32 view)"""
+    off = (max(self.n, 1) * 16 + 255) // 256 * 256
+    return self.buffer[off:off + 4 * self.n].view(torch.int32)
 
 
 def project_bwd(cam, cfg, position, log_scaling, rotation, alpha_logit, sh, sh_degree, g2d, d_g2d, d_rgb,
@@ -117,7 +133,7 @@ class TileMapBuffers:
     self.counters = torch.zeros((4,), device=device, dtype=torch.int32)
 
 
-def tile_map(cfg, g2d, depth, width, height, max_overlaps=None, buffers=None, counts=None):
+def tile_map(cfg, g2d, depth, width, height, max_overlaps=None, buffers=None, tile_info=None):
   """gs_tile_map.  With max_overlaps=None the exact total is read back first (one host sync, like the
   reference's mapper); the training path passes reusable `buffers` and never syncs.
   Returns (overlap_to_point[max_overlaps], tile_ranges (T,2), counters[4], buffers)."""
@@ -129,7 +145,10 @@ def tile_map(cfg, g2d, depth, width, height, max_overlaps=None, buffers=None, co
     buffers = TileMapBuffers(m, max_overlaps, width, height, g2d.device)
   b = buffers
   assert b.m >= m and b.width == width and b.height == height
-  L.check(L.load().gs_tile_map(C.byref(cfg), m, L.ptr(g2d), L.ptr(depth), L.ptr(counts), width, height, b.max_overlaps,
+  if tile_info is not None:
+    assert tile_info.n == m and tile_info.width == width and tile_info.height == height
+  L.check(L.load().gs_tile_map(C.byref(cfg), m, L.ptr(g2d), L.ptr(depth),
+                               None if tile_info is None else L.ptr(tile_info.buffer), width, height, b.max_overlaps,
                                L.ptr(b.workspace), b.workspace.numel(), L.ptr(b.overlap_to_point),
                                L.ptr(b.tile_ranges), L.ptr(b.counters), L.stream()))
   return b.overlap_to_point, b.tile_ranges, b.counters, b

@@ -129,7 +129,7 @@ class SplatScene:
     stride = ops.acc_stride(3)
     w = dict(W=W, H=H, n=n,
              g2d=torch.empty((n, 6), device=dev), depth=torch.empty((n,), device=dev), rgb=torch.empty((n, 3), device=dev),
-             acc=torch.zeros((n, stride), device=dev), counts=torch.zeros((n,), device=dev, dtype=torch.int32),
+             acc=torch.zeros((n, stride), device=dev), tinfo=ops.TileInfo(n, W, H, dev),
              image=torch.empty((H, W, 3), device=dev), final_T=torch.empty((H, W), device=dev),
              n_contrib=torch.empty((H, W), device=dev, dtype=torch.int32), d_image=torch.empty((H, W, 3), device=dev),
              loss_sums=torch.zeros((2,), device=dev), tile=None)
@@ -142,7 +142,7 @@ class SplatScene:
     if w["tile"] is None:
       cap = self.config.max_overlaps
       if cap <= 0:
-        cap = int(int(w["counts"].sum(dtype=torch.int64).item()) * 1.5) + 65536
+        cap = int(int(w["tinfo"].counts.sum(dtype=torch.int64).item()) * 1.5) + 65536
       w["tile"] = ops.TileMapBuffers(self.n, cap, cam.width, cam.height, self.device)
     return w["tile"]
 
@@ -167,10 +167,10 @@ class SplatScene:
     p = self.p
     self._mark("begin")
     ops.project_fwd(cam, self.raster_cfg, p["position"], p["log_scaling"], p["rotation"], p["alpha_logit"], p["sh"],
-                    self.config.sh_degree, acc=w["acc"], out=(w["g2d"], w["depth"], w["rgb"]), tile_counts=w["counts"])
+                    self.config.sh_degree, acc=w["acc"], out=(w["g2d"], w["depth"], w["rgb"]), tile_info=w["tinfo"])
     self._mark("project_fwd")
     tb = self._tile_buffers(w, cam)
-    ops.tile_map(self.raster_cfg, w["g2d"], w["depth"], cam.width, cam.height, buffers=tb, counts=w["counts"])
+    ops.tile_map(self.raster_cfg, w["g2d"], w["depth"], cam.width, cam.height, buffers=tb, tile_info=w["tinfo"])
     self._mark("tile_map")
     _, _, _, vis, med = ops.raster_fwd(self.raster_cfg, w["g2d"], w["rgb"], w["depth"], tb.overlap_to_point,
                                        tb.tile_ranges, cam.width, cam.height, visibility=visibility, median=median,

@@ -153,19 +153,21 @@ def test_radix_sort_device_count():
 
 
 def test_project_counts_feed_tile_map():
-  """gs_project_fwd's tile_counts equal gs_tile_count's, and gs_tile_map(counts_in) gives the identical map."""
+  """gs_project_fwd's tile info carries gs_tile_count's counts, and gs_tile_map(tile_info_in) gives the identical map."""
   W, H = 200, 150
   cam = random_camera(W, H); cfg = go.make_config()
   g = random_gaussians(9000, seed=22, scale=0.1)
   gc = {k: cu(v) for k, v in g.items()}
   lcfg = to_lib_config(cfg)
-  counts = torch.full((9000,), -1, device="cuda", dtype=torch.int32)
+  info = ops.TileInfo(9000, W, H, "cuda")
+  info.buffer.fill_(0xff)
   g2d, depth, _ = ops.project_fwd(to_lib_camera(cam), lcfg, gc["position"], gc["log_scaling"], gc["rotation"],
-                                  gc["alpha_logit"], gc["sh"], 3, tile_counts=counts)
+                                  gc["alpha_logit"], gc["sh"], 3, tile_info=info)
+  counts = info.counts
   ref_counts, counters = ops.tile_count(lcfg, g2d, depth, W, H)
   assert torch.equal(counts, ref_counts)
   a = ops.tile_map(lcfg, g2d, depth, W, H)
-  b = ops.tile_map(lcfg, g2d, depth, W, H, counts=counts)
+  b = ops.tile_map(lcfg, g2d, depth, W, H, tile_info=info)
   total = int(a[2][0].item())
   assert torch.equal(a[0][:total], b[0][:total]) and torch.equal(a[1], b[1]) and torch.equal(a[2], b[2])
   assert int(a[2][3].item()) == int((counts > 0).sum().item())
