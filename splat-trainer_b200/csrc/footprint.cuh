@@ -29,7 +29,7 @@ __device__ __forceinline__ float det_logf(float x) {
 
 struct Footprint {
   int tx0, tx1, ty0, ty1;
-  float mx, my, ca, cb, cc, k2;
+  float mx, my, ca, cb, cc, k2, sxy, syx;
   bool valid;
 };
 
@@ -38,7 +38,7 @@ __device__ __forceinline__ Footprint row_footprint(float mx, float my, float ca,
   Footprint fp;
   fp.valid = false;
   fp.tx0 = fp.ty0 = 0; fp.tx1 = fp.ty1 = -1;
-  fp.mx = mx; fp.my = my; fp.ca = ca; fp.cb = cb; fp.cc = cc; fp.k2 = 0.f;
+  fp.mx = mx; fp.my = my; fp.ca = ca; fp.cb = cb; fp.cc = cc; fp.k2 = 0.f; fp.sxy = 0.f; fp.syx = 0.f;
   if (!(op > thr)) return fp;
   if (!(depth > 0.0f) || !(depth < 3.0e38f)) return fp;
   if (!(fabsf(mx) < 1.0e6f) || !(fabsf(my) < 1.0e6f)) return fp;
@@ -61,6 +61,8 @@ __device__ __forceinline__ Footprint row_footprint(float mx, float my, float ca,
   if (tx0 > tx1 || ty0 > ty1) return fp;
   fp.tx0 = tx0; fp.tx1 = tx1; fp.ty0 = ty0; fp.ty1 = ty1;
   fp.k2 = k2;
+  fp.sxy = -__fdiv_rn(cb, cc);  // dy of the closest point per unit dx, and vice versa (hoisted out of tile_hit)
+  fp.syx = -__fdiv_rn(cb, ca);
   fp.valid = true;
   return fp;
 }
@@ -81,7 +83,7 @@ __device__ __forceinline__ bool tile_hit(const Footprint &fp, int tx, int ty, in
   float cb2 = __fmul_rn(2.0f, fp.cb);
   if (!in_x) {
     float dx = (dxl > 0.0f) ? dxl : dxr;
-    float dy = clampf_(__fdiv_rn(-__fmul_rn(fp.cb, dx), fp.cc), dyl, dyr);
+    float dy = clampf_(__fmul_rn(fp.sxy, dx), dyl, dyr);
     float q0 = __fmul_rn(__fmul_rn(fp.ca, dx), dx), q1 = __fmul_rn(__fmul_rn(cb2, dx), dy),
           q2 = __fmul_rn(__fmul_rn(fp.cc, dy), dy);
     float q = __fadd_rn(__fadd_rn(q0, q1), q2);
@@ -89,7 +91,7 @@ __device__ __forceinline__ bool tile_hit(const Footprint &fp, int tx, int ty, in
   }
   if (!in_y) {
     float dy = (dyl > 0.0f) ? dyl : dyr;
-    float dx = clampf_(__fdiv_rn(-__fmul_rn(fp.cb, dy), fp.ca), dxl, dxr);
+    float dx = clampf_(__fmul_rn(fp.syx, dy), dxl, dxr);
     float q0 = __fmul_rn(__fmul_rn(fp.ca, dx), dx), q1 = __fmul_rn(__fmul_rn(cb2, dx), dy),
           q2 = __fmul_rn(__fmul_rn(fp.cc, dy), dy);
     float q = __fadd_rn(__fadd_rn(q0, q1), q2);
@@ -169,11 +171,8 @@ __device__ __forceinline__ int footprint_record(const Footprint &fp, int W, int 
         if (tile_hit(fp, tx, ty, W, H)) mask |= 1ull << bit;
     count = __popcll(mask);
     if (count == 0) return 0;
-    RecView v;
-    v.tx0 = fp.tx0; v.ty0 = fp.ty0; v.w = w; v.h = h; v.mask = mask; v.big = false; v.nsuper = 0;
-    int ns = 0;
-    for (int sy = fp.ty0 / GS_SUPER; sy <= fp.ty1 / GS_SUPER; ++sy)
-      for (int sx = fp.tx0 / GS_SUPER; sx <= fp.tx1 / GS_SUPER; ++sx) ns += rec_submask(v, sx, sy) != 0ull;
+    // super-tiles of the rect (conservative: one whose sub-mask turns out empty just expands to nothing)
+    int ns = (fp.tx1 / GS_SUPER - fp.tx0 / GS_SUPER + 1) * (fp.ty1 / GS_SUPER - fp.ty0 / GS_SUPER + 1);
     rec = make_uint4((uint32_t)fp.tx0 | ((uint32_t)fp.ty0 << 16), (uint32_t)w | ((uint32_t)h << 8) | ((uint32_t)ns << 16),
                      (uint32_t)mask, (uint32_t)(mask >> 32));
   } else {

@@ -226,14 +226,17 @@ __global__ void __launch_bounds__(RT) k_raster_bwd(CfgDev cfg, const float *__re
   __shared__ int s_max[RT / 32];
   TileCtx tc = tile_ctx(ranges, W, H, TX);
   float T[4], last_a[4] = {0.f, 0.f, 0.f, 0.f};
-  float dC[4][C], rec[4][C], lastc[4][C];
+  // per pixel: dL/dC and the SCALAR projections onto it of the colour composited behind the current splat (R) and of
+  // the last blended splat's colour (lastq): dL/dα needs only (f − rec)·dL/dC, so the per-channel recurrence of the
+  // usual formulation collapses to one scalar recurrence (fewer registers, fewer FMAs)
+  float dC[4][C], R[4], lastq[4];
   int nc[4];
   int mynmax = 0;
 #pragma unroll
   for (int p = 0; p < 4; ++p) {
-    T[p] = 1.f; nc[p] = 0;
+    T[p] = 1.f; nc[p] = 0; R[p] = 0.f; lastq[p] = 0.f;
 #pragma unroll
-    for (int ch = 0; ch < C; ++ch) { dC[p][ch] = 0.f; rec[p][ch] = 0.f; lastc[p][ch] = 0.f; }
+    for (int ch = 0; ch < C; ++ch) dC[p][ch] = 0.f;
     if (tc.in[p]) {
       int64_t pix = pixel_index(p, W, TX);
       T[p] = final_T[pix];
@@ -285,16 +288,15 @@ __global__ void __launch_bounds__(RT) k_raster_bwd(CfgDev cfg, const float *__re
             float Tp = __fdividef(T[p], 1.0f - a);
             T[p] = Tp;
             float w = a * Tp;
-            float dLda = 0.f;
+            float q = 0.f;
 #pragma unroll
             for (int ch = 0; ch < C; ++ch) {
-              float f = sF[ch][k];
-              rec[p][ch] = last_a[p] * lastc[p][ch] + (1.0f - last_a[p]) * rec[p][ch];
-              lastc[p][ch] = f;
-              dLda += (f - rec[p][ch]) * dC[p][ch];
+              q += sF[ch][k] * dC[p][ch];
               v[6 + ch] += w * dC[p][ch];
             }
-            dLda *= Tp;
+            R[p] = last_a[p] * lastq[p] + (1.0f - last_a[p]) * R[p];
+            lastq[p] = q;
+            float dLda = (q - R[p]) * Tp;
             last_a[p] = a;
             v[8 + C] += w;
             v[6 + C] += fabsf(a * dLda);

@@ -208,7 +208,6 @@ __global__ void __launch_bounds__(EM_THREADS) k_super_emit(const float *__restri
   }
   for (int sy = sy0; sy <= sy1; ++sy)
     for (int sx = sx0; sx <= sx1; ++sx) {
-      if (!v.big && rec_submask(v, sx, sy) == 0ull) continue;
       int sid = sy * SXN + sx;
       if (o < cap) {
         skeys[o] = (uint32_t)sid;
@@ -395,63 +394,85 @@ __global__ void __launch_bounds__(EX_THREADS) k_expand(const float *__restrict__
   }
 }
 
-// One block per super-tile, one thread per sub-tile: turns the chunk counts of the super-tile into exclusive
+// One block per super-tile, 16 chunk groups x 64 sub-tiles: turns the chunk counts of the super-tile into exclusive
 // prefixes (in place) and the column totals into per-tile totals.  The last block to finish scans the totals into
-// tile_ranges and the counters: [0] total overlaps O, [1] overflow flag, [2] min(O, capacity).
-__global__ void __launch_bounds__(64) k_chunk_prefix(const int32_t *__restrict__ stab, int NS, int SXN, int TX, int TY,
-                                                     int32_t *__restrict__ chunk_counts, int32_t *__restrict__ totals,
-                                                     uint32_t *__restrict__ done, int64_t max_overlaps,
-                                                     const int32_t *__restrict__ scounters, int32_t *__restrict__ ranges,
-                                                     int32_t *__restrict__ counters) {
-  const int sid = blockIdx.x, s = threadIdx.x;
+// tile_ranges (+ per-tile first slots) and the counters: [0] total overlaps O, [1] overflow flag, [2] min(O, capacity).
+constexpr int CP_GROUPS = 16;
+constexpr int CP_THREADS = CP_GROUPS * 64;
+
+__global__ void __launch_bounds__(CP_THREADS) k_chunk_prefix(const int32_t *__restrict__ stab, int NS, int SXN, int TX, int TY,
+                                                             int32_t *__restrict__ chunk_counts, int32_t *__restrict__ totals,
+                                                             uint32_t *__restrict__ done, int64_t max_overlaps,
+                                                             const int32_t *__restrict__ scounters, int32_t *__restrict__ ranges,
+                                                             int32_t *__restrict__ counters) {
+  __shared__ int s_g[CP_GROUPS][64];
+  __shared__ int s_warp[33];
+  __shared__ long long s_carry;
+  __shared__ bool s_last;
+  const int sid = blockIdx.x, s = threadIdx.x & 63, g = threadIdx.x >> 6;
   const int c0 = stab[NS + 1 + sid], c1 = stab[NS + 2 + sid];
-  int run = 0;
-  int c = c0;
-  for (; c + 4 <= c1; c += 4) {
-    int v[4];
+  const int len = (c1 - c0 + CP_GROUPS - 1) / CP_GROUPS;
+  const int b0 = min(c0 + g * len, c1), b1 = min(b0 + len, c1);
+  int sum = 0;
+  for (int c = b0; c < b1; ++c) sum += chunk_counts[(size_t)c * 64 + s];
+  s_g[g][s] = sum;
+  __syncthreads();
+  int run = 0, tot = 0;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) v[i] = chunk_counts[(size_t)(c + i) * 64 + s];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) { chunk_counts[(size_t)(c + i) * 64 + s] = run; run += v[i]; }
+  for (int i = 0; i < CP_GROUPS; ++i) {
+    int v = s_g[i][s];
+    if (i < g) run += v;
+    tot += v;
   }
-  for (; c < c1; ++c) {
+  for (int c = b0; c < b1; ++c) {
     int v = chunk_counts[(size_t)c * 64 + s];
     chunk_counts[(size_t)c * 64 + s] = run;
     run += v;
   }
-  int tx = GS_SUPER * (sid % SXN) + (s & (GS_SUPER - 1)), ty = GS_SUPER * (sid / SXN) + (s >> 3);
-  if (tx < TX && ty < TY) totals[ty * TX + tx] = run;
+  if (g == 0) {
+    int tx = GS_SUPER * (sid % SXN) + (s & (GS_SUPER - 1)), ty = GS_SUPER * (sid / SXN) + (s >> 3);
+    if (tx < TX && ty < TY) totals[ty * TX + tx] = tot;
+  }
   __threadfence();
-  __shared__ bool s_last;
   __syncthreads();
-  if (threadIdx.x == 0) s_last = atomicAdd(done, 1u) == (uint32_t)(NS - 1);
+  if (threadIdx.x == 0) {
+    s_last = atomicAdd(done, 1u) == (uint32_t)(NS - 1);
+    s_carry = 0;
+  }
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  // last block: exclusive scan of the T tile totals (64 threads, 8 tiles per thread per round)
-  __shared__ int s_w[2];
-  __shared__ long long s_carry;
-  if (threadIdx.x == 0) s_carry = 0;
-  __syncthreads();
+  // last block: exclusive scan of the T tile totals, 4 tiles per thread per round
   const int T = TX * TY;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  for (int base = 0; base < T; base += 64 * 8) {
-    int t0 = base + threadIdx.x * 8;
-    int v[8], sum = 0;
+  for (int base = 0; base < T; base += CP_THREADS * 4) {
+    int t0 = base + threadIdx.x * 4;
+    int v[4], ssum = 0;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { v[i] = (t0 + i < T) ? __ldcg(totals + t0 + i) : 0; sum += v[i]; }
-    int inc = sum;
+    for (int i = 0; i < 4; ++i) { v[i] = (t0 + i < T) ? __ldcg(totals + t0 + i) : 0; ssum += v[i]; }
+    int inc = ssum;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       int t = __shfl_up_sync(GS_FULL, inc, o);
       if (lane >= o) inc += t;
     }
-    if (lane == 31) s_w[w] = inc;
+    if (lane == 31) s_warp[w] = inc;
     __syncthreads();
-    long long b = s_carry + (w ? s_w[0] : 0) + inc - sum;
-    int tot = s_w[0] + s_w[1];
+    if (w == 0) {
+      int x = s_warp[lane], xi = x;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+      for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(GS_FULL, xi, o);
+        if (lane >= o) xi += t;
+      }
+      s_warp[lane] = xi - x;
+      if (lane == 31) s_warp[32] = xi;
+    }
+    __syncthreads();
+    long long b = s_carry + s_warp[w] + inc - ssum;
+    int round_total = s_warp[32];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
       if (t0 + i < T) {
         long long lo = min(b, (long long)max_overlaps), hi = min(b + v[i], (long long)max_overlaps);
         ranges[2 * (t0 + i)] = hi > lo ? (int32_t)lo : 0;  // empty tiles read [0,0)
@@ -461,7 +482,7 @@ __global__ void __launch_bounds__(64) k_chunk_prefix(const int32_t *__restrict__
       b += v[i];
     }
     __syncthreads();
-    if (threadIdx.x == 0) s_carry += tot;
+    if (threadIdx.x == 0) s_carry += round_total;
     __syncthreads();
   }
   if (threadIdx.x == 0) {
@@ -597,7 +618,7 @@ extern "C" int gs_tile_map(const gs_raster_config *h_cfg, int64_t m, const float
   k_expand<false><<<w.ex_chunks, EX_THREADS, ex_smem, st>>>(g2d, depth, info.recs, thr, width, height, SXN, w.ns, w.sv[in_b],
                                                             w.stab, w.masks, w.chunk_counts, nullptr, max_overlaps, nullptr);
   GS_LAUNCH_CHECK();
-  k_chunk_prefix<<<w.ns, 64, 0, st>>>(w.stab, w.ns, SXN, TX, TY, w.chunk_counts, w.totals, tickets + 2, max_overlaps,
+  k_chunk_prefix<<<w.ns, CP_THREADS, 0, st>>>(w.stab, w.ns, SXN, TX, TY, w.chunk_counts, w.totals, tickets + 2, max_overlaps,
                                       scounters, tile_ranges, counters);
   GS_LAUNCH_CHECK();
   if (max_overlaps == 0) return GS_OK;
