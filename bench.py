@@ -278,7 +278,7 @@ def run_b200(args):
   counters = w["tile"].counters.cpu().tolist()
   O = int(counters[0])
   V = int((w["g2d"][:, 5] > 0).sum().item())
-  v_opt = int((w["acc"][:, 11] > 0).logical_and(w["g2d"][:, 5] > 0).sum().item())
+  v_opt = int(scene._vis_idx.count.item())  # rows the last optimiser step touched (device-side visible.nonzero())
   P, T, D = W * H, ((W + 15) // 16) * ((H + 15) // 16), 11 + 3 * (deg + 1) ** 2
   bytes_ = algorithmic_bytes(n, D, V, O, P, T, v_opt)
   hbm, which = peaks()

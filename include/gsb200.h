@@ -171,14 +171,16 @@ int gs_raster_fwd(const gs_raster_config *h_cfg, int channels, int64_t m,
  *     transpose-reduction, one vector of atomics per (warp, splat).  acc row layout
  *     (acc_stride = gs_raster_acc_stride(channels) floats, must be zeroed by the caller or by
  *     gs_project_fwd):  [0..5] dL/dg2d, [6..6+C) dL/dfeature, [6+C] prune_cost,
- *     [7+C] split_score, [8+C] visibility (Σ α·T, same value the forward flag produces). */
+ *     [7+C] split_score, [8+C] visibility (Σ α·T, same value the forward flag produces).
+ *     vis_plane (nullable, m): if given, the visibility sums go to this contiguous plane instead of
+ *     acc[.][8+C], so later passes find the rows a render touched by streaming 4 B per row. */
 int gs_raster_acc_stride(int channels);
 int gs_raster_bwd(const gs_raster_config *h_cfg, int channels, int64_t m,
                   const float *g2d, const float *features,
                   const int32_t *overlap_to_point, const int32_t *tile_ranges,
                   int width, int height,
                   const float *final_T, const int32_t *n_contrib, const float *d_image,
-                  float *acc, int acc_stride, void *stream);
+                  float *acc, int acc_stride, float *vis_plane, void *stream);
 
 /* L1 + MSE photometric loss against a target, fused with the reference's post-activation
  * clamp(image,0,1) (scene/color_model.py:154-160; trainer/trainer.py:465-476):
@@ -214,6 +216,11 @@ size_t gs_visible_indexes_workspace_bytes(int64_t n);
 int gs_visible_indexes(int64_t n, const float *visible, int32_t *indexes, int32_t *count_dev,
                        void *workspace, size_t workspace_bytes, void *stream);
 
+/* gs_optim_vis_update + gs_visible_indexes fused into one pass over `visible` (one kernel, no host sync). */
+size_t gs_optim_begin_workspace_bytes(int64_t n);
+int gs_optim_begin(const gs_optim_config *h_cfg, int64_t n, const float *visible, float *running_vis, float *step,
+                   int32_t *indexes, int32_t *count_dev, void *workspace, size_t workspace_bytes, void *stream);
+
 /* One parameter group (ParameterClass.step(visibility, indexes, basis), reference
  * scene/mlp_scene.py:214-230).  Rows with visible[i] <= 0 are skipped (the reference's
  * `indexes = visible.nonzero()` done in-kernel, no host sync).  exp_avg is n×dim;
@@ -238,13 +245,15 @@ int gs_optim_step(const gs_optim_config *h_cfg, int kind, int64_t n,
  *   max_scale_px = max(.), points_in_view += (vis>0), visibility += vis, scene_visible += vis,
  *   split_score = exp_lerp(split_alpha, old, new), prune_cost = exp_lerp(prune_alpha, old, new)
  *   with exp_lerp(t,a,b) = m + log(lerp(e^(a-m), e^(b-m), t)), m = max(a,b) (util/misc.py:56-59).
- * heur points at (prune_cost, split_score) pairs with row stride heur_stride; vis has stride vis_stride. */
+ * heur points at (prune_cost, split_score) pairs with row stride heur_stride; vis has stride vis_stride.
+ * clear_acc / clear_vis (nullable): after a visible row (vis > 0) is consumed its clear_stride accumulator floats and
+ * its vis entry are zeroed, so the raster-backward accumulator is all-zero again for the next image without a memset. */
 int gs_accumulate_stats(int64_t m, const int64_t *idx, const float *g2d,
                         const float *vis, int vis_stride, const float *heur, int heur_stride,
                         float split_alpha, float prune_alpha,
                         float *prune_cost, float *split_score, float *max_scale_px,
                         int16_t *points_in_view, float *visibility, float *scene_visible,
-                        void *stream);
+                        float *clear_acc, int clear_stride, float *clear_vis, void *stream);
 
 /* take_n (reference controller/target_controller.py:150-160): mask of the k smallest
  * (descending=0) or largest values; ties at the threshold broken by lowest index, so exactly

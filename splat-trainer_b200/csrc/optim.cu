@@ -103,6 +103,98 @@ extern "C" int gs_visible_indexes(int64_t n, const float *visible, int32_t *inde
   return GS_OK;
 }
 
+// Fused start of the optimiser step: gs_optim_vis_update + gs_visible_indexes in ONE pass over `visible`
+// (single-pass chained-scan compaction): for rows with visible > 0: step += 1, running_vis = lerp(vis_beta), and the
+// ascending row list / its length are written.
+constexpr int OB_THREADS = 256;
+constexpr int OB_ITEMS = 8;
+constexpr int OB_TILE = OB_THREADS * OB_ITEMS;
+
+__global__ void __launch_bounds__(OB_THREADS) k_optim_begin(int64_t n, float vis_beta, const float *__restrict__ visible,
+                                                            float *__restrict__ running_vis, float *__restrict__ step,
+                                                            uint32_t *__restrict__ status, uint32_t *__restrict__ ticket,
+                                                            int32_t *__restrict__ indexes, int32_t *__restrict__ count_dev) {
+  __shared__ int s_warp[8];
+  __shared__ int s_tile;
+  __shared__ uint32_t s_prefix;
+  if (threadIdx.x == 0) s_tile = (int)atomicAdd(ticket, 1u);
+  __syncthreads();
+  const int tile = s_tile;
+  int64_t base = (int64_t)tile * OB_TILE + (int64_t)threadIdx.x * OB_ITEMS;
+  float v[OB_ITEMS];
+  if (base + OB_ITEMS <= n) {
+    const float4 *p = reinterpret_cast<const float4 *>(visible + base);
+    float4 a = p[0], b = p[1];
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  } else {
+#pragma unroll
+    for (int i = 0; i < OB_ITEMS; ++i) v[i] = (base + i < n) ? visible[base + i] : 0.f;
+  }
+  int sum = 0;
+#pragma unroll
+  for (int i = 0; i < OB_ITEMS; ++i) sum += v[i] > 0.f;
+  // block exclusive scan (256 threads)
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  int inc = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int t = __shfl_up_sync(GS_FULL, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) s_warp[w] = inc;
+  __syncthreads();
+  int wo = 0, tot = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    int c = s_warp[i];
+    if (i < w) wo += c;
+    tot += c;
+  }
+  int ex = wo + inc - sum;
+  if (threadIdx.x == 0) gs_st_status(status + tile, (uint32_t)tot | (tile == 0 ? GS_LB_INCL : GS_LB_LOCAL));
+  if (threadIdx.x < 32) {
+    uint32_t prefix = gs_lookback_warp(status, tile);
+    if (threadIdx.x == 0) {
+      if (tile > 0) gs_st_status(status + tile, (prefix + (uint32_t)tot) | GS_LB_INCL);
+      s_prefix = prefix;
+      if (tile == (int)gridDim.x - 1) *count_dev = (int32_t)(prefix + (uint32_t)tot);
+    }
+  }
+  __syncthreads();
+  uint32_t pos = s_prefix + (uint32_t)ex;
+#pragma unroll
+  for (int i = 0; i < OB_ITEMS; ++i) {
+    if (v[i] > 0.f) {
+      int64_t r = base + i;
+      indexes[pos++] = (int32_t)r;
+      step[r] += 1.0f;
+      running_vis[r] = vis_beta * running_vis[r] + (1.0f - vis_beta) * v[i];
+    }
+  }
+}
+
+extern "C" size_t gs_optim_begin_workspace_bytes(int64_t n) {
+  size_t tiles = (size_t)((n > 0 ? n : 1) + OB_TILE - 1) / OB_TILE;
+  return gs_align256((64 + tiles) * 4) + 256;
+}
+
+extern "C" int gs_optim_begin(const gs_optim_config *c, int64_t n, const float *visible, float *running_vis, float *step,
+                              int32_t *indexes, int32_t *count_dev, void *workspace, size_t workspace_bytes, void *stream) {
+  GS_REQUIRE(c && count_dev, "null argument");
+  GS_REQUIRE(n >= 0 && n < ((int64_t)1 << 30), "n must be < 2^30");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n == 0) { GS_CUDA(cudaMemsetAsync(count_dev, 0, 4, st)); return GS_OK; }
+  GS_REQUIRE(visible && running_vis && step && indexes && workspace, "null argument");
+  if (workspace_bytes < gs_optim_begin_workspace_bytes(n)) { gs_set_error("gs_optim_begin: workspace too small"); return GS_ERR_WORKSPACE; }
+  uintptr_t a = ((uintptr_t)workspace + 255) & ~(uintptr_t)255;
+  int tiles = gs_div_up(n, OB_TILE);
+  GS_CUDA(cudaMemsetAsync((void *)a, 0, (64 + (size_t)tiles) * 4, st));
+  uint32_t *ticket = (uint32_t *)a, *status = ticket + 64;
+  k_optim_begin<<<tiles, OB_THREADS, 0, st>>>(n, c->vis_beta, visible, running_vis, step, status, ticket, indexes, count_dev);
+  GS_LAUNCH_CHECK();
+  return GS_OK;
+}
+
 extern "C" int gs_optim_vis_update(const gs_optim_config *c, int64_t n, const float *visible, float *running_vis,
                                    float *step, void *stream) {
   GS_REQUIRE(c && visible && running_vis && step, "null argument");
@@ -318,7 +410,8 @@ __global__ void __launch_bounds__(256) k_accumulate_stats(int64_t m, const int64
                                                           float prune_alpha, float *__restrict__ prune_cost,
                                                           float *__restrict__ split_score, float *__restrict__ max_scale_px,
                                                           int16_t *__restrict__ points_in_view, float *__restrict__ visibility,
-                                                          float *__restrict__ scene_visible) {
+                                                          float *__restrict__ scene_visible, float *__restrict__ clear_acc,
+                                                          int clear_stride, float *__restrict__ clear_vis) {
   int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= m) return;
   const float2 *g = reinterpret_cast<const float2 *>(g2d + GS_G2D_STRIDE * r);
@@ -335,22 +428,33 @@ __global__ void __launch_bounds__(256) k_accumulate_stats(int64_t m, const int64
   float scale_px = sqrtf(fmaxf(lam, 0.f));
   if (scale_px > max_scale_px[i]) max_scale_px[i] = scale_px;
   float v = vis[(int64_t)vis_stride * r];
-  if (v > 0.f) points_in_view[i] += 1;
-  visibility[i] += v;
-  if (scene_visible) scene_visible[i] += v;
-  split_score[i] = exp_lerp(split_alpha, split_score[i], heur[(int64_t)heur_stride * r + 1]);
-  prune_cost[i] = exp_lerp(prune_alpha, prune_cost[i], heur[(int64_t)heur_stride * r]);
+  float h_prune = heur[(int64_t)heur_stride * r], h_split = heur[(int64_t)heur_stride * r + 1];
+  if (v > 0.f) {
+    points_in_view[i] += 1;
+    visibility[i] += v;
+    if (scene_visible) scene_visible[i] += v;
+  }
+  split_score[i] = exp_lerp(split_alpha, split_score[i], h_split);
+  prune_cost[i] = exp_lerp(prune_alpha, prune_cost[i], h_prune);
+  if (v > 0.f) {
+    if (clear_acc) {
+      float *a = clear_acc + (int64_t)clear_stride * r;
+      for (int k = 0; k < clear_stride; ++k) a[k] = 0.f;
+    }
+    if (clear_vis) clear_vis[r] = 0.f;
+  }
 }
 
 extern "C" int gs_accumulate_stats(int64_t m, const int64_t *idx, const float *g2d, const float *vis, int vis_stride,
                                    const float *heur, int heur_stride, float split_alpha, float prune_alpha,
                                    float *prune_cost, float *split_score, float *max_scale_px, int16_t *points_in_view,
-                                   float *visibility, float *scene_visible, void *stream) {
+                                   float *visibility, float *scene_visible, float *clear_acc, int clear_stride,
+                                   float *clear_vis, void *stream) {
   GS_REQUIRE(g2d && vis && heur && prune_cost && split_score && max_scale_px && points_in_view && visibility, "null argument");
   if (m <= 0) return GS_OK;
   k_accumulate_stats<<<gs_div_up(m, 256), 256, 0, (cudaStream_t)stream>>>(m, idx, g2d, vis, vis_stride, heur, heur_stride,
                                                                           split_alpha, prune_alpha, prune_cost, split_score,
-                                                                          max_scale_px, points_in_view, visibility, scene_visible);
+                                                                          max_scale_px, points_in_view, visibility, scene_visible, clear_acc, clear_stride, clear_vis);
   GS_LAUNCH_CHECK();
   return GS_OK;
 }

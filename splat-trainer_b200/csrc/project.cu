@@ -226,8 +226,8 @@ __global__ void __launch_bounds__(128) k_project_bwd(CamDev cam, CfgDev cfg, int
                                                      float *__restrict__ g_alpha_logit, float *__restrict__ g_sh, int accumulate) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
+  if (row_vis && !(row_vis[(int64_t)row_vis_stride * i] > 0.f)) return;  // blended by no pixel (contiguous plane: test first)
   if (!(g2d[GS_G2D_STRIDE * i + 5] > 0.f)) return;  // culled in forward
-  if (row_vis && !(row_vis[(int64_t)row_vis_stride * i] > 0.f)) return;  // blended by no pixel
   float px = position[3 * i], py = position[3 * i + 1], pz = position[3 * i + 2];
   Proj t;
   float4 q = reinterpret_cast<const float4 *>(rotation)[i];

@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(RT) k_raster_bwd(CfgDev cfg, const float *__re
                                                    const int32_t *__restrict__ o2p, const int32_t *__restrict__ ranges,
                                                    int W, int H, int TX, const float *__restrict__ final_T,
                                                    const int32_t *__restrict__ n_contrib, const float *__restrict__ d_image,
-                                                   float *__restrict__ acc, int acc_stride) {
+                                                   float *__restrict__ acc, int acc_stride, float *__restrict__ vis_plane) {
   constexpr int NV = (9 + C <= 12) ? 12 : 16;
   __shared__ float4 sA[RT];
   __shared__ float4 sB[RT];
@@ -317,8 +317,11 @@ __global__ void __launch_bounds__(RT) k_raster_bwd(CfgDev cfg, const float *__re
         v[2] *= -0.5f * LOG2E; v[3] *= -LOG2E; v[4] *= -0.5f * LOG2E;
         int index; bool valid;
         float tot = (NV == 12) ? multi_reduce12(v, lane, index, valid) : multi_reduce16(v, lane, index, valid);
-        if (valid && index < 9 + C && tot != 0.f)
-          atomicAdd(acc + (int64_t)acc_stride * __float_as_int(B.w) + index, tot);
+        if (valid && index < 9 + C && tot != 0.f) {
+          int id = __float_as_int(B.w);
+          float *dst = (vis_plane && index == 8 + C) ? vis_plane + id : acc + (int64_t)acc_stride * id + index;
+          atomicAdd(dst, tot);
+        }
       }
     }
   }
@@ -364,7 +367,7 @@ extern "C" int gs_raster_fwd(const gs_raster_config *h_cfg, int channels, int64_
 extern "C" int gs_raster_bwd(const gs_raster_config *h_cfg, int channels, int64_t m, const float *g2d, const float *features,
                              const int32_t *overlap_to_point, const int32_t *tile_ranges, int width, int height,
                              const float *final_T, const int32_t *n_contrib, const float *d_image, float *acc,
-                             int acc_stride, void *stream) {
+                             int acc_stride, float *vis_plane, void *stream) {
   (void)m;
   GS_REQUIRE(h_cfg && h_cfg->tile_size == GS_TILE, "tile_size must be 16");
   GS_REQUIRE(acc_stride >= 9 + channels, "acc_stride too small");
@@ -373,9 +376,9 @@ extern "C" int gs_raster_bwd(const gs_raster_config *h_cfg, int channels, int64_
   int TX = (width + GS_TILE - 1) / GS_TILE, TY = (height + GS_TILE - 1) / GS_TILE;
   int tiles = TX * TY;
   switch (channels) {
-    case 1: k_raster_bwd<1><<<tiles, RT, 0, st>>>(cfg, g2d, features, overlap_to_point, tile_ranges, width, height, TX, final_T, n_contrib, d_image, acc, acc_stride); break;
-    case 3: k_raster_bwd<3><<<tiles, RT, 0, st>>>(cfg, g2d, features, overlap_to_point, tile_ranges, width, height, TX, final_T, n_contrib, d_image, acc, acc_stride); break;
-    case 4: k_raster_bwd<4><<<tiles, RT, 0, st>>>(cfg, g2d, features, overlap_to_point, tile_ranges, width, height, TX, final_T, n_contrib, d_image, acc, acc_stride); break;
+    case 1: k_raster_bwd<1><<<tiles, RT, 0, st>>>(cfg, g2d, features, overlap_to_point, tile_ranges, width, height, TX, final_T, n_contrib, d_image, acc, acc_stride, vis_plane); break;
+    case 3: k_raster_bwd<3><<<tiles, RT, 0, st>>>(cfg, g2d, features, overlap_to_point, tile_ranges, width, height, TX, final_T, n_contrib, d_image, acc, acc_stride, vis_plane); break;
+    case 4: k_raster_bwd<4><<<tiles, RT, 0, st>>>(cfg, g2d, features, overlap_to_point, tile_ranges, width, height, TX, final_T, n_contrib, d_image, acc, acc_stride, vis_plane); break;
     default: gs_set_error("gs_raster_bwd: channels must be 1, 3 or 4"); return GS_ERR_UNSUPPORTED;
   }
   GS_LAUNCH_CHECK();

@@ -54,13 +54,15 @@ SIGNATURES = {
   "gs_radix_sort_pairs": (_I, [_P, _P, _P, _P, _L, _P, _I, _I, _P, _Z, _P]),
   "gs_raster_fwd": (_I, [_CFG, _I, _L, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, _P, _P]),
   "gs_raster_acc_stride": (_I, [_I]),
-  "gs_raster_bwd": (_I, [_CFG, _I, _L, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, _I, _P]),
+  "gs_raster_bwd": (_I, [_CFG, _I, _L, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, _I, _P, _P]),
   "gs_loss_l1_mse": (_I, [_L, _P, _P, _P, _F, _F, _P, _P, _P]),
+  "gs_optim_begin_workspace_bytes": (_Z, [_L]),
+  "gs_optim_begin": (_I, [_OPT, _L, _P, _P, _P, _P, _P, _P, _Z, _P]),
   "gs_optim_vis_update": (_I, [_OPT, _L, _P, _P, _P, _P]),
   "gs_visible_indexes_workspace_bytes": (_Z, [_L]),
   "gs_visible_indexes": (_I, [_L, _P, _P, _P, _P, _Z, _P]),
   "gs_optim_step": (_I, [_OPT, _I, _L, _P, _P, _I, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _F, _F, _I, _P]),
-  "gs_accumulate_stats": (_I, [_L, _P, _P, _P, _I, _P, _I, _F, _F, _P, _P, _P, _P, _P, _P, _P]),
+  "gs_accumulate_stats": (_I, [_L, _P, _P, _P, _I, _P, _I, _F, _F, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P]),
   "gs_select_topk_workspace_bytes": (_Z, [_L]),
   "gs_select_topk_mask": (_I, [_P, _L, _L, _I, _P, _P, _Z, _P]),
   "gs_compact_workspace_bytes": (_Z, [_L]),

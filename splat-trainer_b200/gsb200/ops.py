@@ -195,14 +195,15 @@ def raster_fwd(cfg, g2d, features, depth, overlap_to_point, tile_ranges, width, 
 
 
 def raster_bwd(cfg, g2d, features, overlap_to_point, tile_ranges, width, height, final_T, n_contrib, d_image,
-               acc=None):
-  """gs_raster_bwd; acc (m, acc_stride) must be zero on entry (allocated zeroed if None)."""
+               acc=None, vis_plane=None):
+  """gs_raster_bwd; acc (m, acc_stride) must be zero on entry (allocated zeroed if None).
+  vis_plane (m,): receives the visibility sums instead of acc[:, 8+C] (must be zero on entry too)."""
   m, ch = g2d.shape[0], features.shape[1]
   if acc is None:
     acc = torch.zeros((m, acc_stride(ch)), device=g2d.device, dtype=torch.float32)
   L.check(L.load().gs_raster_bwd(C.byref(cfg), ch, m, L.ptr(g2d), L.ptr(features), L.ptr(overlap_to_point),
                                  L.ptr(tile_ranges), width, height, L.ptr(final_T), L.ptr(n_contrib),
-                                 L.ptr(_f32(d_image)), L.ptr(acc), acc.shape[1], L.stream()))
+                                 L.ptr(_f32(d_image)), L.ptr(acc), acc.shape[1], L.ptr(vis_plane), L.stream()))
   return acc
 
 
@@ -238,6 +239,17 @@ class VisibleIndexes:
     self.nbytes = L.load().gs_visible_indexes_workspace_bytes(n)
     self.workspace = torch.empty((self.nbytes,), device=device, dtype=torch.uint8)
 
+  def begin(self, ocfg, visible, running_vis, step):
+    """gs_optim_begin: visibility state update + index list in one kernel."""
+    assert visible.shape[0] == self.n
+    if not hasattr(self, "begin_ws"):
+      self.begin_bytes = L.load().gs_optim_begin_workspace_bytes(self.n)
+      self.begin_ws = torch.empty((self.begin_bytes,), device=visible.device, dtype=torch.uint8)
+    L.check(L.load().gs_optim_begin(C.byref(ocfg), self.n, L.ptr(_f32(visible)), L.ptr(running_vis), L.ptr(step),
+                                    L.ptr(self.indexes), L.ptr(self.count), L.ptr(self.begin_ws), self.begin_bytes,
+                                    L.stream()))
+    return self
+
   def update(self, visible):
     assert visible.shape[0] == self.n
     L.check(L.load().gs_visible_indexes(self.n, L.ptr(_f32(visible)), L.ptr(self.indexes), L.ptr(self.count),
@@ -256,7 +268,8 @@ def optim_step(ocfg, kind, lr, param, grad, exp_avg, exp_avg_sq, visible, runnin
                                  L.ptr(basis_q), post, post_lo, post_hi, int(zero_grad), L.stream()))
 
 
-def accumulate_stats(idx, g2d, vis, heur, split_alpha, prune_alpha, state, scene_visible=None):
+def accumulate_stats(idx, g2d, vis, heur, split_alpha, prune_alpha, state, scene_visible=None, clear_acc=None,
+                     clear_vis=None):
   """vis: (m,) or a column view; heur: (m,2)-like view whose row stride is heur.stride(0) with
   [.,0]=prune_cost, [.,1]=split_score.  state: dict of the PointState tensors (updated in place)."""
   m = g2d.shape[0]
@@ -265,7 +278,8 @@ def accumulate_stats(idx, g2d, vis, heur, split_alpha, prune_alpha, state, scene
                                        heur.stride(0), split_alpha, prune_alpha, L.ptr(state["prune_cost"]),
                                        L.ptr(state["split_score"]), L.ptr(state["max_scale_px"]),
                                        L.ptr(state["points_in_view"]), L.ptr(state["visibility"]),
-                                       L.ptr(scene_visible), L.stream()))
+                                       L.ptr(scene_visible), L.ptr(clear_acc),
+                                       0 if clear_acc is None else clear_acc.shape[1], L.ptr(clear_vis), L.stream()))
 
 
 def select_topk_mask(values, k, descending):

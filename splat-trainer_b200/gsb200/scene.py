@@ -129,7 +129,7 @@ class SplatScene:
     stride = ops.acc_stride(3)
     w = dict(W=W, H=H, n=n,
              g2d=torch.empty((n, 6), device=dev), depth=torch.empty((n,), device=dev), rgb=torch.empty((n, 3), device=dev),
-             acc=torch.zeros((n, stride), device=dev), tinfo=ops.TileInfo(n, W, H, dev),
+             acc=torch.zeros((n, stride), device=dev), vis=torch.zeros((n,), device=dev), tinfo=ops.TileInfo(n, W, H, dev),
              image=torch.empty((H, W, 3), device=dev), final_T=torch.empty((H, W), device=dev),
              n_contrib=torch.empty((H, W), device=dev, dtype=torch.int32), d_image=torch.empty((H, W, 3), device=dev),
              loss_sums=torch.zeros((2,), device=dev), tile=None)
@@ -167,7 +167,7 @@ class SplatScene:
     p = self.p
     self._mark("begin")
     ops.project_fwd(cam, self.raster_cfg, p["position"], p["log_scaling"], p["rotation"], p["alpha_logit"], p["sh"],
-                    self.config.sh_degree, acc=w["acc"], out=(w["g2d"], w["depth"], w["rgb"]), tile_info=w["tinfo"])
+                    self.config.sh_degree, out=(w["g2d"], w["depth"], w["rgb"]), tile_info=w["tinfo"])
     self._mark("project_fwd")
     tb = self._tile_buffers(w, cam)
     ops.tile_map(self.raster_cfg, w["g2d"], w["depth"], cam.width, cam.height, buffers=tb, tile_info=w["tinfo"])
@@ -197,15 +197,17 @@ class SplatScene:
     self._mark("loss")
     acc = w["acc"]
     ops.raster_bwd(self.raster_cfg, w["g2d"], w["rgb"], tb.overlap_to_point, tb.tile_ranges, cam.width, cam.height,
-                   w["final_T"], w["n_contrib"], w["d_image"], acc=acc)
+                   w["final_T"], w["n_contrib"], w["d_image"], acc=acc, vis_plane=w["vis"])
     self._mark("raster_bwd")
     p = self.p
     ops.project_bwd(cam, self.raster_cfg, p["position"], p["log_scaling"], p["rotation"], p["alpha_logit"], p["sh"],
-                    c.sh_degree, w["g2d"], acc[:, 0:6], acc[:, 6:9], None, row_vis=acc[:, 11], grads=self.g,
+                    c.sh_degree, w["g2d"], acc[:, 0:6], acc[:, 6:9], None, row_vis=w["vis"], grads=self.g,
                     accumulate=True)
     self._mark("project_bwd")
-    ops.accumulate_stats(None, w["g2d"], acc[:, 11], acc[:, 9:11], c.split_alpha, c.prune_alpha, self.stats,
-                         scene_visible=self.visible)
+    # the statistics pass is the accumulator's last reader: it clears the rows this image touched, so `acc` / `vis`
+    # are all-zero again for the next image without a 48·N-byte memset
+    ops.accumulate_stats(None, w["g2d"], w["vis"], acc[:, 9:11], c.split_alpha, c.prune_alpha, self.stats,
+                         scene_visible=self.visible, clear_acc=acc, clear_vis=w["vis"])
     self._mark("stats")
     return w["loss_sums"]
 
@@ -214,10 +216,10 @@ class SplatScene:
     c, o = self.config, self.ocfg
     vis, rv, st = self.visible, self.running_vis, self.opt_step
     self._mark("optim_begin")
-    ops.optim_vis_update(o, vis, rv, st)
     if self._vis_idx is None or self._vis_idx.n != self.n:
       self._vis_idx = ops.VisibleIndexes(self.n, self.device)
-    ix = self._vis_idx.update(vis)  # device-side visible.nonzero() (reference mlp_scene.py:217), no host sync
+    # visibility state + device-side visible.nonzero() (reference mlp_scene.py:217) in one kernel, no host sync
+    ix = self._vis_idx.begin(o, vis, rv, st)
     p, g, m1, m2 = self.p, self.g, self.m1, self.m2
     # position first: its local basis is built from log_scaling / rotation BEFORE their update (mlp_scene.py:219)
     ops.optim_step(o, L.GS_GROUP_LOCAL_VECTOR, c.lr_position, p["position"], g["position"], m1["position"],
