@@ -250,8 +250,10 @@ def run_b200(args):
   e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
   with ClockSampler(local) as clocks:
     e0.record()
+    h0 = time.perf_counter()
     for i in range(args.steps):
       step(args.warmup + i, dev_targets)
+    host_enqueue_ms = 1e3 * (time.perf_counter() - h0) / args.steps  # CPU time to enqueue one step (no sync inside)
     e1.record()
     barrier()
   ms = e0.elapsed_time(e1)
@@ -304,7 +306,7 @@ def run_b200(args):
                              "fwd+bwd+fused visibility-aware LaProp step", "images_per_step": world,
                  "l2": "inputs larger than L2 (params+grads+moments 2.8 GB, overlap list > 126 MB)",
                  "parallelism": f"dp{world}", "V_in_view": V, "O_overlaps": O, "V_optimised": v_opt, "overflow": overflow},
-      "stages_ms": stages,
+      "stages_ms": stages, "host_enqueue_ms_per_step": host_enqueue_ms,
       "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
                    "traffic": None, "peak_source": which, "algorithmic_bytes": bytes_[dom],
                    "iteration": {"algorithmic_bytes": iter_bytes, "achieved": iter_bytes / (ms_step * 1e-3) / 1e9,

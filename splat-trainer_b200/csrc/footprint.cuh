@@ -29,7 +29,7 @@ __device__ __forceinline__ float det_logf(float x) {
 
 struct Footprint {
   int tx0, tx1, ty0, ty1;
-  float mx, my, ca, cb, cc, k2, sxy, syx;
+  float mx, my, k2, syx, g, inv_ca, dy_right;  // per-row span constants, see row_span
   bool valid;
 };
 
@@ -38,7 +38,7 @@ __device__ __forceinline__ Footprint row_footprint(float mx, float my, float ca,
   Footprint fp;
   fp.valid = false;
   fp.tx0 = fp.ty0 = 0; fp.tx1 = fp.ty1 = -1;
-  fp.mx = mx; fp.my = my; fp.ca = ca; fp.cb = cb; fp.cc = cc; fp.k2 = 0.f; fp.sxy = 0.f; fp.syx = 0.f;
+  fp.mx = mx; fp.my = my; fp.k2 = 0.f; fp.syx = 0.f; fp.g = 0.f; fp.inv_ca = 0.f; fp.dy_right = 0.f;
   if (!(op > thr)) return fp;
   if (!(depth > 0.0f) || !(depth < 3.0e38f)) return fp;
   if (!(fabsf(mx) < 1.0e6f) || !(fabsf(my) < 1.0e6f)) return fp;
@@ -61,50 +61,53 @@ __device__ __forceinline__ Footprint row_footprint(float mx, float my, float ca,
   if (tx0 > tx1 || ty0 > ty1) return fp;
   fp.tx0 = tx0; fp.tx1 = tx1; fp.ty0 = ty0; fp.ty1 = ty1;
   fp.k2 = k2;
-  fp.sxy = -__fdiv_rn(cb, cc);  // dy of the closest point per unit dx, and vice versa (hoisted out of tile_hit)
+  // for a fixed dy the ellipse spans dx = syx·dy ± sqrt((k2 − g·dy²)·inv_ca); its rightmost point (dx = +ex) lies at
+  // dy_right = −(cb/cc)·ex, its leftmost at −dy_right
   fp.syx = -__fdiv_rn(cb, ca);
+  fp.g = __fdiv_rn(detc, ca);
+  fp.inv_ca = __fdiv_rn(1.0f, ca);
+  fp.dy_right = __fmul_rn(-__fdiv_rn(cb, cc), ex);
   fp.valid = true;
   return fp;
 }
 
 __device__ __forceinline__ float clampf_(float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); }
 
-// exact test: does the k2-ellipse reach any pixel centre of tile (tx,ty)?
-__device__ __forceinline__ bool tile_hit(const Footprint &fp, int tx, int ty, int W, int H) {
-  int px1 = min(tx * GS_TILE + GS_TILE - 1, W - 1);
+// Tiles [txa, txb] of tile row ty whose pixel-centre rectangle the k2-ellipse reaches (empty if txa > txb).
+// The ellipse cut by the band dy ∈ [dyl, dyr] is convex, so its x-range is [min x_left, max x_right] with
+// x_right(dy) = syx·dy + hw(dy) concave (maximal at the band point closest to dy_right) and x_left convex:
+// two square roots per tile ROW instead of a closest-point test per TILE.
+__device__ __forceinline__ void row_span(const Footprint &fp, int ty, int H, int &txa, int &txb) {
+  txa = 0; txb = -1;
   int py1 = min(ty * GS_TILE + GS_TILE - 1, H - 1);
-  float dxl = __fsub_rn(__fadd_rn((float)(tx * GS_TILE), 0.5f), fp.mx);
-  float dxr = __fsub_rn(__fadd_rn((float)px1, 0.5f), fp.mx);
   float dyl = __fsub_rn(__fadd_rn((float)(ty * GS_TILE), 0.5f), fp.my);
   float dyr = __fsub_rn(__fadd_rn((float)py1, 0.5f), fp.my);
-  bool in_x = (dxl <= 0.0f) && (dxr >= 0.0f), in_y = (dyl <= 0.0f) && (dyr >= 0.0f);
-  if (in_x && in_y) return true;
-  float qmin = 3.0e38f;
-  float cb2 = __fmul_rn(2.0f, fp.cb);
-  if (!in_x) {
-    float dx = (dxl > 0.0f) ? dxl : dxr;
-    float dy = clampf_(__fmul_rn(fp.sxy, dx), dyl, dyr);
-    float q0 = __fmul_rn(__fmul_rn(fp.ca, dx), dx), q1 = __fmul_rn(__fmul_rn(cb2, dx), dy),
-          q2 = __fmul_rn(__fmul_rn(fp.cc, dy), dy);
-    float q = __fadd_rn(__fadd_rn(q0, q1), q2);
-    if (q < qmin) qmin = q;
-  }
-  if (!in_y) {
-    float dy = (dyl > 0.0f) ? dyl : dyr;
-    float dx = clampf_(__fmul_rn(fp.syx, dy), dxl, dxr);
-    float q0 = __fmul_rn(__fmul_rn(fp.ca, dx), dx), q1 = __fmul_rn(__fmul_rn(cb2, dx), dy),
-          q2 = __fmul_rn(__fmul_rn(fp.cc, dy), dy);
-    float q = __fadd_rn(__fadd_rn(q0, q1), q2);
-    if (q < qmin) qmin = q;
-  }
-  return qmin <= fp.k2;
+  float dy0 = clampf_(0.0f, dyl, dyr);
+  float t0 = __fmul_rn(__fmul_rn(fp.g, dy0), dy0);
+  if (!(__fsub_rn(fp.k2, t0) >= 0.0f)) return;  // the band misses the ellipse
+  float dyR = clampf_(fp.dy_right, dyl, dyr), dyL = clampf_(-fp.dy_right, dyl, dyr);
+  float rR = __fsub_rn(fp.k2, __fmul_rn(__fmul_rn(fp.g, dyR), dyR));
+  float rL = __fsub_rn(fp.k2, __fmul_rn(__fmul_rn(fp.g, dyL), dyL));
+  if (rR < 0.0f) rR = 0.0f;
+  if (rL < 0.0f) rL = 0.0f;
+  float xr = __fadd_rn(__fmul_rn(fp.syx, dyR), __fsqrt_rn(__fmul_rn(rR, fp.inv_ca)));
+  float xl = __fsub_rn(__fmul_rn(fp.syx, dyL), __fsqrt_rn(__fmul_rn(rL, fp.inv_ca)));
+  float x_lo = __fadd_rn(fp.mx, xl), x_hi = __fadd_rn(fp.mx, xr);
+  int a = (int)ceilf(__fmul_rn(__fsub_rn(x_lo, 15.5f), 0.0625f));
+  int b = (int)floorf(__fmul_rn(__fsub_rn(x_hi, 0.5f), 0.0625f));
+  txa = max(a, fp.tx0);
+  txb = min(b, fp.tx1);
 }
 
 __device__ __forceinline__ int footprint_count(const Footprint &fp, int W, int H) {
+  (void)W;
   if (!fp.valid) return 0;
   int c = 0;
-  for (int ty = fp.ty0; ty <= fp.ty1; ++ty)
-    for (int tx = fp.tx0; tx <= fp.tx1; ++tx) c += tile_hit(fp, tx, ty, W, H) ? 1 : 0;
+  for (int ty = fp.ty0; ty <= fp.ty1; ++ty) {
+    int a, b;
+    row_span(fp, ty, H, a, b);
+    c += max(0, b - a + 1);
+  }
   return c;
 }
 
@@ -148,12 +151,18 @@ __device__ __forceinline__ unsigned long long rec_submask(const RecView &v, int 
 
 // exact hit mask of ANY valid footprint restricted to super-tile (sx, sy) (used for big rows)
 __device__ __forceinline__ unsigned long long footprint_submask(const Footprint &fp, int sx, int sy, int W, int H) {
+  (void)W;
   unsigned long long sub = 0ull;
   int ty_lo = max(fp.ty0, GS_SUPER * sy), ty_hi = min(fp.ty1, GS_SUPER * sy + GS_SUPER - 1);
-  int tx_lo = max(fp.tx0, GS_SUPER * sx), tx_hi = min(fp.tx1, GS_SUPER * sx + GS_SUPER - 1);
-  for (int ty = ty_lo; ty <= ty_hi; ++ty)
-    for (int tx = tx_lo; tx <= tx_hi; ++tx)
-      if (tile_hit(fp, tx, ty, W, H)) sub |= 1ull << (GS_SUPER * (ty & (GS_SUPER - 1)) + (tx & (GS_SUPER - 1)));
+  for (int ty = ty_lo; ty <= ty_hi; ++ty) {
+    int a, b;
+    row_span(fp, ty, H, a, b);
+    a = max(a, GS_SUPER * sx); b = min(b, GS_SUPER * sx + GS_SUPER - 1);
+    if (b >= a) {
+      unsigned long long bits = ((1ull << (b - a + 1)) - 1ull) << (a & (GS_SUPER - 1));
+      sub |= bits << (GS_SUPER * (ty & (GS_SUPER - 1)));
+    }
+  }
   return sub;
 }
 
@@ -163,24 +172,25 @@ __device__ __forceinline__ int footprint_record(const Footprint &fp, int W, int 
   if (!fp.valid) return 0;
   int w = fp.tx1 - fp.tx0 + 1, h = fp.ty1 - fp.ty0 + 1;
   int count = 0;
+  int ns = (fp.tx1 / GS_SUPER - fp.tx0 / GS_SUPER + 1) * (fp.ty1 / GS_SUPER - fp.ty0 / GS_SUPER + 1);  // conservative
   if (w * h <= 64) {
     unsigned long long mask = 0ull;
-    int bit = 0;
-    for (int ty = fp.ty0; ty <= fp.ty1; ++ty)
-      for (int tx = fp.tx0; tx <= fp.tx1; ++tx, ++bit)
-        if (tile_hit(fp, tx, ty, W, H)) mask |= 1ull << bit;
+    for (int ty = fp.ty0; ty <= fp.ty1; ++ty) {
+      int a, b;
+      row_span(fp, ty, H, a, b);
+      if (b >= a) mask |= ((b - a + 1 >= 64) ? ~0ull : ((1ull << (b - a + 1)) - 1ull)) << ((ty - fp.ty0) * w + (a - fp.tx0));
+    }
     count = __popcll(mask);
     if (count == 0) return 0;
-    // super-tiles of the rect (conservative: one whose sub-mask turns out empty just expands to nothing)
-    int ns = (fp.tx1 / GS_SUPER - fp.tx0 / GS_SUPER + 1) * (fp.ty1 / GS_SUPER - fp.ty0 / GS_SUPER + 1);
     rec = make_uint4((uint32_t)fp.tx0 | ((uint32_t)fp.ty0 << 16), (uint32_t)w | ((uint32_t)h << 8) | ((uint32_t)ns << 16),
                      (uint32_t)mask, (uint32_t)(mask >> 32));
   } else {
-    for (int ty = fp.ty0; ty <= fp.ty1; ++ty)
-      for (int tx = fp.tx0; tx <= fp.tx1; ++tx)
-        count += tile_hit(fp, tx, ty, W, H) ? 1 : 0;
+    for (int ty = fp.ty0; ty <= fp.ty1; ++ty) {
+      int a, b;
+      row_span(fp, ty, H, a, b);
+      count += max(0, b - a + 1);
+    }
     if (count == 0) return 0;
-    int ns = (fp.tx1 / GS_SUPER - fp.tx0 / GS_SUPER + 1) * (fp.ty1 / GS_SUPER - fp.ty0 / GS_SUPER + 1);
     rec = make_uint4((uint32_t)fp.tx0 | ((uint32_t)fp.ty0 << 16), ((uint32_t)ns << 16) | GS_REC_BIG, 0u, 0u);
   }
   return count;

@@ -214,28 +214,35 @@ __global__ void __launch_bounds__(128) k_project_fwd(CamDev cam, CfgDev cfg, int
   }
 }
 
+// one row of the projection / SH backward
 template <int DEG>
-__global__ void __launch_bounds__(128) k_project_bwd(CamDev cam, CfgDev cfg, int64_t n, const float *__restrict__ position,
-                                                     const float *__restrict__ log_scaling, const float *__restrict__ rotation,
-                                                     const float *__restrict__ alpha_logit, const float *__restrict__ sh,
-                                                     const float *__restrict__ g2d, const float *__restrict__ d_g2d,
-                                                     int d_g2d_stride, const float *__restrict__ d_rgb, int d_rgb_stride,
-                                                     const float *__restrict__ d_depth, const float *__restrict__ row_vis,
-                                                     int row_vis_stride, float *__restrict__ g_position,
-                                                     float *__restrict__ g_log_scaling, float *__restrict__ g_rotation,
-                                                     float *__restrict__ g_alpha_logit, float *__restrict__ g_sh, int accumulate) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  if (row_vis && !(row_vis[(int64_t)row_vis_stride * i] > 0.f)) return;  // blended by no pixel (contiguous plane: test first)
-  if (!(g2d[GS_G2D_STRIDE * i + 5] > 0.f)) return;  // culled in forward
+__device__ __forceinline__ void project_bwd_row(const CamDev &cam, const CfgDev &cfg, int64_t i, const float *__restrict__ position,
+                                                const float *__restrict__ log_scaling, const float *__restrict__ rotation,
+                                                const float *__restrict__ alpha_logit, const float *__restrict__ sh,
+                                                const float *__restrict__ d_g2d, int d_g2d_stride,
+                                                const float *__restrict__ d_rgb, int d_rgb_stride,
+                                                const float *__restrict__ d_depth, float *__restrict__ g_position,
+                                                float *__restrict__ g_log_scaling, float *__restrict__ g_rotation,
+                                                float *__restrict__ g_alpha_logit, float *__restrict__ g_sh, int accumulate) {
+  // every load of the row is issued up front (rows are scattered over GBs of planes: each access is a full DRAM +
+  // TLB round trip, and the few rows with work leave no other warps to hide it behind)
+  constexpr int KK = (DEG + 1) * (DEG + 1);
   float px = position[3 * i], py = position[3 * i + 1], pz = position[3 * i + 2];
-  Proj t;
+  float ls0 = log_scaling[3 * i], ls1 = log_scaling[3 * i + 1], ls2 = log_scaling[3 * i + 2];
+  float al = alpha_logit[i];
   float4 q = reinterpret_cast<const float4 *>(rotation)[i];
-  if (!project_one(cam, cfg, px, py, pz, log_scaling[3 * i], log_scaling[3 * i + 1], log_scaling[3 * i + 2], q,
-                   alpha_logit[i], t))
-    return;
   const float *dg = d_g2d + (int64_t)d_g2d_stride * i;
   float d_u = dg[0], d_v = dg[1], d_ca = dg[2], d_cb = dg[3], d_cc = dg[4], d_op = dg[5];
+  float dc_pre[3] = {0.f, 0.f, 0.f};
+  float shv[3 * KK];
+  if (sh && d_rgb) {
+    const float *dr = d_rgb + (int64_t)d_rgb_stride * i;
+    dc_pre[0] = dr[0]; dc_pre[1] = dr[1]; dc_pre[2] = dr[2];
+    load_sh_row<KK>(sh + (int64_t)3 * KK * i, shv);
+  }
+  float dd = d_depth ? d_depth[i] : 0.f;
+  Proj t;
+  if (!project_one(cam, cfg, px, py, pz, ls0, ls1, ls2, q, al, t)) return;
   // conic -> covariance: S = -C G C
   float Ga = d_ca, Gb = 0.5f * d_cb, Gc = d_cc;
   float M00 = t.ca * Ga + t.cb * Gb, M01 = t.ca * Gb + t.cb * Gc;
@@ -301,23 +308,21 @@ __global__ void __launch_bounds__(128) k_project_bwd(CamDev cam, CfgDev cfg, int
   g_ty += cam.fy * d_v;
   float g_x = g_tx * iz, g_y = g_ty * iz;
   g_z += -(g_tx * t.tx + g_ty * t.ty) * iz;
-  if (d_depth) g_z += d_depth[i];
+  g_z += dd;
   float gp[3];
 #pragma unroll
   for (int k = 0; k < 3; ++k) gp[k] = T[k] * g_x + T[4 + k] * g_y + T[8 + k] * g_z;
 
   if (sh && d_rgb) {
-    constexpr int K = (DEG + 1) * (DEG + 1);
-    const float *dr = d_rgb + (int64_t)d_rgb_stride * i;
-    float dc[3] = {dr[0], dr[1], dr[2]};
+    constexpr int K = KK;
+    const float dc[3] = {dc_pre[0], dc_pre[1], dc_pre[2]};
     float dx = px - cam.cam_pos[0], dy = py - cam.cam_pos[1], dz = pz - cam.cam_pos[2];
     float len = sqrtf(dx * dx + dy * dy + dz * dz);
     float inv = len > 0.f ? 1.0f / len : 0.f;
     float nx = dx * inv, ny = dy * inv, nz = dz * inv;
     float Y[16];
     sh_basis<DEG>(nx, ny, nz, Y);
-    float v[3 * K];
-    load_sh_row<K>(sh + (int64_t)3 * K * i, v);
+    const float *v = shv;
     float wk[16];
 #pragma unroll
     for (int k = 0; k < K; ++k) wk[k] = v[k] * dc[0] + v[K + k] * dc[1] + v[2 * K + k] * dc[2];
@@ -361,6 +366,43 @@ __global__ void __launch_bounds__(128) k_project_bwd(CamDev cam, CfgDev cfg, int
     reinterpret_cast<float4 *>(g_rotation)[i] = make_float4(gq[0], gq[1], gq[2], gq[3]);
     g_alpha_logit[i] = gal;
   }
+}
+
+// Block-compacted backward: a block first collects the rows of its slice that have work (blended by a pixel /
+// in view) into shared memory — in a trained scene only a few percent of the rows are — and then its threads walk
+// that dense list, so warps stay full instead of dragging one active lane each through ~60 scattered accesses.
+constexpr int PB_THREADS = 128;
+constexpr int PB_ITEMS = 8;
+constexpr int PB_ROWS = PB_THREADS * PB_ITEMS;
+
+template <int DEG>
+__global__ void __launch_bounds__(PB_THREADS) k_project_bwd(CamDev cam, CfgDev cfg, int64_t n, const float *__restrict__ position,
+                                                            const float *__restrict__ log_scaling, const float *__restrict__ rotation,
+                                                            const float *__restrict__ alpha_logit, const float *__restrict__ sh,
+                                                            const float *__restrict__ g2d, const float *__restrict__ d_g2d,
+                                                            int d_g2d_stride, const float *__restrict__ d_rgb, int d_rgb_stride,
+                                                            const float *__restrict__ d_depth, const float *__restrict__ row_vis,
+                                                            int row_vis_stride, float *__restrict__ g_position,
+                                                            float *__restrict__ g_log_scaling, float *__restrict__ g_rotation,
+                                                            float *__restrict__ g_alpha_logit, float *__restrict__ g_sh, int accumulate) {
+  __shared__ int s_list[PB_ROWS];
+  __shared__ int s_count;
+  if (threadIdx.x == 0) s_count = 0;
+  __syncthreads();
+  int64_t base = (int64_t)blockIdx.x * PB_ROWS;
+#pragma unroll
+  for (int k = 0; k < PB_ITEMS; ++k) {
+    int64_t i = base + k * PB_THREADS + threadIdx.x;
+    if (i >= n) continue;
+    if (row_vis && !(row_vis[(int64_t)row_vis_stride * i] > 0.f)) continue;  // blended by no pixel (contiguous plane: test first)
+    if (!(g2d[GS_G2D_STRIDE * i + 5] > 0.f)) continue;                       // culled in forward
+    s_list[atomicAdd(&s_count, 1)] = (int)(i - base);
+  }
+  __syncthreads();
+  int cnt = s_count;
+  for (int k = threadIdx.x; k < cnt; k += PB_THREADS)
+    project_bwd_row<DEG>(cam, cfg, base + s_list[k], position, log_scaling, rotation, alpha_logit, sh, d_g2d, d_g2d_stride,
+                         d_rgb, d_rgb_stride, d_depth, g_position, g_log_scaling, g_rotation, g_alpha_logit, g_sh, accumulate);
 }
 
 // ---- evaluate_sh_at -------------------------------------------------------------------------------
@@ -456,8 +498,8 @@ extern "C" int gs_project_bwd(const gs_camera *h_cam, const gs_raster_config *h_
   CamDev cam = gs_make_cam(h_cam, h_cfg);
   CfgDev cfg = gs_make_cfg(h_cfg);
   cudaStream_t st = (cudaStream_t)stream;
-  int blocks = gs_div_up(n, 128);
-  GS_DISPATCH_DEG(sh_degree, (k_project_bwd<D><<<blocks, 128, 0, st>>>(cam, cfg, n, position, log_scaling, rotation,
+  int blocks = gs_div_up(n, PB_ROWS);
+  GS_DISPATCH_DEG(sh_degree, (k_project_bwd<D><<<blocks, PB_THREADS, 0, st>>>(cam, cfg, n, position, log_scaling, rotation,
                                                                         alpha_logit, sh, g2d, d_g2d, d_g2d_stride, d_rgb,
                                                                         d_rgb_stride, d_depth, row_vis, row_vis_stride,
                                                                         g_position, g_log_scaling, g_rotation, g_alpha_logit, g_sh, accumulate)));

@@ -41,6 +41,7 @@ class Trainer:
     self.world_size, self.rank = world_size, rank
     self.step_count = 0
     self._dev_target = None
+    self._grads_clean = False  # unknown history of scene.grads until the first step has run
 
   def _to_device(self, image):
     """host (pinned) uint8/float image -> reusable device buffer, async on the current stream
@@ -66,12 +67,13 @@ class Trainer:
     scene = self.scene
     mine = batch[self.rank::self.world_size]
     total = None
-    for cam, image in mine:
-      sums = scene.forward_backward(cam, self._to_device(image))
+    for k, (cam, image) in enumerate(mine):
+      sums = scene.forward_backward(cam, self._to_device(image), first=(k == 0 and self._grads_clean))
       total = sums.clone() if total is None else total + sums
     self.step_count += len(batch)  # the reference counts images, trainer/trainer.py:532
     self.exchange_gradients()
     scene.step()
+    self._grads_clean = True  # scene.step() cleared every gradient row it consumed
     if read_loss:
       return [float(x) for x in total.cpu().tolist()] if total is not None else [0.0, 0.0]
     return total
