@@ -289,8 +289,12 @@ def run_b200(args):
   achieved = bytes_[dom] / (dom_ms * 1e-3) / 1e9
   iter_bytes = sum(bytes_.values())
   ms_step = ms / args.steps
-  tile_bits = max(1, (T - 1).bit_length())
-  launches_image = 1 + (1 + 4 * 5 + 3 + 1 + 1 + ((tile_bits + 7) // 8) * 5 + 1) + 1 + 1 + 1 + 1 + 1
+  # kernels of libgsb200 per image: project_fwd, tile map (live compaction, depth sort = histogram + 4 passes,
+  # super-tile pairs, their sort = histogram + passes, segment tables, expand count, chunk prefix, expand write),
+  # raster_fwd, loss, raster_bwd, project_bwd, statistics; per step: optimiser begin + 5 parameter groups
+  n_super = ((W + 127) // 128) * ((H + 127) // 128)
+  super_passes = (max(1, (n_super - 1).bit_length()) + 7) // 8
+  launches_image = 1 + (1 + 5 + 1 + 1 + super_passes + 4) + 5
   launches = launches_image + 6
 
   if rank == 0:
