@@ -1,0 +1,96 @@
+"""Camera-batch data parallelism, host logic, world_size 2 over gloo on CPU.
+
+The kernels need a GPU, so the scene is a stub with the SplatScene surface the Trainer touches (grads / visible /
+forward_backward / step); what is checked is the Trainer's own logic: rank r takes batch[r::world], gradients and the
+`visible` plane are SUMMED (not averaged: the reference accumulates .grad over the batch, trainer/trainer.py:500-514),
+every rank ends the step with identical parameters, equal to the sequential single-process result, and the image counter
+advances by len(batch) (trainer/trainer.py:532)."""
+import os
+import socket
+import sys
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "splat-trainer_b200"))
+
+N, D = 64, 5
+
+
+class StubScene:
+  """parameters (N,D); image k contributes gradient rows only where its 'camera' sees them."""
+  device = torch.device("cpu")
+
+  def __init__(self):
+    self.params = torch.arange(N * D, dtype=torch.float32).reshape(N, D) / 10.0
+    self.grads = torch.zeros(N * D + N)  # packed gradients + `visible` at the tail (one collective moves both)
+    self.visible = self.grads[N * D:]
+    self.seen = []
+
+  def _mark(self, name):
+    pass
+
+  def forward_backward(self, cam, image, first=False):
+    k = int(cam)
+    rows = torch.arange(N)[(torch.arange(N) + k) % 3 == 0]
+    g = self.grads[:N * D].view(N, D)
+    if first:
+      assert float(self.grads.abs().sum()) == 0.0, "first image of a step must find a clean gradient buffer"
+    g[rows] += (k + 1) * image.float().mean() * torch.ones(D)
+    self.visible[rows] += 0.25 * (k + 1)
+    self.seen.append(k)
+    return torch.tensor([float(k), float(k * k)])
+
+  def step(self):
+    g = self.grads[:N * D].view(N, D)
+    vis = self.visible > 0
+    self.params[vis] -= 0.1 * g[vis] / self.visible[vis].unsqueeze(1)
+    self.grads.zero_()
+
+
+def run_step(world, rank, batch):
+  from gsb200.trainer import Trainer
+  scene = StubScene()
+  tr = Trainer(scene, world, rank)
+  losses = [tr.training_step(b) for b in batch]
+  return scene, tr, losses
+
+
+def make_batches():
+  g = torch.Generator().manual_seed(0)
+  images = [torch.randint(0, 255, (4, 4, 3), generator=g, dtype=torch.uint8) for _ in range(8)]
+  return [[(k, images[k]) for k in range(0, 4)], [(k, images[k]) for k in range(4, 8)]]
+
+
+def worker(rank, world, port, out):
+  os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+  dist.init_process_group("gloo", rank=rank, world_size=world)
+  scene, tr, losses = run_step(world, rank, make_batches())
+  torch.save(dict(params=scene.params, seen=scene.seen, steps=tr.step_count, losses=[l.tolist() for l in losses]),
+             os.path.join(out, f"rank{rank}.pt"))
+  dist.destroy_process_group()
+
+
+def free_port():
+  with socket.socket() as s:
+    s.bind(("127.0.0.1", 0))
+    return s.getsockname()[1]
+
+
+def test_two_ranks_equal_sequential(tmp_path):
+  world = 2
+  mp.spawn(worker, args=(world, free_port(), str(tmp_path)), nprocs=world, join=True)
+  r = [torch.load(os.path.join(tmp_path, f"rank{k}.pt")) for k in range(world)]
+  seq_scene, seq_tr, _ = run_step(1, 0, make_batches())
+  # sharding: rank r renders batch[r::world] of every step
+  assert r[0]["seen"] == [0, 2, 4, 6] and r[1]["seen"] == [1, 3, 5, 7]
+  assert sorted(r[0]["seen"] + r[1]["seen"]) == seq_scene.seen
+  # SUM semantics: both ranks hold the sequential result
+  assert torch.allclose(r[0]["params"], seq_scene.params, rtol=0, atol=1e-5)
+  assert torch.equal(r[0]["params"], r[1]["params"])
+  # the step counter counts images of the whole batch on every rank
+  assert r[0]["steps"] == r[1]["steps"] == seq_tr.step_count == 8
+  # per-rank losses are the sums over the rank's own images
+  assert r[0]["losses"][0] == [0.0 + 2.0, 0.0 + 4.0] and r[1]["losses"][0] == [1.0 + 3.0, 1.0 + 9.0]
