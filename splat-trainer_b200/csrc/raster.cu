@@ -11,6 +11,7 @@
 // 12 lanes, which issue one coalesced vector of fp32 reductions (RED) per (warp, splat) — instead
 // of 12 x 5 butterfly shuffles and 12 separate atomics.  No tensor cores: FMA/SFU/LSU bound.
 #include "common.cuh"
+#include "footprint.cuh"  // det_logf
 
 constexpr int RT = 64;  // threads per tile
 constexpr float LOG2E = 1.4426950408889634f;
@@ -54,19 +55,38 @@ __device__ __forceinline__ int64_t pixel_index(int p, int W, int TX) {
 }
 
 // stage one splat record into shared memory (conic pre-scaled for exp2)
+// Returns the (slightly loosened) half-height of the splat's support {alpha >= thr} around its mean row: used only to
+// skip whole warps (16x8 pixel halves of the tile) the splat cannot reach; the exact per-pixel test still decides.
 template <int C>
-__device__ __forceinline__ void stage_splat(int slot, int id, const float *__restrict__ g2d, const float *__restrict__ feat,
-                                            float thr, float4 *sA, float4 *sB, float (*sF)[RT]) {
+__device__ __forceinline__ float stage_splat(int slot, int id, const float *__restrict__ g2d, const float *__restrict__ feat,
+                                             float thr, float4 *sA, float4 *sB, float (*sF)[RT]) {
   const float2 *g = reinterpret_cast<const float2 *>(g2d + (int64_t)GS_G2D_STRIDE * id);
   float2 a = __ldg(g), b = __ldg(g + 1), c = __ldg(g + 2);
   float op = c.y;
-  // alpha >= thr  <=>  p' >= log2(thr/op); loosen slightly so the exact alpha test below decides
-  float pmin = (op > 0.f) ? (log2f(thr / op) - 1.0e-3f) : 1.0f;
-  sA[slot] = make_float4(a.x, a.y, -0.5f * LOG2E * b.x, -LOG2E * b.y);
-  sB[slot] = make_float4(-0.5f * LOG2E * c.x, op, pmin, __int_as_float(id));
+  // Spec R blend test, decided in the exponent domain with IEEE round-to-nearest ops only (bit-identical in the
+  // oracle): a pixel blends iff pcut <= p' <= 0, p' = log2(e)·power, pcut = log2(thr/op)  (<=> op·exp(power) >= thr)
+  float pcut = (op > 0.f) ? __fmul_rn(det_logf(__fdiv_rn(thr, op)), LOG2E) : 1.0f;
+  sA[slot] = make_float4(a.x, a.y, __fmul_rn(-0.5f * LOG2E, b.x), __fmul_rn(-LOG2E, b.y));
+  sB[slot] = make_float4(__fmul_rn(-0.5f * LOG2E, c.x), op, pcut, __int_as_float(id));
   const float *f = feat + (int64_t)C * id;
 #pragma unroll
   for (int ch = 0; ch < C; ++ch) sF[ch][slot] = __ldg(f + ch);
+  // y half-extent of {q <= k2}: sqrt(k2 * Sigma_yy), Sigma_yy = ca / det(conic), k2 = 2 ln(op/thr) = -2 ln2 pcut
+  float det = b.x * c.x - b.y * b.y;
+  float k2 = fmaxf(-2.0f * LN2 * pcut, 0.f);
+  return (det > 0.f) ? sqrtf(k2 * b.x / det) * 1.001f + 0.01f : 3.0e38f;
+}
+
+// per-warp candidate mask of a staged batch: bit k set iff staged splat k can reach this warp's 8 pixel rows
+__device__ __forceinline__ void publish_masks(bool staged, float my, float ey, float row0, unsigned (*s_mask)[2]) {
+  // warp r covers pixel-centre rows row0 + 8r + 0.5 .. row0 + 8r + 7.5
+  bool t0 = staged && (my + ey >= row0 + 0.5f) && (my - ey <= row0 + 7.5f);
+  bool t1 = staged && (my + ey >= row0 + 8.5f) && (my - ey <= row0 + 15.5f);
+  unsigned m0 = __ballot_sync(GS_FULL, t0), m1 = __ballot_sync(GS_FULL, t1);
+  if ((threadIdx.x & 31) == 0) {
+    s_mask[0][threadIdx.x >> 5] = m0;
+    s_mask[1][threadIdx.x >> 5] = m1;
+  }
 }
 
 template <int C, bool VIS, bool MEDIAN>
@@ -80,7 +100,10 @@ __global__ void __launch_bounds__(RT) k_raster_fwd(CfgDev cfg, const float *__re
   __shared__ float4 sB[RT];
   __shared__ float sF[C][RT];
   __shared__ float sD[MEDIAN ? RT : 1];
+  __shared__ unsigned s_mask[2][2];
   TileCtx tc = tile_ctx(ranges, W, H, TX);
+  const int wid = threadIdx.x >> 5;
+  const float row0 = (float)((blockIdx.x / TX) * GS_TILE);
   float T[4] = {1.f, 1.f, 1.f, 1.f};
   float col[4][C];
   float med[4] = {0.f, 0.f, 0.f, 0.f};
@@ -98,37 +121,40 @@ __global__ void __launch_bounds__(RT) k_raster_fwd(CfgDev cfg, const float *__re
     bool all_done = done[0] && done[1] && done[2] && done[3];
     if (__syncthreads_and(all_done)) break;  // also orders the previous batch's reads before the new writes
     int j = base + threadIdx.x;
+    float ey = 0.f, my = 0.f;
     if (j < tc.n) {
       int id = o2p[tc.begin + j];
-      stage_splat<C>(threadIdx.x, id, g2d, feat, cfg.thr, sA, sB, sF);
+      ey = stage_splat<C>(threadIdx.x, id, g2d, feat, cfg.thr, sA, sB, sF);
+      my = sA[threadIdx.x].y;
       if (MEDIAN) sD[threadIdx.x] = depth[id];
     }
+    publish_masks(j < tc.n, my, ey, row0, s_mask);
     __syncthreads();
-    int cnt = min(RT, tc.n - base);
-    for (int k = 0; k < cnt; ++k) {
+    unsigned long long cand = (unsigned long long)s_mask[wid][0] | ((unsigned long long)s_mask[wid][1] << 32);
+    while (cand) {
       if (!VIS && all_done) break;
+      int k = __ffsll((long long)cand) - 1;
+      cand &= cand - 1;
       float4 A = sA[k], B = sB[k];
       float dx[2] = {fx[0] - A.x, fx[1] - A.x}, dy[2] = {fy[0] - A.y, fy[1] - A.y};
-      float ax[2] = {A.z * dx[0] * dx[0], A.z * dx[1] * dx[1]};
-      float cy[2] = {B.x * dy[0] * dy[0], B.x * dy[1] * dy[1]};
-      float bx[2] = {A.w * dx[0], A.w * dx[1]};
+      float ax[2] = {__fmul_rn(__fmul_rn(A.z, dx[0]), dx[0]), __fmul_rn(__fmul_rn(A.z, dx[1]), dx[1])};
+      float cy[2] = {__fmul_rn(__fmul_rn(B.x, dy[0]), dy[0]), __fmul_rn(__fmul_rn(B.x, dy[1]), dy[1])};
+      float bx[2] = {__fmul_rn(A.w, dx[0]), __fmul_rn(A.w, dx[1])};
       float vsum = 0.f;
 #pragma unroll
       for (int p = 0; p < 4; ++p) {
-        float pw = ax[p & 1] + cy[p >> 1] + bx[p & 1] * dy[p >> 1];
+        float pw = __fmaf_rn(bx[p & 1], dy[p >> 1], __fadd_rn(ax[p & 1], cy[p >> 1]));
         if (!done[p] && pw <= 0.f && pw >= B.z) {
           float a = fminf(cfg.amax, B.y * ex2_approx(pw));
-          if (a >= cfg.thr) {
-            float w = a * T[p];
+          float w = a * T[p];
 #pragma unroll
-            for (int ch = 0; ch < C; ++ch) col[p][ch] += w * sF[ch][k];
-            float Tn = T[p] * (1.0f - a);
-            if (MEDIAN && T[p] >= 0.5f && Tn < 0.5f) med[p] = sD[k];
-            T[p] = Tn;
-            last[p] = base + k + 1;
-            if (Tn < cfg.tmin) done[p] = true;
-            vsum += w;
-          }
+          for (int ch = 0; ch < C; ++ch) col[p][ch] += w * sF[ch][k];
+          float Tn = T[p] * (1.0f - a);
+          if (MEDIAN && T[p] >= 0.5f && Tn < 0.5f) med[p] = sD[k];
+          T[p] = Tn;
+          last[p] = base + k + 1;
+          if (Tn < cfg.tmin) done[p] = true;
+          vsum += w;
         }
       }
       if (VIS) {
@@ -224,7 +250,10 @@ __global__ void __launch_bounds__(RT) k_raster_bwd(CfgDev cfg, const float *__re
   __shared__ float4 sB[RT];
   __shared__ float sF[C][RT];
   __shared__ int s_max[RT / 32];
+  __shared__ unsigned s_mask[2][2];
   TileCtx tc = tile_ctx(ranges, W, H, TX);
+  const int wid = threadIdx.x >> 5;
+  const float row0 = (float)((blockIdx.x / TX) * GS_TILE);
   float T[4], last_a[4] = {0.f, 0.f, 0.f, 0.f};
   // per pixel: dL/dC and the SCALAR projections onto it of the colour composited behind the current splat (R) and of
   // the last blended splat's colour (lastq): dL/dα needs only (f − rec)·dL/dC, so the per-channel recurrence of the
@@ -259,57 +288,65 @@ __global__ void __launch_bounds__(RT) k_raster_bwd(CfgDev cfg, const float *__re
   for (; top > 0; top -= RT) {
     int lo = max(0, top - RT), cnt = top - lo;
     __syncthreads();
+    float ey = 0.f, my = 0.f;
     if ((int)threadIdx.x < cnt) {
       int id = o2p[tc.begin + lo + threadIdx.x];
-      stage_splat<C>(threadIdx.x, id, g2d, feat, cfg.thr, sA, sB, sF);
+      ey = stage_splat<C>(threadIdx.x, id, g2d, feat, cfg.thr, sA, sB, sF);
+      my = sA[threadIdx.x].y;
     }
+    publish_masks((int)threadIdx.x < cnt, my, ey, row0, s_mask);
     __syncthreads();
-    for (int k = cnt - 1; k >= 0; --k) {
+    unsigned long long cand = (unsigned long long)s_mask[wid][0] | ((unsigned long long)s_mask[wid][1] << 32);
+    {  // this warp's own pixels stop at wmax: later list positions cannot contribute to it
+      int wn = wmax - lo;
+      if (wn < RT) cand &= (wn > 0) ? ((1ull << wn) - 1ull) : 0ull;
+    }
+    while (cand) {
+      int k = 63 - __clzll((long long)cand);
+      cand ^= 1ull << k;
       int pos = lo + k;
       float4 A = sA[k], B = sB[k];
       float dx[2] = {fx[0] - A.x, fx[1] - A.x}, dy[2] = {fy[0] - A.y, fy[1] - A.y};
-      float ax[2] = {A.z * dx[0] * dx[0], A.z * dx[1] * dx[1]};
-      float cy[2] = {B.x * dy[0] * dy[0], B.x * dy[1] * dy[1]};
-      float bx[2] = {A.w * dx[0], A.w * dx[1]};
+      float ax[2] = {__fmul_rn(__fmul_rn(A.z, dx[0]), dx[0]), __fmul_rn(__fmul_rn(A.z, dx[1]), dx[1])};
+      float cy[2] = {__fmul_rn(__fmul_rn(B.x, dy[0]), dy[0]), __fmul_rn(__fmul_rn(B.x, dy[1]), dy[1])};
+      float bx[2] = {__fmul_rn(A.w, dx[0]), __fmul_rn(A.w, dx[1])};
       float v[NV];
 #pragma unroll
       for (int i = 0; i < NV; ++i) v[i] = 0.f;
       bool touched = false;
 #pragma unroll
       for (int p = 0; p < 4; ++p) {
-        float pw = ax[p & 1] + cy[p >> 1] + bx[p & 1] * dy[p >> 1];
+        float pw = __fmaf_rn(bx[p & 1], dy[p >> 1], __fadd_rn(ax[p & 1], cy[p >> 1]));
         if (pos < nc[p] && pw <= 0.f && pw >= B.z) {
           float G = ex2_approx(pw);
           float a = B.y * G;
           bool clamped = a > cfg.amax;
           a = fminf(a, cfg.amax);
-          if (a >= cfg.thr) {
-            touched = true;
-            float Tp = __fdividef(T[p], 1.0f - a);
-            T[p] = Tp;
-            float w = a * Tp;
-            float q = 0.f;
+          touched = true;
+          float Tp = __fdividef(T[p], 1.0f - a);
+          T[p] = Tp;
+          float w = a * Tp;
+          float q = 0.f;
 #pragma unroll
-            for (int ch = 0; ch < C; ++ch) {
-              q += sF[ch][k] * dC[p][ch];
-              v[6 + ch] += w * dC[p][ch];
-            }
-            R[p] = last_a[p] * lastq[p] + (1.0f - last_a[p]) * R[p];
-            lastq[p] = q;
-            float dLda = (q - R[p]) * Tp;
-            last_a[p] = a;
-            v[8 + C] += w;
-            v[6 + C] += fabsf(a * dLda);
-            if (!clamped) {
-              float ddx = dx[p & 1], ddy = dy[p >> 1];
-              float dp = B.y * dLda * G * LN2;  // dL/dp', p' = log2(e)·power
-              float gx = -dp * (2.0f * A.z * ddx + A.w * ddy);
-              float gy = -dp * (2.0f * B.x * ddy + A.w * ddx);
-              v[0] += gx; v[1] += gy;
-              v[2] += dp * ddx * ddx; v[3] += dp * ddx * ddy; v[4] += dp * ddy * ddy;
-              v[5] += G * dLda;
-              v[7 + C] += fabsf(gx) + fabsf(gy);
-            }
+          for (int ch = 0; ch < C; ++ch) {
+            q += sF[ch][k] * dC[p][ch];
+            v[6 + ch] += w * dC[p][ch];
+          }
+          R[p] = last_a[p] * lastq[p] + (1.0f - last_a[p]) * R[p];
+          lastq[p] = q;
+          float dLda = (q - R[p]) * Tp;
+          last_a[p] = a;
+          v[8 + C] += w;
+          v[6 + C] += fabsf(a * dLda);
+          if (!clamped) {
+            float ddx = dx[p & 1], ddy = dy[p >> 1];
+            float dp = B.y * dLda * G * LN2;  // dL/dp', p' = log2(e)·power
+            float gx = -dp * (2.0f * A.z * ddx + A.w * ddy);
+            float gy = -dp * (2.0f * B.x * ddy + A.w * ddx);
+            v[0] += gx; v[1] += gy;
+            v[2] += dp * ddx * ddx; v[3] += dp * ddx * ddy; v[4] += dp * ddy * ddy;
+            v[5] += G * dLda;
+            v[7 + C] += fabsf(gx) + fabsf(gy);
           }
         }
       }

@@ -34,7 +34,7 @@ def _setup(W, H, n, seed, channels=3, scale=0.1, sh_degree=3, **cfgkw):
 
 
 @pytest.mark.parametrize("channels", [1, 3, 4])
-@pytest.mark.parametrize("size,n", [((96, 64), 600), ((101, 75), 3000), ((320, 240), 20000)])
+@pytest.mark.parametrize("size,n", [((96, 64), 600), ((101, 75), 3000), ((320, 240), 20000), ((640, 480), 100000)])
 def test_raster_fwd_matches_oracle(channels, size, n):
   W, H = size
   s = _setup(W, H, n, seed=30, channels=channels)
@@ -44,16 +44,14 @@ def test_raster_fwd_matches_oracle(channels, size, n):
                                                      npy(s["o2p"])[:s["total"]], npy(s["ranges"]), W, H,
                                                      visibility=True, median=True)
   image, fT, nc, vis, med = map(npy, (image, fT, nc, vis, med))
-  err = np.abs(image - rimage).max(axis=-1)
-  # a pixel whose alpha sits exactly on the 1/255 cut or the saturation stop may flip between exp() flavours
-  bad = err > IMG_TOL
-  assert bad.mean() < 2e-3, (bad.mean(), err.max())
-  assert err.max() < 2e-2
-  assert np.abs(fT - rfT)[~bad].max() < IMG_TOL
-  assert (nc != rnc).mean() < 5e-3
+  # the blend decision is taken in the exponent domain with IEEE ops shared by both sides (DESIGN.md "Spec R"), so no
+  # pixel may flip: strict max-abs over the whole image, identical contributor counts and median depths
+  assert np.abs(image - rimage).max() < IMG_TOL
+  assert np.abs(fT - rfT).max() < IMG_TOL
+  assert (nc != rnc).mean() < 1e-5
   scale = max(rvis.max(), 1.0)
-  assert np.abs(vis - rvis).max() / scale < 1e-3
-  assert ((med != rmed) & ~bad).mean() < 2e-3
+  assert np.abs(vis - rvis).max() / scale < 1e-4
+  assert (med != rmed).mean() < 1e-5
 
 
 def test_raster_fwd_no_visibility_early_exit_same_image():
@@ -146,8 +144,8 @@ def test_project_bwd_matches_oracle(antialias, sh_degree):
 
 def test_full_chain_matches_oracle_chain():
   """whole path params -> image -> grads on the GPU vs the whole path in the oracle (each with its own
-  intermediates).  Image within 1e-4; parameter gradients within 1e-4 of each column's range for 99.9 %
-  of the entries (rows whose cull/threshold decision sits on an fp32 rounding boundary excepted)."""
+  intermediates).  Image max-abs within 1e-4; parameter gradients within 1e-4 of each column's range for 99.9 %
+  of the entries (projection rounding can move a row across a cull boundary)."""
   W, H = 160, 120
   orc = oracle()
   cam = random_camera(W, H); cfg = go.make_config()
@@ -176,8 +174,7 @@ def test_full_chain_matches_oracle_chain():
   ops.raster_bwd(lcfg, g2d, rgb, o2p, ranges, W, H, fT, nc, dimg, acc=acc)
   grads = ops.project_bwd(lcam, lcfg, gc["position"], gc["log_scaling"], gc["rotation"], gc["alpha_logit"], gc["sh"], 3,
                           g2d, acc[:, 0:6], acc[:, 6:9], None, row_vis=acc[:, 11])
-  err = np.abs(npy(image) - rimage).max(axis=-1)
-  assert (err > IMG_TOL).mean() < 2e-3 and err.max() < 2e-2, ((err > IMG_TOL).mean(), err.max())
+  assert np.abs(npy(image) - rimage).max() < IMG_TOL
   np.testing.assert_allclose(npy(sums), rsums, rtol=1e-4)
   for name in ["position", "log_scaling", "rotation", "alpha_logit", "sh"]:
     a, r = npy(grads[name]).reshape(n, -1), rgrads[name].reshape(n, -1)
