@@ -40,6 +40,9 @@ def parse():
   ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
   ap.add_argument("--points", type=int, default=0, help="override the splat count (testing only)")
   ap.add_argument("--no-cpu-baseline", action="store_true")
+  ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl", "dense"],
+                  help="N>1 gradient/statistics exchange: per-image records over peer memory (auto/peer), records "
+                       "all-gathered by NCCL, or the dense SUM all-reduce of the packed gradient buffer")
   return ap.parse_args()
 
 
@@ -220,7 +223,7 @@ def run_b200(args):
   torch.cuda.empty_cache()
   dev_targets = [t.cuda() for t in host_targets]
   scene = SplatScene(g, SceneConfig(sh_degree=deg))
-  trainer = Trainer(scene, world, rank)
+  trainer = Trainer(scene, world, rank, exchange=args.exchange)
 
   def batch_for(i, targets):
     # the step's full batch has `world` images; only this rank's entry is materialised (others are None-padded)
@@ -242,6 +245,21 @@ def run_b200(args):
   if scene.overflowed():
     scene.grow_overlaps(2.0)
     step(0, dev_targets)
+  exchange_info = None
+  if trainer.exchange is not None:
+    # size the records from the rows the warm-up images really blended (one host read at start-up, all ranks agree)
+    rows = trainer.calibrate_exchange(margin=1.5)
+    for i in range(2):
+      step(i, dev_targets)
+    torch.cuda.synchronize()
+    ex = trainer.exchange
+    exchange_info = {"transport": ex.transport, "record_capacity_rows": ex.cap, "rows_per_image": rows,
+                     "bytes_read_per_peer_image": ex.bytes_per_image(rows),
+                     "dense_allreduce_bytes": int(scene.grads.numel() * 4)}
+    if getattr(ex, "fallback_reason", None):
+      exchange_info["peer_unavailable"] = ex.fallback_reason[:200]
+  elif world > 1:
+    exchange_info = {"transport": "dense-allreduce", "dense_allreduce_bytes": int(scene.grads.numel() * 4)}
 
   # ---- device-resident throughput (value) with per-stage CUDA events ----------------------------------------------
   timer = StageTimer()
@@ -296,6 +314,8 @@ def run_b200(args):
   super_passes = (max(1, (n_super - 1).bit_length()) + 7) // 8
   launches_image = 1 + (1 + 5 + 1 + 1 + super_passes + 4) + 5
   launches = launches_image + 6
+  if trainer.exchange is not None:
+    launches += 1 + 2  # pack = 2 kernels in place of the statistics pass; fold = 2 kernels (NCCL's own not counted)
 
   if rank == 0:
     line = {
@@ -321,6 +341,10 @@ def run_b200(args):
       "clocks": clocks.summary(),
       "last_loss_mse": loss[1] / (P * 3),
     }
+    if exchange_info:
+      if trainer.exchange is not None:
+        exchange_info["overflow"] = any(o for _, o in trainer.exchange.counts())
+      line["exchange"] = exchange_info
     if world == 1 and not args.no_cpu_baseline:
       cpu = CpuIteration(g, views[:1], [host_targets[0].numpy()], deg)
       cpu.iteration(0)  # warm-up (page faults, OpenMP pool)

@@ -286,6 +286,41 @@ int gs_split_positions(int64_t s, const int64_t *split_idx, const float *positio
 int gs_gather_rows(const void *src, void *dst, int64_t s, const int64_t *idx, int row_bytes,
                    int repeat, int64_t out_offset, void *stream);
 
+/* ---------------------------------------------------------------------------------------
+ * (6) Camera-batch data parallelism (new capability — the reference loops over the batch on one GPU,
+ *     trainer/trainer.py:500-514).  Every image's contribution (gradient rows of the splats a pixel blended,
+ *     their visibility and heuristics, and which rows were in view) is PACKED into one record; every rank then
+ *     FOLDS the records of all images of the step in image order, which reproduces the reference's sequential
+ *     `.grad` accumulation and PointState.add_rendering order (controller/point_state.py:34-50) on every replica.
+ *     Records may be local or peer-GPU (NVLink-mapped) memory.
+ * ------------------------------------------------------------------------------------- */
+#define GS_EXCHANGE_MAX_GROUPS 8
+#define GS_EXCHANGE_MAX_IMAGES 64
+typedef struct gs_exchange_groups {
+  int32_t count;                          /* parameter groups, in record-plane order            */
+  int32_t dim[GS_EXCHANGE_MAX_GROUPS];    /* floats per row of each group                       */
+  float *grad[GS_EXCHANGE_MAX_GROUPS];    /* n × dim dense gradient plane of each group         */
+} gs_exchange_groups;
+
+/* bytes of one record for n Gaussians, `cap` visible rows and row_floats = Σ dim floats per row */
+size_t gs_exchange_record_bytes(int64_t n, int64_t cap, int row_floats);
+size_t gs_exchange_pack_workspace_bytes(int64_t n);
+/* After one image's backward (gradient planes hold THIS image's rows only): updates the rank's own max_scale_px
+ * (order independent; MAX-reduced across ranks before a densification), writes the record, moves the gradient rows
+ * of the visible splats into it and zeroes them at the source, and clears the consumed accumulator rows like
+ * gs_accumulate_stats.  record[0] = visible count (int32), record[1] = overflow flag (count > cap: grow and redo). */
+int gs_exchange_pack(int64_t n, const float *g2d, const float *vis, int vis_stride, const float *heur,
+                     int heur_stride, float *max_scale_px, float *clear_acc, int clear_stride,
+                     float *clear_vis, const gs_exchange_groups *groups, void *record, int64_t cap,
+                     void *workspace, size_t workspace_bytes, void *stream);
+/* records: HOST array of n_images device (or peer) pointers, in image order.  Adds every record's rows into the
+ * gradient planes and folds the statistics: split_score / prune_cost by exp_lerp over in-view rows (0 for rows no
+ * pixel blended), points_in_view += 1, visibility += vis, scene_visible += vis for blended rows. */
+int gs_exchange_fold(int64_t n, int n_images, const void *const *records, int64_t cap,
+                     const gs_exchange_groups *groups, float split_alpha, float prune_alpha,
+                     float *prune_cost, float *split_score, int16_t *points_in_view, float *visibility,
+                     float *scene_visible, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,118 @@
+"""ImageExchange — the one exchange step of camera-batch data parallelism.
+
+Every rank packs what ITS images of the step contributed (gradient rows of the splats a pixel blended, their
+visibility / heuristics, in-view bit planes) into fixed-capacity records; then every rank folds the records of ALL
+images of the step in image order.  The fold reproduces the reference's sequential accumulation
+(trainer/trainer.py:500-514, controller/point_state.py:34-50) on every replica, so replicas stay bit-identical.
+
+Transport (the records are written once and read in place):
+  "peer"  records live in torch symmetric memory; after a stream-ordered NCCL barrier the fold kernels load the other
+          ranks' records straight over NVLink (no all-gather, no staging copy, only `count` rows move).  Records are
+          double-buffered by step parity so one barrier per step is enough.
+  "nccl"  plain buffers + one all_gather_into_tensor of the fixed-capacity records, folded from the local copy.
+  "local" world size 1 (or tests): records of several emulated ranks in one process.
+"""
+import torch
+import torch.distributed as dist
+
+from . import lib as L
+from . import ops
+
+ATTRS = ("position", "log_scaling", "rotation", "alpha_logit", "sh")
+
+
+class ImageExchange:
+  def __init__(self, scene, world=1, rank=0, cap=0, images_per_rank=1, transport="auto", group=None):
+    self.scene, self.world, self.rank, self.k = scene, world, rank, images_per_rank
+    self.group = group
+    self.n = scene.n
+    dev = scene.device
+    self.groups, self.row_floats = ops.exchange_groups([scene.g[a] for a in ATTRS])
+    # capacity: rows one image can blend; 0 = a quarter of the scene (grown on overflow, like max_overlaps)
+    self.cap = int(cap) if cap > 0 else max(4096, self.n // 4)
+    self.rec_bytes = ops.exchange_record_bytes(self.n, self.cap, self.row_floats)
+    self.workspace = torch.empty((int(L.load().gs_exchange_pack_workspace_bytes(self.n)),), device=dev, dtype=torch.uint8)
+    self.parity = 0
+    self.transport = transport
+    if transport == "auto":
+      self.transport = "peer" if world > 1 else "local"
+    slot_bytes = self.k * self.rec_bytes
+    if self.transport == "peer":
+      try:
+        import torch.distributed._symmetric_memory as symm
+        self.buf = symm.empty((2 * slot_bytes,), dtype=torch.uint8, device=dev)
+        self.handle = symm.rendezvous(self.buf, group or dist.group.WORLD)
+        self.peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        self.buf.zero_()
+      except Exception as e:  # symmetric memory unavailable on this box: NCCL all-gather transport (still GPU-only)
+        if transport == "peer":
+          raise
+        self.transport, self.fallback_reason = "nccl", repr(e)
+    if self.transport == "nccl":
+      self.buf = torch.zeros((slot_bytes,), device=dev, dtype=torch.uint8)
+      self.gathered = torch.zeros((world * slot_bytes,), device=dev, dtype=torch.uint8)
+    elif self.transport == "local":
+      self.buf = torch.zeros((slot_bytes,), device=dev, dtype=torch.uint8)
+    self._token = torch.zeros((1,), device=dev)
+    self._grads_ptr = scene.grads.data_ptr()
+
+  def stale(self):
+    """True once the scene re-allocated its packed buffers (densification): build a new ImageExchange."""
+    return self.n != self.scene.n or self._grads_ptr != self.scene.grads.data_ptr()
+
+  # ---- this rank's side ----------------------------------------------------------------------------------
+  def _local_offset(self, slot, parity=None):
+    parity = self.parity if parity is None else parity
+    base = parity * self.k * self.rec_bytes if self.transport == "peer" else 0
+    return base + slot * self.rec_bytes
+
+  def record(self, slot, parity=None):
+    o = self._local_offset(slot, parity)
+    return self.buf[o:o + self.rec_bytes]
+
+  def pack(self, slot, w, acc):
+    """after project_bwd of one image (scene.g holds that image's rows only): write record `slot`."""
+    scene = self.scene
+    ops.exchange_pack(w["g2d"], w["vis"], acc[:, 9:11], scene.stats["max_scale_px"], self.groups, self.record(slot),
+                      self.cap, self.workspace, clear_acc=acc, clear_vis=w["vis"])
+
+  # ---- the exchange --------------------------------------------------------------------------------------
+  def record_ptrs(self):
+    """addresses of the step's records in image order: image j = rank + world·slot (batch[rank::world])."""
+    out = []
+    for slot in range(self.k):
+      for r in range(self.world):
+        if self.transport == "peer":
+          out.append(self.peer_ptrs[r] + self._local_offset(slot))
+        elif self.transport == "nccl":
+          out.append(self.gathered.data_ptr() + r * self.k * self.rec_bytes + slot * self.rec_bytes)
+        else:
+          out.append(self.buf.data_ptr() + slot * self.rec_bytes)
+    return out
+
+  def fold(self, extra_ptrs=None):
+    """make every rank's records visible, then fold them in image order into scene.g / scene.visible / scene.stats."""
+    scene, c = self.scene, self.scene.config
+    if self.transport == "peer":
+      # stream-ordered NCCL barrier: every rank's pack kernels have completed before any rank's fold starts
+      dist.all_reduce(self._token, group=self.group)
+    elif self.transport == "nccl":
+      dist.all_gather_into_tensor(self.gathered, self.buf, group=self.group)
+    ptrs = extra_ptrs if extra_ptrs is not None else self.record_ptrs()
+    ops.exchange_fold(self.n, ptrs, self.cap, self.groups, c.split_alpha, c.prune_alpha, scene.stats,
+                      scene_visible=scene.visible)
+    if self.transport == "peer":
+      self.parity ^= 1
+
+  def counts(self):
+    """(visible rows, overflow flag) of this rank's records of the LAST folded step — host sync, off the hot path."""
+    out = []
+    for slot in range(self.k):
+      h = self.record(slot, self.parity ^ 1)[:8].view(torch.int32).cpu().tolist()
+      out.append((h[0], bool(h[1])))
+    return out
+
+  def bytes_per_image(self, count):
+    """bytes a peer actually reads of one record with `count` visible rows (the three bit/rank planes, idx, aux, rows)."""
+    words = (self.n + 31) // 32
+    return 8 + 3 * 4 * words + count * (4 + 16 + 4 * self.row_floats)

@@ -33,8 +33,17 @@ class OptimConfig(C.Structure):  # gs_optim_config
               ("bias_correction", C.c_int32)]
 
 
+GS_EXCHANGE_MAX_GROUPS, GS_EXCHANGE_MAX_IMAGES = 8, 64
+
+
+class ExchangeGroups(C.Structure):  # gs_exchange_groups
+  _fields_ = [("count", C.c_int32), ("dim", C.c_int32 * GS_EXCHANGE_MAX_GROUPS),
+              ("grad", C.c_void_p * GS_EXCHANGE_MAX_GROUPS)]
+
+
 _P, _I, _L, _F, _Z = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t
 _CAM, _CFG, _OPT = C.POINTER(Camera), C.POINTER(RasterConfig), C.POINTER(OptimConfig)
+_XG = C.POINTER(ExchangeGroups)
 
 # name -> (restype, argtypes); one entry per symbol declared in include/gsb200.h
 SIGNATURES = {
@@ -70,6 +79,10 @@ SIGNATURES = {
   "gs_compact_rows": (_I, [_P, _P, _L, _I, _P, _P]),
   "gs_split_positions": (_I, [_L, _P, _P, _P, _P, _P, _F, _P, _P, _L, _P]),
   "gs_gather_rows": (_I, [_P, _P, _L, _P, _I, _I, _L, _P]),
+  "gs_exchange_record_bytes": (_Z, [_L, _L, _I]),
+  "gs_exchange_pack_workspace_bytes": (_Z, [_L]),
+  "gs_exchange_pack": (_I, [_L, _P, _P, _I, _P, _I, _P, _P, _I, _P, _XG, _P, _L, _P, _Z, _P]),
+  "gs_exchange_fold": (_I, [_L, _I, C.POINTER(C.c_void_p), _L, _XG, _F, _F, _P, _P, _P, _P, _P, _P]),
 }
 
 _lib = None

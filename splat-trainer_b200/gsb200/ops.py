@@ -327,3 +327,41 @@ def gather_rows(src, dst, idx, repeat=1, out_offset=0):
   row_bytes = src.element_size() * (src.numel() // max(n, 1)) if n > 0 else src.element_size()
   L.check(L.load().gs_gather_rows(L.ptr(src), L.ptr(dst), s, L.ptr(idx), row_bytes, repeat, out_offset, L.stream()))
   return dst
+
+
+# ---- camera-batch data parallelism: per-image exchange records (include/gsb200.h section 6) ---------------------
+def exchange_groups(grad_planes):
+  """grad_planes: list of contiguous (n, ...) float32 CUDA tensors (one per parameter group, record-plane order)."""
+  g = L.ExchangeGroups()
+  assert 1 <= len(grad_planes) <= L.GS_EXCHANGE_MAX_GROUPS
+  g.count = len(grad_planes)
+  total = 0
+  for k, t in enumerate(grad_planes):
+    dim = int(t.numel() // t.shape[0])
+    g.dim[k] = dim
+    g.grad[k] = L.ptr(t)
+    total += dim
+  return g, total
+
+
+def exchange_record_bytes(n, cap, row_floats):
+  return int(L.load().gs_exchange_record_bytes(n, cap, row_floats))
+
+
+def exchange_pack(g2d, vis, heur, max_scale_px, groups, record, cap, workspace, clear_acc=None, clear_vis=None):
+  """record: uint8 CUDA tensor of >= exchange_record_bytes; vis (n,) / heur (n,2)-like strided views as in
+  accumulate_stats."""
+  n = g2d.shape[0]
+  L.check(L.load().gs_exchange_pack(n, L.ptr(g2d), vis.data_ptr(), vis.stride(0), heur.data_ptr(), heur.stride(0),
+                                    L.ptr(max_scale_px), L.ptr(clear_acc), 0 if clear_acc is None else clear_acc.shape[1],
+                                    L.ptr(clear_vis), C.byref(groups), record.data_ptr(), int(cap), L.ptr(workspace),
+                                    workspace.numel(), L.stream()))
+
+
+def exchange_fold(n, record_ptrs, cap, groups, split_alpha, prune_alpha, state, scene_visible=None):
+  """record_ptrs: device (or peer-mapped) addresses of the step's records in image order."""
+  arr = (C.c_void_p * len(record_ptrs))(*[int(p) for p in record_ptrs])
+  L.check(L.load().gs_exchange_fold(n, len(record_ptrs), arr, int(cap), C.byref(groups), split_alpha, prune_alpha,
+                                    L.ptr(state["prune_cost"]), L.ptr(state["split_score"]),
+                                    L.ptr(state["points_in_view"]), L.ptr(state["visibility"]), L.ptr(scene_visible),
+                                    L.stream()))

@@ -186,12 +186,14 @@ class SplatScene:
                 median_depth=med, g2d=w["g2d"], depth=w["depth"])
 
   # ---- one training image: forward + loss + backward + statistics ------------------------------------------
-  def forward_backward(self, cam, target, first=False):
+  def forward_backward(self, cam, target, first=False, exchange=None, slot=0):
     """Reference trainer/trainer.py:500-514 for one image (render → loss → backward → add_rendering), fused:
     gradients are ADDED into self.g (batch = sum), statistics into self.stats / self.visible.
     target: (H,W,3) float32 in [0,1] or uint8 on the device.  Returns loss_sums (device, 2): Σ|d|, Σd².
     first=True (the step's first image, gradient buffer all-zero: the optimiser clears the rows it consumes): rows are
-    WRITTEN instead of read-modified-written."""
+    WRITTEN instead of read-modified-written.
+    exchange (an ImageExchange, camera-batch DP): the image's gradient rows and statistics are packed into record
+    `slot` instead of being applied here; ImageExchange.fold() applies every rank's records in image order."""
     w, tb, _, _ = self._forward(cam)
     c = self.config
     w["loss_sums"].zero_()
@@ -204,8 +206,13 @@ class SplatScene:
     p = self.p
     ops.project_bwd(cam, self.raster_cfg, p["position"], p["log_scaling"], p["rotation"], p["alpha_logit"], p["sh"],
                     c.sh_degree, w["g2d"], acc[:, 0:6], acc[:, 6:9], None, row_vis=w["vis"], grads=self.g,
-                    accumulate=not first)
+                    accumulate=not (first or exchange is not None))
     self._mark("project_bwd")
+    if exchange is not None:
+      # the dense gradient buffer holds this image's rows only (pack moves them out and zeroes them again)
+      exchange.pack(slot, w, acc)
+      self._mark("pack")
+      return w["loss_sums"]
     # the statistics pass is the accumulator's last reader: it clears the rows this image touched, so `acc` / `vis`
     # are all-zero again for the next image without a 48·N-byte memset
     ops.accumulate_stats(None, w["g2d"], w["vis"], acc[:, 9:11], c.split_alpha, c.prune_alpha, self.stats,

@@ -36,12 +36,24 @@ class StageTimer:
 
 
 class Trainer:
-  def __init__(self, scene, world_size=1, rank=0):
+  def __init__(self, scene, world_size=1, rank=0, exchange="auto", exchange_cap=0, images_per_rank=1):
+    """exchange: "auto" (sparse per-image records over peer memory when world_size > 1), "peer", "nccl" (records
+    all-gathered with NCCL), "dense" (SUM all-reduce of the whole packed gradient buffer; statistics stay per rank)
+    or an ImageExchange instance."""
     self.scene = scene
     self.world_size, self.rank = world_size, rank
     self.step_count = 0
     self._dev_target = None
     self._grads_clean = False  # unknown history of scene.grads until the first step has run
+    self.exchange = None
+    if isinstance(exchange, str):
+      if world_size > 1 and exchange != "dense":
+        from .exchange import ImageExchange
+        scene.zero_grad()
+        self.exchange = ImageExchange(scene, world_size, rank, cap=exchange_cap, images_per_rank=images_per_rank,
+                                      transport=exchange)
+    else:
+      self.exchange = exchange
 
   def _to_device(self, image):
     """host (pinned) uint8/float image -> reusable device buffer, async on the current stream
@@ -56,9 +68,34 @@ class Trainer:
   def exchange_gradients(self):
     """SUM (not mean: reference accumulates .grad over the batch, trainer/trainer.py:500-514) of the packed
     gradient buffer; the tail plane carries `visible` so one collective moves both."""
-    if self.world_size > 1:
+    if self.exchange is not None:
+      self.exchange.fold()
+      self.scene._mark("exchange")
+    elif self.world_size > 1:
       dist.all_reduce(self.scene.grads, op=dist.ReduceOp.SUM)
-      self.scene._mark("allreduce")
+      self.scene._mark("exchange")
+
+  def calibrate_exchange(self, margin=1.5):
+    """size the exchange records from the rows the last step's images blended (max over ranks) × margin.  One host
+    read + one tiny collective, at start-up or after a densification; returns the measured rows per image."""
+    ex = self.exchange
+    rows = max(c for c, _ in ex.counts())
+    if self.world_size > 1:
+      t = torch.tensor([rows], device=self.scene.device, dtype=torch.int64)
+      dist.all_reduce(t, op=dist.ReduceOp.MAX, group=ex.group)
+      rows = int(t.item())
+    from .exchange import ImageExchange
+    cap = min(self.scene.n, int(rows * margin) + 4096)
+    self.scene.zero_grad()
+    self.exchange = ImageExchange(self.scene, ex.world, ex.rank, cap=cap, images_per_rank=ex.k, transport=ex.transport,
+                                  group=ex.group)
+    return rows
+
+  def sync_statistics(self):
+    """before a densification under DP: max_scale_px is kept per rank (MAX is order independent), every other
+    statistic is already identical on all ranks (folded in image order by the exchange)."""
+    if self.world_size > 1:
+      dist.all_reduce(self.scene.stats["max_scale_px"], op=dist.ReduceOp.MAX)
 
   def training_step(self, batch, read_loss=False):
     """batch: list of (camera, target image) for the WHOLE step (all ranks pass the same list); this rank
@@ -67,8 +104,16 @@ class Trainer:
     scene = self.scene
     mine = batch[self.rank::self.world_size]
     total = None
+    if self.exchange is not None and self.exchange.stale():  # the scene was re-allocated by a densification
+      from .exchange import ImageExchange
+      e = self.exchange
+      scene.zero_grad()
+      self.exchange = ImageExchange(scene, e.world, e.rank, cap=e.cap, images_per_rank=e.k, transport=e.transport, group=e.group)
+    if self.exchange is not None and len(mine) != self.exchange.k:
+      raise L.GsError(f"the exchange was sized for {self.exchange.k} image(s) per rank, got {len(mine)}")
     for k, (cam, image) in enumerate(mine):
-      sums = scene.forward_backward(cam, self._to_device(image), first=(k == 0 and self._grads_clean))
+      sums = scene.forward_backward(cam, self._to_device(image), first=(k == 0 and self._grads_clean),
+                                    exchange=self.exchange, slot=k)
       total = sums.clone() if total is None else total + sums
     self.step_count += len(batch)  # the reference counts images, trainer/trainer.py:532
     self.exchange_gradients()

@@ -32,16 +32,21 @@ class StubScene:
   def _mark(self, name):
     pass
 
-  def forward_backward(self, cam, image, first=False):
+  def forward_backward(self, cam, image, first=False, exchange=None, slot=0):
     k = int(cam)
     rows = torch.arange(N)[(torch.arange(N) + k) % 3 == 0]
     g = self.grads[:N * D].view(N, D)
-    if first:
+    if first or exchange is not None:
       assert float(self.grads.abs().sum()) == 0.0, "first image of a step must find a clean gradient buffer"
     g[rows] += (k + 1) * image.float().mean() * torch.ones(D)
     self.visible[rows] += 0.25 * (k + 1)
     self.seen.append(k)
+    if exchange is not None:
+      exchange.pack(slot, self)
     return torch.tensor([float(k), float(k * k)])
+
+  def zero_grad(self):
+    self.grads.zero_()
 
   def step(self):
     g = self.grads[:N * D].view(N, D)
@@ -50,10 +55,40 @@ class StubScene:
     self.grads.zero_()
 
 
-def run_step(world, rank, batch):
+class StubExchange:
+  """the ImageExchange protocol the Trainer drives (pack per image slot, one fold per step, records applied in image
+  order j = rank + world*slot), with dense CPU records moved by a gloo all_gather."""
+
+  def __init__(self, world, rank, k):
+    self.world, self.rank, self.k = world, rank, k
+    self.records = torch.zeros(k, N * D + N)
+    self.folds = 0
+
+  def stale(self):
+    return False
+
+  def pack(self, slot, scene):
+    self.records[slot].copy_(scene.grads)
+    scene.grads.zero_()  # the dense buffer is clean again; fold() adds every image's record in image order
+
+  def fold(self):
+    gathered = [torch.zeros_like(self.records) for _ in range(self.world)]
+    dist.all_gather(gathered, self.records)
+    for slot in range(self.k):
+      for r in range(self.world):
+        self.scene.grads += gathered[r][slot]
+    self.folds += 1
+
+
+def run_step(world, rank, batch, mode="dense"):
   from gsb200.trainer import Trainer
   scene = StubScene()
-  tr = Trainer(scene, world, rank)
+  if mode == "records" and world > 1:
+    ex = StubExchange(world, rank, len(batch[0]) // world)
+    ex.scene = scene
+    tr = Trainer(scene, world, rank, exchange=ex)
+  else:
+    tr = Trainer(scene, world, rank, exchange="dense")
   losses = [tr.training_step(b) for b in batch]
   return scene, tr, losses
 
@@ -64,10 +99,12 @@ def make_batches():
   return [[(k, images[k]) for k in range(0, 4)], [(k, images[k]) for k in range(4, 8)]]
 
 
-def worker(rank, world, port, out):
+def worker(rank, world, port, out, mode):
   os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
   dist.init_process_group("gloo", rank=rank, world_size=world)
-  scene, tr, losses = run_step(world, rank, make_batches())
+  scene, tr, losses = run_step(world, rank, make_batches(), mode)
+  if mode == "records":
+    assert tr.exchange.folds == 2, "one fold per optimiser step"
   torch.save(dict(params=scene.params, seen=scene.seen, steps=tr.step_count, losses=[l.tolist() for l in losses]),
              os.path.join(out, f"rank{rank}.pt"))
   dist.destroy_process_group()
@@ -79,9 +116,15 @@ def free_port():
     return s.getsockname()[1]
 
 
-def test_two_ranks_equal_sequential(tmp_path):
+import pytest
+
+
+@pytest.mark.parametrize("mode", ["dense", "records"])
+def test_two_ranks_equal_sequential(tmp_path, mode):
+  """dense: SUM all-reduce of the packed gradient buffer; records: per-image records packed by every rank and folded
+  in image order (the ImageExchange protocol)."""
   world = 2
-  mp.spawn(worker, args=(world, free_port(), str(tmp_path)), nprocs=world, join=True)
+  mp.spawn(worker, args=(world, free_port(), str(tmp_path), mode), nprocs=world, join=True)
   r = [torch.load(os.path.join(tmp_path, f"rank{k}.pt")) for k in range(world)]
   seq_scene, seq_tr, _ = run_step(1, 0, make_batches())
   # sharding: rank r renders batch[r::world] of every step
@@ -94,3 +137,22 @@ def test_two_ranks_equal_sequential(tmp_path):
   assert r[0]["steps"] == r[1]["steps"] == seq_tr.step_count == 8
   # per-rank losses are the sums over the rank's own images
   assert r[0]["losses"][0] == [0.0 + 2.0, 0.0 + 4.0] and r[1]["losses"][0] == [1.0 + 3.0, 1.0 + 9.0]
+
+
+def test_record_pointers_follow_image_order():
+  """image j of a step is batch[j]; rank r holds images r, r+world, ... in slots 0, 1, ...: the fold must visit
+  (slot 0: rank 0..W-1), (slot 1: rank 0..W-1), ... for every transport."""
+  from gsb200.exchange import ImageExchange
+  ex = ImageExchange.__new__(ImageExchange)
+  ex.world, ex.k, ex.rec_bytes, ex.parity = 3, 2, 1000, 1
+  ex.transport, ex.peer_ptrs = "peer", [10_000_000, 20_000_000, 30_000_000]
+  off = ex.parity * ex.k * ex.rec_bytes
+  assert ex.record_ptrs() == [10_000_000 + off, 20_000_000 + off, 30_000_000 + off,
+                              10_000_000 + off + 1000, 20_000_000 + off + 1000, 30_000_000 + off + 1000]
+  ex.transport = "nccl"
+
+  class G:
+    def data_ptr(self):
+      return 500
+  ex.gathered = G()
+  assert ex.record_ptrs() == [500, 500 + 2000, 500 + 4000, 500 + 1000, 500 + 3000, 500 + 5000]

@@ -1,0 +1,84 @@
+"""torchrun --nproc-per-node W tools/dp_check.py [transport]: camera-batch DP on W real GPUs vs the sequential path.
+
+Every rank trains a small scene for a few steps with one image per rank per step; at the end all ranks must hold
+bit-identical parameters / moments / statistics, and rank 0 re-runs the same batches sequentially on its own GPU
+(world size 1, batch of W images) and checks the DP result against it.  Prints one line per check and exits non-zero
+on failure.  Used by tests/test_gpu_multi.py (needs >= 2 GPUs) and by hand through `gpurun --gpus 2`."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "splat-trainer_b200"))
+
+
+def main():
+  transport = sys.argv[1] if len(sys.argv) > 1 else "auto"
+  world, rank, local = int(os.environ["WORLD_SIZE"]), int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
+  torch.cuda.set_device(local)
+  dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+  from gsb200 import lib as L
+  from gsb200 import synthetic as syn
+  from gsb200.scene import SceneConfig, SplatScene
+  from gsb200.trainer import Trainer
+  n, W, H, steps = 40000, 320, 240, 4
+  g = syn.garden_scene(n, 2, seed=5, focal=0.5 * W / np.tan(np.radians(25.0)))
+  cams = [L.make_camera(c["T"], c["fx"], c["fy"], c["cx"], c["cy"], W, H) for c in syn.ring_cameras(16, W, H)]
+  gen = torch.Generator(device="cuda").manual_seed(0)
+  targets = [torch.rand((H, W, 3), device="cuda", generator=gen) for _ in range(world * steps)]
+  batches = [[(cams[(s * world + r) % len(cams)], targets[s * world + r]) for r in range(world)] for s in range(steps)]
+
+  scene = SplatScene(g, SceneConfig(sh_degree=2))
+  tr = Trainer(scene, world, rank, exchange=transport, exchange_cap=n)
+  for b in batches[:2]:
+    tr.training_step(b)
+  if tr.exchange is not None:
+    rows = tr.calibrate_exchange()
+    assert rows > 100, rows
+  for b in batches[2:]:
+    tr.training_step(b)
+  tr.sync_statistics()
+  torch.cuda.synchronize()
+  ok = True
+  mode = tr.exchange.transport if tr.exchange is not None else "dense"
+  # 1. replicas bit-identical
+  names = ["params", "exp_avg", "exp_avg_sq_flat", "running_vis", "opt_step"]
+  tensors = [getattr(scene, k) for k in names] + ([scene.stats[k].float() for k in sorted(scene.stats)] if mode != "dense" else [])
+  for name, t in zip(names + sorted(scene.stats), tensors):
+    lo, hi = t.clone(), t.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    same = bool(torch.equal(lo, hi))
+    ok &= same
+    if rank == 0:
+      print(f"[{mode}] replicas identical {name}: {same}")
+  # 2. equal to the sequential path (rank 0 only; fp32 atomics => summation-order tolerance)
+  if rank == 0:
+    seq = SplatScene(g, SceneConfig(sh_degree=2))
+    seq_tr = Trainer(seq)
+    for b in batches:
+      seq_tr.training_step(b)
+    torch.cuda.synchronize()
+    for name in ("position", "log_scaling", "rotation", "alpha_logit", "sh"):
+      d = (scene.p[name] - seq.p[name]).abs().max().item()
+      good = d < 5e-4
+      ok &= good
+      print(f"[{mode}] vs sequential {name}: max abs diff {d:.3e} {'ok' if good else 'FAIL'}")
+    if mode != "dense":
+      piv = bool(torch.equal(scene.stats["points_in_view"], seq.stats["points_in_view"]))
+      print(f"[{mode}] vs sequential points_in_view identical: {piv}")
+      for k in ("prune_cost", "split_score", "visibility", "max_scale_px"):
+        d = ((scene.stats[k] - seq.stats[k]).abs() / (seq.stats[k].abs() + 1e-3)).max().item()
+        good = d < 2e-2
+        ok &= good
+        print(f"[{mode}] vs sequential {k}: max rel diff {d:.3e} {'ok' if good else 'FAIL'}")
+  flag = torch.tensor([0 if ok else 1], device="cuda")
+  dist.all_reduce(flag)
+  dist.destroy_process_group()
+  sys.exit(1 if flag.item() else 0)
+
+
+if __name__ == "__main__":
+  main()
