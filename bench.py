@@ -40,7 +40,7 @@ def parse():
   ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
   ap.add_argument("--points", type=int, default=0, help="override the splat count (testing only)")
   ap.add_argument("--no-cpu-baseline", action="store_true")
-  ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl", "dense"],
+  ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl", "dense", "local"],
                   help="N>1 gradient/statistics exchange: per-image records over peer memory (auto/peer), records "
                        "all-gathered by NCCL, or the dense SUM all-reduce of the packed gradient buffer")
   return ap.parse_args()
@@ -223,7 +223,11 @@ def run_b200(args):
   torch.cuda.empty_cache()
   dev_targets = [t.cuda() for t in host_targets]
   scene = SplatScene(g, SceneConfig(sh_degree=deg))
-  trainer = Trainer(scene, world, rank, exchange=args.exchange)
+  if args.exchange == "local":  # N=1 only: run the pack/fold kernels of the DP exchange on one GPU (for profiling them)
+    from gsb200.exchange import ImageExchange
+    trainer = Trainer(scene, 1, 0, exchange=ImageExchange(scene, 1, 0, transport="local"))
+  else:
+    trainer = Trainer(scene, world, rank, exchange=args.exchange)
 
   def batch_for(i, targets):
     # the step's full batch has `world` images; only this rank's entry is materialised (others are None-padded)

@@ -80,6 +80,18 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+// exp_lerp(t, a, b) = m + log(lerp(e^(a-m), e^(b-m), t)), m = max(a, b)  (reference util/misc.py:56-59, with torch.lerp's
+// two branches).  One of the two exponentials is always e^0 = 1 and exp_lerp(t, a, a) = a + log(1) = a: both are taken
+// as shortcuts, which is bit-identical to evaluating them.  Shared by gs_accumulate_stats and gs_exchange_fold so the
+// sequential and the data-parallel statistics are the same arithmetic.
+__device__ __forceinline__ float gs_exp_lerp(float t, float a, float b) {
+  if (a == b) return a;
+  float m = fmaxf(a, b);
+  float ea = (a >= b) ? 1.0f : expf(a - m), eb = (b >= a) ? 1.0f : expf(b - m);
+  float l = t < 0.5f ? ea + t * (eb - ea) : eb - (eb - ea) * (1.0f - t);
+  return m + logf(l);
+}
+
 // ---- exclusive scan of int32 (scan.cu) -------------------------------------------------------
 // out[i] = sum_{j<i} in[idx ? idx[j] : j]; total (nullable) receives the full sum.
 // n_dev (nullable) bounds the element count on the device (<= n).  partials: >= gs_scan_partials(n) ints.

@@ -59,115 +59,146 @@ struct RecordsDev {
   const void *rec[GS_EXCHANGE_MAX_IMAGES];
 };
 
-__device__ __forceinline__ float exp_lerp_x(float t, float a, float b) {  // reference util/misc.py:56-59 (= optim.cu)
-  float m = fmaxf(a, b);
-  float ea = expf(a - m), eb = expf(b - m);
-  float l = t < 0.5f ? ea + t * (eb - ea) : eb - (eb - ea) * (1.0f - t);
-  return m + logf(l);
-}
-
 constexpr int PK_THREADS = 256;
-constexpr int PK_ITERS = 8;
+constexpr int PK_ITERS = 4;
 constexpr int PK_TILE = PK_THREADS * PK_ITERS;  // rows per CTA; a warp covers one 32-row word per iteration
 
-// Pass A of the pack: one sweep over the image's rows.  Ordered single-pass compaction (chained scan over CTAs) of the
-// visible rows, the three bit/rank planes, the rank's own max_scale_px, and the clearing of the raster accumulator.
-__global__ void __launch_bounds__(PK_THREADS) k_pack_stats(int64_t n, int64_t cap, const float *__restrict__ g2d,
-                                                           const float *__restrict__ vis, int vis_stride,
-                                                           const float *__restrict__ heur, int heur_stride,
-                                                           float *__restrict__ max_scale_px, float *__restrict__ clear_acc,
-                                                           int clear_stride, float *__restrict__ clear_vis, RecView rv,
-                                                           uint32_t *__restrict__ status, uint32_t *__restrict__ ticket) {
-  __shared__ int s_cnt[PK_ITERS * 8];
-  __shared__ int s_tile;
-  __shared__ uint32_t s_prefix;
-  if (threadIdx.x == 0) s_tile = (int)atomicAdd(ticket, 1u);
-  __syncthreads();
-  const int tile = s_tile;
+// Pack pass 1: one sweep over the image's rows, no inter-CTA dependency: in-view / visible bit planes, the per-word
+// visible count (left in the `base` plane for pass 2), and the rank's own max_scale_px.  Every row's loads are issued
+// before the first dependent use (the sweep is latency bound otherwise).
+__global__ void __launch_bounds__(PK_THREADS) k_pack_sweep(int64_t n, const float *__restrict__ g2d, const float *__restrict__ vis,
+                                                           int vis_stride, float *__restrict__ max_scale_px, RecView rv) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  float v[PK_ITERS], hp[PK_ITERS], hs[PK_ITERS];
-  unsigned vb[PK_ITERS];
+  float2 ca_cb[PK_ITERS], cc_op[PK_ITERS];
+  float v[PK_ITERS], ms[PK_ITERS];
 #pragma unroll
   for (int it = 0; it < PK_ITERS; ++it) {
-    int64_t r = (int64_t)tile * PK_TILE + it * PK_THREADS + threadIdx.x;
-    bool inview = false;
-    v[it] = 0.f; hp[it] = 0.f; hs[it] = 0.f;
+    int64_t r = (int64_t)blockIdx.x * PK_TILE + it * PK_THREADS + threadIdx.x;
+    ca_cb[it] = make_float2(1.f, 0.f); cc_op[it] = make_float2(1.f, 0.f); v[it] = 0.f; ms[it] = 0.f;
     if (r < n) {
       const float2 *g = reinterpret_cast<const float2 *>(g2d + GS_G2D_STRIDE * r);
-      float2 cc_op = g[2];
-      if (cc_op.y > 0.f) {
-        inview = true;
-        float2 ca_cb = g[1];
-        float ca = ca_cb.x, cb = ca_cb.y, cc = cc_op.x;
-        float detc = ca * cc - cb * cb;
-        float cxx = cc / detc, cyy = ca / detc, cxy = -cb / detc;
-        float mid = 0.5f * (cxx + cyy);
-        float disc = mid * mid - (cxx * cyy - cxy * cxy);
-        float lam = mid + sqrtf(fmaxf(disc, 0.f));
-        float scale_px = sqrtf(fmaxf(lam, 0.f));
-        if (scale_px > max_scale_px[r]) max_scale_px[r] = scale_px;
-        float vv = vis[(int64_t)vis_stride * r];
-        if (vv > 0.f) {
-          v[it] = vv;
-          hp[it] = heur[(int64_t)heur_stride * r];
-          hs[it] = heur[(int64_t)heur_stride * r + 1];
-          if (clear_acc) {
-            float *a = clear_acc + (int64_t)clear_stride * r;
-            for (int k = 0; k < clear_stride; ++k) a[k] = 0.f;
-          }
-          if (clear_vis) clear_vis[r] = 0.f;
-        }
-      }
-    }
-    unsigned ib = __ballot_sync(GS_FULL, inview);
-    vb[it] = __ballot_sync(GS_FULL, v[it] > 0.f);
-    int64_t r0 = (int64_t)tile * PK_TILE + it * PK_THREADS + w * 32;  // first row of this warp's word
-    if (lane == 0) {
-      s_cnt[it * 8 + w] = __popc(vb[it]);
-      if (r0 < n) { rv.inview[r0 >> 5] = ib; rv.visbits[r0 >> 5] = vb[it]; }
+      ca_cb[it] = g[1]; cc_op[it] = g[2];
+      v[it] = vis[(int64_t)vis_stride * r];
+      ms[it] = max_scale_px[r];
     }
   }
-  __syncthreads();
-  // exclusive scan of the 64 word counts (order: iteration-major = ascending rows)
-  int tot = 0;
-  if (threadIdx.x < 32) {
-    int a = s_cnt[2 * lane], b = s_cnt[2 * lane + 1];
-    int inc = a + b;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      int t = __shfl_up_sync(GS_FULL, inc, o);
-      if (lane >= o) inc += t;
+  for (int it = 0; it < PK_ITERS; ++it) {
+    int64_t r = (int64_t)blockIdx.x * PK_TILE + it * PK_THREADS + threadIdx.x;
+    bool inview = cc_op[it].y > 0.f;  // rows past n carry opacity 0
+    if (inview) {
+      float ca = ca_cb[it].x, cb = ca_cb[it].y, cc = cc_op[it].x;
+      float detc = ca * cc - cb * cb;
+      float cxx = cc / detc, cyy = ca / detc, cxy = -cb / detc;
+      float mid = 0.5f * (cxx + cyy);
+      float disc = mid * mid - (cxx * cyy - cxy * cxy);
+      float lam = mid + sqrtf(fmaxf(disc, 0.f));
+      float scale_px = sqrtf(fmaxf(lam, 0.f));
+      if (scale_px > ms[it]) max_scale_px[r] = scale_px;
     }
-    tot = __shfl_sync(GS_FULL, inc, 31);
-    int ex = inc - (a + b);
-    s_cnt[2 * lane] = ex;
-    s_cnt[2 * lane + 1] = ex + a;
-    if (lane == 0) gs_st_status(status + tile, (uint32_t)tot | (tile == 0 ? GS_LB_INCL : GS_LB_LOCAL));
+    unsigned ib = __ballot_sync(GS_FULL, inview);
+    unsigned vb = __ballot_sync(GS_FULL, inview && v[it] > 0.f);
+    int64_t r0 = (int64_t)blockIdx.x * PK_TILE + it * PK_THREADS + w * 32;  // first row of this warp's word
+    if (lane == 0 && r0 < n) {
+      rv.inview[r0 >> 5] = ib; rv.visbits[r0 >> 5] = vb; rv.base[r0 >> 5] = (uint32_t)__popc(vb);
+    }
+  }
+}
+
+// Pack pass 2: exclusive scan of the word counts in place (chained scan over a few dozen CTAs of 4096 words each — the
+// look-back chain is short because a CTA covers 131072 rows) + the record header.
+constexpr int PB_THREADS = 256;
+constexpr int PB_ITEMS = 16;
+constexpr int PB_TILE = PB_THREADS * PB_ITEMS;
+__global__ void __launch_bounds__(PB_THREADS) k_pack_base(int64_t words, int64_t cap, RecView rv, uint32_t *__restrict__ status,
+                                                          uint32_t *__restrict__ ticket) {
+  __shared__ uint32_t s_warp[PB_THREADS / 32];
+  __shared__ uint32_t s_prefix;
+  __shared__ int s_tile;
+  if (threadIdx.x == 0) s_tile = (int)atomicAdd(ticket, 1u);
+  __syncthreads();
+  const int tile = s_tile;  // ticket order: every predecessor of a running tile has already started
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  int64_t first = (int64_t)tile * PB_TILE + (int64_t)threadIdx.x * PB_ITEMS;
+  uint32_t c[PB_ITEMS];
+  uint32_t sum = 0;
+#pragma unroll
+  for (int k = 0; k < PB_ITEMS; k += 4) {
+    uint4 q = make_uint4(0u, 0u, 0u, 0u);
+    if (first + k + 3 < words) q = *reinterpret_cast<const uint4 *>(rv.base + first + k);
+    else {
+      if (first + k < words) q.x = rv.base[first + k];
+      if (first + k + 1 < words) q.y = rv.base[first + k + 1];
+      if (first + k + 2 < words) q.z = rv.base[first + k + 2];
+    }
+    c[k] = q.x; c[k + 1] = q.y; c[k + 2] = q.z; c[k + 3] = q.w;
+    sum += q.x + q.y + q.z + q.w;
+  }
+  uint32_t inc = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(GS_FULL, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) s_warp[w] = inc;
+  __syncthreads();
+  uint32_t wo = 0, tot = 0;
+#pragma unroll
+  for (int k = 0; k < PB_THREADS / 32; ++k) {
+    uint32_t x = s_warp[k];
+    if (k < w) wo += x;
+    tot += x;
+  }
+  if (threadIdx.x == 0) gs_st_status(status + tile, tot | (tile == 0 ? GS_LB_INCL : GS_LB_LOCAL));
+  if (threadIdx.x < 32) {
     uint32_t prefix = gs_lookback_warp(status, tile);
     if (lane == 0) {
-      if (tile > 0) gs_st_status(status + tile, (prefix + (uint32_t)tot) | GS_LB_INCL);
+      if (tile > 0) gs_st_status(status + tile, (prefix + tot) | GS_LB_INCL);
       s_prefix = prefix;
       if (tile == (int)gridDim.x - 1) {
-        uint32_t total = prefix + (uint32_t)tot;
+        uint32_t total = prefix + tot;
         rv.header[0] = (int32_t)total;
         rv.header[1] = total > (uint32_t)cap ? 1 : 0;
       }
     }
   }
   __syncthreads();
+  uint32_t run = s_prefix + wo + inc - sum;
 #pragma unroll
-  for (int it = 0; it < PK_ITERS; ++it) {
-    int64_t r = (int64_t)tile * PK_TILE + it * PK_THREADS + threadIdx.x;
-    uint32_t wbase = s_prefix + (uint32_t)s_cnt[it * 8 + w];
-    int64_t r0 = (int64_t)tile * PK_TILE + it * PK_THREADS + w * 32;
-    if (lane == 0 && r0 < n) rv.base[r0 >> 5] = wbase;
-    if (v[it] > 0.f) {
-      uint32_t pos = wbase + __popc(vb[it] & ((1u << lane) - 1u));
-      if (pos < (uint32_t)cap) {
-        rv.idx[pos] = (int32_t)r;
-        rv.aux[pos] = make_float4(v[it], hp[it], hs[it], 0.f);
-      }
+  for (int k = 0; k < PB_ITEMS; ++k) {
+    if (first + k < words) rv.base[first + k] = run;
+    run += c[k];
+  }
+}
+
+// Pack pass 3: the ascending list of visible rows with their (visibility, prune, split) triple, straight from the bit
+// and rank planes; clears the consumed raster accumulator rows like gs_accumulate_stats does.  A thread scans 4 rows.
+__global__ void __launch_bounds__(256) k_pack_list(int64_t n, int64_t cap, const float *__restrict__ vis, int vis_stride,
+                                                   const float *__restrict__ heur, int heur_stride, float *__restrict__ clear_acc,
+                                                   int clear_stride, float *__restrict__ clear_vis, RecView rv) {
+  int64_t r0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (r0 >= n) return;
+  unsigned vb = rv.visbits[r0 >> 5];
+  unsigned mine = (vb >> (r0 & 31)) & 0xfu;
+  if (!mine) return;
+  uint32_t base = rv.base[r0 >> 5];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    if (!(mine & (1u << q))) continue;
+    int64_t r = r0 + q;
+    unsigned bit = 1u << (r & 31);
+    uint32_t pos = base + __popc(vb & (bit - 1u));
+    float v = vis[(int64_t)vis_stride * r];
+    float hp = heur[(int64_t)heur_stride * r], hs = heur[(int64_t)heur_stride * r + 1];
+    if (pos < (uint32_t)cap) {
+      rv.idx[pos] = (int32_t)r;
+      rv.aux[pos] = make_float4(v, hp, hs, 0.f);
     }
+    if (clear_acc) {
+      float *a = clear_acc + (int64_t)clear_stride * r;
+      for (int k = 0; k < clear_stride; ++k) a[k] = 0.f;
+    }
+    if (clear_vis) clear_vis[r] = 0.f;
   }
 }
 
@@ -191,83 +222,122 @@ __global__ void __launch_bounds__(256) k_pack_rows(int64_t cap, RecView rv, Grou
   }
 }
 
-// Fold, statistics: one thread per row, images strictly in order.  All loads from the (possibly remote) records of a
-// chunk of images are issued before the first dependent use.
-constexpr int FS_CHUNK = 8;
+// Fold, statistics: a thread owns 4 consecutive rows (one float4 of each statistic, all in one 32-row word), images
+// strictly in order.  The rows' own statistics and all loads from the (possibly remote) records of a chunk of images
+// are issued before the first dependent use.
+constexpr int FS_CHUNK = 4;
 __global__ void __launch_bounds__(256) k_fold_stats(int64_t n, int64_t cap, RecordsDev recs, float split_alpha, float prune_alpha,
                                                     float *__restrict__ prune_cost, float *__restrict__ split_score,
                                                     int16_t *__restrict__ points_in_view, float *__restrict__ visibility,
                                                     float *__restrict__ scene_visible) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const int64_t w = i >> 5;
-  const unsigned bit = 1u << (i & 31), below = bit - 1u;
-  bool loaded = false;
-  float split = 0.f, prune = 0.f;
+  int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i0 >= n) return;
+  const int64_t w = i0 >> 5;
+  const int sh = (int)(i0 & 31);
+  const size_t words = (size_t)((n + 31) / 32);
+  const size_t plane = al256(words * 4);
+  const size_t aux_off = 256 + 3 * plane + al256((size_t)cap * 4);
+  const bool full = i0 + 3 < n;
+  float split[4], prune[4];
+  if (full) {
+    float4 a = *reinterpret_cast<const float4 *>(split_score + i0), b = *reinterpret_cast<const float4 *>(prune_cost + i0);
+    split[0] = a.x; split[1] = a.y; split[2] = a.z; split[3] = a.w;
+    prune[0] = b.x; prune[1] = b.y; prune[2] = b.z; prune[3] = b.w;
+  } else {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      split[q] = (i0 + q < n) ? split_score[i0 + q] : 0.f;
+      prune[q] = (i0 + q < n) ? prune_cost[i0 + q] : 0.f;
+    }
+  }
+  unsigned any = 0u;
   for (int j0 = 0; j0 < recs.count; j0 += FS_CHUNK) {
     unsigned iv[FS_CHUNK], vv[FS_CHUNK], bb[FS_CHUNK];
-    float4 ax[FS_CHUNK];
 #pragma unroll
     for (int c = 0; c < FS_CHUNK; ++c) {
       iv[c] = vv[c] = bb[c] = 0u;
       if (j0 + c < recs.count) {
-        RecView rv = rec_view(const_cast<void *>(recs.rec[j0 + c]), n, cap);
-        iv[c] = rv.inview[w]; vv[c] = rv.visbits[w]; bb[c] = rv.base[w];
+        const char *base = (const char *)recs.rec[j0 + c] + 256;
+        iv[c] = *(const uint32_t *)(base + 4 * w);
+        vv[c] = *(const uint32_t *)(base + plane + 4 * w);
+        bb[c] = *(const uint32_t *)(base + 2 * plane + 4 * w);
       }
     }
 #pragma unroll
     for (int c = 0; c < FS_CHUNK; ++c) {
-      ax[c] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (vv[c] & bit) {
-        uint32_t pos = bb[c] + __popc(vv[c] & below);
-        if (pos < (uint32_t)cap) ax[c] = rec_view(const_cast<void *>(recs.rec[j0 + c]), n, cap).aux[pos];
-      }
-    }
+      unsigned in4 = (iv[c] >> sh) & 0xfu;
+      if (!in4) continue;
+      any |= in4;
+      unsigned vis4 = (vv[c] >> sh) & 0xfu;
 #pragma unroll
-    for (int c = 0; c < FS_CHUNK; ++c) {
-      if (!(iv[c] & bit)) continue;
-      if (!loaded) { split = split_score[i]; prune = prune_cost[i]; loaded = true; }
-      if (ax[c].x > 0.f) {
-        points_in_view[i] += 1;
-        visibility[i] += ax[c].x;
-        if (scene_visible) scene_visible[i] += ax[c].x;
+      for (int q = 0; q < 4; ++q) {
+        if (!(in4 & (1u << q))) continue;
+        float hp = 0.f, hs = 0.f;
+        if (vis4 & (1u << q)) {
+          uint32_t pos = bb[c] + __popc(vv[c] & ((1u << (sh + q)) - 1u));
+          if (pos < (uint32_t)cap) {
+            float4 ax = *(const float4 *)((const char *)recs.rec[j0 + c] + aux_off + 16 * (size_t)pos);
+            if (ax.x > 0.f) {
+              points_in_view[i0 + q] += 1;
+              visibility[i0 + q] += ax.x;
+              if (scene_visible) scene_visible[i0 + q] += ax.x;
+            }
+            hp = ax.y; hs = ax.z;
+          }
+        }
+        split[q] = gs_exp_lerp(split_alpha, split[q], hs);
+        prune[q] = gs_exp_lerp(prune_alpha, prune[q], hp);
       }
-      split = exp_lerp_x(split_alpha, split, ax[c].z);
-      prune = exp_lerp_x(prune_alpha, prune, ax[c].y);
     }
   }
-  if (loaded) { split_score[i] = split; prune_cost[i] = prune; }
+  if (!any) return;
+  if (full) {
+    *reinterpret_cast<float4 *>(split_score + i0) = make_float4(split[0], split[1], split[2], split[3]);
+    *reinterpret_cast<float4 *>(prune_cost + i0) = make_float4(prune[0], prune[1], prune[2], prune[3]);
+  } else {
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (i0 + q < n) { split_score[i0 + q] = split[q]; prune_cost[i0 + q] = prune[q]; }
+  }
 }
 
-// Fold, gradient rows: a CTA owns a contiguous range of Gaussian rows (a multiple of 32, so the record positions of
-// the range come straight from the rank plane) and adds image after image into the dense gradient planes.
-__global__ void __launch_bounds__(256) k_fold_rows(int64_t n, int64_t cap, int64_t rows_per_cta, RecordsDev recs, GroupsDev gd) {
-  __shared__ int s_lo[GS_EXCHANGE_MAX_IMAGES], s_hi[GS_EXCHANGE_MAX_IMAGES];
-  int64_t a = (int64_t)blockIdx.x * rows_per_cta, b = min(a + rows_per_cta, n);
-  if (a >= n) return;
-  for (int j = threadIdx.x; j < recs.count; j += blockDim.x) {
-    RecView rv = rec_view(const_cast<void *>(recs.rec[j]), n, cap);
-    int count = min(rv.header[0], (int)cap);
-    int lo = (int)rv.base[a >> 5];
-    int hi = (b >= n) ? count : (int)rv.base[b >> 5];
-    s_lo[j] = min(lo, count);
-    s_hi[j] = min(hi, count);
-  }
-  __syncthreads();
-  for (int j = 0; j < recs.count; ++j) {
-    RecView rv = rec_view(const_cast<void *>(recs.rec[j]), n, cap);
-    int lo = s_lo[j], m = s_hi[j] - lo;
-    for (int t = threadIdx.x; t < m * gd.total; t += blockDim.x) {
-      int r = lo + t / gd.total, e = t % gd.total;
-      int g = 0;
+// Fold, gradient rows: a warp owns one 32-row word.  For every row some image blended, each lane keeps one element of
+// the dense gradient row in a register and adds the images' record rows in image order — no barrier, no atomics, and
+// the record loads of different images are independent of each other (one NVLink round trip per row, not per image).
+__global__ void __launch_bounds__(256, 8) k_fold_rows(int64_t n, int64_t cap, RecordsDev recs, GroupsDev gd) {
+  const int lane = threadIdx.x & 31;
+  const int64_t words = (n + 31) / 32;
+  const size_t plane = al256((size_t)words * 4);
+  const size_t rows_off = 256 + 3 * plane + al256((size_t)cap * 4) + al256((size_t)cap * 16);
+  const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < words; w += warps) {
+    unsigned any = 0u;
+    for (int j = 0; j < recs.count; ++j) any |= *(const uint32_t *)((const char *)recs.rec[j] + 256 + plane + 4 * w);
+    while (any) {
+      int b = __ffs(any) - 1;
+      any &= any - 1;
+      const unsigned bit = 1u << b;
+      const int64_t id = w * 32 + b;
+      for (int e = lane; e < gd.total; e += 32) {
+        int g = 0;
 #pragma unroll
-      for (int k = 1; k < GS_EXCHANGE_MAX_GROUPS; ++k) g += (k < gd.count && e >= gd.start[k]);
-      int k = e - gd.start[g], dim = gd.dim[g];
-      float val = rv.rows[(int64_t)cap * gd.start[g] + (int64_t)r * dim + k];
-      int64_t id = rv.idx[r];
-      gd.grad[g][id * dim + k] += val;
+        for (int k = 1; k < GS_EXCHANGE_MAX_GROUPS; ++k) g += (k < gd.count && e >= gd.start[k]);
+        const int k = e - gd.start[g], dim = gd.dim[g];
+        const int64_t rplane = (int64_t)cap * gd.start[g];
+        float *dst = gd.grad[g] + id * dim + k;
+        float acc = *dst;
+#pragma unroll 4
+        for (int j = 0; j < recs.count; ++j) {
+          const char *rec = (const char *)recs.rec[j];
+          unsigned vb = *(const uint32_t *)(rec + 256 + plane + 4 * w);
+          if (!(vb & bit)) continue;
+          uint32_t pos = *(const uint32_t *)(rec + 256 + 2 * plane + 4 * w) + __popc(vb & (bit - 1u));
+          if (pos >= (uint32_t)cap) continue;
+          acc += ((const float *)(rec + rows_off))[rplane + (int64_t)pos * dim + k];
+        }
+        *dst = acc;
+      }
     }
-    __syncthreads();  // image j's adds are complete (and visible block-wide) before image j+1 touches the same rows
   }
 }
 
@@ -297,7 +367,8 @@ extern "C" size_t gs_exchange_record_bytes(int64_t n, int64_t cap, int row_float
 }
 
 extern "C" size_t gs_exchange_pack_workspace_bytes(int64_t n) {
-  size_t tiles = (size_t)((n > 0 ? n : 1) + PK_TILE - 1) / PK_TILE;
+  size_t words = (size_t)(((n > 0 ? n : 1) + 31) / 32);
+  size_t tiles = (words + PB_TILE - 1) / PB_TILE;
   return gs_align256((64 + tiles) * 4) + 256;
 }
 
@@ -313,14 +384,21 @@ extern "C" int gs_exchange_pack(int64_t n, const float *g2d, const float *vis, i
   if (workspace_bytes < gs_exchange_pack_workspace_bytes(n)) { gs_set_error("gs_exchange_pack: workspace too small"); return GS_ERR_WORKSPACE; }
   cudaStream_t st = (cudaStream_t)stream;
   uintptr_t a = ((uintptr_t)workspace + 255) & ~(uintptr_t)255;
-  int tiles = gs_div_up(n, PK_TILE);
+  int64_t words = (n + 31) / 32;
+  int tiles = gs_div_up(words, PB_TILE);
   GS_CUDA(cudaMemsetAsync((void *)a, 0, (64 + (size_t)tiles) * 4, st));
   uint32_t *ticket = (uint32_t *)a, *status = ticket + 64;
   RecView rv = rec_view(record, n, cap);
-  k_pack_stats<<<tiles, PK_THREADS, 0, st>>>(n, cap, g2d, vis, vis_stride, heur, heur_stride, max_scale_px, clear_acc,
-                                             clear_stride, clear_vis, rv, status, ticket);
+  k_pack_sweep<<<gs_div_up(n, PK_TILE), PK_THREADS, 0, st>>>(n, g2d, vis, vis_stride, max_scale_px, rv);
   GS_LAUNCH_CHECK();
-  k_pack_rows<<<148 * 4, 256, 0, st>>>(cap, rv, gd);
+  k_pack_base<<<tiles, PB_THREADS, 0, st>>>(words, cap, rv, status, ticket);
+  GS_LAUNCH_CHECK();
+  k_pack_list<<<gs_div_up((n + 3) / 4, 256), 256, 0, st>>>(n, cap, vis, vis_stride, heur, heur_stride, clear_acc, clear_stride, clear_vis, rv);
+  GS_LAUNCH_CHECK();
+  {  // one warp per record row where the machine has room for them (the count is only known on the device)
+    int64_t want = (cap + 7) / 8;
+    k_pack_rows<<<(int)(want < 148 * 32 ? want : 148 * 32), 256, 0, st>>>(cap, rv, gd);
+  }
   GS_LAUNCH_CHECK();
   return GS_OK;
 }
@@ -341,13 +419,13 @@ extern "C" int gs_exchange_fold(int64_t n, int n_images, const void *const *reco
     GS_REQUIRE(j >= n_images || records[j], "null record");
   }
   cudaStream_t st = (cudaStream_t)stream;
-  k_fold_stats<<<gs_div_up(n, 256), 256, 0, st>>>(n, cap, rd, split_alpha, prune_alpha, prune_cost, split_score, points_in_view,
-                                                  visibility, scene_visible);
+  k_fold_stats<<<gs_div_up((n + 3) / 4, 256), 256, 0, st>>>(n, cap, rd, split_alpha, prune_alpha, prune_cost, split_score,
+                                                            points_in_view, visibility, scene_visible);
   GS_LAUNCH_CHECK();
-  int ctas = 148 * 8;
-  int64_t rows_per_cta = ((n + ctas - 1) / ctas + 31) / 32 * 32;
-  int grid = gs_div_up(n, rows_per_cta);
-  k_fold_rows<<<grid, 256, 0, st>>>(n, cap, rows_per_cta, rd, gd);
+  {
+    int64_t words = (n + 31) / 32, want = (words + 7) / 8;
+    k_fold_rows<<<(int)(want < 148 * 64 ? want : 148 * 64), 256, 0, st>>>(n, cap, rd, gd);
+  }
   GS_LAUNCH_CHECK();
   return GS_OK;
 }

@@ -397,13 +397,6 @@ extern "C" int gs_optim_step(const gs_optim_config *h, int kind, int64_t n, cons
 }
 
 // ---- statistics --------------------------------------------------------------------------------------
-__device__ __forceinline__ float exp_lerp(float t, float a, float b) {  // reference util/misc.py:56-59
-  float m = fmaxf(a, b);
-  float ea = expf(a - m), eb = expf(b - m);
-  float l = t < 0.5f ? ea + t * (eb - ea) : eb - (eb - ea) * (1.0f - t);  // torch.lerp's two branches
-  return m + logf(l);
-}
-
 __global__ void __launch_bounds__(256) k_accumulate_stats(int64_t m, const int64_t *__restrict__ idx, const float *__restrict__ g2d,
                                                           const float *__restrict__ vis, int vis_stride,
                                                           const float *__restrict__ heur, int heur_stride, float split_alpha,
@@ -434,8 +427,8 @@ __global__ void __launch_bounds__(256) k_accumulate_stats(int64_t m, const int64
     visibility[i] += v;
     if (scene_visible) scene_visible[i] += v;
   }
-  split_score[i] = exp_lerp(split_alpha, split_score[i], h_split);
-  prune_cost[i] = exp_lerp(prune_alpha, prune_cost[i], h_prune);
+  split_score[i] = gs_exp_lerp(split_alpha, split_score[i], h_split);
+  prune_cost[i] = gs_exp_lerp(prune_alpha, prune_cost[i], h_prune);
   if (v > 0.f) {
     if (clear_acc) {
       float *a = clear_acc + (int64_t)clear_stride * r;
