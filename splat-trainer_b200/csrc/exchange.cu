@@ -18,7 +18,8 @@
 //   base     uint32[(n+31)/32]   number of visible rows before word w (rank of row i = base + popc(bits below i))
 //   idx      int32[cap]          ascending visible rows
 //   aux      float4[cap]         (visibility, prune heuristic, split heuristic, 0)
-//   rows     float[cap·D]        gradient rows, one plane of cap·dim per parameter group
+//   rows     float[cap·P]        gradient rows, row-major, padded to P = D rounded up to 16 floats: a row is one or two
+//                                coalesced (NVLink-friendly) warp loads; group g's dim floats start at Σ dims before g
 #include "common.cuh"
 
 namespace {
@@ -47,12 +48,26 @@ __host__ __device__ inline RecView rec_view(void *rec, int64_t n, int64_t cap) {
   return v;
 }
 
+__host__ __device__ inline int row_pad(int d) { return (d + 15) / 16 * 16; }
+
 struct GroupsDev {
   int count, total;
   int dim[GS_EXCHANGE_MAX_GROUPS];
   int start[GS_EXCHANGE_MAX_GROUPS];  // first flattened element of the group
   float *grad[GS_EXCHANGE_MAX_GROUPS];
 };
+
+// group of flattened row element e -> (offset inside the group, dim, dense plane).  Static indices only: a dynamically
+// indexed kernel-parameter array becomes a divergent constant-bank load per lane (measured: 430 stall cycles/instr).
+__device__ __forceinline__ void group_of(const GroupsDev &gd, int e, int &k_in, int &dim, float *&plane) {
+  int start = 0;
+  dim = gd.dim[0]; plane = gd.grad[0];
+#pragma unroll
+  for (int k = 1; k < GS_EXCHANGE_MAX_GROUPS; ++k) {
+    if (k < gd.count && e >= gd.start[k]) { dim = gd.dim[k]; plane = gd.grad[k]; start = gd.start[k]; }
+  }
+  k_in = e - start;
+}
 
 struct RecordsDev {
   int count;
@@ -202,22 +217,28 @@ __global__ void __launch_bounds__(256) k_pack_list(int64_t n, int64_t cap, const
   }
 }
 
-// Pass B of the pack: move the gradient rows of the visible list into the record's planes and clear them at the
-// source, so the dense gradient buffer is all-zero again when the fold adds every image's rows in image order.
+// Pack pass 4: move the gradient rows of the visible list into the record (row-major) and clear them at the source, so
+// the dense gradient buffer is all-zero again when the fold adds every image's rows in image order.  A warp per row.
 __global__ void __launch_bounds__(256) k_pack_rows(int64_t cap, RecView rv, GroupsDev gd) {
   int count = min(rv.header[0], (int)cap);
   int warps = (gridDim.x * blockDim.x) >> 5;
   int lane = threadIdx.x & 31;
+  const int pad = row_pad(gd.total);
   for (int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; j < count; j += warps) {
     int64_t id = rv.idx[j];
-    for (int e = lane; e < gd.total; e += 32) {
-      int g = 0;
-#pragma unroll
-      for (int k = 1; k < GS_EXCHANGE_MAX_GROUPS; ++k) g += (k < gd.count && e >= gd.start[k]);
-      int k = e - gd.start[g], dim = gd.dim[g];
-      float *src = gd.grad[g] + id * dim + k;
-      rv.rows[(int64_t)cap * gd.start[g] + (int64_t)j * dim + k] = *src;
-      *src = 0.f;
+    for (int e = lane; e < pad; e += 32) {
+      float val = 0.f;
+      float *src = nullptr;
+      if (e < gd.total) {
+        int k, dim; float *plane;
+        group_of(gd, e, k, dim, plane);
+        src = plane + id * dim + k;
+        val = __ldcg(src);
+      }
+      rv.rows[(int64_t)j * pad + e] = val;
+      // clear AFTER the dependent record store: a store issued right behind the load of the same address stalled the
+      // L1 miss path (measured 220 us instead of 15 us for this kernel)
+      if (src) __stcg(src, 0.f);
     }
   }
 }
@@ -301,41 +322,74 @@ __global__ void __launch_bounds__(256) k_fold_stats(int64_t n, int64_t cap, Reco
   }
 }
 
-// Fold, gradient rows: a warp owns one 32-row word.  For every row some image blended, each lane keeps one element of
-// the dense gradient row in a register and adds the images' record rows in image order — no barrier, no atomics, and
-// the record loads of different images are independent of each other (one NVLink round trip per row, not per image).
+// Fold, gradient rows: a warp owns one 32-row word.  Lane j first fetches image j's visible word and rank base (ONE
+// round trip for all images), then for every row some image blended each lane keeps two elements of the dense
+// gradient row in registers and adds the images' record rows in image order — no barrier, no atomics.  A record row
+// is one coalesced 8-B-per-lane warp load (256 B for SH3), the unit NVLink moves efficiently.
 __global__ void __launch_bounds__(256, 8) k_fold_rows(int64_t n, int64_t cap, RecordsDev recs, GroupsDev gd) {
   const int lane = threadIdx.x & 31;
   const int64_t words = (n + 31) / 32;
   const size_t plane = al256((size_t)words * 4);
   const size_t rows_off = 256 + 3 * plane + al256((size_t)cap * 4) + al256((size_t)cap * 16);
+  const int pad = row_pad(gd.total);
   const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   for (int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < words; w += warps) {
-    unsigned any = 0u;
-    for (int j = 0; j < recs.count; ++j) any |= *(const uint32_t *)((const char *)recs.rec[j] + 256 + plane + 4 * w);
+    unsigned vb0 = 0u, bs0 = 0u, vb1 = 0u, bs1 = 0u;  // images lane and lane + 32
+    if (lane < recs.count) {
+      const char *rec = (const char *)recs.rec[lane] + 256;
+      vb0 = *(const uint32_t *)(rec + plane + 4 * w); bs0 = *(const uint32_t *)(rec + 2 * plane + 4 * w);
+    }
+    if (lane + 32 < recs.count) {
+      const char *rec = (const char *)recs.rec[lane + 32] + 256;
+      vb1 = *(const uint32_t *)(rec + plane + 4 * w); bs1 = *(const uint32_t *)(rec + 2 * plane + 4 * w);
+    }
+    unsigned any = __reduce_or_sync(GS_FULL, vb0 | vb1);
     while (any) {
-      int b = __ffs(any) - 1;
+      const int b = __ffs(any) - 1;
       any &= any - 1;
       const unsigned bit = 1u << b;
       const int64_t id = w * 32 + b;
-      for (int e = lane; e < gd.total; e += 32) {
-        int g = 0;
+      const unsigned m0 = __ballot_sync(GS_FULL, (vb0 & bit) != 0u), m1 = __ballot_sync(GS_FULL, (vb1 & bit) != 0u);
+      const unsigned p0 = bs0 + __popc(vb0 & (bit - 1u)), p1 = bs1 + __popc(vb1 & (bit - 1u));  // row position in my images
+      for (int e0 = 0; e0 < pad; e0 += 64) {  // warp-uniform trip count: the shuffles below need every lane
+        const int e = e0 + 2 * lane;
+        const bool act = e < pad;
+        // the two elements e, e+1 of the row: their group planes in the dense gradient buffer
+        float *dst[2];
 #pragma unroll
-        for (int k = 1; k < GS_EXCHANGE_MAX_GROUPS; ++k) g += (k < gd.count && e >= gd.start[k]);
-        const int k = e - gd.start[g], dim = gd.dim[g];
-        const int64_t rplane = (int64_t)cap * gd.start[g];
-        float *dst = gd.grad[g] + id * dim + k;
-        float acc = *dst;
-#pragma unroll 4
-        for (int j = 0; j < recs.count; ++j) {
-          const char *rec = (const char *)recs.rec[j];
-          unsigned vb = *(const uint32_t *)(rec + 256 + plane + 4 * w);
-          if (!(vb & bit)) continue;
-          uint32_t pos = *(const uint32_t *)(rec + 256 + 2 * plane + 4 * w) + __popc(vb & (bit - 1u));
-          if (pos >= (uint32_t)cap) continue;
-          acc += ((const float *)(rec + rows_off))[rplane + (int64_t)pos * dim + k];
+        for (int q = 0; q < 2; ++q) {
+          dst[q] = nullptr;
+          if (e + q < gd.total) {
+            int k, dim; float *plane;
+            group_of(gd, e + q, k, dim, plane);
+            dst[q] = plane + id * dim + k;
+          }
         }
-        *dst = acc;
+        float a0 = dst[0] ? *dst[0] : 0.f, a1 = dst[1] ? *dst[1] : 0.f;
+        // the row's images in batches of 4: all record loads of a batch are in flight together (one NVLink round
+        // trip), the adds then run in image order
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          unsigned m = half ? m1 : m0;
+          const unsigned pmine = half ? p1 : p0;
+          while (m) {
+            float2 v[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              v[c] = make_float2(0.f, 0.f);
+              const bool have = m != 0u;
+              const int j = have ? __ffs(m) - 1 : 0;
+              m &= m - 1;  // (0 & anything stays 0)
+              const unsigned pos = __shfl_sync(GS_FULL, pmine, j);
+              if (have && act && pos < (unsigned)cap)
+                v[c] = *(const float2 *)((const char *)recs.rec[j + 32 * half] + rows_off + 4 * ((size_t)pos * pad + e));
+            }
+#pragma unroll
+            for (int c = 0; c < 4; ++c) { a0 += v[c].x; a1 += v[c].y; }
+          }
+        }
+        if (dst[0]) *dst[0] = a0;
+        if (dst[1]) *dst[1] = a1;
       }
     }
   }
@@ -363,7 +417,7 @@ int make_groups(const gs_exchange_groups *h, GroupsDev *gd) {
 extern "C" size_t gs_exchange_record_bytes(int64_t n, int64_t cap, int row_floats) {
   if (n < 0 || cap < 0 || row_floats < 0) return 0;
   size_t words = (size_t)((n + 31) / 32);
-  return 256 + 3 * al256(words * 4) + al256((size_t)cap * 4) + al256((size_t)cap * 16) + al256((size_t)cap * row_floats * 4);
+  return 256 + 3 * al256(words * 4) + al256((size_t)cap * 4) + al256((size_t)cap * 16) + al256((size_t)cap * row_pad(row_floats) * 4);
 }
 
 extern "C" size_t gs_exchange_pack_workspace_bytes(int64_t n) {

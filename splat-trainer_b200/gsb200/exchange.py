@@ -98,6 +98,7 @@ class ImageExchange:
       dist.all_reduce(self._token, group=self.group)
     elif self.transport == "nccl":
       dist.all_gather_into_tensor(self.gathered, self.buf, group=self.group)
+    scene._mark("exchange_wait")  # barrier / all-gather, including the wait for the slowest rank's image
     ptrs = extra_ptrs if extra_ptrs is not None else self.record_ptrs()
     ops.exchange_fold(self.n, ptrs, self.cap, self.groups, c.split_alpha, c.prune_alpha, scene.stats,
                       scene_visible=scene.visible)
