@@ -225,12 +225,15 @@ def run_b200(args):
   scene = SplatScene(g, SceneConfig(sh_degree=deg))
   if args.exchange == "local":  # N=1 only: run the pack/fold kernels of the DP exchange on one GPU (for profiling them)
     from gsb200.exchange import ImageExchange
-    trainer = Trainer(scene, 1, 0, exchange=ImageExchange(scene, 1, 0, transport="local"))
+    local_k = int(os.environ.get("GS_LOCAL_IMAGES", "1"))  # K different images per step packed + folded on one GPU
+    trainer = Trainer(scene, 1, 0, exchange=ImageExchange(scene, 1, 0, transport="local", images_per_rank=local_k))
   else:
     trainer = Trainer(scene, world, rank, exchange=args.exchange)
 
   def batch_for(i, targets):
     # the step's full batch has `world` images; only this rank's entry is materialised (others are None-padded)
+    if args.exchange == "local":
+      return [(lcams[(i + q) % len(lcams)], targets[(i + q) % len(targets)]) for q in range(trainer.exchange.k)]
     b = [None] * world
     b[rank] = (lcams[i % len(lcams)], targets[i % len(targets)])
     return b

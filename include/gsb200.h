@@ -314,12 +314,15 @@ int gs_exchange_pack(int64_t n, const float *g2d, const float *vis, int vis_stri
                      float *clear_vis, const gs_exchange_groups *groups, void *record, int64_t cap,
                      void *workspace, size_t workspace_bytes, void *stream);
 /* records: HOST array of n_images device (or peer) pointers, in image order.  Adds every record's rows into the
- * gradient planes and folds the statistics: split_score / prune_cost by exp_lerp over in-view rows (0 for rows no
- * pixel blended), points_in_view += 1, visibility += vis, scene_visible += vis for blended rows. */
+ * gradient planes and their visibility into scene_visible (every rank needs both in full for the optimiser), and folds
+ * the controller statistics of rows [stats_begin, stats_end) (4-row aligned; the whole scene on one GPU, this rank's
+ * slice under DP — the statistics are only read at a densification, where the slices are all-gathered):
+ * split_score / prune_cost by exp_lerp over in-view rows (0 for rows no pixel blended), points_in_view += 1,
+ * visibility += vis for blended rows. */
 int gs_exchange_fold(int64_t n, int n_images, const void *const *records, int64_t cap,
                      const gs_exchange_groups *groups, float split_alpha, float prune_alpha,
                      float *prune_cost, float *split_score, int16_t *points_in_view, float *visibility,
-                     float *scene_visible, void *stream);
+                     int64_t stats_begin, int64_t stats_end, float *scene_visible, void *stream);
 
 #ifdef __cplusplus
 }

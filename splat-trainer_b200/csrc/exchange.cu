@@ -18,8 +18,9 @@
 //   base     uint32[(n+31)/32]   number of visible rows before word w (rank of row i = base + popc(bits below i))
 //   idx      int32[cap]          ascending visible rows
 //   aux      float4[cap]         (visibility, prune heuristic, split heuristic, 0)
-//   rows     float[cap·P]        gradient rows, row-major, padded to P = D rounded up to 16 floats: a row is one or two
-//                                coalesced (NVLink-friendly) warp loads; group g's dim floats start at Σ dims before g
+//   rows     float[cap·P]        gradient rows, row-major: D gradient floats (group g's dim floats start at Σ dims before
+//                                g), then the row's visibility, padded to P = 16-float multiple: a row is one or two
+//                                coalesced (NVLink-friendly) warp loads
 #include "common.cuh"
 
 namespace {
@@ -48,13 +49,15 @@ __host__ __device__ inline RecView rec_view(void *rec, int64_t n, int64_t cap) {
   return v;
 }
 
-__host__ __device__ inline int row_pad(int d) { return (d + 15) / 16 * 16; }
+// floats per record row: the D gradient floats + the row's visibility (element D), rounded up to 16 floats
+__host__ __device__ inline int row_pad(int d) { return (d + 1 + 15) / 16 * 16; }
 
 struct GroupsDev {
   int count, total;
   int dim[GS_EXCHANGE_MAX_GROUPS];
   int start[GS_EXCHANGE_MAX_GROUPS];  // first flattened element of the group
   float *grad[GS_EXCHANGE_MAX_GROUPS];
+  float *vis;  // fold only: the scene's `visible` plane, fed by element `total` of every record row (nullable)
 };
 
 // group of flattened row element e -> (offset inside the group, dim, dense plane).  Static indices only: a dynamically
@@ -234,6 +237,8 @@ __global__ void __launch_bounds__(256) k_pack_rows(int64_t cap, RecView rv, Grou
         group_of(gd, e, k, dim, plane);
         src = plane + id * dim + k;
         val = __ldcg(src);
+      } else if (e == gd.total) {
+        val = rv.aux[j].x;  // the row's visibility travels with its gradients (the fold sums it into `visible`)
       }
       rv.rows[(int64_t)j * pad + e] = val;
       // clear AFTER the dependent record store: a store issued right behind the load of the same address stalled the
@@ -250,15 +255,15 @@ constexpr int FS_CHUNK = 4;
 __global__ void __launch_bounds__(256) k_fold_stats(int64_t n, int64_t cap, RecordsDev recs, float split_alpha, float prune_alpha,
                                                     float *__restrict__ prune_cost, float *__restrict__ split_score,
                                                     int16_t *__restrict__ points_in_view, float *__restrict__ visibility,
-                                                    float *__restrict__ scene_visible) {
-  int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
-  if (i0 >= n) return;
+                                                    int64_t row_begin, int64_t row_end) {
+  int64_t i0 = row_begin + ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;  // row_begin is a multiple of 4
+  if (i0 >= row_end) return;
   const int64_t w = i0 >> 5;
   const int sh = (int)(i0 & 31);
   const size_t words = (size_t)((n + 31) / 32);
   const size_t plane = al256(words * 4);
   const size_t aux_off = 256 + 3 * plane + al256((size_t)cap * 4);
-  const bool full = i0 + 3 < n;
+  const bool full = i0 + 3 < row_end;
   float split[4], prune[4];
   if (full) {
     float4 a = *reinterpret_cast<const float4 *>(split_score + i0), b = *reinterpret_cast<const float4 *>(prune_cost + i0);
@@ -267,8 +272,8 @@ __global__ void __launch_bounds__(256) k_fold_stats(int64_t n, int64_t cap, Reco
   } else {
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      split[q] = (i0 + q < n) ? split_score[i0 + q] : 0.f;
-      prune[q] = (i0 + q < n) ? prune_cost[i0 + q] : 0.f;
+      split[q] = (i0 + q < row_end) ? split_score[i0 + q] : 0.f;
+      prune[q] = (i0 + q < row_end) ? prune_cost[i0 + q] : 0.f;
     }
   }
   unsigned any = 0u;
@@ -301,7 +306,6 @@ __global__ void __launch_bounds__(256) k_fold_stats(int64_t n, int64_t cap, Reco
             if (ax.x > 0.f) {
               points_in_view[i0 + q] += 1;
               visibility[i0 + q] += ax.x;
-              if (scene_visible) scene_visible[i0 + q] += ax.x;
             }
             hp = ax.y; hs = ax.z;
           }
@@ -318,7 +322,7 @@ __global__ void __launch_bounds__(256) k_fold_stats(int64_t n, int64_t cap, Reco
   } else {
 #pragma unroll
     for (int q = 0; q < 4; ++q)
-      if (i0 + q < n) { split_score[i0 + q] = split[q]; prune_cost[i0 + q] = prune[q]; }
+      if (i0 + q < row_end) { split_score[i0 + q] = split[q]; prune_cost[i0 + q] = prune[q]; }
   }
 }
 
@@ -333,6 +337,16 @@ __global__ void __launch_bounds__(256, 8) k_fold_rows(int64_t n, int64_t cap, Re
   const size_t rows_off = 256 + 3 * plane + al256((size_t)cap * 4) + al256((size_t)cap * 16);
   const int pad = row_pad(gd.total);
   const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  // this lane's two elements of the first 64 floats of a row (all of it for SH degree <= 3): group plane, dim, offset
+  int hk[2], hdim[2];
+  float *hplane[2];
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int e = 2 * lane + q;
+    hk[q] = 0; hdim[q] = 0; hplane[q] = nullptr;
+    if (e < gd.total) group_of(gd, e, hk[q], hdim[q], hplane[q]);
+    else if (e == gd.total) { hdim[q] = 1; hplane[q] = gd.vis; }
+  }
   for (int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < words; w += warps) {
     unsigned vb0 = 0u, bs0 = 0u, vb1 = 0u, bs1 = 0u;  // images lane and lane + 32
     if (lane < recs.count) {
@@ -358,11 +372,17 @@ __global__ void __launch_bounds__(256, 8) k_fold_rows(int64_t n, int64_t cap, Re
         float *dst[2];
 #pragma unroll
         for (int q = 0; q < 2; ++q) {
-          dst[q] = nullptr;
-          if (e + q < gd.total) {
-            int k, dim; float *plane;
-            group_of(gd, e + q, k, dim, plane);
-            dst[q] = plane + id * dim + k;
+          if (e0 == 0) {
+            dst[q] = hplane[q] ? hplane[q] + id * hdim[q] + hk[q] : nullptr;
+          } else {
+            dst[q] = nullptr;
+            if (e + q < gd.total) {
+              int k, dim; float *plane;
+              group_of(gd, e + q, k, dim, plane);
+              dst[q] = plane + id * dim + k;
+            } else if (e + q == gd.total && gd.vis) {
+              dst[q] = gd.vis + id;
+            }
           }
         }
         float a0 = dst[0] ? *dst[0] : 0.f, a1 = dst[1] ? *dst[1] : 0.f;
@@ -409,6 +429,7 @@ int make_groups(const gs_exchange_groups *h, GroupsDev *gd) {
     }
   }
   gd->total = s;
+  gd->vis = nullptr;
   return 0;
 }
 
@@ -459,13 +480,16 @@ extern "C" int gs_exchange_pack(int64_t n, const float *g2d, const float *vis, i
 
 extern "C" int gs_exchange_fold(int64_t n, int n_images, const void *const *records, int64_t cap,
                                 const gs_exchange_groups *groups, float split_alpha, float prune_alpha, float *prune_cost,
-                                float *split_score, int16_t *points_in_view, float *visibility, float *scene_visible,
-                                void *stream) {
+                                float *split_score, int16_t *points_in_view, float *visibility, int64_t stats_begin,
+                                int64_t stats_end, float *scene_visible, void *stream) {
   GS_REQUIRE(n > 0 && n < ((int64_t)1 << 30), "n must be in [1, 2^30)");
   GS_REQUIRE(n_images >= 1 && n_images <= GS_EXCHANGE_MAX_IMAGES, "n_images must be 1..GS_EXCHANGE_MAX_IMAGES");
   GS_REQUIRE(records && prune_cost && split_score && points_in_view && visibility, "null argument");
+  GS_REQUIRE(stats_begin >= 0 && stats_begin <= stats_end && stats_end <= n, "bad statistics row range");
+  GS_REQUIRE(stats_begin % 4 == 0 && (stats_end % 4 == 0 || stats_end == n), "statistics row range must be 4-row aligned");
   GroupsDev gd;
   GS_REQUIRE(make_groups(groups, &gd) == 0, "bad parameter groups");
+  gd.vis = scene_visible;
   RecordsDev rd;
   rd.count = n_images;
   for (int j = 0; j < GS_EXCHANGE_MAX_IMAGES; ++j) {
@@ -473,9 +497,12 @@ extern "C" int gs_exchange_fold(int64_t n, int n_images, const void *const *reco
     GS_REQUIRE(j >= n_images || records[j], "null record");
   }
   cudaStream_t st = (cudaStream_t)stream;
-  k_fold_stats<<<gs_div_up((n + 3) / 4, 256), 256, 0, st>>>(n, cap, rd, split_alpha, prune_alpha, prune_cost, split_score,
-                                                            points_in_view, visibility, scene_visible);
-  GS_LAUNCH_CHECK();
+  if (stats_end > stats_begin) {
+    int64_t threads = (stats_end - stats_begin + 3) / 4;
+    k_fold_stats<<<gs_div_up(threads, 256), 256, 0, st>>>(n, cap, rd, split_alpha, prune_alpha, prune_cost, split_score,
+                                                          points_in_view, visibility, stats_begin, stats_end);
+    GS_LAUNCH_CHECK();
+  }
   {
     int64_t words = (n + 31) / 32, want = (words + 7) / 8;
     k_fold_rows<<<(int)(want < 148 * 64 ? want : 148 * 64), 256, 0, st>>>(n, cap, rd, gd);

@@ -11,6 +11,10 @@ Transport (the records are written once and read in place):
           double-buffered by step parity so one barrier per step is enough.
   "nccl"  plain buffers + one all_gather_into_tensor of the fixed-capacity records, folded from the local copy.
   "local" world size 1 (or tests): records of several emulated ranks in one process.
+
+Every rank needs the summed gradients and `visible` in full (replicated optimiser), so those are folded for all rows by
+every rank; the controller statistics (split_score, prune_cost, points_in_view, visibility) are folded by each rank for
+its own row slice only and all-gathered when a densification reads them (Trainer.sync_statistics).
 """
 import torch
 import torch.distributed as dist
@@ -54,6 +58,12 @@ class ImageExchange:
     elif self.transport == "local":
       self.buf = torch.zeros((slot_bytes,), device=dev, dtype=torch.uint8)
     self._token = torch.zeros((1,), device=dev)
+    # controller statistics are only read at a densification: every rank folds them for its own slice of the rows
+    # (Trainer.sync_statistics all-gathers the slices), so the statistics cost per rank does not grow with the world
+    self.slice_len = (self.n + world - 1) // world
+    self.slice_len = (self.slice_len + 127) // 128 * 128
+    b = min(rank * self.slice_len, self.n)
+    self.stats_rows = (b, min(b + self.slice_len, self.n)) if world > 1 else (0, self.n)
     self._grads_ptr = scene.grads.data_ptr()
 
   def stale(self):
@@ -101,7 +111,7 @@ class ImageExchange:
     scene._mark("exchange_wait")  # barrier / all-gather, including the wait for the slowest rank's image
     ptrs = extra_ptrs if extra_ptrs is not None else self.record_ptrs()
     ops.exchange_fold(self.n, ptrs, self.cap, self.groups, c.split_alpha, c.prune_alpha, scene.stats,
-                      scene_visible=scene.visible)
+                      scene_visible=scene.visible, stats_rows=self.stats_rows)
     if self.transport == "peer":
       self.parity ^= 1
 

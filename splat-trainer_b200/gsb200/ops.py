@@ -358,10 +358,12 @@ def exchange_pack(g2d, vis, heur, max_scale_px, groups, record, cap, workspace, 
                                     workspace.numel(), L.stream()))
 
 
-def exchange_fold(n, record_ptrs, cap, groups, split_alpha, prune_alpha, state, scene_visible=None):
-  """record_ptrs: device (or peer-mapped) addresses of the step's records in image order."""
+def exchange_fold(n, record_ptrs, cap, groups, split_alpha, prune_alpha, state, scene_visible=None, stats_rows=None):
+  """record_ptrs: device (or peer-mapped) addresses of the step's records in image order.  stats_rows: (begin, end) of
+  the rows whose controller statistics this call folds (default: all)."""
   arr = (C.c_void_p * len(record_ptrs))(*[int(p) for p in record_ptrs])
+  b, e = (0, n) if stats_rows is None else stats_rows
   L.check(L.load().gs_exchange_fold(n, len(record_ptrs), arr, int(cap), C.byref(groups), split_alpha, prune_alpha,
                                     L.ptr(state["prune_cost"]), L.ptr(state["split_score"]),
-                                    L.ptr(state["points_in_view"]), L.ptr(state["visibility"]), L.ptr(scene_visible),
-                                    L.stream()))
+                                    L.ptr(state["points_in_view"]), L.ptr(state["visibility"]), int(b), int(e),
+                                    L.ptr(scene_visible), L.stream()))

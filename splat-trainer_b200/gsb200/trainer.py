@@ -92,10 +92,25 @@ class Trainer:
     return rows
 
   def sync_statistics(self):
-    """before a densification under DP: max_scale_px is kept per rank (MAX is order independent), every other
-    statistic is already identical on all ranks (folded in image order by the exchange)."""
-    if self.world_size > 1:
-      dist.all_reduce(self.scene.stats["max_scale_px"], op=dist.ReduceOp.MAX)
+    """before a densification (or any read of scene.stats) under DP: max_scale_px is kept per rank (MAX is order
+    independent); the other statistics were folded in image order by the rank that owns the row slice — all-gather the
+    slices.  Afterwards scene.stats is complete and identical on every rank."""
+    if self.world_size <= 1:
+      return
+    st = self.scene.stats
+    dist.all_reduce(st["max_scale_px"], op=dist.ReduceOp.MAX)
+    ex = self.exchange
+    if ex is None or ex.stats_rows == (0, self.scene.n):
+      return
+    b, e = ex.stats_rows
+    for k in ("prune_cost", "split_score", "visibility", "points_in_view"):
+      t = st[k]
+      dt = torch.int32 if t.dtype == torch.int16 else t.dtype  # NCCL has no int16
+      send = torch.zeros((ex.slice_len,), device=t.device, dtype=dt)
+      send[:e - b] = t[b:e].to(dt)
+      out = torch.empty((self.world_size * ex.slice_len,), device=t.device, dtype=dt)
+      dist.all_gather_into_tensor(out, send, group=ex.group)
+      t.copy_(out[:self.scene.n].to(t.dtype))
 
   def training_step(self, batch, read_loss=False):
     """batch: list of (camera, target image) for the WHOLE step (all ranks pass the same list); this rank

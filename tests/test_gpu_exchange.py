@@ -90,6 +90,24 @@ def test_pack_fold_equals_sequential_accumulation(n, images, p_view, p_vis, cap)
     assert torch.equal(ex_state[k], seq_state[k]), k
   # max_scale_px is kept per rank and MAX-reduced before a densification
   assert torch.equal(torch.stack(rank_max).amax(dim=0), seq_state["max_scale_px"])
+  # statistics folded slice by slice (what the ranks of a DP job do) == folded whole
+  if n >= 64:
+    h = (n // 2) // 4 * 4
+    sl_state, sl_vis = _state(n), torch.zeros((n,), device="cuda")
+    scratch = [torch.zeros((n, d), device="cuda") for d in DIMS]
+    sgroups, _ = ops.exchange_groups(scratch)
+    ptrs = [records[j].data_ptr() for j in range(images)]
+    ops.exchange_fold(n, ptrs, cap, sgroups, sa, pa, sl_state, scene_visible=sl_vis, stats_rows=(0, h))
+    assert not sl_state["split_score"][h:].any() and not sl_state["points_in_view"][h:].any()
+    for t in scratch:
+      t.zero_()
+    sl_vis.zero_()
+    ops.exchange_fold(n, ptrs, cap, sgroups, sa, pa, sl_state, scene_visible=sl_vis, stats_rows=(h, n))
+    for k in ("prune_cost", "split_score", "points_in_view", "visibility"):
+      assert torch.equal(sl_state[k], ex_state[k]), k
+    assert torch.equal(sl_vis, ex_vis)
+    for t, g in zip(scratch, ex_grads):
+      assert torch.equal(t, g)
   # and against the CPU oracle's sequential restatement
   for k in ("prune_cost", "split_score", "visibility"):
     np.testing.assert_allclose(npy(ex_state[k]), ref_state[k], rtol=2e-5, atol=2e-6, err_msg=k)
