@@ -123,8 +123,14 @@ class CpuIteration:
     image, fT, nc, _, _ = o.raster_fwd(cfg, g2d, rgb, depth, o2p, ranges, W, H, visibility=False)
     dimg, sums = o.loss_l1_mse(image, None, 0.0, 10.0, target_u8=self.targets[i % len(self.targets)])
     acc = o.raster_bwd(cfg, g2d, rgb, o2p, ranges, W, H, fT, nc, dimg)
+    # reg_loss with the reference's yaml weights, like SplatScene.forward_backward
+    vis = np.ascontiguousarray(acc[:, 11]); d_op = np.ascontiguousarray(acc[:, 5])
+    d_depth = np.zeros_like(vis); d_ls = np.zeros((vis.shape[0], 3), np.float32)
+    o.reg_loss((0.01, 1.0, 1e-4), g2d, depth, g["log_scaling"], vis, d_op, d_depth, d_ls)
+    acc[:, 5] = d_op
     grads = o.project_bwd(cam, cfg, g["position"], g["log_scaling"], g["rotation"], g["alpha_logit"], g["sh"], self.deg,
-                          g2d, acc[:, 0:6], acc[:, 6:9], None, row_vis=acc[:, 11])
+                          g2d, acc[:, 0:6], acc[:, 6:9], d_depth, row_vis=acc[:, 11])
+    grads["log_scaling"] = grads["log_scaling"] + d_ls
     st = self.stats
     o.accumulate_stats(None, g2d, np.ascontiguousarray(acc[:, 11]), np.ascontiguousarray(acc[:, 9:11]), 0.01, 0.1, st)
     vis = st["scene_visible"]

@@ -324,6 +324,30 @@ int gs_exchange_fold(int64_t n, int n_images, const void *const *records, int64_
                      float *prune_cost, float *split_score, int16_t *points_in_view, float *visibility,
                      int64_t stats_begin, int64_t stats_end, float *scene_visible, void *stream);
 
+/* ---------------------------------------------------------------------------------------
+ * (7) Per-step controller / scene passes over every splat.
+ * ------------------------------------------------------------------------------------- */
+/* MCMCController.step, noise branch (reference controller/mcmc_controller.py:91-100): rows with
+ * points_in_view > min_views move by point_basis(log_scaling, rotation) · (randn · soft_lt(sigmoid(alpha_logit),
+ * opacity_threshold/2, margin 16) · noise_level)   (soft_lt util/misc.py:20-37, sample_gaussians
+ * gaussians/split.py:31-36).  randn: caller-supplied N(0,1) draws (n×3), so every rank and the oracle add the same
+ * noise.  The prune/respawn branch (:76-89) is mask algebra + gs_select_topk_mask + the densification kernels. */
+int gs_mcmc_noise(int64_t n, const float *alpha_logit, const float *log_scaling, const float *rotation,
+                  const int16_t *points_in_view, int min_views, float opacity_threshold, float noise_level,
+                  const float *randn, float *position, void *stream);
+
+/* MLPScene.compute_reg / reg_loss (reference scene/mlp_scene.py:246-288; saturate util/misc.py:68-69) over the rows a
+ * pixel blended (vis > 0, weight w = vis, m = their count; rows are Gaussians, opacity = g2d[5], depth = z_cam):
+ *   scale = mean(w·Σ exp(s)²/depth²)   opacity = mean(w·(1−e^(−4·op))²·Σ exp(s)²/depth²)   aspect = mean(w·max exp(s)/min exp(s))
+ * compute_sums != 0: sums[0..2] = Σ of the three terms, sums[3] = m (device floats; the loss is Σ weight_k·sums[k]/m).
+ * Any gradient pointer non-NULL: gradients of Σ weight_k·reg_k using sums[3] (from this or an earlier call on the
+ * stream) are ADDED to d_opacity[i·stride] (the raster accumulator's opacity column), WRITTEN to d_depth[i] (read by
+ * gs_project_bwd for blended rows only) and ADDED to d_log_scaling (n×3).  The specular term belongs to the colour
+ * MLP and is not part of this path. */
+int gs_reg_loss(int64_t n, float w_scale, float w_opacity, float w_aspect, const float *g2d, const float *depth,
+                const float *log_scaling, const float *vis, int vis_stride, float *sums, int compute_sums,
+                float *d_opacity, int d_opacity_stride, float *d_depth, float *d_log_scaling, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -276,3 +276,22 @@ class Oracle:
                                  self.p(rotation), self.p(uniform), self.creal(sep), self.p(op), self.p(ols),
                                  C.c_int64(0))
     return op, ols
+
+  def mcmc_noise(self, alpha_logit, log_scaling, rotation, points_in_view, min_views, opacity_threshold, noise_level,
+                 randn, position):
+    """in place on `position` (must be this oracle's real dtype and contiguous)."""
+    al, ls, q, rn = map(self.r, (alpha_logit, log_scaling, rotation, randn))
+    piv = np.ascontiguousarray(points_in_view, np.int16)
+    assert position.dtype == self.real and position.flags["C_CONTIGUOUS"]
+    self.lib.gso_mcmc_noise(C.c_int64(al.shape[0]), self.p(al), self.p(ls), self.p(q), self.p(piv), C.c_int(min_views),
+                            self.creal(opacity_threshold), self.creal(noise_level), self.p(rn), self.p(position))
+
+  def reg_loss(self, weights, g2d, depth, log_scaling, vis, d_opacity=None, d_depth=None, d_log_scaling=None):
+    """weights = (scale, opacity, aspect).  Returns sums (4,); gradient arrays (own dtype, contiguous (n,)/(n,3))
+    are updated in place when given."""
+    g2d, depth, ls, vis = map(self.r, (g2d, depth, log_scaling, vis))
+    sums = np.zeros(4, self.real)
+    self.lib.gso_reg_loss(C.c_int64(g2d.shape[0]), self.creal(weights[0]), self.creal(weights[1]), self.creal(weights[2]),
+                          self.p(g2d), self.p(depth), self.p(ls), self.p(vis), self.p(sums), self.p(d_opacity), C.c_int(1),
+                          self.p(d_depth), self.p(d_log_scaling))
+    return sums

@@ -367,3 +367,29 @@ def exchange_fold(n, record_ptrs, cap, groups, split_alpha, prune_alpha, state, 
                                     L.ptr(state["prune_cost"]), L.ptr(state["split_score"]),
                                     L.ptr(state["points_in_view"]), L.ptr(state["visibility"]), int(b), int(e),
                                     L.ptr(scene_visible), L.stream()))
+
+
+# ---- per-step controller / scene passes (include/gsb200.h section 7) -----------------------------------------------
+def mcmc_noise(alpha_logit, log_scaling, rotation, points_in_view, min_views, opacity_threshold, noise_level, randn,
+               position):
+  """in place on position (n,3); randn (n,3) N(0,1) draws supplied by the caller."""
+  n = position.shape[0]
+  assert points_in_view.dtype == torch.int16
+  L.check(L.load().gs_mcmc_noise(n, L.ptr(_f32(alpha_logit)), L.ptr(_f32(log_scaling)), L.ptr(_f32(rotation)),
+                                 L.ptr(points_in_view), int(min_views), float(opacity_threshold), float(noise_level),
+                                 L.ptr(_f32(randn)), L.ptr(_f32(position)), L.stream()))
+
+
+def reg_loss(weights, g2d, depth, log_scaling, vis, sums=None, compute_sums=True, d_opacity=None, d_depth=None,
+             d_log_scaling=None):
+  """weights = (scale, opacity, aspect).  vis / d_opacity may be strided column views.  Returns sums (4,) on the device:
+  Σ scale terms, Σ opacity terms, Σ aspect terms, number of blended rows."""
+  n = g2d.shape[0]
+  if sums is None:
+    sums = torch.zeros((4,), device=g2d.device, dtype=torch.float32)
+  L.check(L.load().gs_reg_loss(n, float(weights[0]), float(weights[1]), float(weights[2]), L.ptr(_f32(g2d)),
+                               L.ptr(_f32(depth)), L.ptr(_f32(log_scaling)), vis.data_ptr(), vis.stride(0), L.ptr(sums),
+                               int(compute_sums), None if d_opacity is None else d_opacity.data_ptr(),
+                               0 if d_opacity is None else d_opacity.stride(0), L.ptr(d_depth), L.ptr(d_log_scaling),
+                               L.stream()))
+  return sums

@@ -40,6 +40,9 @@ class SceneConfig:
   antialias: bool = False        # reference trainer/trainer.py:308-310: blur_cov = 0.0 if antialias else 0.3
   blur_cov: float = 0.3
   max_overlaps: int = 0          # capacity of the tile-overlap list; 0 = calibrate on first use
+  # reg_weight (scale, opacity, aspect): reference config/scene/mlp.yaml:16-19 at t = 0 (the log_decay schedules are the
+  # caller's: assign scene.config.reg_weights per step).  (0, 0, 0) disables the two regularisation sweeps.
+  reg_weights: tuple = (0.01, 1.0, 1e-4)
 
 
 def _plane_offsets(n, dims):
@@ -132,7 +135,8 @@ class SplatScene:
              acc=torch.zeros((n, stride), device=dev), vis=torch.zeros((n,), device=dev), tinfo=ops.TileInfo(n, W, H, dev),
              image=torch.empty((H, W, 3), device=dev), final_T=torch.empty((H, W), device=dev),
              n_contrib=torch.empty((H, W), device=dev, dtype=torch.int32), d_image=torch.empty((H, W, 3), device=dev),
-             loss_sums=torch.zeros((2,), device=dev), tile=None)
+             loss_sums=torch.zeros((2,), device=dev), reg_sums=torch.zeros((4,), device=dev),
+             d_depth=torch.zeros((n,), device=dev), tile=None)
     self._work = w
     return w
 
@@ -185,6 +189,39 @@ class SplatScene:
     return dict(image=w["image"].clamp(0, 1), raw=w["image"], weight=1.0 - w["final_T"], visibility=vis,
                 median_depth=med, g2d=w["g2d"], depth=w["depth"])
 
+  def query_visibility(self, cam):
+    """MLPScene.query_visibility (reference scene/mlp_scene.py:372-381): forward-only render for (idx, visibility) of
+    the splats a pixel blends.  Returns (idx int64 ascending, visibility) — one host sync for the count, like the
+    reference's nonzero()."""
+    _, _, vis, _ = self._forward(cam, visibility=True)
+    idx = (vis > 0).nonzero().squeeze(1)
+    return idx, vis[idx]
+
+  def reg_value(self):
+    """Σ weight_k · reg_k of the last forward_backward image (device scalar; reference reg_loss's return value)."""
+    s, wts = self._work["reg_sums"], self.config.reg_weights
+    return (wts[0] * s[0] + wts[1] * s[1] + wts[2] * s[2]) / s[3].clamp_min(1.0)
+
+  # ---- MCMC controller (reference controller/mcmc_controller.py:69-100) ---------------------------------------------
+  def mcmc_noise(self, noise_level, min_views=5, opacity_threshold=0.1, randn=None):
+    """noise branch (:91-100).  randn: (N,3) N(0,1) draws (None: torch's CUDA generator; seed it identically on every
+    rank).  The reference writes through a boolean-masked TensorDict copy; the intended effect — the noise is added to
+    the positions — is what is implemented."""
+    if randn is None:
+      randn = torch.randn((self.n, 3), device=self.device)
+    ops.mcmc_noise(self.p["alpha_logit"], self.p["log_scaling"], self.p["rotation"], self.stats["points_in_view"], min_views,
+                   opacity_threshold, noise_level, randn, self.p["position"])
+
+  def mcmc_find_prune_split(self, opacity_threshold=0.1, max_scale_px=200.0, min_split_px=0.0):
+    """prune / respawn branch (:76-89): prune large or transparent splats and split as many by top split_score."""
+    st = self.stats
+    opacity = torch.sigmoid(self.p["alpha_logit"])
+    prune_mask = (st["max_scale_px"] > max_scale_px) | (opacity < opacity_threshold)
+    n = int(prune_mask.sum().item())
+    score = torch.where(prune_mask | (st["max_scale_px"] < min_split_px), torch.zeros_like(st["split_score"]), st["split_score"])
+    split_mask = ops.select_topk_mask(score, n, descending=1)
+    return split_mask, prune_mask
+
   # ---- one training image: forward + loss + backward + statistics ------------------------------------------
   def forward_backward(self, cam, target, first=False, exchange=None, slot=0):
     """Reference trainer/trainer.py:500-514 for one image (render → loss → backward → add_rendering), fused:
@@ -204,9 +241,19 @@ class SplatScene:
                    w["final_T"], w["n_contrib"], w["d_image"], acc=acc, vis_plane=w["vis"])
     self._mark("raster_bwd")
     p = self.p
+    reg = any(x != 0.0 for x in c.reg_weights)
+    if reg:
+      # reg_loss (reference scene/mlp_scene.py:246-288) over the rows this image blended: its gradient w.r.t. the
+      # projected opacity / depth joins the raster gradients BEFORE the projection backward consumes them
+      ops.reg_loss(c.reg_weights, w["g2d"], w["depth"], p["log_scaling"], w["vis"], sums=w["reg_sums"], compute_sums=True,
+                   d_opacity=acc[:, 5], d_depth=w["d_depth"])
+      self._mark("reg")
     ops.project_bwd(cam, self.raster_cfg, p["position"], p["log_scaling"], p["rotation"], p["alpha_logit"], p["sh"],
-                    c.sh_degree, w["g2d"], acc[:, 0:6], acc[:, 6:9], None, row_vis=w["vis"], grads=self.g,
-                    accumulate=not (first or exchange is not None))
+                    c.sh_degree, w["g2d"], acc[:, 0:6], acc[:, 6:9], w["d_depth"] if reg else None, row_vis=w["vis"],
+                    grads=self.g, accumulate=not (first or exchange is not None))
+    if reg:  # the direct d/d log_scaling part, on top of the rows the projection backward just wrote
+      ops.reg_loss(c.reg_weights, w["g2d"], w["depth"], p["log_scaling"], w["vis"], sums=w["reg_sums"], compute_sums=False,
+                   d_log_scaling=self.g["log_scaling"])
     self._mark("project_bwd")
     if exchange is not None:
       # the dense gradient buffer holds this image's rows only (pack moves them out and zeroes them again)

@@ -164,6 +164,51 @@ def main():
   split_mask, prune_mask = env["find_split_prune_indexes"](ctrl, 0.3, 3300)
   np.savez(os.path.join(OUT, "find_split_prune.npz"), t=np.float32(0.3), target_points=np.int64(3300),
            split_mask=split_mask.numpy(), prune_mask=prune_mask.numpy(), **{f"in_{k}": v for k, v in stats_in.items()})
+  # ---- MCMC controller: controller/mcmc_controller.py:69-100 -----------------------------------------------------
+  # noise branch (:91-100), executed with the reference's own soft_lt and sample_gaussians on recorded normals
+  n = 500
+  al = rng.normal(-1.0, 2.0, (n, 1)).astype(np.float32)
+  ls = rng.normal(-2, 1, (n, 3)).astype(np.float32); q = rng.normal(0, 1, (n, 4)).astype(np.float32)
+  pos = rng.normal(0, 1, (n, 3)).astype(np.float32)
+  piv = rng.integers(0, 12, n).astype(np.int16)
+  randn = rng.normal(0, 1, (n, 3)).astype(np.float32)
+  thr, min_views, level = 0.1, 5, 0.37
+  enough = torch.from_numpy(piv.astype(np.int64)) > min_views
+  opacity = torch.sigmoid(f32(al)).squeeze(1)
+  target = misc.soft_lt(opacity, thr / 2, margin=16.0)
+  sub = TensorDict(dict(log_scaling=f32(ls)[enough], rotation=f32(q)[enough]), [int(enough.sum())])
+  noise = f32(randn)[enough] * (target[enough] * level).unsqueeze(1)
+  out_pos = f32(pos).clone()
+  out_pos[enough] += split.sample_gaussians(sub, noise)
+  # prune / respawn branch (:76-89) with the reference's take_n
+  tn = extract("controller/target_controller.py", {"take_n"}, dict(torch=torch))["take_n"]
+  max_scale = f32(rng.uniform(0, 260, n)); sscore = f32(rng.uniform(0, 3, n))
+  prune_mask = (max_scale > 200.0) | (opacity < thr)
+  k = int(prune_mask.sum().item())
+  too_small = max_scale < 1.5
+  masked = torch.where(prune_mask | too_small, 0, sscore)
+  split_mask = tn(masked, k, descending=True)
+  np.savez(os.path.join(OUT, "mcmc.npz"), alpha_logit=al, log_scaling=ls, rotation=q, position=pos, points_in_view=piv,
+           randn=randn, opacity_threshold=np.float32(thr), min_views=np.int32(min_views), noise_level=np.float32(level),
+           out_position=out_pos.numpy(), max_scale_px=max_scale.numpy(), split_score=sscore.numpy(),
+           min_split_px=np.float32(1.5), prune_mask=prune_mask.numpy(), split_mask=split_mask.numpy())
+
+  # ---- regularisation: scene/mlp_scene.py:246-265 (compute_reg) + util/misc.py:68-69 (saturate) ------------------
+  env = extract("scene/mlp_scene.py", {"compute_reg"}, dict(torch=torch, saturate=misc.saturate))
+  m = 700
+  op = torch.from_numpy(rng.uniform(0.01, 0.99, m).astype(np.float32)).requires_grad_()
+  lsr = torch.from_numpy(rng.normal(-2, 1, (m, 3)).astype(np.float32)).requires_grad_()
+  dep = torch.from_numpy(rng.uniform(0.3, 20, (m, 1)).astype(np.float32)).requires_grad_()
+  wv = f32(rng.uniform(1e-3, 30, m))
+  regs = env["compute_reg"](None, op, lsr, dep, torch.zeros((m, 1)), wv)
+  weights = dict(scale=0.01, opacity=1.0, aspect=1e-4)  # config/scene/mlp.yaml:16-19 at t = 0
+  total = sum(regs[k] * w for k, w in weights.items())
+  total.backward()
+  np.savez(os.path.join(OUT, "reg_loss.npz"), opacity=op.detach().numpy(), log_scaling=lsr.detach().numpy(),
+           depths=dep.detach().numpy(), weight=wv.numpy(), w_scale=np.float32(0.01), w_opacity=np.float32(1.0),
+           w_aspect=np.float32(1e-4), reg_scale=regs["scale"].item(), reg_opacity=regs["opacity"].item(),
+           reg_aspect=regs["aspect"].item(), total=total.item(), d_opacity=op.grad.numpy(), d_log_scaling=lsr.grad.numpy(),
+           d_depths=dep.grad.numpy())
   print("golden vectors written to", OUT)
 
 

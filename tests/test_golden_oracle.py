@@ -123,3 +123,51 @@ def test_find_split_prune_matches_reference(orc):
   assert np.array_equal(split, g["split_mask"])
   n = stats["prune_cost"].shape[0]
   assert n - prune.sum() + split.sum() == int(g["target_points"])  # densify count invariant
+
+
+def test_mcmc_noise_matches_reference(orc):
+  """controller/mcmc_controller.py:91-100 run with the reference's own soft_lt / sample_gaussians on recorded normals."""
+  g = gold("mcmc.npz")
+  pos = g["position"].copy()
+  orc.mcmc_noise(g["alpha_logit"][:, 0], g["log_scaling"], g["rotation"], g["points_in_view"], int(g["min_views"]),
+                 float(g["opacity_threshold"]), float(g["noise_level"]), g["randn"], pos)
+  moved = g["points_in_view"] > int(g["min_views"])
+  assert moved.sum() > 100 and (~moved).sum() > 100
+  assert np.array_equal(pos[~moved], g["position"][~moved])
+  np.testing.assert_allclose(pos, g["out_position"], rtol=2e-5, atol=2e-6)
+  assert np.abs(pos[moved] - g["position"][moved]).max() > 1e-3
+
+
+def test_mcmc_prune_respawn_masks_match_reference(orc):
+  """controller/mcmc_controller.py:76-89: prune mask and the take_n respawn mask (same count)."""
+  g = gold("mcmc.npz")
+  op = 1.0 / (1.0 + np.exp(-g["alpha_logit"][:, 0].astype(np.float64)))
+  prune = (g["max_scale_px"] > 200.0) | (op.astype(np.float32) < float(g["opacity_threshold"]))
+  assert np.array_equal(prune, g["prune_mask"])
+  score = np.where(prune | (g["max_scale_px"] < float(g["min_split_px"])), 0.0, g["split_score"]).astype(np.float32)
+  split = orc.select_topk_mask(score, int(prune.sum()), descending=1)
+  assert np.array_equal(split, g["split_mask"])
+
+
+def test_reg_loss_matches_reference(orc):
+  """scene/mlp_scene.py:246-265 (compute_reg) and its autograd gradients with the yaml weights."""
+  g = gold("reg_loss.npz")
+  m = g["opacity"].shape[0]
+  g2d = np.zeros((m, 6), np.float32); g2d[:, 5] = g["opacity"]
+  w = (float(g["w_scale"]), float(g["w_opacity"]), float(g["w_aspect"]))
+  d_op, d_dep, d_ls = np.zeros(m, np.float32), np.zeros(m, np.float32), np.zeros((m, 3), np.float32)
+  sums = orc.reg_loss(w, g2d, g["depths"][:, 0], g["log_scaling"], g["weight"], d_op, d_dep, d_ls)
+  assert sums[3] == m
+  np.testing.assert_allclose(sums[0] / m, g["reg_scale"], rtol=1e-5)
+  np.testing.assert_allclose(sums[1] / m, g["reg_opacity"], rtol=1e-5)
+  np.testing.assert_allclose(sums[2] / m, g["reg_aspect"], rtol=1e-5)
+  total = (w[0] * sums[0] + w[1] * sums[1] + w[2] * sums[2]) / m
+  np.testing.assert_allclose(total, g["total"], rtol=1e-5)
+  np.testing.assert_allclose(d_op, g["d_opacity"], rtol=2e-4, atol=1e-9)
+  np.testing.assert_allclose(d_dep, g["d_depths"][:, 0], rtol=2e-4, atol=1e-9)
+  np.testing.assert_allclose(d_ls, g["d_log_scaling"], rtol=2e-4, atol=1e-9)
+  # rows no pixel blended (vis == 0) are outside the mean and get no gradient
+  vis = g["weight"].copy(); vis[::3] = 0
+  d2 = np.zeros(m, np.float32)
+  s2 = orc.reg_loss(w, g2d, g["depths"][:, 0], g["log_scaling"], vis, d2, None, None)
+  assert s2[3] == (vis > 0).sum() and np.all(d2[::3] == 0)
