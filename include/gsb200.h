@@ -348,6 +348,19 @@ int gs_reg_loss(int64_t n, float w_scale, float w_opacity, float w_aspect, const
                 const float *log_scaling, const float *vis, int vis_stride, float *sums, int compute_sums,
                 float *d_opacity, int d_opacity_stride, float *d_depth, float *d_log_scaling, void *stream);
 
+/* ---------------------------------------------------------------------------------------
+ * (8) Multi-scale SSIM loss: Trainer.compute_ssim_loss, reference trainer/trainer.py:450-462 with
+ *     self.ssim = fused_ssim(padding="valid") (:112; fused-ssim's published algorithm: 11x11 Gaussian window sigma 1.5,
+ *     zero padded, C1 = 0.01^2, C2 = 0.03^2, map cropped by 5 px).  loss = weight * mean_l (1 - ssim_l), level l >= 1 on
+ *     2x2 average-pooled images.  pred: raw render H x W x C channels-last, clamped to [0,1] on load like the L1/MSE loss
+ *     (scene/color_model.py:154-160); target fp32 or uint8.  ssim_sums[l] = Σ of the SSIM map over the valid crop of
+ *     level l (device; ssim_l = ssim_sums[l] / ((H_l-10)(W_l-10)C)).  d_pred (nullable): weight * d loss / d pred is
+ *     ADDED (run after gs_loss_l1_mse, which writes it). */
+size_t gs_ssim_workspace_bytes(int height, int width, int channels, int levels);
+int gs_ssim_loss(int height, int width, int channels, int levels, const float *pred, const float *target,
+                 const uint8_t *target_u8, float weight, float *d_pred, float *ssim_sums, void *workspace,
+                 size_t workspace_bytes, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -295,3 +295,14 @@ class Oracle:
                           self.p(g2d), self.p(depth), self.p(ls), self.p(vis), self.p(sums), self.p(d_opacity), C.c_int(1),
                           self.p(d_depth), self.p(d_log_scaling))
     return sums
+
+  def ssim_loss(self, pred, target, levels=3, weight=1.0, want_grad=True):
+    """pred/target (H,W,C).  Returns (weight * loss, weight * d loss/d pred or None, ssim of level 0)."""
+    pred, target = self.r(pred), self.r(target)
+    H, W, Cc = pred.shape
+    d = np.zeros_like(pred) if want_grad else None
+    s0 = self.creal(0)
+    self.lib.gso_ssim_loss.restype = C.c_float if self.real == np.float32 else C.c_double
+    loss = self.lib.gso_ssim_loss(C.c_int(H), C.c_int(W), C.c_int(Cc), C.c_int(levels), self.p(pred), self.p(target),
+                                  self.creal(weight), self.p(d), C.byref(s0))
+    return float(loss), d, float(s0.value)

@@ -393,3 +393,34 @@ def reg_loss(weights, g2d, depth, log_scaling, vis, sums=None, compute_sums=True
                                0 if d_opacity is None else d_opacity.stride(0), L.ptr(d_depth), L.ptr(d_log_scaling),
                                L.stream()))
   return sums
+
+
+# ---- multi-scale SSIM loss (include/gsb200.h section 8) -------------------------------------------------------------
+def ssim_workspace(height, width, channels, levels, device="cuda"):
+  nbytes = int(L.load().gs_ssim_workspace_bytes(height, width, channels, levels))
+  return torch.empty((nbytes,), device=device, dtype=torch.uint8)
+
+
+def ssim_counts(height, width, channels, levels):
+  """number of map entries in the valid crop of every level (denominators of ssim_l)."""
+  out = []
+  for _ in range(levels):
+    out.append(max(height - 10, 0) * max(width - 10, 0) * channels)
+    height, width = height // 2, width // 2
+  return out
+
+
+def ssim_loss(pred, target, levels=3, weight=1.0, d_pred=None, sums=None, workspace=None):
+  """pred (H,W,C) raw render; target float32 or uint8 (H,W,C).  d_pred: gradient ADDED in place.  Returns sums (levels,)
+  on the device: Σ of the SSIM map over the valid crop per level (loss = weight·mean_l(1 − sums[l]/ssim_counts[l]))."""
+  H, W, C_ = pred.shape
+  if workspace is None:
+    workspace = ssim_workspace(H, W, C_, levels, pred.device)
+  if sums is None:
+    sums = torch.zeros((levels,), device=pred.device, dtype=torch.float32)
+  tf = target if target.dtype == torch.float32 else None
+  tu = target if target.dtype == torch.uint8 else None
+  assert tf is not None or tu is not None, "target must be float32 or uint8"
+  L.check(L.load().gs_ssim_loss(H, W, C_, int(levels), L.ptr(_f32(pred)), L.ptr(tf), L.ptr(tu), float(weight), L.ptr(d_pred),
+                                L.ptr(sums), L.ptr(workspace), workspace.numel(), L.stream()))
+  return sums

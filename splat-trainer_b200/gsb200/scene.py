@@ -35,6 +35,8 @@ class SceneConfig:
   optim: dict = dataclasses.field(default_factory=dict)  # overrides of make_optim_config (LaProp, .8/.95, ...)
   w_l1: float = 0.0              # reference trainer/config.py:67-70, config/trainer/default.yaml:52-55
   w_mse: float = 10.0
+  w_ssim: float = 1.0            # ssim_weight / ssim_levels: reference config/trainer/default.yaml:52,55
+  ssim_levels: int = 3
   split_alpha: float = 0.01      # reference controller/point_state.py:49-50
   prune_alpha: float = 0.1
   antialias: bool = False        # reference trainer/trainer.py:308-310: blur_cov = 0.0 if antialias else 0.3
@@ -136,7 +138,9 @@ class SplatScene:
              image=torch.empty((H, W, 3), device=dev), final_T=torch.empty((H, W), device=dev),
              n_contrib=torch.empty((H, W), device=dev, dtype=torch.int32), d_image=torch.empty((H, W, 3), device=dev),
              loss_sums=torch.zeros((2,), device=dev), reg_sums=torch.zeros((4,), device=dev),
-             d_depth=torch.zeros((n,), device=dev), tile=None)
+             d_depth=torch.zeros((n,), device=dev), tile=None,
+             ssim_sums=torch.zeros((max(self.config.ssim_levels, 1),), device=dev),
+             ssim_ws=ops.ssim_workspace(H, W, 3, max(self.config.ssim_levels, 1), dev) if self.config.w_ssim != 0.0 else None)
     self._work = w
     return w
 
@@ -197,6 +201,13 @@ class SplatScene:
     idx = (vis > 0).nonzero().squeeze(1)
     return idx, vis[idx]
 
+  def ssim_value(self):
+    """(weighted multi-scale SSIM loss, SSIM of level 0) of the last forward_backward image — device scalars."""
+    w, c = self._work, self.config
+    counts = torch.tensor(ops.ssim_counts(w["H"], w["W"], 3, c.ssim_levels), device=self.device, dtype=torch.float32)
+    ssim = w["ssim_sums"] / counts.clamp_min(1.0)
+    return c.w_ssim * (1.0 - ssim).mean(), ssim[0]
+
   def reg_value(self):
     """Σ weight_k · reg_k of the last forward_backward image (device scalar; reference reg_loss's return value)."""
     s, wts = self._work["reg_sums"], self.config.reg_weights
@@ -235,6 +246,9 @@ class SplatScene:
     c = self.config
     w["loss_sums"].zero_()
     ops.loss_l1_mse(w["image"], target, c.w_l1, c.w_mse, d_pred=w["d_image"], sums=w["loss_sums"])
+    if c.w_ssim != 0.0:  # multi-scale SSIM (reference trainer/trainer.py:450-462); its gradient joins d_image
+      ops.ssim_loss(w["image"], target, c.ssim_levels, c.w_ssim, d_pred=w["d_image"], sums=w["ssim_sums"],
+                    workspace=w["ssim_ws"])
     self._mark("loss")
     acc = w["acc"]
     ops.raster_bwd(self.raster_cfg, w["g2d"], w["rgb"], tb.overlap_to_point, tb.tile_ranges, cam.width, cam.height,

@@ -89,8 +89,9 @@ def _scene(n=20000, W=320, H=240, **cfg):
 
 
 def test_training_image_with_reg_matches_oracle_chain():
-  """forward_backward with the reference's reg weights == the oracle chain with gso_reg_loss between the raster and the
-  projection backward (gradients of photometric loss + reg_loss, reference trainer/trainer.py:478-514)."""
+  """forward_backward with the reference's default loss (MSE 10 + 3-level SSIM 1.0 + reg_loss, reference
+  trainer/trainer.py:465-498, config/trainer/default.yaml:52-55) == the oracle chain with gso_ssim_loss after the MSE and
+  gso_reg_loss between the raster and the projection backward."""
   W, H = 320, 240
   wts = (0.01, 1.0, 1e-4)
   g, cam, ocam, scene = _scene(W=W, H=H, reg_weights=wts)
@@ -104,6 +105,9 @@ def test_training_image_with_reg_matches_oracle_chain():
   o2p, ranges, total, _ = orc.tile_map(cfg, g2d, depth, W, H)
   image, fT, nc, _, _ = orc.raster_fwd(cfg, g2d, rgb, depth, o2p, ranges, W, H)
   dimg, _ = orc.loss_l1_mse(image, target, 0.0, 10.0)
+  # + multi-scale SSIM with the reference's default weight / levels (through the clamp)
+  ssim_ref, dssim, _ = orc.ssim_loss(np.clip(image, 0, 1), target, levels=3, weight=1.0)
+  dimg = dimg + np.where((image >= 0) & (image <= 1), dssim, 0).astype(np.float32)
   acc = orc.raster_bwd(cfg, g2d, rgb, o2p, ranges, W, H, fT, nc, dimg)
   vis = np.ascontiguousarray(acc[:, 11])
   d_op = np.ascontiguousarray(acc[:, 5]); d_depth = np.zeros_like(vis); d_ls = np.zeros((vis.shape[0], 3), np.float32)
@@ -117,6 +121,7 @@ def test_training_image_with_reg_matches_oracle_chain():
   assert sums[3] > 500
   reg_ref = (wts[0] * sums[0] + wts[1] * sums[1] + wts[2] * sums[2]) / sums[3]
   np.testing.assert_allclose(float(scene.reg_value().item()), reg_ref, rtol=1e-3)
+  np.testing.assert_allclose(float(scene.ssim_value()[0].item()), ssim_ref, rtol=1e-4)
   for name in ("position", "log_scaling", "rotation", "alpha_logit", "sh"):
     a, r = npy(scene.g[name]).reshape(vis.shape[0], -1), grads[name].reshape(vis.shape[0], -1)
     scale = np.abs(r).max(axis=0) + 1e-12
