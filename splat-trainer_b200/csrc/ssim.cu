@@ -4,7 +4,8 @@
 //
 // Images are H x W x C channels-last fp32 (level 0: the raw render, clamped to [0,1] on load like the reference's
 // post_activation; target fp32 or uint8).  One CTA = one 16x16 pixel tile: the 26x26xC halo tile is staged in shared
-// memory once (coalesced rows), then per channel a horizontal and a vertical 11-tap pass run out of shared memory.
+// memory once (coalesced rows), then a horizontal and a vertical 11-tap pass run out of shared memory for all channels
+// at once, register-tiled: a thread filters 4 consecutive outputs from 14 loaded inputs.
 // forward: per-pixel partial derivatives of the map (w.r.t. mu1, E[pp], E[pt]; zero outside the valid crop) + the
 //          sum of the map over the valid crop;
 // backward: the three partial maps blurred with the same window, combined into d pred.
@@ -24,69 +25,124 @@ struct Win { float g[11]; };
 
 __device__ __forceinline__ float clamp01(float v) { return fminf(fmaxf(v, 0.f), 1.f); }
 
+constexpr int SG = 4;             // outputs per thread along the filtered axis (register tiling: 14 loads feed 4 outputs)
+
+// 4 outputs of an 11-tap filter from 14 consecutive inputs
+__device__ __forceinline__ void taps4(const Win &win, const float *v, float *out) {
+#pragma unroll
+  for (int o = 0; o < SG; ++o) {
+    float a = 0.f;
+#pragma unroll
+    for (int k = 0; k < 11; ++k) a += win.g[k] * v[o + k];
+    out[o] = a;
+  }
+}
+
+// dynamic shared memory: sP | sT (SH*SH*C each) | sHz (5 * SH*ST*C)
 template <int C>
 __global__ void __launch_bounds__(ST * ST) k_ssim_fwd(Win win, int H, int W, const float *__restrict__ pred, int clamp_pred,
                                                       const float *__restrict__ target, const uint8_t *__restrict__ target_u8,
                                                       float *__restrict__ dm1, float *__restrict__ dm2, float *__restrict__ dm3,
                                                       float *__restrict__ sum_out) {
-  __shared__ float sP[SH * SH * C];
-  __shared__ float sT[SH * SH * C];
-  __shared__ float sHz[5][SH * ST];
+  extern __shared__ float ssim_smem[];
+  float *sP = ssim_smem, *sT = sP + SH * SH * C, *sHz = sT + SH * SH * C;
+  constexpr int HZ = SH * ST * C;  // one horizontally filtered plane
   __shared__ float s_red[ST * ST / 32];
   const int tid = threadIdx.x;
   const int tx0 = blockIdx.x * ST, ty0 = blockIdx.y * ST;
-  for (int i = tid; i < SH * SH * C; i += ST * ST) {
-    int c = i % C, rx = (i / C) % SH, ry = i / (C * SH);
-    int gx = tx0 - SR + rx, gy = ty0 - SR + ry;
-    float p = 0.f, t = 0.f;
-    if (gx >= 0 && gx < W && gy >= 0 && gy < H) {
-      int64_t gi = ((int64_t)gy * W + gx) * C + c;
-      p = pred[gi];
-      if (clamp_pred) p = clamp01(p);
-      t = target_u8 ? (float)target_u8[gi] / 255.0f : target[gi];
+  {  // halo tile load, fully unrolled so that every global load is in flight before the first use (the tile is a
+     // handful of loads per thread: a rolled loop pays one DRAM round trip per iteration)
+    constexpr int NL = (SH * SH * C + ST * ST - 1) / (ST * ST);
+    float pl[NL], tl[NL];
+#pragma unroll
+    for (int it = 0; it < NL; ++it) {
+      int i = tid + it * ST * ST;
+      int c = i % C, rx = (i / C) % SH, ry = i / (C * SH);
+      int gx = tx0 - SR + rx, gy = ty0 - SR + ry;
+      pl[it] = 0.f; tl[it] = 0.f;
+      if (i < SH * SH * C && gx >= 0 && gx < W && gy >= 0 && gy < H) {
+        int64_t gi = ((int64_t)gy * W + gx) * C + c;
+        pl[it] = pred[gi];
+        tl[it] = target_u8 ? (float)target_u8[gi] : target[gi];
+      }
     }
-    sP[i] = p; sT[i] = t;
+#pragma unroll
+    for (int it = 0; it < NL; ++it) {
+      int i = tid + it * ST * ST;
+      if (i < SH * SH * C) {
+        sP[i] = clamp_pred ? clamp01(pl[it]) : pl[it];
+        sT[i] = target_u8 ? tl[it] / 255.0f : tl[it];
+      }
+    }
   }
   __syncthreads();
-  const int lx = tid % ST, ly = tid / ST;
-  const int gx = tx0 + lx, gy = ty0 + ly;
-  const bool inside = gx < W && gy < H;
-  const bool valid = inside && gx >= SR && gx < W - SR && gy >= SR && gy < H - SR;
+  // horizontal pass: a thread filters 4 consecutive x of one (halo row, channel) for the 5 quantities p, t, pp, tt, pt
+  for (int i = tid; i < SH * (ST / SG) * C; i += ST * ST) {
+    int c = i % C, xg = (i / C) % (ST / SG), ry = i / (C * (ST / SG));
+    float pv[SG + 10], tv[SG + 10], tmp[SG + 10], out[SG];
+#pragma unroll
+    for (int k = 0; k < SG + 10; ++k) {
+      int j = (ry * SH + xg * SG + k) * C + c;
+      pv[k] = sP[j]; tv[k] = sT[j];
+    }
+    const int o0 = (ry * ST + xg * SG) * C + c;
+    taps4(win, pv, out);
+#pragma unroll
+    for (int o = 0; o < SG; ++o) sHz[0 * HZ + o0 + o * C] = out[o];
+    taps4(win, tv, out);
+#pragma unroll
+    for (int o = 0; o < SG; ++o) sHz[1 * HZ + o0 + o * C] = out[o];
+#pragma unroll
+    for (int k = 0; k < SG + 10; ++k) tmp[k] = pv[k] * pv[k];
+    taps4(win, tmp, out);
+#pragma unroll
+    for (int o = 0; o < SG; ++o) sHz[2 * HZ + o0 + o * C] = out[o];
+#pragma unroll
+    for (int k = 0; k < SG + 10; ++k) tmp[k] = tv[k] * tv[k];
+    taps4(win, tmp, out);
+#pragma unroll
+    for (int o = 0; o < SG; ++o) sHz[3 * HZ + o0 + o * C] = out[o];
+#pragma unroll
+    for (int k = 0; k < SG + 10; ++k) tmp[k] = pv[k] * tv[k];
+    taps4(win, tmp, out);
+#pragma unroll
+    for (int o = 0; o < SG; ++o) sHz[4 * HZ + o0 + o * C] = out[o];
+  }
+  __syncthreads();
+  // vertical pass: a thread owns 4 consecutive rows of one (column, channel)
   const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
   float local = 0.f;
-  for (int c = 0; c < C; ++c) {
-    for (int i = tid; i < SH * ST; i += ST * ST) {
-      int x = i % ST, ry = i / ST;
-      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+  for (int i = tid; i < ST * (ST / SG) * C; i += ST * ST) {
+    int c = i % C, lx = (i / C) % ST, yg = i / (C * ST);
+    float q[5][SG];
 #pragma unroll
-      for (int k = 0; k < 11; ++k) {
-        float p = sP[(ry * SH + x + k) * C + c], t = sT[(ry * SH + x + k) * C + c], g = win.g[k];
-        a0 += g * p; a1 += g * t; a2 += g * p * p; a3 += g * t * t; a4 += g * p * t;
+    for (int a = 0; a < 5; ++a) {
+      float v[SG + 10];
+#pragma unroll
+      for (int k = 0; k < SG + 10; ++k) v[k] = sHz[a * HZ + ((yg * SG + k) * ST + lx) * C + c];
+      taps4(win, v, q[a]);
+    }
+    const int gx = tx0 + lx;
+#pragma unroll
+    for (int o = 0; o < SG; ++o) {
+      const int gy = ty0 + yg * SG + o;
+      const bool inside = gx < W && gy < H;
+      const bool valid = inside && gx >= SR && gx < W - SR && gy >= SR && gy < H - SR;
+      float m1 = q[0][o], m2 = q[1][o];
+      float s1 = q[2][o] - m1 * m1, s2 = q[3][o] - m2 * m2, s12 = q[4][o] - m1 * m2;
+      float A = 2.f * m1 * m2 + C1, B = 2.f * s12 + C2, Cc = m1 * m1 + m2 * m2 + C1, D = s1 + s2 + C2;
+      float icd = 1.0f / (Cc * D);
+      float map = A * B * icd;
+      if (valid) local += map;
+      if (inside) {
+        int64_t gi = ((int64_t)gy * W + gx) * C + c;
+        float w = valid ? 1.f : 0.f;
+        // d map / d mu1 with E[pp], E[pt] fixed (s1, s12 depend on mu1), d map / d E[pp], d map / d E[pt]
+        dm1[gi] = w * (2.f * m2 * (B - A) * icd - 2.f * m1 * map / Cc + 2.f * m1 * map / D);
+        dm2[gi] = w * (-map / D);
+        dm3[gi] = w * (2.f * A * icd);
       }
-      sHz[0][i] = a0; sHz[1][i] = a1; sHz[2][i] = a2; sHz[3][i] = a3; sHz[4][i] = a4;
     }
-    __syncthreads();
-    float m1 = 0.f, m2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
-#pragma unroll
-    for (int k = 0; k < 11; ++k) {
-      int i = (ly + k) * ST + lx;
-      float g = win.g[k];
-      m1 += g * sHz[0][i]; m2 += g * sHz[1][i]; e11 += g * sHz[2][i]; e22 += g * sHz[3][i]; e12 += g * sHz[4][i];
-    }
-    float s1 = e11 - m1 * m1, s2 = e22 - m2 * m2, s12 = e12 - m1 * m2;
-    float A = 2.f * m1 * m2 + C1, B = 2.f * s12 + C2, Cc = m1 * m1 + m2 * m2 + C1, D = s1 + s2 + C2;
-    float icd = 1.0f / (Cc * D);
-    float map = A * B * icd;
-    if (valid) local += map;
-    if (inside) {
-      int64_t gi = ((int64_t)gy * W + gx) * C + c;
-      float w = valid ? 1.f : 0.f;
-      // d map / d mu1 with E[pp], E[pt] fixed (s1, s12 depend on mu1), d map / d E[pp], d map / d E[pt]
-      dm1[gi] = w * (2.f * m2 * (B - A) * icd - 2.f * m1 * map / Cc + 2.f * m1 * map / D);
-      dm2[gi] = w * (-map / D);
-      dm3[gi] = w * (2.f * A * icd);
-    }
-    __syncthreads();
   }
   local = warp_sum(local);
   if ((tid & 31) == 0) s_red[tid >> 5] = local;
@@ -99,63 +155,79 @@ __global__ void __launch_bounds__(ST * ST) k_ssim_fwd(Win win, int H, int W, con
 }
 
 // d[i] (+)= scale * (G*dm1 + 2 p G*dm2 + t G*dm3); level 0 honours the clamp (no gradient where the raw render left [0,1])
+// dynamic shared memory: sM (3 * SH*SH*C) | sHz (3 * SH*ST*C)
 template <int C>
 __global__ void __launch_bounds__(ST * ST) k_ssim_bwd(Win win, int H, int W, const float *__restrict__ pred, int clamp_pred,
                                                       const float *__restrict__ target, const uint8_t *__restrict__ target_u8,
                                                       const float *__restrict__ dm1, const float *__restrict__ dm2,
                                                       const float *__restrict__ dm3, float scale, float *__restrict__ d_out,
                                                       int accumulate, const float *__restrict__ d_coarse, int hc, int wc) {
-  __shared__ float sM[3][SH * SH * C];
-  __shared__ float sHz[3][SH * ST];
+  extern __shared__ float ssim_smem[];
+  constexpr int HM = SH * SH * C, HZ = SH * ST * C;
+  float *sM = ssim_smem, *sHz = sM + 3 * HM;
   const int tid = threadIdx.x;
   const int tx0 = blockIdx.x * ST, ty0 = blockIdx.y * ST;
-  for (int i = tid; i < SH * SH * C; i += ST * ST) {
-    int c = i % C, rx = (i / C) % SH, ry = i / (C * SH);
-    int gx = tx0 - SR + rx, gy = ty0 - SR + ry;
-    float a = 0.f, b = 0.f, d = 0.f;
-    if (gx >= 0 && gx < W && gy >= 0 && gy < H) {
-      int64_t gi = ((int64_t)gy * W + gx) * C + c;
-      a = dm1[gi]; b = dm2[gi]; d = dm3[gi];
+  {  // halo tile load of the three partial maps, unrolled (all loads in flight together)
+    constexpr int NL = (HM + ST * ST - 1) / (ST * ST);
+    float la[NL], lb[NL], ld[NL];
+#pragma unroll
+    for (int it = 0; it < NL; ++it) {
+      int i = tid + it * ST * ST;
+      int c = i % C, rx = (i / C) % SH, ry = i / (C * SH);
+      int gx = tx0 - SR + rx, gy = ty0 - SR + ry;
+      la[it] = 0.f; lb[it] = 0.f; ld[it] = 0.f;
+      if (i < HM && gx >= 0 && gx < W && gy >= 0 && gy < H) {
+        int64_t gi = ((int64_t)gy * W + gx) * C + c;
+        la[it] = dm1[gi]; lb[it] = dm2[gi]; ld[it] = dm3[gi];
+      }
     }
-    sM[0][i] = a; sM[1][i] = b; sM[2][i] = d;
+#pragma unroll
+    for (int it = 0; it < NL; ++it) {
+      int i = tid + it * ST * ST;
+      if (i < HM) { sM[i] = la[it]; sM[HM + i] = lb[it]; sM[2 * HM + i] = ld[it]; }
+    }
   }
   __syncthreads();
-  const int lx = tid % ST, ly = tid / ST;
-  const int gx = tx0 + lx, gy = ty0 + ly;
-  const bool inside = gx < W && gy < H;
-  for (int c = 0; c < C; ++c) {
-    for (int i = tid; i < SH * ST; i += ST * ST) {
-      int x = i % ST, ry = i / ST;
-      float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+  for (int i = tid; i < SH * (ST / SG) * C; i += ST * ST) {
+    int c = i % C, xg = (i / C) % (ST / SG), ry = i / (C * (ST / SG));
+    const int o0 = (ry * ST + xg * SG) * C + c;
 #pragma unroll
-      for (int k = 0; k < 11; ++k) {
-        int j = (ry * SH + x + k) * C + c;
-        float g = win.g[k];
-        a0 += g * sM[0][j]; a1 += g * sM[1][j]; a2 += g * sM[2][j];
-      }
-      sHz[0][i] = a0; sHz[1][i] = a1; sHz[2][i] = a2;
-    }
-    __syncthreads();
-    float c1 = 0.f, c2 = 0.f, c3 = 0.f;
+    for (int a = 0; a < 3; ++a) {
+      float v[SG + 10], out[SG];
 #pragma unroll
-    for (int k = 0; k < 11; ++k) {
-      int i = (ly + k) * ST + lx;
-      float g = win.g[k];
-      c1 += g * sHz[0][i]; c2 += g * sHz[1][i]; c3 += g * sHz[2][i];
+      for (int k = 0; k < SG + 10; ++k) v[k] = sM[a * HM + (ry * SH + xg * SG + k) * C + c];
+      taps4(win, v, out);
+#pragma unroll
+      for (int o = 0; o < SG; ++o) sHz[a * HZ + o0 + o * C] = out[o];
     }
-    if (inside) {
+  }
+  __syncthreads();
+  for (int i = tid; i < ST * (ST / SG) * C; i += ST * ST) {
+    int c = i % C, lx = (i / C) % ST, yg = i / (C * ST);
+    float q[3][SG];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      float v[SG + 10];
+#pragma unroll
+      for (int k = 0; k < SG + 10; ++k) v[k] = sHz[a * HZ + ((yg * SG + k) * ST + lx) * C + c];
+      taps4(win, v, q[a]);
+    }
+    const int gx = tx0 + lx;
+#pragma unroll
+    for (int o = 0; o < SG; ++o) {
+      const int gy = ty0 + yg * SG + o;
+      if (!(gx < W && gy < H)) continue;
       int64_t gi = ((int64_t)gy * W + gx) * C + c;
       float raw = pred[gi];
       float p = clamp_pred ? clamp01(raw) : raw;
       float t = target_u8 ? (float)target_u8[gi] / 255.0f : target[gi];
-      float d = scale * (c1 + 2.f * p * c2 + t * c3);
+      float d = scale * (q[0][o] + 2.f * p * q[1][o] + t * q[2][o]);
       // transpose of the 2x2 average pooling: a quarter of the next coarser level's gradient (already complete: the
       // backward runs coarse to fine), for pixels inside the pooled area (floor sizes)
       if (d_coarse && (gy >> 1) < hc && (gx >> 1) < wc) d += 0.25f * d_coarse[((int64_t)(gy >> 1) * wc + (gx >> 1)) * C + c];
       if (clamp_pred && !(raw >= 0.f && raw <= 1.f)) d = 0.f;
       if (accumulate) d_out[gi] += d; else d_out[gi] = d;
     }
-    __syncthreads();
   }
 }
 
@@ -208,6 +280,10 @@ template <int C>
 static int ssim_run(int H, int W, int levels, const float *pred, const float *target, const uint8_t *target_u8, float weight,
                     float *d_pred, float *ssim_sums, void *workspace, cudaStream_t st) {
   Win win = make_window();
+  const size_t fwd_smem = (size_t)(2 * SH * SH + 5 * SH * ST) * C * sizeof(float);
+  const size_t bwd_smem = (size_t)(3 * SH * SH + 3 * SH * ST) * C * sizeof(float);
+  GS_CUDA(cudaFuncSetAttribute(k_ssim_fwd<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem));
+  GS_CUDA(cudaFuncSetAttribute(k_ssim_bwd<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem));
   uintptr_t a = ((uintptr_t)workspace + 255) & ~(uintptr_t)255;
   const float *p[8], *t[8];
   float *d[8], *dm[8][3];
@@ -234,7 +310,7 @@ static int ssim_run(int H, int W, int levels, const float *pred, const float *ta
   for (int l = 0; l < levels; ++l) {
     if (hs[l] <= 0 || ws[l] <= 0) continue;
     dim3 grid((ws[l] + ST - 1) / ST, (hs[l] + ST - 1) / ST);
-    k_ssim_fwd<C><<<grid, ST * ST, 0, st>>>(win, hs[l], ws[l], p[l], l == 0, t[l], l == 0 ? target_u8 : nullptr, dm[l][0],
+    k_ssim_fwd<C><<<grid, ST * ST, fwd_smem, st>>>(win, hs[l], ws[l], p[l], l == 0, t[l], l == 0 ? target_u8 : nullptr, dm[l][0],
                                             dm[l][1], dm[l][2], ssim_sums + l);
     GS_LAUNCH_CHECK();
   }
@@ -246,7 +322,7 @@ static int ssim_run(int H, int W, int levels, const float *pred, const float *ta
     // loss = weight * mean_l (1 - ssim_l), ssim_l = sum_l / count_l
     float scale = count > 0 ? (float)(-(double)weight / ((double)levels * count)) : 0.f;
     bool has_coarse = l + 1 < levels && hs[l + 1] > 0 && ws[l + 1] > 0;
-    k_ssim_bwd<C><<<grid, ST * ST, 0, st>>>(win, hs[l], ws[l], p[l], l == 0, t[l], l == 0 ? target_u8 : nullptr, dm[l][0],
+    k_ssim_bwd<C><<<grid, ST * ST, bwd_smem, st>>>(win, hs[l], ws[l], p[l], l == 0, t[l], l == 0 ? target_u8 : nullptr, dm[l][0],
                                             dm[l][1], dm[l][2], scale, d[l], l == 0, has_coarse ? d[l + 1] : nullptr,
                                             has_coarse ? hs[l + 1] : 0, has_coarse ? ws[l + 1] : 0);
     GS_LAUNCH_CHECK();
