@@ -49,7 +49,7 @@ def parse():
 def measured_traffic(stage):
   """dram__bytes_read.sum + dram__bytes_write.sum of the stage's kernels per image from the committed ncu --set full
   capture of this same command (profiles/: cold-cache, serialised launches), or None."""
-  path = os.path.join(ROOT, "profiles", "r1j_traffic.json")
+  path = os.path.join(ROOT, "profiles", "r1k_traffic.json")
   try:
     with open(path) as f:
       return json.load(f)["dram_bytes_per_image"].get(stage)
@@ -360,7 +360,7 @@ def run_b200(args):
                  "parallelism": f"dp{world}", "V_in_view": V, "O_overlaps": O, "V_optimised": v_opt, "overflow": overflow},
       "stages_ms": stages, "host_enqueue_ms_per_step": host_enqueue_ms,
       "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                   "traffic": measured_traffic(dom), "traffic_source": "profiles/r1j_traffic.json (ncu --set full)",
+                   "traffic": measured_traffic(dom), "traffic_source": "profiles/r1k_traffic.json (ncu --set full)",
                    "peak_source": which, "algorithmic_bytes": bytes_[dom],
                    "iteration": {"algorithmic_bytes": iter_bytes, "achieved": iter_bytes / (ms_step * 1e-3) / 1e9,
                                  "frac": iter_bytes / (ms_step * 1e-3) / 1e9 / hbm}},
