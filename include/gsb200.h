@@ -66,6 +66,13 @@ typedef struct gs_raster_config {
   float frustum_clamp;              /* 1.3: |x/z| clamp (× half-FOV tangent) in the Jacobian */
 } gs_raster_config;
 
+/* Regularisation gradients fused into gs_project_bwd (section 7 has the standalone pass they equal). */
+typedef struct gs_reg_fuse {
+  float w_scale, w_opacity, w_aspect; /* weights of the scale / opacity / aspect terms                     */
+  const float *sums;                  /* device float[4] written by gs_reg_loss(compute_sums=1) this image   */
+  const float *depth;                 /* device (n) camera depth plane of gs_project_fwd                     */
+} gs_reg_fuse;
+
 void gs_default_raster_config(gs_raster_config *cfg);
 int gs_version(void);
 const char *gs_last_error(void);
@@ -97,14 +104,17 @@ size_t gs_tile_info_bytes(int64_t n, int width, int height);
  * blended has an exactly-zero image gradient, so the fused path neither reads its SH row nor
  * touches its gradient row (keeps the gradient buffer all-zero outside the visible set).
  * Gradients are ADDED into g_* when accumulate != 0 (batch = sum, reference
- * trainer/trainer.py:500-514), else written for in-view rows only (culled rows untouched). */
+ * trainer/trainer.py:500-514), else written for in-view rows only (culled rows untouched).
+ * reg (nullable, host struct): the gradients of the image's regularisation terms (gs_reg_loss's d_opacity, d_depth and
+ * d_log_scaling, reference scene/mlp_scene.py:246-288) are computed per row here instead of by two extra sweeps;
+ * needs row_vis (the weights) and reg->sums from gs_reg_loss(compute_sums=1). */
 int gs_project_bwd(const gs_camera *h_cam, const gs_raster_config *h_cfg, int64_t n,
                    const float *position, const float *log_scaling, const float *rotation,
                    const float *alpha_logit, const float *sh, int sh_degree,
                    const float *g2d,
                    const float *d_g2d, int d_g2d_stride,
                    const float *d_rgb, int d_rgb_stride,
-                   const float *d_depth, const float *row_vis, int row_vis_stride,
+                   const float *d_depth, const float *row_vis, int row_vis_stride, const gs_reg_fuse *reg,
                    float *g_position, float *g_log_scaling, float *g_rotation,
                    float *g_alpha_logit, float *g_sh, int accumulate, void *stream);
 

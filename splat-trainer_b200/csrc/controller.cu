@@ -4,6 +4,7 @@
 //   gs_reg_loss     MLPScene.compute_reg / reg_loss (reference scene/mlp_scene.py:246-288, util/misc.py:68-69 saturate)
 // Both are single streaming sweeps (HBM bound); rows the step does not touch are skipped after one 2- or 4-byte read.
 #include "common.cuh"
+#include "reg.cuh"
 
 // point_basis (reference gaussians/split.py:15-19): B[3*j+k] = R[j][k] * max(exp(s_k), eps)
 __device__ __forceinline__ void ctl_point_basis(const float *__restrict__ ls, const float *__restrict__ q, float eps, float *B) {
@@ -55,32 +56,6 @@ extern "C" int gs_mcmc_noise(int64_t n, const float *alpha_logit, const float *l
 }
 
 // ---- regularisation --------------------------------------------------------------------------------------------
-struct RegTerms {
-  float ns, sat, dsat, aspect, inv_d, s2[3];
-  int kmax, kmin;
-};
-
-__device__ __forceinline__ RegTerms reg_terms(float op, float d, const float *__restrict__ ls) {
-  RegTerms t;
-  float s[3] = {expf(ls[0]), expf(ls[1]), expf(ls[2])};
-  t.inv_d = 1.0f / d;
-  float id2 = t.inv_d * t.inv_d;
-#pragma unroll
-  for (int k = 0; k < 3; ++k) t.s2[k] = s[k] * s[k] * id2;
-  t.ns = t.s2[0] + t.s2[1] + t.s2[2];
-  float e = 1.0f / expf(4.0f * op), u = 1.0f - e;  // saturate(op, gain 4, k 2) = (1 - 1/exp(4 op))^2
-  t.sat = u * u;
-  t.dsat = 8.0f * u * e;
-  t.kmax = 0; t.kmin = 0;
-#pragma unroll
-  for (int k = 1; k < 3; ++k) {
-    if (s[k] > s[t.kmax]) t.kmax = k;
-    if (s[k] < s[t.kmin]) t.kmin = k;
-  }
-  t.aspect = s[t.kmax] / s[t.kmin];
-  return t;
-}
-
 // pass 1: Σ over blended rows of w·(scale, opacity, aspect) terms and their count
 __global__ void __launch_bounds__(256) k_reg_sums(int64_t n, const float *__restrict__ g2d, const float *__restrict__ depth,
                                                   const float *__restrict__ log_scaling, const float *__restrict__ vis,
@@ -149,19 +124,12 @@ __global__ void __launch_bounds__(256) k_reg_grads(int64_t n, float w_scale, flo
     float c = w / m;
     float d = depth[i];
     RegTerms t = reg_terms(op, d, log_scaling + 3 * i);
-    float cn = (w_scale + w_opacity * t.sat) * c;  // d total / d norm_scale
-    if (d_opacity) d_opacity[(int64_t)d_opacity_stride * i] += w_opacity * c * t.ns * t.dsat;
-    if (d_depth) d_depth[i] = cn * (-2.0f * t.ns * t.inv_d);
+    RegGrad g = reg_grad(t, c, w_scale, w_opacity, w_aspect);
+    if (d_opacity) d_opacity[(int64_t)d_opacity_stride * i] += g.d_op;
+    if (d_depth) d_depth[i] = g.d_depth;
     if (d_log_scaling) {
 #pragma unroll
-      for (int k = 0; k < 3; ++k) {
-        float g = cn * 2.0f * t.s2[k];
-        if (t.kmax != t.kmin) {
-          if (k == t.kmax) g += w_aspect * c * t.aspect;
-          if (k == t.kmin) g -= w_aspect * c * t.aspect;
-        }
-        d_log_scaling[3 * i + k] += g;
-      }
+      for (int k = 0; k < 3; ++k) d_log_scaling[3 * i + k] += g.d_ls[k];
     }
   }
 }

@@ -7,6 +7,7 @@
 // kernel's DRAM traffic is 44·N + (192 + 48)·V bytes forward.  HBM-bound; no tensor cores.
 #include "common.cuh"
 #include "footprint.cuh"
+#include "reg.cuh"
 
 // ---- SH basis: reference scene/mlp/rsh.py:110-157 (rsh_cart_3) ------------------------------------
 template <int DEG>
@@ -221,7 +222,8 @@ __device__ __forceinline__ void project_bwd_row(const CamDev &cam, const CfgDev 
                                                 const float *__restrict__ alpha_logit, const float *__restrict__ sh,
                                                 const float *__restrict__ d_g2d, int d_g2d_stride,
                                                 const float *__restrict__ d_rgb, int d_rgb_stride,
-                                                const float *__restrict__ d_depth, float *__restrict__ g_position,
+                                                const float *__restrict__ d_depth, const RegFuse &reg, float row_w,
+                                                const float *__restrict__ g2d, float *__restrict__ g_position,
                                                 float *__restrict__ g_log_scaling, float *__restrict__ g_rotation,
                                                 float *__restrict__ g_alpha_logit, float *__restrict__ g_sh, int accumulate) {
   // every load of the row is issued up front (rows are scattered over GBs of planes: each access is a full DRAM +
@@ -241,8 +243,20 @@ __device__ __forceinline__ void project_bwd_row(const CamDev &cam, const CfgDev 
     load_sh_row<KK>(sh + (int64_t)3 * KK * i, shv);
   }
   float dd = d_depth ? d_depth[i] : 0.f;
+  float reg_op = 0.f, reg_z = 1.f, reg_m = 0.f;
+  if (reg.sums) { reg_op = g2d[GS_G2D_STRIDE * i + 5]; reg_z = reg.depth[i]; reg_m = reg.sums[3]; }
   Proj t;
   if (!project_one(cam, cfg, px, py, pz, ls0, ls1, ls2, q, al, t)) return;
+  // regularisation gradients of this image (same arithmetic as k_reg_grads): they enter through the 2-D opacity,
+  // the depth and log_scaling
+  float reg_ls[3] = {0.f, 0.f, 0.f};
+  if (reg.sums && reg_m > 0.f && row_w > 0.f) {
+    const float lsv[3] = {ls0, ls1, ls2};
+    RegGrad rg = reg_grad(reg_terms(reg_op, reg_z, lsv), row_w / reg_m, reg.w_scale, reg.w_opacity, reg.w_aspect);
+    d_op += rg.d_op;
+    dd += rg.d_depth;
+    reg_ls[0] = rg.d_ls[0]; reg_ls[1] = rg.d_ls[1]; reg_ls[2] = rg.d_ls[2];
+  }
   // conic -> covariance: S = -C G C
   float Ga = d_ca, Gb = 0.5f * d_cb, Gc = d_cc;
   float M00 = t.ca * Ga + t.cb * Gb, M01 = t.ca * Gb + t.cb * Gc;
@@ -283,7 +297,7 @@ __device__ __forceinline__ void project_bwd_row(const CamDev &cam, const CfgDev 
       gR[3 * j + k] = gM * t.s[k];
       gs += gM * t.R[3 * j + k];
     }
-    gls[k] = gs * t.s[k];
+    gls[k] = gs * t.s[k] + reg_ls[k];
   }
   float x = t.qx, y = t.qy, z = t.qz, w = t.qw;
   float gq[4];
@@ -382,7 +396,7 @@ __global__ void __launch_bounds__(PB_THREADS) k_project_bwd(CamDev cam, CfgDev c
                                                             const float *__restrict__ g2d, const float *__restrict__ d_g2d,
                                                             int d_g2d_stride, const float *__restrict__ d_rgb, int d_rgb_stride,
                                                             const float *__restrict__ d_depth, const float *__restrict__ row_vis,
-                                                            int row_vis_stride, float *__restrict__ g_position,
+                                                            int row_vis_stride, RegFuse reg, float *__restrict__ g_position,
                                                             float *__restrict__ g_log_scaling, float *__restrict__ g_rotation,
                                                             float *__restrict__ g_alpha_logit, float *__restrict__ g_sh, int accumulate) {
   __shared__ int s_list[PB_ROWS];
@@ -400,9 +414,12 @@ __global__ void __launch_bounds__(PB_THREADS) k_project_bwd(CamDev cam, CfgDev c
   }
   __syncthreads();
   int cnt = s_count;
-  for (int k = threadIdx.x; k < cnt; k += PB_THREADS)
-    project_bwd_row<DEG>(cam, cfg, base + s_list[k], position, log_scaling, rotation, alpha_logit, sh, d_g2d, d_g2d_stride,
-                         d_rgb, d_rgb_stride, d_depth, g_position, g_log_scaling, g_rotation, g_alpha_logit, g_sh, accumulate);
+  for (int k = threadIdx.x; k < cnt; k += PB_THREADS) {
+    int64_t i = base + s_list[k];
+    float row_w = reg.sums ? row_vis[(int64_t)row_vis_stride * i] : 0.f;
+    project_bwd_row<DEG>(cam, cfg, i, position, log_scaling, rotation, alpha_logit, sh, d_g2d, d_g2d_stride, d_rgb, d_rgb_stride,
+                         d_depth, reg, row_w, g2d, g_position, g_log_scaling, g_rotation, g_alpha_logit, g_sh, accumulate);
+  }
 }
 
 // ---- evaluate_sh_at -------------------------------------------------------------------------------
@@ -491,9 +508,16 @@ extern "C" int gs_project_bwd(const gs_camera *h_cam, const gs_raster_config *h_
                               const float *log_scaling, const float *rotation, const float *alpha_logit, const float *sh,
                               int sh_degree, const float *g2d, const float *d_g2d, int d_g2d_stride, const float *d_rgb,
                               int d_rgb_stride, const float *d_depth, const float *row_vis, int row_vis_stride,
-                              float *g_position, float *g_log_scaling, float *g_rotation, float *g_alpha_logit, float *g_sh, int accumulate, void *stream) {
+                              const gs_reg_fuse *h_reg, float *g_position, float *g_log_scaling, float *g_rotation,
+                              float *g_alpha_logit, float *g_sh, int accumulate, void *stream) {
   GS_REQUIRE(h_cam && h_cfg, "null camera/config");
   GS_REQUIRE(d_g2d && d_g2d_stride >= 6, "d_g2d stride must be >= 6");
+  RegFuse reg = {0.f, 0.f, 0.f, nullptr, nullptr};
+  if (h_reg) {
+    GS_REQUIRE(h_reg->sums && h_reg->depth && row_vis && g2d, "fused regularisation needs sums, depth, row_vis and g2d");
+    reg.w_scale = h_reg->w_scale; reg.w_opacity = h_reg->w_opacity; reg.w_aspect = h_reg->w_aspect;
+    reg.sums = h_reg->sums; reg.depth = h_reg->depth;
+  }
   if (n <= 0) return GS_OK;
   CamDev cam = gs_make_cam(h_cam, h_cfg);
   CfgDev cfg = gs_make_cfg(h_cfg);
@@ -501,7 +525,7 @@ extern "C" int gs_project_bwd(const gs_camera *h_cam, const gs_raster_config *h_
   int blocks = gs_div_up(n, PB_ROWS);
   GS_DISPATCH_DEG(sh_degree, (k_project_bwd<D><<<blocks, PB_THREADS, 0, st>>>(cam, cfg, n, position, log_scaling, rotation,
                                                                         alpha_logit, sh, g2d, d_g2d, d_g2d_stride, d_rgb,
-                                                                        d_rgb_stride, d_depth, row_vis, row_vis_stride,
+                                                                        d_rgb_stride, d_depth, row_vis, row_vis_stride, reg,
                                                                         g_position, g_log_scaling, g_rotation, g_alpha_logit, g_sh, accumulate)));
   GS_LAUNCH_CHECK();
   return GS_OK;

@@ -41,9 +41,15 @@ class ExchangeGroups(C.Structure):  # gs_exchange_groups
               ("grad", C.c_void_p * GS_EXCHANGE_MAX_GROUPS)]
 
 
+class RegFuse(C.Structure):  # gs_reg_fuse
+  _fields_ = [("w_scale", C.c_float), ("w_opacity", C.c_float), ("w_aspect", C.c_float), ("sums", C.c_void_p),
+              ("depth", C.c_void_p)]
+
+
 _P, _I, _L, _F, _Z = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t
 _CAM, _CFG, _OPT = C.POINTER(Camera), C.POINTER(RasterConfig), C.POINTER(OptimConfig)
 _XG = C.POINTER(ExchangeGroups)
+_REG = C.POINTER(RegFuse)
 
 # name -> (restype, argtypes); one entry per symbol declared in include/gsb200.h
 SIGNATURES = {
@@ -51,7 +57,7 @@ SIGNATURES = {
   "gs_version": (_I, []),
   "gs_last_error": (C.c_char_p, []),
   "gs_project_fwd": (_I, [_CAM, _CFG, _L, _P, _P, _P, _P, _P, _I, _P, _P, _P, _P, _I, _P, _P]),
-  "gs_project_bwd": (_I, [_CAM, _CFG, _L, _P, _P, _P, _P, _P, _I, _P, _P, _I, _P, _I, _P, _P, _I,
+  "gs_project_bwd": (_I, [_CAM, _CFG, _L, _P, _P, _P, _P, _P, _I, _P, _P, _I, _P, _I, _P, _P, _I, _REG,
                           _P, _P, _P, _P, _P, _I, _P]),
   "gs_sh_eval_fwd": (_I, [_L, _P, _P, _I, _P, C.POINTER(C.c_float), _P, _P]),
   "gs_sh_eval_bwd": (_I, [_L, _P, _P, _I, _P, C.POINTER(C.c_float), _P, _P, _P, _P]),

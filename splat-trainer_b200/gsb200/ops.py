@@ -55,9 +55,10 @@ class TileInfo:
 
 
 def project_bwd(cam, cfg, position, log_scaling, rotation, alpha_logit, sh, sh_degree, g2d, d_g2d, d_rgb,
-                d_depth=None, row_vis=None, grads=None, accumulate=False):
+                d_depth=None, row_vis=None, grads=None, accumulate=False, reg=None):
   """gs_project_bwd.  d_g2d / d_rgb / row_vis may be column views of one (n, stride) accumulator.
-  grads: dict(position, log_scaling, rotation, alpha_logit, sh) to write/accumulate into (allocated if None)."""
+  grads: dict(position, log_scaling, rotation, alpha_logit, sh) to write/accumulate into (allocated if None).
+  reg: (weights (scale, opacity, aspect), sums (4,), depth (n,)) — fuse the regularisation gradients of reg_loss."""
   n = position.shape[0]
   dev = position.device
   if grads is None:
@@ -77,9 +78,13 @@ def project_bwd(cam, cfg, position, log_scaling, rotation, alpha_logit, sh, sh_d
   p_dg, s_dg = strided(d_g2d)
   p_dr, s_dr = strided(d_rgb)
   p_rv, s_rv = strided(row_vis)
+  fuse = None
+  if reg is not None:
+    wts, sums, depth = reg
+    fuse = C.byref(L.RegFuse(float(wts[0]), float(wts[1]), float(wts[2]), L.ptr(sums), L.ptr(_f32(depth))))
   L.check(L.load().gs_project_bwd(C.byref(cam), C.byref(cfg), n, L.ptr(position), L.ptr(log_scaling), L.ptr(rotation),
                                   L.ptr(alpha_logit), L.ptr(sh), sh_degree, L.ptr(g2d), p_dg, s_dg, p_dr, s_dr,
-                                  L.ptr(d_depth), p_rv, s_rv, L.ptr(grads["position"]), L.ptr(grads["log_scaling"]),
+                                  L.ptr(d_depth), p_rv, s_rv, fuse, L.ptr(grads["position"]), L.ptr(grads["log_scaling"]),
                                   L.ptr(grads["rotation"]), L.ptr(grads["alpha_logit"]), L.ptr(grads.get("sh")),
                                   int(accumulate), L.stream()))
   return grads

@@ -138,7 +138,7 @@ class SplatScene:
              image=torch.empty((H, W, 3), device=dev), final_T=torch.empty((H, W), device=dev),
              n_contrib=torch.empty((H, W), device=dev, dtype=torch.int32), d_image=torch.empty((H, W, 3), device=dev),
              loss_sums=torch.zeros((2,), device=dev), reg_sums=torch.zeros((4,), device=dev),
-             d_depth=torch.zeros((n,), device=dev), tile=None,
+             tile=None,
              ssim_sums=torch.zeros((max(self.config.ssim_levels, 1),), device=dev),
              ssim_ws=ops.ssim_workspace(H, W, 3, max(self.config.ssim_levels, 1), dev) if self.config.w_ssim != 0.0 else None)
     self._work = w
@@ -257,17 +257,15 @@ class SplatScene:
     p = self.p
     reg = any(x != 0.0 for x in c.reg_weights)
     if reg:
-      # reg_loss (reference scene/mlp_scene.py:246-288) over the rows this image blended: its gradient w.r.t. the
-      # projected opacity / depth joins the raster gradients BEFORE the projection backward consumes them
-      ops.reg_loss(c.reg_weights, w["g2d"], w["depth"], p["log_scaling"], w["vis"], sums=w["reg_sums"], compute_sums=True,
-                   d_opacity=acc[:, 5], d_depth=w["d_depth"])
+      # reg_loss (reference scene/mlp_scene.py:246-288) over the rows this image blended.  One sweep for the sums (the
+      # gradients need the blended-row count); the gradients w.r.t. the projected opacity / depth / log_scaling are
+      # formed per row inside the projection backward, which already holds everything they need
+      ops.reg_loss(c.reg_weights, w["g2d"], w["depth"], p["log_scaling"], w["vis"], sums=w["reg_sums"], compute_sums=True)
       self._mark("reg")
     ops.project_bwd(cam, self.raster_cfg, p["position"], p["log_scaling"], p["rotation"], p["alpha_logit"], p["sh"],
-                    c.sh_degree, w["g2d"], acc[:, 0:6], acc[:, 6:9], w["d_depth"] if reg else None, row_vis=w["vis"],
-                    grads=self.g, accumulate=not (first or exchange is not None))
-    if reg:  # the direct d/d log_scaling part, on top of the rows the projection backward just wrote
-      ops.reg_loss(c.reg_weights, w["g2d"], w["depth"], p["log_scaling"], w["vis"], sums=w["reg_sums"], compute_sums=False,
-                   d_log_scaling=self.g["log_scaling"])
+                    c.sh_degree, w["g2d"], acc[:, 0:6], acc[:, 6:9], None, row_vis=w["vis"], grads=self.g,
+                    accumulate=not (first or exchange is not None),
+                    reg=(c.reg_weights, w["reg_sums"], w["depth"]) if reg else None)
     self._mark("project_bwd")
     if exchange is not None:
       # the dense gradient buffer holds this image's rows only (pack moves them out and zeroes them again)
