@@ -248,6 +248,24 @@ int gs_optim_step(const gs_optim_config *h_cfg, int kind, int64_t n,
                   const float *basis_log_scaling, const float *basis_rotation,
                   int post, float post_lo, float post_hi, int zero_grad, void *stream);
 
+/* Several parameter groups in ONE launch (the reference steps its groups one after the other,
+ * scene/mlp_scene.py:214-230; groups are independent of each other except that `position` reads log_scaling /
+ * rotation as its basis BEFORE their update, :219).  The groups of a call run concurrently, so a call is refused
+ * (GS_ERR_INVALID) when one of its groups updates a plane another one reads as basis — put that group in a later call.
+ * Results equal gs_optim_step called once per group, bit for bit. */
+#define GS_OPTIM_MAX_GROUPS 8
+typedef struct gs_optim_group {
+  int32_t kind, dim;                       /* GS_GROUP_*, elements per row                   */
+  float lr;
+  float *param, *grad, *exp_avg, *exp_avg_sq;
+  const float *basis_ls, *basis_q;         /* LOCAL_VECTOR only                              */
+  int32_t post;                            /* GS_POST_*                                      */
+  float post_lo, post_hi;
+} gs_optim_group;
+int gs_optim_step_groups(const gs_optim_config *h_cfg, int64_t n, const int32_t *indexes, const int32_t *count_dev,
+                         int n_groups, const gs_optim_group *h_groups, const float *visible, const float *running_vis,
+                         const float *step, int zero_grad, void *stream);
+
 /* PointState.add_rendering (reference controller/point_state.py:34-50) + MLPScene.add_rendering
  * (scene/mlp_scene.py:242-244) for one rendering whose rows are Gaussians (fused path, idx=NULL)
  * or listed by idx (m rows -> Gaussian idx[i]).  In-view rows: opacity (g2d[5]) > 0.

@@ -337,15 +337,19 @@ __device__ __forceinline__ void optim_row(const OptDev &c, int64_t i, int l, boo
 // Grid-stride over rows.  Dense mode (indexes == NULL): row r is Gaussian r, rows with visible <= 0 idle.
 // Indexed mode: row r is Gaussian indexes[r], r < *count_dev (the device-side `visible.nonzero()` of the
 // reference, scene/mlp_scene.py:217, with no host read-back) — only the rows the step touches are ever read.
+struct OptGroupDev {
+  int variant, dim, post;
+  float lr, post_lo, post_hi;
+  float *param, *grad, *exp_avg, *exp_avg_sq;
+  const float *basis_ls, *basis_q;
+};
+struct OptGroupsDev { OptGroupDev g[GS_OPTIM_MAX_GROUPS]; };
+
 template <int KIND, int LANES, int EPL>
-__global__ void __launch_bounds__(256) k_optim_step(OptDev c, int64_t n, const int32_t *__restrict__ indexes,
-                                                    const int32_t *__restrict__ count_dev, int dim, float lr,
-                                                    float *__restrict__ param, float *__restrict__ grad,
-                                                    float *__restrict__ exp_avg, float *__restrict__ exp_avg_sq,
-                                                    const float *__restrict__ visible, const float *__restrict__ running_vis,
-                                                    const float *__restrict__ step, const float *__restrict__ basis_ls,
-                                                    const float *__restrict__ basis_q, int post, float post_lo, float post_hi,
-                                                    int zero_grad) {
+__device__ __forceinline__ void optim_sweep(const OptDev &c, int64_t n, const int32_t *__restrict__ indexes,
+                                            const int32_t *__restrict__ count_dev, const OptGroupDev &g,
+                                            const float *__restrict__ visible, const float *__restrict__ running_vis,
+                                            const float *__restrict__ step, int zero_grad) {
   int64_t rows = indexes ? min((int64_t)*count_dev, n) : n;
   int64_t total = rows * LANES;
   int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -354,9 +358,80 @@ __global__ void __launch_bounds__(256) k_optim_step(OptDev c, int64_t n, const i
     int64_t r = t / LANES;
     bool row_ok = r < rows;
     int64_t i = row_ok ? (indexes ? (int64_t)indexes[r] : r) : 0;
-    optim_row<KIND, LANES, EPL>(c, i, (int)(t % LANES), row_ok, dim, lr, param, grad, exp_avg, exp_avg_sq, visible, running_vis,
-                                step, basis_ls, basis_q, post, post_lo, post_hi, zero_grad);
+    optim_row<KIND, LANES, EPL>(c, i, (int)(t % LANES), row_ok, g.dim, g.lr, g.param, g.grad, g.exp_avg, g.exp_avg_sq, visible,
+                                running_vis, step, g.basis_ls, g.basis_q, g.post, g.post_lo, g.post_hi, zero_grad);
   }
+}
+
+// variant = the (KIND, LANES, EPL) instantiation a group runs with
+__host__ __device__ inline int optim_variant(int kind, int dim) {
+  if (kind == GS_GROUP_LOCAL_VECTOR) return 0;
+  int w = dim <= 4 ? 0 : (dim <= 16 ? 1 : 2);
+  return 1 + (kind == GS_GROUP_SCALAR ? 0 : 3) + w;
+}
+__host__ inline int optim_variant_lanes(int variant) {
+  const int lanes[7] = {1, 1, 4, 16, 1, 4, 16};
+  return lanes[variant];
+}
+
+// One launch for several parameter groups: blockIdx.y selects the group (a CTA-uniform read of the parameter block).
+__global__ void __launch_bounds__(256) k_optim_groups(OptDev c, int64_t n, const int32_t *__restrict__ indexes,
+                                                      const int32_t *__restrict__ count_dev, OptGroupsDev gs,
+                                                      const float *__restrict__ visible, const float *__restrict__ running_vis,
+                                                      const float *__restrict__ step, int zero_grad) {
+  const OptGroupDev &g = gs.g[blockIdx.y];
+  switch (g.variant) {
+    case 0: optim_sweep<2, 1, 3>(c, n, indexes, count_dev, g, visible, running_vis, step, zero_grad); break;
+    case 1: optim_sweep<0, 1, 4>(c, n, indexes, count_dev, g, visible, running_vis, step, zero_grad); break;
+    case 2: optim_sweep<0, 4, 4>(c, n, indexes, count_dev, g, visible, running_vis, step, zero_grad); break;
+    case 3: optim_sweep<0, 16, 4>(c, n, indexes, count_dev, g, visible, running_vis, step, zero_grad); break;
+    case 4: optim_sweep<1, 1, 4>(c, n, indexes, count_dev, g, visible, running_vis, step, zero_grad); break;
+    case 5: optim_sweep<1, 4, 4>(c, n, indexes, count_dev, g, visible, running_vis, step, zero_grad); break;
+    default: optim_sweep<1, 16, 4>(c, n, indexes, count_dev, g, visible, running_vis, step, zero_grad); break;
+  }
+}
+
+static int optim_check_group(const gs_optim_group &q) {
+  GS_REQUIRE(q.param && q.grad && q.exp_avg && q.exp_avg_sq, "null argument");
+  GS_REQUIRE(q.dim >= 1 && q.dim <= 64, "dim must be 1..64");
+  GS_REQUIRE(q.kind >= 0 && q.kind <= 2, "bad group kind");
+  GS_REQUIRE(q.kind != GS_GROUP_LOCAL_VECTOR || (q.dim == 3 && q.basis_ls && q.basis_q), "local_vector needs dim 3 and a basis");
+  return GS_OK;
+}
+
+extern "C" int gs_optim_step_groups(const gs_optim_config *h, int64_t n, const int32_t *indexes, const int32_t *count_dev,
+                                    int n_groups, const gs_optim_group *groups, const float *visible, const float *running_vis,
+                                    const float *step, int zero_grad, void *stream) {
+  GS_REQUIRE(h && groups && visible && running_vis && step, "null argument");
+  GS_REQUIRE(n_groups >= 1 && n_groups <= GS_OPTIM_MAX_GROUPS, "1..GS_OPTIM_MAX_GROUPS groups per call");
+  GS_REQUIRE((indexes == nullptr) == (count_dev == nullptr), "indexes and count_dev go together");
+  OptGroupsDev gs;
+  int64_t want = 1;
+  for (int k = 0; k < n_groups; ++k) {
+    const gs_optim_group &q = groups[k];
+    int rc = optim_check_group(q);
+    if (rc != GS_OK) return rc;
+    // the groups of one call run concurrently: none may update a plane another one reads as its basis
+    for (int j = 0; j < n_groups; ++j)
+      GS_REQUIRE(!(j != k && groups[j].kind == GS_GROUP_LOCAL_VECTOR && (groups[j].basis_ls == q.param || groups[j].basis_q == q.param)),
+                 "a group of the call updates the basis of another one: put it in a later call");
+    OptGroupDev &d = gs.g[k];
+    d.variant = optim_variant(q.kind, q.dim);
+    d.dim = q.dim; d.post = q.post; d.lr = q.lr; d.post_lo = q.post_lo; d.post_hi = q.post_hi;
+    d.param = q.param; d.grad = q.grad; d.exp_avg = q.exp_avg; d.exp_avg_sq = q.exp_avg_sq;
+    d.basis_ls = q.basis_ls; d.basis_q = q.basis_q;
+    int64_t w = (n * optim_variant_lanes(d.variant) + 255) / 256;
+    want = w > want ? w : want;
+  }
+  if (n <= 0) return GS_OK;
+  OptDev c = {h->mode, h->beta1, h->beta2, h->eps, h->vis_beta, h->vis_smooth, h->grad_clip, h->bias_correction};
+  // grid: per group enough CTAs to fill the machine (148 SMs x 8 resident CTAs of 256 threads), never more than the
+  // work; the sweeps are latency bound (scattered rows), so the widest group sets the pace and the CTAs of narrow
+  // groups that find no rows leave at once
+  dim3 grid((unsigned)(want < 148 * 8 ? want : 148 * 8), (unsigned)n_groups);
+  k_optim_groups<<<grid, 256, 0, (cudaStream_t)stream>>>(c, n, indexes, count_dev, gs, visible, running_vis, step, zero_grad);
+  GS_LAUNCH_CHECK();
+  return GS_OK;
 }
 
 extern "C" int gs_optim_step(const gs_optim_config *h, int kind, int64_t n, const int32_t *indexes, const int32_t *count_dev,
@@ -364,36 +439,8 @@ extern "C" int gs_optim_step(const gs_optim_config *h, int kind, int64_t n, cons
                              float *exp_avg, float *exp_avg_sq, const float *visible, const float *running_vis,
                              const float *step, const float *basis_ls, const float *basis_q, int post, float post_lo,
                              float post_hi, int zero_grad, void *stream) {
-  GS_REQUIRE(h && param && grad && exp_avg && exp_avg_sq && visible && running_vis && step, "null argument");
-  GS_REQUIRE(dim >= 1 && dim <= 64, "dim must be 1..64");
-  GS_REQUIRE(kind >= 0 && kind <= 2, "bad group kind");
-  GS_REQUIRE(kind != GS_GROUP_LOCAL_VECTOR || (dim == 3 && basis_ls && basis_q), "local_vector needs dim 3 and a basis");
-  GS_REQUIRE((indexes == nullptr) == (count_dev == nullptr), "indexes and count_dev go together");
-  if (n <= 0) return GS_OK;
-  OptDev c = {h->mode, h->beta1, h->beta2, h->eps, h->vis_beta, h->vis_smooth, h->grad_clip, h->bias_correction};
-  cudaStream_t st = (cudaStream_t)stream;
-  // grid: enough CTAs to fill the machine (148 SMs x 8 resident CTAs of 256 threads), never more than the work
-#define GS_OPT(KIND, LANES, EPL)                                                                                    \
-  do {                                                                                                               \
-    int64_t want = (n * LANES + 255) / 256;                                                                          \
-    int grid = (int)(want < 148 * 8 ? want : 148 * 8);                                                               \
-    k_optim_step<KIND, LANES, EPL><<<grid, 256, 0, st>>>(c, n, indexes, count_dev, dim, lr, param, grad, exp_avg,    \
-                                                         exp_avg_sq, visible, running_vis, step, basis_ls, basis_q, \
-                                                         post, post_lo, post_hi, zero_grad);                        \
-  } while (0)
-  if (kind == GS_GROUP_LOCAL_VECTOR) GS_OPT(2, 1, 3);
-  else if (kind == GS_GROUP_SCALAR) {
-    if (dim <= 4) GS_OPT(0, 1, 4);
-    else if (dim <= 16) GS_OPT(0, 4, 4);
-    else GS_OPT(0, 16, 4);
-  } else {
-    if (dim <= 4) GS_OPT(1, 1, 4);
-    else if (dim <= 16) GS_OPT(1, 4, 4);
-    else GS_OPT(1, 16, 4);
-  }
-#undef GS_OPT
-  GS_LAUNCH_CHECK();
-  return GS_OK;
+  gs_optim_group q = {kind, dim, lr, param, grad, exp_avg, exp_avg_sq, basis_ls, basis_q, post, post_lo, post_hi};
+  return gs_optim_step_groups(h, n, indexes, count_dev, 1, &q, visible, running_vis, step, zero_grad, stream);
 }
 
 // ---- statistics --------------------------------------------------------------------------------------

@@ -41,6 +41,15 @@ class ExchangeGroups(C.Structure):  # gs_exchange_groups
               ("grad", C.c_void_p * GS_EXCHANGE_MAX_GROUPS)]
 
 
+GS_OPTIM_MAX_GROUPS = 8
+
+
+class OptimGroup(C.Structure):  # gs_optim_group
+  _fields_ = [("kind", C.c_int32), ("dim", C.c_int32), ("lr", C.c_float), ("param", C.c_void_p), ("grad", C.c_void_p),
+              ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p), ("basis_ls", C.c_void_p), ("basis_q", C.c_void_p),
+              ("post", C.c_int32), ("post_lo", C.c_float), ("post_hi", C.c_float)]
+
+
 class RegFuse(C.Structure):  # gs_reg_fuse
   _fields_ = [("w_scale", C.c_float), ("w_opacity", C.c_float), ("w_aspect", C.c_float), ("sums", C.c_void_p),
               ("depth", C.c_void_p)]
@@ -76,6 +85,7 @@ SIGNATURES = {
   "gs_optim_vis_update": (_I, [_OPT, _L, _P, _P, _P, _P]),
   "gs_visible_indexes_workspace_bytes": (_Z, [_L]),
   "gs_visible_indexes": (_I, [_L, _P, _P, _P, _P, _Z, _P]),
+  "gs_optim_step_groups": (_I, [_OPT, _L, _P, _P, _I, C.POINTER(OptimGroup), _P, _P, _P, _I, _P]),
   "gs_optim_step": (_I, [_OPT, _I, _L, _P, _P, _I, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _F, _F, _I, _P]),
   "gs_accumulate_stats": (_I, [_L, _P, _P, _P, _I, _P, _I, _F, _F, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P]),
   "gs_select_topk_workspace_bytes": (_Z, [_L]),

@@ -273,6 +273,24 @@ def optim_step(ocfg, kind, lr, param, grad, exp_avg, exp_avg_sq, visible, runnin
                                  L.ptr(basis_q), post, post_lo, post_hi, int(zero_grad), L.stream()))
 
 
+def optim_group(kind, lr, param, grad, exp_avg, exp_avg_sq, basis_ls=None, basis_q=None, post=L.GS_POST_NONE, post_lo=0.0,
+                post_hi=0.0):
+  """one gs_optim_group entry for optim_step_groups."""
+  n = param.shape[0]
+  dim = param.numel() // max(n, 1) if n > 0 else 1
+  return L.OptimGroup(kind, dim, lr, L.ptr(_f32(param)), L.ptr(_f32(grad)), L.ptr(exp_avg), L.ptr(exp_avg_sq),
+                      L.ptr(basis_ls), L.ptr(basis_q), post, post_lo, post_hi)
+
+
+def optim_step_groups(ocfg, n, groups, visible, running_vis, step, zero_grad=True, indexes=None):
+  """gs_optim_step_groups: the listed groups (optim_group entries) in one launch; bit-identical to one optim_step per
+  group as long as no group of the call updates another one's basis (the library refuses that)."""
+  arr = (L.OptimGroup * len(groups))(*groups)
+  L.check(L.load().gs_optim_step_groups(C.byref(ocfg), n, None if indexes is None else L.ptr(indexes.indexes),
+                                        None if indexes is None else L.ptr(indexes.count), len(groups), arr, L.ptr(visible),
+                                        L.ptr(running_vis), L.ptr(step), int(zero_grad), L.stream()))
+
+
 def accumulate_stats(idx, g2d, vis, heur, split_alpha, prune_alpha, state, scene_visible=None, clear_acc=None,
                      clear_vis=None):
   """vis: (m,) or a column view; heur: (m,2)-like view whose row stride is heur.stride(0) with

@@ -234,16 +234,19 @@ class SplatScene:
     return split_mask, prune_mask
 
   # ---- one training image: forward + loss + backward + statistics ------------------------------------------
-  def forward_backward(self, cam, target, first=False, exchange=None, slot=0):
+  def forward_backward(self, cam, target, first=False, exchange=None, slot=0, target_ready=None):
     """Reference trainer/trainer.py:500-514 for one image (render → loss → backward → add_rendering), fused:
     gradients are ADDED into self.g (batch = sum), statistics into self.stats / self.visible.
     target: (H,W,3) float32 in [0,1] or uint8 on the device.  Returns loss_sums (device, 2): Σ|d|, Σd².
     first=True (the step's first image, gradient buffer all-zero: the optimiser clears the rows it consumes): rows are
     WRITTEN instead of read-modified-written.
     exchange (an ImageExchange, camera-batch DP): the image's gradient rows and statistics are packed into record
-    `slot` instead of being applied here; ImageExchange.fold() applies every rank's records in image order."""
+    `slot` instead of being applied here; ImageExchange.fold() applies every rank's records in image order.
+    target_ready: CUDA event of a side-stream upload of `target`; the stream waits for it right before the loss."""
     w, tb, _, _ = self._forward(cam)
     c = self.config
+    if target_ready is not None:
+      torch.cuda.current_stream().wait_event(target_ready)
     w["loss_sums"].zero_()
     ops.loss_l1_mse(w["image"], target, c.w_l1, c.w_mse, d_pred=w["d_image"], sums=w["loss_sums"])
     if c.w_ssim != 0.0:  # multi-scale SSIM (reference trainer/trainer.py:450-462); its gradient joins d_image
@@ -289,16 +292,19 @@ class SplatScene:
     # visibility state + device-side visible.nonzero() (reference mlp_scene.py:217) in one kernel, no host sync
     ix = self._vis_idx.begin(o, vis, rv, st)
     p, g, m1, m2 = self.p, self.g, self.m1, self.m2
-    # position first: its local basis is built from log_scaling / rotation BEFORE their update (mlp_scene.py:219)
-    ops.optim_step(o, L.GS_GROUP_LOCAL_VECTOR, c.lr_position, p["position"], g["position"], m1["position"],
-                   m2["position"], vis, rv, st, basis_ls=p["log_scaling"], basis_q=p["rotation"], indexes=ix)
-    ops.optim_step(o, L.GS_GROUP_SCALAR, c.lr_log_scaling, p["log_scaling"], g["log_scaling"], m1["log_scaling"],
-                   m2["log_scaling"], vis, rv, st, post=L.GS_POST_CLAMP, post_lo=-8.0, post_hi=8.0, indexes=ix)
-    ops.optim_step(o, L.GS_GROUP_VECTOR, c.lr_rotation, p["rotation"], g["rotation"], m1["rotation"], m2["rotation"],
-                   vis, rv, st, post=L.GS_POST_NORMALIZE, indexes=ix)
-    ops.optim_step(o, L.GS_GROUP_SCALAR, c.lr_alpha_logit, p["alpha_logit"], g["alpha_logit"], m1["alpha_logit"],
-                   m2["alpha_logit"], vis, rv, st, indexes=ix)
-    ops.optim_step(o, L.GS_GROUP_VECTOR, c.lr_sh, p["sh"], g["sh"], m1["sh"], m2["sh"], vis, rv, st, indexes=ix)
+    # two launches instead of five: position's local basis is built from log_scaling / rotation BEFORE their update
+    # (mlp_scene.py:219), so those two groups go in the second launch; groups within a launch are independent
+    G = ops.optim_group
+    ops.optim_step_groups(o, self.n, [
+      G(L.GS_GROUP_LOCAL_VECTOR, c.lr_position, p["position"], g["position"], m1["position"], m2["position"],
+        basis_ls=p["log_scaling"], basis_q=p["rotation"]),
+      G(L.GS_GROUP_SCALAR, c.lr_alpha_logit, p["alpha_logit"], g["alpha_logit"], m1["alpha_logit"], m2["alpha_logit"]),
+      G(L.GS_GROUP_VECTOR, c.lr_sh, p["sh"], g["sh"], m1["sh"], m2["sh"])], vis, rv, st, indexes=ix)
+    ops.optim_step_groups(o, self.n, [
+      G(L.GS_GROUP_SCALAR, c.lr_log_scaling, p["log_scaling"], g["log_scaling"], m1["log_scaling"], m2["log_scaling"],
+        post=L.GS_POST_CLAMP, post_lo=-8.0, post_hi=8.0),
+      G(L.GS_GROUP_VECTOR, c.lr_rotation, p["rotation"], g["rotation"], m1["rotation"], m2["rotation"],
+        post=L.GS_POST_NORMALIZE)], vis, rv, st, indexes=ix)
     self._mark("optim")
     vis.zero_()  # zero_grad(): gradient rows were cleared by the optimiser kernels (mlp_scene.py:155-161)
 

@@ -43,7 +43,7 @@ class Trainer:
     self.scene = scene
     self.world_size, self.rank = world_size, rank
     self.step_count = 0
-    self._dev_target = None
+    self._copy_stream, self._target_flip = None, 0
     self._grads_clean = False  # unknown history of scene.grads until the first step has run
     self.exchange = None
     if isinstance(exchange, str):
@@ -56,14 +56,28 @@ class Trainer:
       self.exchange = exchange
 
   def _to_device(self, image):
-    """host (pinned) uint8/float image -> reusable device buffer, async on the current stream
-    (reference trainer/trainer.py:548-553 does the same copy in its loader thread)."""
-    if image.is_cuda:
-      return image
-    if self._dev_target is None or self._dev_target.shape != image.shape or self._dev_target.dtype != image.dtype:
-      self._dev_target = torch.empty(image.shape, dtype=image.dtype, device=self.scene.device)
-    self._dev_target.copy_(image, non_blocking=True)
-    return self._dev_target
+    """host (pinned) uint8/float image -> one of two reusable device buffers, copied on a side stream so the transfer
+    runs under the projection / tile map / raster forward of the same image (reference trainer/trainer.py:548-553 does
+    the copy in its loader thread).  Returns (device image, event the loss must wait for | None)."""
+    if image.is_cuda or torch.device(self.scene.device).type != "cuda":  # already resident (or a host-side stub scene)
+      return image, None
+    if self._copy_stream is None:
+      self._copy_stream = torch.cuda.Stream(device=self.scene.device)
+      self._targets = [None, None]
+      self._consumed = [None, None]
+    k = self._target_flip
+    self._target_flip ^= 1
+    buf = self._targets[k]
+    if buf is None or buf.shape != image.shape or buf.dtype != image.dtype:
+      buf = self._targets[k] = torch.empty(image.shape, dtype=image.dtype, device=self.scene.device)
+    cs = self._copy_stream
+    if self._consumed[k] is not None:
+      cs.wait_event(self._consumed[k])  # the loss of two images ago has finished reading this buffer
+    with torch.cuda.stream(cs):
+      buf.copy_(image, non_blocking=True)
+      ready = torch.cuda.Event()
+      ready.record(cs)
+    return buf, (ready, k)
 
   def exchange_gradients(self):
     """SUM (not mean: reference accumulates .grad over the batch, trainer/trainer.py:500-514) of the packed
@@ -127,8 +141,13 @@ class Trainer:
     if self.exchange is not None and len(mine) != self.exchange.k:
       raise L.GsError(f"the exchange was sized for {self.exchange.k} image(s) per rank, got {len(mine)}")
     for k, (cam, image) in enumerate(mine):
-      sums = scene.forward_backward(cam, self._to_device(image), first=(k == 0 and self._grads_clean),
-                                    exchange=self.exchange, slot=k)
+      target, ready = self._to_device(image)
+      sums = scene.forward_backward(cam, target, first=(k == 0 and self._grads_clean), exchange=self.exchange, slot=k,
+                                    target_ready=None if ready is None else ready[0])
+      if ready is not None:
+        done = torch.cuda.Event()
+        done.record()  # after this image's backward: its loss kernels are long finished with the target
+        self._consumed[ready[1]] = done
       total = sums.clone() if total is None else total + sums
     self.step_count += len(batch)  # the reference counts images, trainer/trainer.py:532
     self.exchange_gradients()

@@ -32,7 +32,7 @@ class StubScene:
   def _mark(self, name):
     pass
 
-  def forward_backward(self, cam, image, first=False, exchange=None, slot=0):
+  def forward_backward(self, cam, image, first=False, exchange=None, slot=0, target_ready=None):
     k = int(cam)
     rows = torch.arange(N)[(torch.arange(N) + k) % 3 == 0]
     g = self.grads[:N * D].view(N, D)

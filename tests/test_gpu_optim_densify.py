@@ -59,6 +59,49 @@ def test_optim_step_matches_oracle(mode, kind, dim, post, indexed):
   assert np.array_equal(npy(dev["param"])[untouched], param[untouched])
 
 
+@pytest.mark.parametrize("indexed", [False, True])
+def test_grouped_launch_equals_one_launch_per_group(indexed):
+  """gs_optim_step_groups (the training step's two launches) == gs_optim_step per group, bit for bit; a call whose
+  groups would race on a basis plane is refused."""
+  rng = np.random.default_rng(7)
+  n = 20011
+  locfg = to_lib_optim(go.make_optim_config(mode=1))
+  dims = dict(position=3, log_scaling=3, rotation=4, alpha_logit=1, sh=48)
+  kinds = dict(position=2, log_scaling=0, rotation=1, alpha_logit=0, sh=1)
+  posts = dict(log_scaling=(2, -8.0, 8.0), rotation=(1, 0.0, 0.0))
+  host = {}
+  for name, d in dims.items():
+    host[name] = dict(param=rng.normal(0, 1, (n, d)).astype(np.float32), grad=rng.normal(0, 1, (n, d)).astype(np.float32),
+                      m1=rng.normal(0, 0.1, (n, d)).astype(np.float32),
+                      m2=rng.uniform(0, 0.1, (n, d) if kinds[name] == 0 else (n,)).astype(np.float32))
+  vis = cu(np.where(rng.uniform(0, 1, n) < 0.3, rng.uniform(0.01, 30, n), 0).astype(np.float32))
+  rv, st = cu(rng.uniform(0.1, 5, n).astype(np.float32)), cu(rng.integers(1, 50, n).astype(np.float32))
+  ix = ops.VisibleIndexes(n, "cuda").update(vis) if indexed else None
+  A = {k: {q: cu(v) for q, v in d.items()} for k, d in host.items()}
+  B = {k: {q: cu(v) for q, v in d.items()} for k, d in host.items()}
+  order = ("position", "log_scaling", "rotation", "alpha_logit", "sh")
+  for name in order:  # reference order, one launch per group (position reads the basis before its update)
+    a = A[name]
+    post = posts.get(name, (0, 0.0, 0.0))
+    ops.optim_step(locfg, kinds[name], 0.01, a["param"], a["grad"], a["m1"], a["m2"], vis, rv, st,
+                   A["log_scaling"]["param"], A["rotation"]["param"], *post, True, indexes=ix)
+
+  def G(name):
+    b = B[name]
+    post = posts.get(name, (0, 0.0, 0.0))
+    basis = (B["log_scaling"]["param"], B["rotation"]["param"]) if name == "position" else (None, None)
+    return ops.optim_group(kinds[name], 0.01, b["param"], b["grad"], b["m1"], b["m2"], *basis, *post)
+
+  ops.optim_step_groups(locfg, n, [G("position"), G("alpha_logit"), G("sh")], vis, rv, st, indexes=ix)
+  ops.optim_step_groups(locfg, n, [G("log_scaling"), G("rotation")], vis, rv, st, indexes=ix)
+  torch.cuda.synchronize()
+  for name in order:
+    for q in ("param", "grad", "m1", "m2"):
+      assert torch.equal(A[name][q], B[name][q]), (name, q)
+  with pytest.raises(L.GsError):
+    ops.optim_step_groups(locfg, n, [G("position"), G("rotation")], vis, rv, st, indexes=ix)
+
+
 def test_accumulate_stats_matches_oracle():
   orc = oracle()
   rng = np.random.default_rng(7)
