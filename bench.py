@@ -211,7 +211,7 @@ def run_reference(args):
           "cpu_baseline": {"value": value, "unit": unit, "cores": cores, "kind": "port",
                            "sample": f"{args.steps} full iterations of the same workload (random uint8 targets)"},
           "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-  print(json.dumps(line), flush=True)
+  emit(line)
 
 
 def run_b200(args):
@@ -390,12 +390,24 @@ def run_b200(args):
       dt = (time.perf_counter() - t0) / reps
       line["cpu_baseline"] = {"value": 1.0 / dt, "unit": "iters/s", "cores": len(os.sched_getaffinity(0)), "kind": "port",
                               "sample": f"{reps} full iterations of the same workload (after 1 warm-up) in the OpenMP oracle"}
-    print(json.dumps(line), flush=True)
+    emit(line)
   if world > 1:
     dist.destroy_process_group()
 
 
+_REAL_STDOUT = sys.stdout
+
+
+def emit(line):
+  """the ONE JSON line goes to the real stdout; everything else any library prints (NCCL's version banner, torchrun
+  notices) was sent to stderr by the redirect in __main__."""
+  _REAL_STDOUT.write(json.dumps(line) + "\n")
+  _REAL_STDOUT.flush()
+
+
 if __name__ == "__main__":
+  _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+  os.dup2(2, 1)
   a = parse()
   if a.impl == "reference":
     run_reference(a)

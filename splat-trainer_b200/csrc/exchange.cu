@@ -330,7 +330,7 @@ __global__ void __launch_bounds__(256) k_fold_stats(int64_t n, int64_t cap, Reco
 // round trip for all images), then for every row some image blended each lane keeps two elements of the dense
 // gradient row in registers and adds the images' record rows in image order — no barrier, no atomics.  A record row
 // is one coalesced 8-B-per-lane warp load (256 B for SH3), the unit NVLink moves efficiently.
-__global__ void __launch_bounds__(256, 4) k_fold_rows(int64_t n, int64_t cap, RecordsDev recs, GroupsDev gd) {
+__global__ void __launch_bounds__(256, 8) k_fold_rows(int64_t n, int64_t cap, RecordsDev recs, GroupsDev gd) {
   const int lane = threadIdx.x & 31;
   const int64_t words = (n + 31) / 32;
   const size_t plane = al256((size_t)words * 4);
@@ -359,84 +359,57 @@ __global__ void __launch_bounds__(256, 4) k_fold_rows(int64_t n, int64_t cap, Re
     }
     unsigned any = __reduce_or_sync(GS_FULL, vb0 | vb1);
     while (any) {
-      // two rows per trip: their gradient loads and record loads are all in flight together
-      int64_t id[2];
-      unsigned m0[2], m1[2], p0[2], p1[2];
-      bool on[2];
-#pragma unroll
-      for (int t = 0; t < 2; ++t) {
-        on[t] = any != 0u;
-        const int b = on[t] ? __ffs(any) - 1 : 0;
-        any &= any - 1;  // (0 stays 0)
-        const unsigned bit = on[t] ? (1u << b) : 0u;
-        id[t] = w * 32 + b;
-        m0[t] = __ballot_sync(GS_FULL, (vb0 & bit) != 0u);
-        m1[t] = __ballot_sync(GS_FULL, (vb1 & bit) != 0u);
-        p0[t] = bs0 + __popc(vb0 & (bit - 1u));  // row position in my images (lanes whose image lacks the row: unused)
-        p1[t] = bs1 + __popc(vb1 & (bit - 1u));
-      }
+      const int b = __ffs(any) - 1;
+      any &= any - 1;
+      const unsigned bit = 1u << b;
+      const int64_t id = w * 32 + b;
+      const unsigned m0 = __ballot_sync(GS_FULL, (vb0 & bit) != 0u), m1 = __ballot_sync(GS_FULL, (vb1 & bit) != 0u);
+      const unsigned p0 = bs0 + __popc(vb0 & (bit - 1u)), p1 = bs1 + __popc(vb1 & (bit - 1u));  // row position in my images
       for (int e0 = 0; e0 < pad; e0 += 64) {  // warp-uniform trip count: the shuffles below need every lane
         const int e = e0 + 2 * lane;
         const bool act = e < pad;
-        // the two elements e, e+1 of each row: their group planes in the dense gradient buffer
-        float *dst[2][2];
-        float acc[2][2];
+        // the two elements e, e+1 of the row: their group planes in the dense gradient buffer
+        float *dst[2];
 #pragma unroll
-        for (int t = 0; t < 2; ++t)
-#pragma unroll
-          for (int q = 0; q < 2; ++q) {
-            float *d = nullptr;
-            if (on[t]) {
-              if (e0 == 0) {
-                d = hplane[q] ? hplane[q] + id[t] * hdim[q] + hk[q] : nullptr;
-              } else if (e + q < gd.total) {
-                int k, dim; float *plane;
-                group_of(gd, e + q, k, dim, plane);
-                d = plane + id[t] * dim + k;
-              } else if (e + q == gd.total && gd.vis) {
-                d = gd.vis + id[t];
-              }
+        for (int q = 0; q < 2; ++q) {
+          if (e0 == 0) {
+            dst[q] = hplane[q] ? hplane[q] + id * hdim[q] + hk[q] : nullptr;
+          } else {
+            dst[q] = nullptr;
+            if (e + q < gd.total) {
+              int k, dim; float *plane;
+              group_of(gd, e + q, k, dim, plane);
+              dst[q] = plane + id * dim + k;
+            } else if (e + q == gd.total && gd.vis) {
+              dst[q] = gd.vis + id;
             }
-            dst[t][q] = d;
-          }
-#pragma unroll
-        for (int t = 0; t < 2; ++t)
-#pragma unroll
-          for (int q = 0; q < 2; ++q) acc[t][q] = dst[t][q] ? *dst[t][q] : 0.f;
-        // the rows' images in batches of 4 per row: all record loads of a trip are in flight together (one NVLink
-        // round trip), the adds then run in image order
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          unsigned ma = half ? m1[0] : m0[0], mb = half ? m1[1] : m0[1];
-          const unsigned pa = half ? p1[0] : p0[0], pb = half ? p1[1] : p0[1];
-          while (ma | mb) {
-            float2 v[2][4];
-#pragma unroll
-            for (int t = 0; t < 2; ++t) {
-              unsigned &m = t ? mb : ma;
-              const unsigned pmine = t ? pb : pa;
-#pragma unroll
-              for (int c = 0; c < 4; ++c) {
-                v[t][c] = make_float2(0.f, 0.f);
-                const bool have = m != 0u;
-                const int j = have ? __ffs(m) - 1 : 0;
-                m &= m - 1;  // (0 & anything stays 0)
-                const unsigned pos = __shfl_sync(GS_FULL, pmine, j);
-                if (have && act && pos < (unsigned)cap)
-                  v[t][c] = *(const float2 *)((const char *)recs.rec[j + 32 * half] + rows_off + 4 * ((size_t)pos * pad + e));
-              }
-            }
-#pragma unroll
-            for (int t = 0; t < 2; ++t)
-#pragma unroll
-              for (int c = 0; c < 4; ++c) { acc[t][0] += v[t][c].x; acc[t][1] += v[t][c].y; }
           }
         }
+        float a0 = dst[0] ? *dst[0] : 0.f, a1 = dst[1] ? *dst[1] : 0.f;
+        // the row's images in batches of 4: all record loads of a batch are in flight together (one NVLink round
+        // trip), the adds then run in image order
 #pragma unroll
-        for (int t = 0; t < 2; ++t)
+        for (int half = 0; half < 2; ++half) {
+          unsigned m = half ? m1 : m0;
+          const unsigned pmine = half ? p1 : p0;
+          while (m) {
+            float2 v[4];
 #pragma unroll
-          for (int q = 0; q < 2; ++q)
-            if (dst[t][q]) *dst[t][q] = acc[t][q];
+            for (int c = 0; c < 4; ++c) {
+              v[c] = make_float2(0.f, 0.f);
+              const bool have = m != 0u;
+              const int j = have ? __ffs(m) - 1 : 0;
+              m &= m - 1;  // (0 & anything stays 0)
+              const unsigned pos = __shfl_sync(GS_FULL, pmine, j);
+              if (have && act && pos < (unsigned)cap)
+                v[c] = *(const float2 *)((const char *)recs.rec[j + 32 * half] + rows_off + 4 * ((size_t)pos * pad + e));
+            }
+#pragma unroll
+            for (int c = 0; c < 4; ++c) { a0 += v[c].x; a1 += v[c].y; }
+          }
+        }
+        if (dst[0]) *dst[0] = a0;
+        if (dst[1]) *dst[1] = a1;
       }
     }
   }
