@@ -1,0 +1,105 @@
+"""BASELINE.json's full-size configurations through size-independent properties (the CPU oracle needs minutes per image
+at these sizes, so it checks the small cases; here the invariants of the path are checked at full scale):
+  C2  3M splats SH3 1297x840   (configs[1], the bench workload)
+  C4  6M splats SH3 3840x2160  (configs[3], high-res stress: large overlap counts through the sort and the backward)
+Invariants: the overlap list is the stable (tile, depth) order and partitions [0, O); O equals the independent count
+pass; forward is idempotent bit for bit; Σ visibility over splats == Σ (1 - final_T) over pixels (every blended
+alpha·T is counted once on each side); a training step touches exactly the rows a pixel blended and leaves the gradient
+buffer clear."""
+import argparse
+
+import pytest
+import torch
+
+import bench
+from gsb200 import lib as L
+from gsb200 import ops
+from gsb200.scene import SceneConfig, SplatScene
+from gsb200.trainer import Trainer
+
+pytestmark = pytest.mark.gpu
+
+
+def _scene(workload):
+  n, deg, W, H, g, cams = bench.make_workload(argparse.Namespace(workload=workload, points=0))
+  scene = SplatScene(g, SceneConfig(sh_degree=deg))
+  lcams = [L.make_camera(c["T"], c["fx"], c["fy"], c["cx"], c["cy"], W, H, c["near"], c["far"]) for c in cams[:2]]
+  return scene, lcams, W, H
+
+
+def _forward_no_overflow(scene, cam):
+  for _ in range(4):
+    w, tb, vis, _ = scene._forward(cam, visibility=True)
+    if not scene.overflowed():
+      return w, tb, vis
+    scene.grow_overlaps(2.0)
+  raise AssertionError("overlap capacity still exceeded after 4 doublings")
+
+
+@pytest.mark.parametrize("workload", ["c2", "c4"])
+def test_fullsize_invariants(workload):
+  scene, cams, W, H = _scene(workload)
+  cam = cams[0]
+  w, tb, vis = _forward_no_overflow(scene, cam)
+  torch.cuda.synchronize()
+  O = int(tb.counters[0].item())
+  assert O > 1_000_000
+  # independent count pass agrees with the mapper
+  _, counters = ops.tile_count(scene.raster_cfg, w["g2d"], w["depth"], W, H)
+  assert int(counters[0].item()) == O
+  # ranges partition [0, O) in tile order
+  r = tb.tile_ranges.to(torch.int64)
+  lens = r[:, 1] - r[:, 0]
+  assert (lens >= 0).all() and int(lens.sum().item()) == O
+  nz = lens > 0
+  starts = r[nz, 0]
+  assert int(starts[0].item()) == 0 and torch.equal(starts[1:], r[nz, 1][:-1])
+  # stable (tile, depth) order: key non-decreasing, ties in ascending row index
+  idx = tb.overlap_to_point[:O].to(torch.int64)
+  assert int(idx.min().item()) >= 0 and int(idx.max().item()) < scene.n
+  tile = torch.repeat_interleave(torch.arange(r.shape[0], device="cuda"), lens)
+  key = (tile << 32) | w["depth"][idx].view(torch.int32).to(torch.int64)
+  assert (w["depth"][idx] > 0).all()
+  d = key[1:] - key[:-1]
+  assert (d >= 0).all()
+  assert (idx[1:][d == 0] > idx[:-1][d == 0]).all()
+  del tile, key, d
+  # every listed row is in view
+  assert (w["g2d"][idx, 5] > 0).all()
+  # Σ_i visibility_i == Σ_pixels (1 - final_T): both sides sum the same alpha·T products
+  lhs = float(vis.double().sum().item())
+  rhs = float((1.0 - w["final_T"].double()).sum().item())
+  assert abs(lhs - rhs) <= 2e-3 * rhs, (lhs, rhs)
+  assert torch.isfinite(w["image"]).all() and (w["final_T"] >= 0).all() and (w["final_T"] <= 1).all()
+  # idempotence: same inputs, same bits (the overlap order is deterministic, blending is sequential per pixel)
+  image, final_T, n_contrib = w["image"].clone(), w["final_T"].clone(), w["n_contrib"].clone()
+  order = tb.overlap_to_point[:O].clone()
+  w2, tb2, _ = _forward_no_overflow(scene, cam)
+  assert torch.equal(order, tb2.overlap_to_point[:O])
+  assert torch.equal(image, w2["image"]) and torch.equal(final_T, w2["final_T"]) and torch.equal(n_contrib, w2["n_contrib"])
+
+
+@pytest.mark.parametrize("workload", ["c2", "c4"])
+def test_fullsize_training_step_touches_only_blended_rows(workload):
+  scene, cams, W, H = _scene(workload)
+  _forward_no_overflow(scene, cams[0])  # sizes the overlap buffers
+  gen = torch.Generator(device="cuda").manual_seed(1)
+  target = (torch.rand((H, W, 3), device="cuda", generator=gen) * 255).to(torch.uint8)
+  before = {k: v.clone() for k, v in scene.p.items()}
+  blended, _ = scene.query_visibility(cams[0])
+  tr = Trainer(scene)
+  loss = tr.training_step([(cams[0], target)], read_loss=True)
+  torch.cuda.synchronize()
+  assert not scene.overflowed()
+  assert all(x == x and x > 0 for x in loss)
+  assert torch.isfinite(scene.params).all()
+  assert not scene.grads.any(), "the optimiser clears every gradient row it consumed"
+  assert not scene.visible.any() and not scene._work["acc"].any() and not scene._work["vis"].any()
+  touched = torch.zeros((scene.n,), device="cuda", dtype=torch.bool)
+  touched[blended] = True
+  for name in ("position", "log_scaling", "rotation", "alpha_logit", "sh"):
+    a, b = scene.p[name].reshape(scene.n, -1), before[name].reshape(scene.n, -1)
+    changed = (a != b).any(dim=1)
+    assert not (changed & ~touched).any(), name
+    assert int(changed.sum().item()) > 0.5 * int(touched.sum().item()), name
+  assert int((scene.stats["points_in_view"] > 0).sum().item()) >= int(touched.sum().item())
