@@ -362,11 +362,12 @@ def run_b200(args):
       "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
       "config": {"workload": f"{args.workload}: {n} splats SH{deg} {W}x{H}, camera batch = {world} (1 image per GPU per step), "
                              "fwd + loss (MSE 10 + 3-level SSIM 1.0 + reg) + bwd + fused visibility-aware LaProp step", "images_per_step": world,
-                 "l2": "inputs larger than L2 (params+grads+moments 2.8 GB, overlap list > 126 MB)",
+                 "l2": f"inputs larger than L2 (params+grads+moments {4 * 4 * D * n / 1e9:.1f} GB, overlap list {4 * O / 1e6:.0f} MB)",
                  "parallelism": f"dp{world}", "V_in_view": V, "O_overlaps": O, "V_optimised": v_opt, "overflow": overflow},
       "stages_ms": stages, "host_enqueue_ms_per_step": host_enqueue_ms,
       "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                   "traffic": measured_traffic(dom), "traffic_source": "profiles/r1k_traffic.json (ncu --set full)",
+                   "traffic": measured_traffic(dom) if args.workload == "c2" and not args.points else None,
+                   "traffic_source": "profiles/r1k_traffic.json (ncu --set full of the c2 command)",
                    "peak_source": which, "algorithmic_bytes": bytes_[dom],
                    "iteration": {"algorithmic_bytes": iter_bytes, "achieved": iter_bytes / (ms_step * 1e-3) / 1e9,
                                  "frac": iter_bytes / (ms_step * 1e-3) / 1e9 / hbm}},
