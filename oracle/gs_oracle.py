@@ -306,3 +306,51 @@ class Oracle:
     loss = self.lib.gso_ssim_loss(C.c_int(H), C.c_int(W), C.c_int(Cc), C.c_int(levels), self.p(pred), self.p(target),
                                   self.creal(weight), self.p(d), C.byref(s0))
     return float(loss), d, float(s0.value)
+
+  # -- (9) colour MLP --------------------------------------------------------------
+  COLOR_WEIGHTS = ("base_w1", "base_b1", "base_w2", "base_b2", "dir_wsh", "dir_bsh", "dir_w1", "dir_b1", "dir_w2", "dir_b2")
+
+  def rsh(self, degree, dirs):
+    """real spherical harmonics of unit vectors (m,3) -> (m, (degree+1)^2), reference scene/mlp/rsh.py convention."""
+    dirs = self.r(dirs)
+    out = np.zeros((dirs.shape[0], (degree + 1) ** 2), self.real)
+    for i in range(dirs.shape[0]):
+      self.lib.gso_rsh(C.c_int(degree), self.p(dirs[i]), self.p(out[i]))
+    return out
+
+  def _color_args(self, weights, feature, position, cam_pos, glo):
+    W = [self.r(weights[k]) for k in self.COLOR_WEIGHTS]
+    feature, position, cam_pos, glo = map(self.r, (feature, position, cam_pos, glo))
+    pf, gf = feature.shape[1], glo.reshape(-1).shape[0]
+    H = W[2].shape[1]
+    S = W[4].shape[1]
+    deg = int(round(S ** 0.5)) - 1
+    assert W[0].shape == (2 * H, pf + gf) and W[4].shape == (2 * (pf + gf), (deg + 1) ** 2)
+    ptrs = (C.c_void_p * 10)(*[w.ctypes.data for w in W])
+    return W, ptrs, feature, position, cam_pos, glo, pf, gf, H, deg
+
+  def color_mlp_fwd(self, weights, feature, position, cam_pos, glo, in_view=None, half=False):
+    """weights: dict COLOR_WEIGHTS -> arrays shaped like the reference's nn.Linear parameters.
+    Returns (diffuse (n,3), specular (n,3)); rows with in_view <= 0 stay zero."""
+    W, ptrs, feature, position, cam_pos, glo, pf, gf, H, deg = self._color_args(weights, feature, position, cam_pos, glo)
+    n = feature.shape[0]
+    iv = None if in_view is None else self.r(in_view)
+    diffuse, specular = np.zeros((n, 3), self.real), np.zeros((n, 3), self.real)
+    self.lib.gso_color_mlp_fwd(C.c_int64(n), C.c_int(pf), C.c_int(gf), C.c_int(H), C.c_int(deg), ptrs, self.p(feature),
+                               self.p(position), self.p(cam_pos), self.p(glo), self.p(iv), C.c_int(1), C.c_int(int(half)),
+                               self.p(diffuse), self.p(specular))
+    return diffuse, specular
+
+  def color_mlp_bwd(self, weights, feature, position, cam_pos, glo, d_diffuse, d_specular, row_w=None, half=False):
+    """Returns (d_feature (n,pf), d_glo (gf,), dW dict shaped like weights)."""
+    W, ptrs, feature, position, cam_pos, glo, pf, gf, H, deg = self._color_args(weights, feature, position, cam_pos, glo)
+    n = feature.shape[0]
+    rw = None if row_w is None else self.r(row_w)
+    dd, ds = self.r(d_diffuse), self.r(d_specular)
+    d_feature, d_glo = np.zeros((n, pf), self.real), np.zeros((gf,), self.real)
+    dW = [np.zeros_like(w) for w in W]
+    dptrs = (C.c_void_p * 10)(*[w.ctypes.data for w in dW])
+    self.lib.gso_color_mlp_bwd(C.c_int64(n), C.c_int(pf), C.c_int(gf), C.c_int(H), C.c_int(deg), ptrs, self.p(feature),
+                               self.p(position), self.p(cam_pos), self.p(glo), self.p(rw), C.c_int(1), C.c_int(int(half)),
+                               self.p(dd), self.p(ds), self.p(d_feature), self.p(d_glo), dptrs)
+    return d_feature, d_glo, dict(zip(self.COLOR_WEIGHTS, dW))
