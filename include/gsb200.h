@@ -389,6 +389,32 @@ int gs_ssim_loss(int height, int width, int channels, int levels, const float *p
                  const uint8_t *target_u8, float weight, float *d_pred, float *ssim_sums, void *workspace,
                  size_t workspace_bytes, void *stream);
 
+/* ---------------------------------------------------------------------------------------
+ * (9) Colour MLP path of MLPScene: MLPScene.eval_colors -> ColorModel.forward, reference
+ *     scene/mlp_scene.py:352-368, scene/color_model.py:124-149, scene/mlp/torch_mlp.py:52-66,89-135.
+ *     feature = LayerNorm([point feature, GLO feature]) (no affine); diffuse = act(base MLP(feature)); specular =
+ *     act(directional MLP(feature * a + b), intensity_bias -2) with (a, b) = Linear(real SH of normalize(position -
+ *     cam_pos)) (scene/mlp/rsh.py convention); act(o) = sigmoid(o[1:4]) * exp(o[0] + bias) (luminance_activation :74-79).
+ *     Precision follows the reference's torch.autocast(float16): fp16 inputs / weights / outputs on every Linear and
+ *     on the GLU, fp32 accumulation (tensor cores), fp32 LayerNorm, SH and final activation.
+ *     weights[10]: device fp32 arrays shaped like the reference's nn.Linear parameters (row-major (out, in)):
+ *     base_w1 (2H,F) base_b1 (2H) base_w2 (4,H) base_b2 (4) dir_wsh (2F,S) dir_bsh (2F) dir_w1 (2H,F) dir_b1 (2H)
+ *     dir_w2 (4,H) dir_b2 (4); F = point_features + glo_features, S = (sh_degree+1)^2.
+ *     Instantiated: point_features 16, glo_features 32, hidden 32 (one hidden layer), sh_degree 5
+ *     (config/scene/mlp.yaml:33-43); anything else returns GS_ERR_UNSUPPORTED. */
+typedef struct gs_color_mlp {
+  int32_t point_features, glo_features, hidden, sh_degree;
+  const float *weights[10];
+} gs_color_mlp;
+
+/* rgb[i] = diffuse + specular_weight * specular (Colors.total, scene/color_model.py:84-85) for the rows with
+ * in_view[i*in_view_stride] > 0 (NULL: every row; pass the opacity column of g2d); other rows are left untouched.
+ * specular (n,3), nullable: the specular term alone (RenderedPoints.attributes.specular, read by reg_loss).
+ * glo: device (glo_features) — the image's GLO embedding row, or zeros for a non-training view (mlp_scene.py:356-360). */
+int gs_color_mlp_fwd(const gs_color_mlp *h_model, int64_t n, const float *in_view, int in_view_stride,
+                     const float *feature, const float *position, const float *h_cam_pos, const float *glo,
+                     float specular_weight, float *rgb, float *specular, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

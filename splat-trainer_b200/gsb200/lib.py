@@ -50,6 +50,11 @@ class OptimGroup(C.Structure):  # gs_optim_group
               ("post", C.c_int32), ("post_lo", C.c_float), ("post_hi", C.c_float)]
 
 
+class ColorMLP(C.Structure):  # gs_color_mlp
+  _fields_ = [("point_features", C.c_int32), ("glo_features", C.c_int32), ("hidden", C.c_int32), ("sh_degree", C.c_int32),
+              ("weights", C.c_void_p * 10)]
+
+
 class RegFuse(C.Structure):  # gs_reg_fuse
   _fields_ = [("w_scale", C.c_float), ("w_opacity", C.c_float), ("w_aspect", C.c_float), ("sums", C.c_void_p),
               ("depth", C.c_void_p)]
@@ -85,6 +90,7 @@ SIGNATURES = {
   "gs_optim_vis_update": (_I, [_OPT, _L, _P, _P, _P, _P]),
   "gs_visible_indexes_workspace_bytes": (_Z, [_L]),
   "gs_visible_indexes": (_I, [_L, _P, _P, _P, _P, _Z, _P]),
+  "gs_color_mlp_fwd": (_I, [C.POINTER(ColorMLP), _L, _P, _I, _P, _P, C.POINTER(C.c_float), _P, _F, _P, _P, _P]),
   "gs_optim_step_groups": (_I, [_OPT, _L, _P, _P, _I, C.POINTER(OptimGroup), _P, _P, _P, _I, _P]),
   "gs_optim_step": (_I, [_OPT, _I, _L, _P, _P, _I, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _F, _F, _I, _P]),
   "gs_accumulate_stats": (_I, [_L, _P, _P, _P, _I, _P, _I, _F, _F, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P]),

@@ -447,3 +447,29 @@ def ssim_loss(pred, target, levels=3, weight=1.0, d_pred=None, sums=None, worksp
   L.check(L.load().gs_ssim_loss(H, W, C_, int(levels), L.ptr(_f32(pred)), L.ptr(tf), L.ptr(tu), float(weight), L.ptr(d_pred),
                                 L.ptr(sums), L.ptr(workspace), workspace.numel(), L.stream()))
   return sums
+
+
+# ---- colour MLP path (include/gsb200.h section 9) -------------------------------------------------------------------
+COLOR_WEIGHTS = ("base_w1", "base_b1", "base_w2", "base_b2", "dir_wsh", "dir_bsh", "dir_w1", "dir_b1", "dir_w2", "dir_b2")
+
+
+def color_model(weights, point_features=16, glo_features=32, hidden=32, sh_degree=5):
+  """gs_color_mlp from a dict COLOR_WEIGHTS -> fp32 CUDA tensors shaped like the reference's nn.Linear parameters
+  (ColorModel.base_model / directional_model, scene/color_model.py:106-121).  Keeps the tensors alive."""
+  ts = [_f32(weights[k]) for k in COLOR_WEIGHTS]
+  m = L.ColorMLP(point_features, glo_features, hidden, sh_degree, (C.c_void_p * 10)(*[t.data_ptr() for t in ts]))
+  m._keep = ts
+  return m
+
+
+def color_mlp_fwd(model, feature, position, cam_pos, glo, in_view=None, specular_weight=1.0, rgb=None, specular=None):
+  """gs_color_mlp_fwd.  in_view: (n,) or a column view (e.g. g2d[:, 5]); rows with in_view <= 0 are left untouched.
+  Returns (rgb (n,3), specular or None)."""
+  n = feature.shape[0]
+  if rgb is None:
+    rgb = torch.zeros((n, 3), device=feature.device, dtype=torch.float32)
+  cam = _cam_pos3(cam_pos)
+  L.check(L.load().gs_color_mlp_fwd(C.byref(model), n, None if in_view is None else in_view.data_ptr(),
+                                    0 if in_view is None else in_view.stride(0), L.ptr(_f32(feature)), L.ptr(_f32(position)),
+                                    cam, L.ptr(_f32(glo)), float(specular_weight), L.ptr(rgb), L.ptr(specular), L.stream()))
+  return rgb, specular
