@@ -127,7 +127,8 @@ __device__ __forceinline__ void load_weights(Weights &W, const ColorDev &m) {
 
 // lane = row: LayerNorm of [feature, glo] and the SH coefficients of the view direction into the warp's staging tiles.
 // Returns 1 / sigma of the row (the backward needs it).
-__device__ __forceinline__ float stage_row(Stage &st, int lane, bool valid, int64_t i, const float *__restrict__ feature,
+template <typename StageT>
+__device__ __forceinline__ float stage_row(StageT &st, int lane, bool valid, int64_t i, const float *__restrict__ feature,
                                            const float *__restrict__ position, const float (&cam)[3],
                                            const float *__restrict__ s_glo) {
   float v[PF];
@@ -218,7 +219,9 @@ __device__ __forceinline__ void mlp_tile(const __half *__restrict__ w1, const fl
 }
 
 // direction encoder + affine modulation for one 16-row tile: AX = fragments of x = f * a + b, (a, b) = Wsh Y + bsh
-__device__ __forceinline__ void affine_tile(const Weights &W, const Stage &st, int r0, int g, int t, uint32_t (&AX)[3][4]) {
+template <bool SAVE, typename StageT>
+__device__ __forceinline__ void affine_tile(const Weights &W, StageT &st, int r0, int g, int t, uint32_t (&AX)[3][4],
+                                            uint32_t (*av)[2] = nullptr) {
   uint32_t AY[3][4];
 #pragma unroll
   for (int ks = 0; ks < 3; ++ks) load_a(AY[ks], st.yh, KP, r0, 16 * ks, g, t);
@@ -241,6 +244,12 @@ __device__ __forceinline__ void affine_tile(const Weights &W, const Stage &st, i
       float2 hi = *reinterpret_cast<const float2 *>(st.xf + (r0 + g + 8) * KP + col);
       AX[j][2 * q] = pack2(lo.x * hr(ca[0]) + hr(cb[0]), lo.y * hr(ca[1]) + hr(cb[1]));
       AX[j][2 * q + 1] = pack2(hi.x * hr(ca[2]) + hr(cb[2]), hi.y * hr(ca[3]) + hr(cb[3]));
+      if (SAVE) {  // backward: keep a (fp16) and leave x as a tile for the dW pass (over the rows of f it replaces)
+        av[2 * j + q][0] = pack2(ca[0], ca[1]);
+        av[2 * j + q][1] = pack2(ca[2], ca[3]);
+        *reinterpret_cast<uint32_t *>(st.xh + (r0 + g) * KP + col) = AX[j][2 * q];
+        *reinterpret_cast<uint32_t *>(st.xh + (r0 + g + 8) * KP + col) = AX[j][2 * q + 1];
+      }
     }
   }
 }
@@ -290,7 +299,7 @@ __global__ void __launch_bounds__(CM_THREADS) k_color_fwd(ColorDev m, int64_t n,
 #pragma unroll
         for (int ks = 0; ks < 3; ++ks) load_a(A[ks], st.xh, KP, r0, 16 * ks, g, t);
         mlp_tile(W.w1b, W.b1b, W.w2b, W.b2b, st.o[0], r0, g, t, A);
-        affine_tile(W, st, r0, g, t, A);
+        affine_tile<false>(W, st, r0, g, t, A);
         mlp_tile(W.w1d, W.b1d, W.w2d, W.b2d, st.o[1], r0, g, t, A);
       }
       __syncwarp();
@@ -325,6 +334,370 @@ int color_check(const gs_color_mlp *m) {
   return GS_OK;
 }
 
+
+// ---- backward ---------------------------------------------------------------------------------------------------
+// Rows a pixel blended only.  Per 32-row group a warp recomputes the forward, back-propagates through both MLPs with
+// the same fragment chaining (dH is the A operand of dIn = dH W1), leaves dH / dE / dO and the layer inputs as fp16 tiles
+// in shared memory and forms the weight gradients dW = dH^T In as MMAs over the 32 rows (operands transposed on the fly by
+// ldmatrix.trans; a constant-1 column appended to every input tile turns the bias gradient into one more column of dW).
+// dW accumulates in shared memory per CTA (fp32 atomics) and is added to global memory once per CTA.
+constexpr int TP = 72;    // pitch (halfs) of W1^T (in, out) and of the dH tile (64 wide)
+constexpr int OP = 24;    // pitch of W2^T (hidden, out) and of the dO tile (4 valid of 16)
+constexpr int EP = 104;   // pitch of the dE tile (96 wide); 208 B rows, shared with the fp32 df tile (52 floats)
+constexpr int DFP = 52;
+// Loss scale of the fp16 backward operands (dO, dH, dE).  Per-splat colour gradients are 1e-8..1e-2: unscaled they sit in
+// (or below) fp16's subnormal range — the reference's own autocast backward has no GradScaler and loses them.  Everything
+// downstream of dO is linear in it, so the fp32 results are simply multiplied by 1/scale at the end.
+constexpr float GRAD_SCALE = 4096.0f, GRAD_UNSCALE = 1.0f / 4096.0f, HALF_SAT = 60000.0f;
+
+struct WeightsT {
+  __half w1bT[F * TP], w1dT[F * TP], w2bT[H * OP], w2dT[H * OP];
+};
+
+struct GradAcc {  // per-CTA fp32 accumulators, shapes of the reference's parameters
+  float w1b[2 * H * F], b1b[2 * H], w2b[4 * H], b2b[4], wsh[2 * F * S], bsh[2 * F], w1d[2 * H * F], b1d[2 * H], w2d[4 * H], b2d[4];
+  float glo[GF];
+};
+
+struct StageB {
+  __half xh[32 * KP];     // f (fp16) with a ones column at 48; rows are overwritten by x for the directional phase
+  __half yh[32 * KP];     // SH coefficients with a ones column at 36
+  float xf[32 * KP];
+  float o[2][32 * 8];
+  __half dos[2][32 * OP]; // dO of the two MLPs
+  __half gs[32 * HP];     // GLU output with a ones column at 32
+  __half dhs[32 * TP];    // dH
+  __half des[32 * EP];    // dE = [da, db]; the same bytes first hold the base MLP's df (fp32, pitch DFP)
+  float inv[32];
+  int64_t row[32];
+};
+
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t (&r)[4], const __half *p) {
+  uint32_t a = (uint32_t)__cvta_generic_to_shared(p);
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];\n"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(a));
+}
+__device__ __forceinline__ void ldsm_x2_trans(uint32_t &r0, uint32_t &r1, const __half *p) {
+  uint32_t a = (uint32_t)__cvta_generic_to_shared(p);
+  asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0,%1}, [%2];\n" : "=r"(r0), "=r"(r1) : "r"(a));
+}
+
+// dw[m][n] += sum over the warp's 32 rows of At[row][m] * Bt[row][n]   (m < m_valid, n < n_valid);
+// column n == n_valid of Bt is the constant 1: that column of the product is the bias gradient.
+__device__ __forceinline__ void dw_accumulate(float *dw, float *dbias, int m_valid, int n_valid, const __half *At, int pa,
+                                              int m_tiles, const __half *Bt, int pb, int n_tiles, int lane) {
+  int g = lane >> 2, t = lane & 3, id = lane >> 3, r = lane & 7;
+  for (int mo = 0; mo < m_tiles; ++mo) {
+    uint32_t a[2][4];
+#pragma unroll
+    for (int kt = 0; kt < 2; ++kt) ldsm_x4_trans(a[kt], At + (16 * kt + (id >> 1) * 8 + r) * pa + 16 * mo + (id & 1) * 8);
+    for (int ni = 0; ni < n_tiles; ++ni) {
+      float c[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int kt = 0; kt < 2; ++kt) {
+        uint32_t b0, b1;
+        ldsm_x2_trans(b0, b1, Bt + (16 * kt + (id & 1) * 8 + r) * pb + 8 * ni);
+        mma16816(c, a[kt], b0, b1);
+      }
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        int m = 16 * mo + g + ((e >> 1) << 3), nn = 8 * ni + 2 * t + (e & 1);
+        if (m < m_valid && c[e] != 0.f) {
+          if (nn < n_valid) atomicAdd(dw + m * n_valid + nn, c[e]);
+          else if (nn == n_valid) atomicAdd(dbias + m, c[e]);
+        }
+      }
+    }
+  }
+}
+
+// One MLP, one 16-row tile: recompute the GLU layer from the input fragments A, back-propagate dO (tile `dos`) to
+// din = d loss / d input (C layout, 6 column tiles), leave g (GLU output) and dH as fp16 tiles for the dW pass.
+__device__ __forceinline__ void bwd_model(const __half *__restrict__ w1, const float *__restrict__ b1,
+                                          const __half *__restrict__ w1T, const __half *__restrict__ w2T,
+                                          const __half *__restrict__ dos, __half *__restrict__ gs, __half *__restrict__ dhs,
+                                          int r0, int g, int t, const uint32_t (&A)[3][4], float (&din)[6][4]) {
+  uint32_t DO[4];
+  load_a(DO, dos, OP, r0, 0, g, t);
+  uint32_t DH[4][4];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      int nt = 2 * j + q, col = 8 * nt + 2 * t;
+      float ca[4] = {b1[col], b1[col + 1], b1[col], b1[col + 1]};
+      float cb[4] = {b1[H + col], b1[H + col + 1], b1[H + col], b1[H + col + 1]};
+#pragma unroll
+      for (int ks = 0; ks < 3; ++ks) {
+        uint32_t b0, b1r;
+        load_b(b0, b1r, w1, KP, 8 * nt, 16 * ks, g, t);
+        mma16816(ca, A[ks], b0, b1r);
+        load_b(b0, b1r, w1, KP, H + 8 * nt, 16 * ks, g, t);
+        mma16816(cb, A[ks], b0, b1r);
+      }
+      float dg[4] = {0.f, 0.f, 0.f, 0.f};
+      {
+        uint32_t b0, b1r;
+        load_b(b0, b1r, w2T, OP, 8 * nt, 0, g, t);
+        mma16816(dg, DO, b0, b1r);
+      }
+      float gv[4], da[4], db[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float a = hr(ca[e]), b = hr(cb[e]);
+        float sb = 1.0f / (1.0f + __expf(-b));
+        gv[e] = a * sb;
+        da[e] = dg[e] * sb;
+        db[e] = dg[e] * a * sb * (1.0f - sb);
+      }
+      *reinterpret_cast<uint32_t *>(gs + (r0 + g) * HP + col) = pack2(gv[0], gv[1]);
+      *reinterpret_cast<uint32_t *>(gs + (r0 + g + 8) * HP + col) = pack2(gv[2], gv[3]);
+      uint32_t a01 = pack2(da[0], da[1]), a23 = pack2(da[2], da[3]), b01 = pack2(db[0], db[1]), b23 = pack2(db[2], db[3]);
+      *reinterpret_cast<uint32_t *>(dhs + (r0 + g) * TP + col) = a01;
+      *reinterpret_cast<uint32_t *>(dhs + (r0 + g + 8) * TP + col) = a23;
+      *reinterpret_cast<uint32_t *>(dhs + (r0 + g) * TP + H + col) = b01;
+      *reinterpret_cast<uint32_t *>(dhs + (r0 + g + 8) * TP + H + col) = b23;
+      DH[j][2 * q] = a01; DH[j][2 * q + 1] = a23;
+      DH[2 + j][2 * q] = b01; DH[2 + j][2 * q + 1] = b23;
+    }
+  }
+#pragma unroll
+  for (int ni = 0; ni < 6; ++ni) {
+    din[ni][0] = din[ni][1] = din[ni][2] = din[ni][3] = 0.f;
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk) {
+      uint32_t b0, b1r;
+      load_b(b0, b1r, w1T, TP, 8 * ni, 16 * kk, g, t);
+      mma16816(din[ni], DH[kk], b0, b1r);
+    }
+  }
+}
+
+
+struct ColorGradDev {
+  float *w[10];
+};
+
+__device__ __forceinline__ float2 unpack2(uint32_t v) { return __half22float2(*reinterpret_cast<__half2 *>(&v)); }
+
+__global__ void __launch_bounds__(CM_THREADS, 1) k_color_bwd(ColorDev m, ColorGradDev gd, int64_t n, const float *__restrict__ row_w,
+                                                             int row_w_stride, const float *__restrict__ feature,
+                                                             const float *__restrict__ position, float cx, float cy, float cz,
+                                                             const float *__restrict__ glo, float specular_weight,
+                                                             const float *__restrict__ d_rgb, int d_rgb_stride, float w_spec_reg,
+                                                             const float *__restrict__ reg_sums, float *__restrict__ d_feature,
+                                                             float *__restrict__ d_glo) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  unsigned char *sp = smem;
+  Weights &W = *reinterpret_cast<Weights *>(sp); sp += (sizeof(Weights) + 15) & ~(size_t)15;
+  WeightsT &WT = *reinterpret_cast<WeightsT *>(sp); sp += (sizeof(WeightsT) + 15) & ~(size_t)15;
+  GradAcc &acc = *reinterpret_cast<GradAcc *>(sp); sp += (sizeof(GradAcc) + 15) & ~(size_t)15;
+  StageB *stages = reinterpret_cast<StageB *>(sp); sp += CM_WARPS * sizeof(StageB);
+  int *s_list = reinterpret_cast<int *>(sp); sp += CM_CHUNK * sizeof(int);
+  float *s_glo = reinterpret_cast<float *>(sp); sp += GF * sizeof(float);
+  int *s_count = reinterpret_cast<int *>(sp);
+  load_weights(W, m);
+  {
+    uint32_t *z = reinterpret_cast<uint32_t *>(&WT);
+    for (int i = threadIdx.x; i < (int)(sizeof(WeightsT) / 4); i += CM_THREADS) z[i] = 0u;
+    float *za = reinterpret_cast<float *>(&acc);
+    for (int i = threadIdx.x; i < (int)(sizeof(GradAcc) / 4); i += CM_THREADS) za[i] = 0.f;
+    __syncthreads();
+    for (int i = threadIdx.x; i < 2 * H * F; i += CM_THREADS) {
+      int o = i / F, k = i - o * F;
+      WT.w1bT[k * TP + o] = __float2half_rn(m.w[0][i]);
+      WT.w1dT[k * TP + o] = __float2half_rn(m.w[6][i]);
+    }
+    for (int i = threadIdx.x; i < 4 * H; i += CM_THREADS) {
+      int o = i / H, k = i - o * H;
+      WT.w2bT[k * OP + o] = __float2half_rn(m.w[2][i]);
+      WT.w2dT[k * OP + o] = __float2half_rn(m.w[8][i]);
+    }
+  }
+  if (threadIdx.x < GF) s_glo[threadIdx.x] = glo[threadIdx.x];
+  __syncthreads();
+  // specular regulariser (reference scene/mlp_scene.py:262,267): weight * mean_i (w_i * sum_c |specular_ic|), specular > 0
+  float spec_scale = 0.f;
+  if (reg_sums && w_spec_reg != 0.f) {
+    float cnt = reg_sums[3];
+    spec_scale = cnt > 0.f ? w_spec_reg / cnt : 0.f;
+  }
+  const float cam[3] = {cx, cy, cz};
+  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  StageB &st = stages[warp];
+  for (int64_t base = (int64_t)blockIdx.x * CM_CHUNK; base < n; base += (int64_t)gridDim.x * CM_CHUNK) {
+    int cnt = compact_chunk(base, n, row_w, row_w_stride, s_list, s_count);
+    for (int k0 = warp * 32; k0 < cnt; k0 += CM_WARPS * 32) {
+      bool valid = k0 + lane < cnt;
+      int64_t i = valid ? base + s_list[k0 + lane] : 0;
+      float inv = stage_row(st, lane, valid, i, feature, position, cam, s_glo);
+      {  // constant-1 columns: bias gradients come out of the dW products
+        __half2 one = __floats2half2_rn(1.f, 0.f), zero = __floats2half2_rn(0.f, 0.f);
+        __half2 *px = reinterpret_cast<__half2 *>(st.xh + lane * KP + F);
+        px[0] = one; px[1] = zero; px[2] = zero; px[3] = zero;
+        *reinterpret_cast<__half2 *>(st.yh + lane * KP + S) = one;
+        __half2 *pg = reinterpret_cast<__half2 *>(st.gs + lane * HP + H);
+        pg[0] = one; pg[1] = zero; pg[2] = zero; pg[3] = zero;
+      }
+      st.inv[lane] = inv;
+      st.row[lane] = valid ? i : (int64_t)-1;
+      float dcol[2][3] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}};
+      if (valid) {
+        const float *dr = d_rgb + (int64_t)d_rgb_stride * i;
+        float wr = row_w[(int64_t)row_w_stride * i];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          dcol[0][c] = GRAD_SCALE * dr[c];
+          dcol[1][c] = GRAD_SCALE * (specular_weight * dr[c] + spec_scale * wr);
+        }
+      }
+      __syncwarp();
+      // forward (outputs only)
+#pragma unroll 1
+      for (int mt = 0; mt < 2; ++mt) {
+        int r0 = 16 * mt;
+        uint32_t A[3][4];
+#pragma unroll
+        for (int ks = 0; ks < 3; ++ks) load_a(A[ks], st.xh, KP, r0, 16 * ks, g, t);
+        mlp_tile(W.w1b, W.b1b, W.w2b, W.b2b, st.o[0], r0, g, t, A);
+        affine_tile<false>(W, st, r0, g, t, A);
+        mlp_tile(W.w1d, W.b1d, W.w2d, W.b2d, st.o[1], r0, g, t, A);
+      }
+      __syncwarp();
+      // lane = row: gradient at the MLP outputs through luminance_activation
+#pragma unroll
+      for (int md = 0; md < 2; ++md) {
+        const float *o = st.o[md] + lane * 8;
+        float lum = expf(o[0] - (md ? 2.0f : 0.0f));
+        float d0 = 0.f, dc[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          float sg = 1.0f / (1.0f + expf(-o[1 + c]));
+          d0 += dcol[md][c] * sg * lum;
+          dc[c] = dcol[md][c] * sg * (1.0f - sg) * lum;
+        }
+        d0 = fminf(fmaxf(d0, -HALF_SAT), HALF_SAT);  // saturate instead of overflowing to inf (pathological gradients only)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) dc[c] = fminf(fmaxf(dc[c], -HALF_SAT), HALF_SAT);
+        __half2 *pd = reinterpret_cast<__half2 *>(st.dos[md] + lane * OP);
+        pd[0] = __floats2half2_rn(d0, dc[0]);
+        pd[1] = __floats2half2_rn(dc[1], dc[2]);
+#pragma unroll
+        for (int q = 2; q < 8; ++q) pd[q] = __floats2half2_rn(0.f, 0.f);
+      }
+      __syncwarp();
+      float *dfs = reinterpret_cast<float *>(st.des);
+      // base MLP
+#pragma unroll 1
+      for (int mt = 0; mt < 2; ++mt) {
+        int r0 = 16 * mt;
+        uint32_t A[3][4];
+#pragma unroll
+        for (int ks = 0; ks < 3; ++ks) load_a(A[ks], st.xh, KP, r0, 16 * ks, g, t);
+        float din[6][4];
+        bwd_model(W.w1b, W.b1b, WT.w1bT, WT.w2bT, st.dos[0], st.gs, st.dhs, r0, g, t, A, din);
+#pragma unroll
+        for (int ni = 0; ni < 6; ++ni) {
+          *reinterpret_cast<float2 *>(dfs + (r0 + g) * DFP + 8 * ni + 2 * t) = make_float2(din[ni][0], din[ni][1]);
+          *reinterpret_cast<float2 *>(dfs + (r0 + g + 8) * DFP + 8 * ni + 2 * t) = make_float2(din[ni][2], din[ni][3]);
+        }
+      }
+      __syncwarp();
+      dw_accumulate(acc.w1b, acc.b1b, 2 * H, F, st.dhs, TP, 4, st.xh, KP, 7, lane);
+      dw_accumulate(acc.w2b, acc.b2b, 4, H, st.dos[0], OP, 1, st.gs, HP, 5, lane);
+      __syncwarp();
+      // directional MLP
+#pragma unroll 1
+      for (int mt = 0; mt < 2; ++mt) {
+        int r0 = 16 * mt;
+        uint32_t AX[3][4], av[6][2];
+        affine_tile<true>(W, st, r0, g, t, AX, av);
+        float dx[6][4];
+        bwd_model(W.w1d, W.b1d, WT.w1dT, WT.w2dT, st.dos[1], st.gs, st.dhs, r0, g, t, AX, dx);
+        float df[6][4];
+#pragma unroll
+        for (int ni = 0; ni < 6; ++ni) {
+          float2 lo = *reinterpret_cast<const float2 *>(dfs + (r0 + g) * DFP + 8 * ni + 2 * t);
+          float2 hi = *reinterpret_cast<const float2 *>(dfs + (r0 + g + 8) * DFP + 8 * ni + 2 * t);
+          df[ni][0] = lo.x; df[ni][1] = lo.y; df[ni][2] = hi.x; df[ni][3] = hi.y;
+        }
+        __syncwarp();  // every lane has read the base MLP's df rows before dE overwrites the same bytes
+        float s1[2] = {0.f, 0.f}, s2[2] = {0.f, 0.f};
+#pragma unroll
+        for (int ni = 0; ni < 6; ++ni) {
+          int col = 8 * ni + 2 * t;
+          float2 flo = *reinterpret_cast<const float2 *>(st.xf + (r0 + g) * KP + col);
+          float2 fhi = *reinterpret_cast<const float2 *>(st.xf + (r0 + g + 8) * KP + col);
+          float2 alo = unpack2(av[ni][0]), ahi = unpack2(av[ni][1]);
+          float fv[4] = {flo.x, flo.y, fhi.x, fhi.y}, aa[4] = {alo.x, alo.y, ahi.x, ahi.y};
+          float da[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            df[ni][e] += dx[ni][e] * aa[e];
+            da[e] = dx[ni][e] * fv[e];
+            s1[e >> 1] += df[ni][e];
+            s2[e >> 1] += df[ni][e] * fv[e];
+          }
+          *reinterpret_cast<uint32_t *>(st.des + (r0 + g) * EP + col) = pack2(da[0], da[1]);
+          *reinterpret_cast<uint32_t *>(st.des + (r0 + g + 8) * EP + col) = pack2(da[2], da[3]);
+          *reinterpret_cast<uint32_t *>(st.des + (r0 + g) * EP + F + col) = pack2(dx[ni][0], dx[ni][1]);
+          *reinterpret_cast<uint32_t *>(st.des + (r0 + g + 8) * EP + F + col) = pack2(dx[ni][2], dx[ni][3]);
+        }
+        // LayerNorm (no affine) backward: dv = (df - mean(df) - f mean(df f)) / sigma
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          s1[h] += __shfl_xor_sync(GS_FULL, s1[h], 1); s1[h] += __shfl_xor_sync(GS_FULL, s1[h], 2);
+          s2[h] += __shfl_xor_sync(GS_FULL, s2[h], 1); s2[h] += __shfl_xor_sync(GS_FULL, s2[h], 2);
+          s1[h] *= (1.0f / F); s2[h] *= (1.0f / F);
+        }
+        float rinv[2] = {st.inv[r0 + g] * GRAD_UNSCALE, st.inv[r0 + g + 8] * GRAD_UNSCALE};
+        int64_t rrow[2] = {st.row[r0 + g], st.row[r0 + g + 8]};
+#pragma unroll
+        for (int ni = 0; ni < 6; ++ni) {
+          int col = 8 * ni + 2 * t;
+          float2 flo = *reinterpret_cast<const float2 *>(st.xf + (r0 + g) * KP + col);
+          float2 fhi = *reinterpret_cast<const float2 *>(st.xf + (r0 + g + 8) * KP + col);
+          float fv[4] = {flo.x, flo.y, fhi.x, fhi.y}, dv[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) dv[e] = (df[ni][e] - s1[e >> 1] - fv[e] * s2[e >> 1]) * rinv[e >> 1];
+          if (ni < PF / 8) {
+            if (rrow[0] >= 0) *reinterpret_cast<float2 *>(d_feature + rrow[0] * PF + col) = make_float2(dv[0], dv[1]);
+            if (rrow[1] >= 0) *reinterpret_cast<float2 *>(d_feature + rrow[1] * PF + col) = make_float2(dv[2], dv[3]);
+          } else {
+            float c0 = dv[0] + dv[2], c1 = dv[1] + dv[3];  // column sums over the tile's rows -> d glo
+#pragma unroll
+            for (int o = 4; o < 32; o <<= 1) { c0 += __shfl_xor_sync(GS_FULL, c0, o); c1 += __shfl_xor_sync(GS_FULL, c1, o); }
+            if (g == 0) { atomicAdd(acc.glo + col - PF, c0); atomicAdd(acc.glo + col + 1 - PF, c1); }
+          }
+        }
+      }
+      __syncwarp();
+      dw_accumulate(acc.w1d, acc.b1d, 2 * H, F, st.dhs, TP, 4, st.xh, KP, 7, lane);
+      dw_accumulate(acc.w2d, acc.b2d, 4, H, st.dos[1], OP, 1, st.gs, HP, 5, lane);
+      dw_accumulate(acc.wsh, acc.bsh, 2 * F, S, st.des, EP, 6, st.yh, KP, 5, lane);
+      __syncwarp();
+    }
+    __syncthreads();
+  }
+  __syncthreads();
+  // one flush of the CTA's accumulators
+  const float *srcs[10] = {acc.w1b, acc.b1b, acc.w2b, acc.b2b, acc.wsh, acc.bsh, acc.w1d, acc.b1d, acc.w2d, acc.b2d};
+  const int sizes[10] = {2 * H * F, 2 * H, 4 * H, 4, 2 * F * S, 2 * F, 2 * H * F, 2 * H, 4 * H, 4};
+#pragma unroll
+  for (int k = 0; k < 10; ++k)
+    for (int i = threadIdx.x; i < sizes[k]; i += CM_THREADS) {
+      float v = srcs[k][i] * GRAD_UNSCALE;
+      if (v != 0.f) atomicAdd(gd.w[k] + i, v);
+    }
+  if (threadIdx.x < GF && acc.glo[threadIdx.x] != 0.f) atomicAdd(d_glo + threadIdx.x, acc.glo[threadIdx.x]);  // dv is unscaled
+}
+
+size_t color_bwd_smem_bytes() {
+  auto al = [](size_t x) { return (x + 15) & ~(size_t)15; };
+  return al(sizeof(Weights)) + al(sizeof(WeightsT)) + al(sizeof(GradAcc)) + CM_WARPS * sizeof(StageB) + CM_CHUNK * sizeof(int) +
+         GF * sizeof(float) + 16;
+}
+
 }  // namespace
 
 extern "C" int gs_color_mlp_fwd(const gs_color_mlp *h_model, int64_t n, const float *in_view, int in_view_stride,
@@ -346,6 +719,35 @@ extern "C" int gs_color_mlp_fwd(const gs_color_mlp *h_model, int64_t n, const fl
   int grid = (int)(chunks < 148 * 2 ? chunks : 148 * 2);  // persistent: 2 CTAs (97 KB of shared memory each) per SM
   k_color_fwd<<<grid, CM_THREADS, smem, (cudaStream_t)stream>>>(m, n, in_view, in_view_stride, feature, position, h_cam_pos[0],
                                                                 h_cam_pos[1], h_cam_pos[2], glo, specular_weight, rgb, specular);
+  GS_LAUNCH_CHECK();
+  return GS_OK;
+}
+
+extern "C" int gs_color_mlp_bwd(const gs_color_mlp *h_model, const gs_color_mlp *h_grads, int64_t n, const float *row_w,
+                                int row_w_stride, const float *feature, const float *position, const float *h_cam_pos,
+                                const float *glo, float specular_weight, const float *d_rgb, int d_rgb_stride,
+                                float w_specular_reg, const float *reg_sums, float *d_feature, float *d_glo, void *stream) {
+  int rc = color_check(h_model);
+  if (rc != GS_OK) return rc;
+  rc = color_check(h_grads);
+  if (rc != GS_OK) return rc;
+  GS_REQUIRE(row_w && feature && position && h_cam_pos && glo && d_rgb && d_feature && d_glo, "null argument");
+  GS_REQUIRE(d_rgb_stride >= 3, "d_rgb stride must be >= 3");
+  if (n <= 0) return GS_OK;
+  ColorDev m;
+  ColorGradDev gd;
+  for (int k = 0; k < 10; ++k) { m.w[k] = h_model->weights[k]; gd.w[k] = const_cast<float *>(h_grads->weights[k]); }
+  static bool configured = false;
+  size_t smem = color_bwd_smem_bytes();
+  if (!configured) {
+    GS_CUDA(cudaFuncSetAttribute(k_color_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  int64_t chunks = (n + CM_CHUNK - 1) / CM_CHUNK;
+  int grid = (int)(chunks < 148 ? chunks : 148);  // persistent, one CTA per SM (218 KB of shared memory)
+  k_color_bwd<<<grid, CM_THREADS, smem, (cudaStream_t)stream>>>(m, gd, n, row_w, row_w_stride, feature, position, h_cam_pos[0],
+                                                                h_cam_pos[1], h_cam_pos[2], glo, specular_weight, d_rgb,
+                                                                d_rgb_stride, w_specular_reg, reg_sums, d_feature, d_glo);
   GS_LAUNCH_CHECK();
   return GS_OK;
 }

@@ -473,3 +473,16 @@ def color_mlp_fwd(model, feature, position, cam_pos, glo, in_view=None, specular
                                     0 if in_view is None else in_view.stride(0), L.ptr(_f32(feature)), L.ptr(_f32(position)),
                                     cam, L.ptr(_f32(glo)), float(specular_weight), L.ptr(rgb), L.ptr(specular), L.stream()))
   return rgb, specular
+
+
+def color_mlp_bwd(model, grads, feature, position, cam_pos, glo, row_w, d_rgb, d_feature, d_glo, specular_weight=1.0,
+                  w_specular_reg=0.0, reg_sums=None):
+  """gs_color_mlp_bwd.  grads: a color_model() over the gradient tensors (accumulated); row_w / d_rgb may be column
+  views; d_feature (n, point_features) is written for the rows with row_w > 0, d_glo accumulated."""
+  n = feature.shape[0]
+  assert row_w.dtype == torch.float32 and d_rgb.dtype == torch.float32 and row_w.is_cuda and d_rgb.is_cuda
+  assert d_rgb.dim() == 2 and d_rgb.stride(1) == 1 and d_feature.is_contiguous()
+  L.check(L.load().gs_color_mlp_bwd(C.byref(model), C.byref(grads), n, row_w.data_ptr(), row_w.stride(0),
+                                    L.ptr(_f32(feature)), L.ptr(_f32(position)), _cam_pos3(cam_pos), L.ptr(_f32(glo)),
+                                    float(specular_weight), d_rgb.data_ptr(), d_rgb.stride(0), float(w_specular_reg),
+                                    L.ptr(reg_sums), L.ptr(d_feature), L.ptr(d_glo), L.stream()))
