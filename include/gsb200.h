@@ -420,12 +420,14 @@ int gs_color_mlp_fwd(const gs_color_mlp *h_model, int64_t n, const float *in_vie
  * The forward is recomputed (nothing is saved between the two kernels).  w_specular_reg / reg_sums (nullable): the
  * specular regulariser of reg_loss (reference scene/mlp_scene.py:262,267: weight * mean_i(w_i * sum_c |specular_ic|)
  * over the blended rows, count = reg_sums[3] from gs_reg_loss) is added to d specular.
- * d_feature (n, point_features) is WRITTEN for the processed rows; d_glo (glo_features) and h_grads->weights[10]
- * (shaped like the model's weights) are ACCUMULATED (batch = sum, like .grad). */
+ * d_feature (n, point_features) is WRITTEN for the processed rows (ADDED when accumulate != 0; other rows untouched);
+ * d_glo (glo_features) and h_grads->weights[10] (shaped like the model's weights) are ACCUMULATED (batch = sum, like
+ * .grad).  fp16 operands of the backward carry an internal loss scale (the reference's autocast backward has none). */
 int gs_color_mlp_bwd(const gs_color_mlp *h_model, const gs_color_mlp *h_grads, int64_t n, const float *row_w,
                      int row_w_stride, const float *feature, const float *position, const float *h_cam_pos,
                      const float *glo, float specular_weight, const float *d_rgb, int d_rgb_stride,
-                     float w_specular_reg, const float *reg_sums, float *d_feature, float *d_glo, void *stream);
+                     float w_specular_reg, const float *reg_sums, float *d_feature, float *d_glo, int accumulate,
+                     void *stream);
 
 #ifdef __cplusplus
 }

@@ -255,13 +255,14 @@ __device__ __forceinline__ void affine_tile(const Weights &W, StageT &st, int r0
 }
 
 // block compaction of the rows of one chunk that have work (in view / blended), like k_project_bwd
+template <int CHUNK, typename T>
 __device__ __forceinline__ int compact_chunk(int64_t base, int64_t n, const float *__restrict__ mask, int mask_stride,
-                                             int *s_list, int *s_count) {
+                                             T *s_list, int *s_count) {
   if (threadIdx.x == 0) *s_count = 0;
   __syncthreads();
-  for (int k = threadIdx.x; k < CM_CHUNK; k += CM_THREADS) {
+  for (int k = threadIdx.x; k < CHUNK; k += CM_THREADS) {
     int64_t i = base + k;
-    if (i < n && (!mask || mask[(int64_t)mask_stride * i] > 0.f)) s_list[atomicAdd(s_count, 1)] = k;
+    if (i < n && (!mask || mask[(int64_t)mask_stride * i] > 0.f)) s_list[atomicAdd(s_count, 1)] = (T)k;
   }
   __syncthreads();
   return *s_count;
@@ -285,7 +286,7 @@ __global__ void __launch_bounds__(CM_THREADS) k_color_fwd(ColorDev m, int64_t n,
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   Stage &st = stages[warp];
   for (int64_t base = (int64_t)blockIdx.x * CM_CHUNK; base < n; base += (int64_t)gridDim.x * CM_CHUNK) {
-    int cnt = compact_chunk(base, n, in_view, in_view_stride, s_list, s_count);
+    int cnt = compact_chunk<CM_CHUNK>(base, n, in_view, in_view_stride, s_list, s_count);
     for (int k0 = warp * 32; k0 < cnt; k0 += CM_WARPS * 32) {
       bool valid = k0 + lane < cnt;
       int64_t i = valid ? base + s_list[k0 + lane] : 0;
@@ -340,11 +341,14 @@ int color_check(const gs_color_mlp *m) {
 // the same fragment chaining (dH is the A operand of dIn = dH W1), leaves dH / dE / dO and the layer inputs as fp16 tiles
 // in shared memory and forms the weight gradients dW = dH^T In as MMAs over the 32 rows (operands transposed on the fly by
 // ldmatrix.trans; a constant-1 column appended to every input tile turns the bias gradient into one more column of dW).
-// dW accumulates in shared memory per CTA (fp32 atomics) and is added to global memory once per CTA.
+// The dW pass is cooperative: after a round of 128 rows (32 per warp) each warp owns one 16-output slab of every weight
+// matrix and reduces it over all 128 staged rows into the CTA's fp32 accumulators in shared memory (plain
+// read-modify-write: the slab has one owner), which are added to global memory once per CTA.
 constexpr int TP = 72;    // pitch (halfs) of W1^T (in, out) and of the dH tile (64 wide)
 constexpr int OP = 24;    // pitch of W2^T (hidden, out) and of the dO tile (4 valid of 16)
 constexpr int EP = 104;   // pitch of the dE tile (96 wide); 208 B rows, shared with the fp32 df tile (52 floats)
 constexpr int DFP = 52;
+constexpr int CMB_CHUNK = 4096;  // backward: few rows of a chunk were blended, so a round of 128 needs a longer chunk
 // Loss scale of the fp16 backward operands (dO, dH, dE).  Per-splat colour gradients are 1e-8..1e-2: unscaled they sit in
 // (or below) fp16's subnormal range — the reference's own autocast backward has no GradScaler and loses them.  Everything
 // downstream of dO is linear in it, so the fp32 results are simply multiplied by 1/scale at the end.
@@ -382,30 +386,38 @@ __device__ __forceinline__ void ldsm_x2_trans(uint32_t &r0, uint32_t &r1, const 
   asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0,%1}, [%2];\n" : "=r"(r0), "=r"(r1) : "r"(a));
 }
 
-// dw[m][n] += sum over the warp's 32 rows of At[row][m] * Bt[row][n]   (m < m_valid, n < n_valid);
-// column n == n_valid of Bt is the constant 1: that column of the product is the bias gradient.
-__device__ __forceinline__ void dw_accumulate(float *dw, float *dbias, int m_valid, int n_valid, const __half *At, int pa,
-                                              int m_tiles, const __half *Bt, int pb, int n_tiles, int lane) {
+// dw[m][n] += sum over the CTA's 128 staged rows of At[row][m] * Bt[row][n] for the 16 outputs m of tile `mo`
+// (m < m_valid, n < n_valid); column n == n_valid of Bt is the constant 1: that column of the product is the bias
+// gradient.  A0 / B0 point into the first warp's stage, the other stages follow at sizeof(StageB).  The calling warp OWNS
+// the tile's rows of dw: plain read-modify-write, no atomics (float atomics on shared memory are CAS loops).
+__device__ __forceinline__ void dw_coop(float *dw, float *dbias, int m_valid, int n_valid, const __half *A0, int pa, int mo,
+                                        const __half *B0, int pb, int n_tiles, int lane) {
   int g = lane >> 2, t = lane & 3, id = lane >> 3, r = lane & 7;
-  for (int mo = 0; mo < m_tiles; ++mo) {
-    uint32_t a[2][4];
+  uint32_t a[2 * CM_WARPS][4];
 #pragma unroll
-    for (int kt = 0; kt < 2; ++kt) ldsm_x4_trans(a[kt], At + (16 * kt + (id >> 1) * 8 + r) * pa + 16 * mo + (id & 1) * 8);
-    for (int ni = 0; ni < n_tiles; ++ni) {
-      float c[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int sg = 0; sg < CM_WARPS; ++sg) {
+    const __half *At = reinterpret_cast<const __half *>(reinterpret_cast<const char *>(A0) + sg * sizeof(StageB));
+#pragma unroll
+    for (int kt = 0; kt < 2; ++kt) ldsm_x4_trans(a[2 * sg + kt], At + (16 * kt + (id >> 1) * 8 + r) * pa + 16 * mo + (id & 1) * 8);
+  }
+  for (int ni = 0; ni < n_tiles; ++ni) {
+    float c[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int sg = 0; sg < CM_WARPS; ++sg) {
+      const __half *Bt = reinterpret_cast<const __half *>(reinterpret_cast<const char *>(B0) + sg * sizeof(StageB));
 #pragma unroll
       for (int kt = 0; kt < 2; ++kt) {
         uint32_t b0, b1;
         ldsm_x2_trans(b0, b1, Bt + (16 * kt + (id & 1) * 8 + r) * pb + 8 * ni);
-        mma16816(c, a[kt], b0, b1);
+        mma16816(c, a[2 * sg + kt], b0, b1);
       }
+    }
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        int m = 16 * mo + g + ((e >> 1) << 3), nn = 8 * ni + 2 * t + (e & 1);
-        if (m < m_valid && c[e] != 0.f) {
-          if (nn < n_valid) atomicAdd(dw + m * n_valid + nn, c[e]);
-          else if (nn == n_valid) atomicAdd(dbias + m, c[e]);
-        }
+    for (int e = 0; e < 4; ++e) {
+      int m = 16 * mo + g + ((e >> 1) << 3), nn = 8 * ni + 2 * t + (e & 1);
+      if (m < m_valid) {
+        if (nn < n_valid) dw[m * n_valid + nn] += c[e];
+        else if (nn == n_valid) dbias[m] += c[e];
       }
     }
   }
@@ -486,14 +498,14 @@ __global__ void __launch_bounds__(CM_THREADS, 1) k_color_bwd(ColorDev m, ColorGr
                                                              const float *__restrict__ glo, float specular_weight,
                                                              const float *__restrict__ d_rgb, int d_rgb_stride, float w_spec_reg,
                                                              const float *__restrict__ reg_sums, float *__restrict__ d_feature,
-                                                             float *__restrict__ d_glo) {
+                                                             float *__restrict__ d_glo, int accumulate) {
   extern __shared__ __align__(16) unsigned char smem[];
   unsigned char *sp = smem;
   Weights &W = *reinterpret_cast<Weights *>(sp); sp += (sizeof(Weights) + 15) & ~(size_t)15;
   WeightsT &WT = *reinterpret_cast<WeightsT *>(sp); sp += (sizeof(WeightsT) + 15) & ~(size_t)15;
   GradAcc &acc = *reinterpret_cast<GradAcc *>(sp); sp += (sizeof(GradAcc) + 15) & ~(size_t)15;
   StageB *stages = reinterpret_cast<StageB *>(sp); sp += CM_WARPS * sizeof(StageB);
-  int *s_list = reinterpret_cast<int *>(sp); sp += CM_CHUNK * sizeof(int);
+  uint16_t *s_list = reinterpret_cast<uint16_t *>(sp); sp += CMB_CHUNK * sizeof(uint16_t);
   float *s_glo = reinterpret_cast<float *>(sp); sp += GF * sizeof(float);
   int *s_count = reinterpret_cast<int *>(sp);
   load_weights(W, m);
@@ -525,9 +537,11 @@ __global__ void __launch_bounds__(CM_THREADS, 1) k_color_bwd(ColorDev m, ColorGr
   const float cam[3] = {cx, cy, cz};
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   StageB &st = stages[warp];
-  for (int64_t base = (int64_t)blockIdx.x * CM_CHUNK; base < n; base += (int64_t)gridDim.x * CM_CHUNK) {
-    int cnt = compact_chunk(base, n, row_w, row_w_stride, s_list, s_count);
-    for (int k0 = warp * 32; k0 < cnt; k0 += CM_WARPS * 32) {
+  for (int64_t base = (int64_t)blockIdx.x * CMB_CHUNK; base < n; base += (int64_t)gridDim.x * CMB_CHUNK) {
+    int cnt = compact_chunk<CMB_CHUNK>(base, n, row_w, row_w_stride, s_list, s_count);
+    // rounds of 128 rows (32 per warp); every warp takes part in every round: the weight-gradient pass is cooperative
+    for (int kr = 0; kr < cnt; kr += CM_WARPS * 32) {
+      int k0 = kr + warp * 32;
       bool valid = k0 + lane < cnt;
       int64_t i = valid ? base + s_list[k0 + lane] : 0;
       float inv = stage_row(st, lane, valid, i, feature, position, cam, s_glo);
@@ -602,10 +616,10 @@ __global__ void __launch_bounds__(CM_THREADS, 1) k_color_bwd(ColorDev m, ColorGr
           *reinterpret_cast<float2 *>(dfs + (r0 + g + 8) * DFP + 8 * ni + 2 * t) = make_float2(din[ni][2], din[ni][3]);
         }
       }
-      __syncwarp();
-      dw_accumulate(acc.w1b, acc.b1b, 2 * H, F, st.dhs, TP, 4, st.xh, KP, 7, lane);
-      dw_accumulate(acc.w2b, acc.b2b, 4, H, st.dos[0], OP, 1, st.gs, HP, 5, lane);
-      __syncwarp();
+      __syncthreads();
+      dw_coop(acc.w1b, acc.b1b, 2 * H, F, stages[0].dhs, TP, warp, stages[0].xh, KP, 7, lane);
+      if (warp == 0) dw_coop(acc.w2b, acc.b2b, 4, H, stages[0].dos[0], OP, 0, stages[0].gs, HP, 5, lane);
+      __syncthreads();
       // directional MLP
 #pragma unroll 1
       for (int mt = 0; mt < 2; ++mt) {
@@ -661,8 +675,14 @@ __global__ void __launch_bounds__(CM_THREADS, 1) k_color_bwd(ColorDev m, ColorGr
 #pragma unroll
           for (int e = 0; e < 4; ++e) dv[e] = (df[ni][e] - s1[e >> 1] - fv[e] * s2[e >> 1]) * rinv[e >> 1];
           if (ni < PF / 8) {
-            if (rrow[0] >= 0) *reinterpret_cast<float2 *>(d_feature + rrow[0] * PF + col) = make_float2(dv[0], dv[1]);
-            if (rrow[1] >= 0) *reinterpret_cast<float2 *>(d_feature + rrow[1] * PF + col) = make_float2(dv[2], dv[3]);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              if (rrow[h] < 0) continue;
+              float2 *dst = reinterpret_cast<float2 *>(d_feature + rrow[h] * PF + col);
+              float2 v = make_float2(dv[2 * h], dv[2 * h + 1]);
+              if (accumulate) { float2 old = *dst; v.x += old.x; v.y += old.y; }
+              *dst = v;
+            }
           } else {
             float c0 = dv[0] + dv[2], c1 = dv[1] + dv[3];  // column sums over the tile's rows -> d glo
 #pragma unroll
@@ -671,11 +691,12 @@ __global__ void __launch_bounds__(CM_THREADS, 1) k_color_bwd(ColorDev m, ColorGr
           }
         }
       }
-      __syncwarp();
-      dw_accumulate(acc.w1d, acc.b1d, 2 * H, F, st.dhs, TP, 4, st.xh, KP, 7, lane);
-      dw_accumulate(acc.w2d, acc.b2d, 4, H, st.dos[1], OP, 1, st.gs, HP, 5, lane);
-      dw_accumulate(acc.wsh, acc.bsh, 2 * F, S, st.des, EP, 6, st.yh, KP, 5, lane);
-      __syncwarp();
+      __syncthreads();
+      dw_coop(acc.w1d, acc.b1d, 2 * H, F, stages[0].dhs, TP, warp, stages[0].xh, KP, 7, lane);
+      dw_coop(acc.wsh, acc.bsh, 2 * F, S, stages[0].des, EP, warp, stages[0].yh, KP, 5, lane);
+      if (warp < 2) dw_coop(acc.wsh, acc.bsh, 2 * F, S, stages[0].des, EP, CM_WARPS + warp, stages[0].yh, KP, 5, lane);
+      if (warp == 3) dw_coop(acc.w2d, acc.b2d, 4, H, stages[0].dos[1], OP, 0, stages[0].gs, HP, 5, lane);
+      __syncthreads();
     }
     __syncthreads();
   }
@@ -694,8 +715,8 @@ __global__ void __launch_bounds__(CM_THREADS, 1) k_color_bwd(ColorDev m, ColorGr
 
 size_t color_bwd_smem_bytes() {
   auto al = [](size_t x) { return (x + 15) & ~(size_t)15; };
-  return al(sizeof(Weights)) + al(sizeof(WeightsT)) + al(sizeof(GradAcc)) + CM_WARPS * sizeof(StageB) + CM_CHUNK * sizeof(int) +
-         GF * sizeof(float) + 16;
+  return al(sizeof(Weights)) + al(sizeof(WeightsT)) + al(sizeof(GradAcc)) + CM_WARPS * sizeof(StageB) +
+         CMB_CHUNK * sizeof(uint16_t) + GF * sizeof(float) + 16;
 }
 
 }  // namespace
@@ -726,7 +747,8 @@ extern "C" int gs_color_mlp_fwd(const gs_color_mlp *h_model, int64_t n, const fl
 extern "C" int gs_color_mlp_bwd(const gs_color_mlp *h_model, const gs_color_mlp *h_grads, int64_t n, const float *row_w,
                                 int row_w_stride, const float *feature, const float *position, const float *h_cam_pos,
                                 const float *glo, float specular_weight, const float *d_rgb, int d_rgb_stride,
-                                float w_specular_reg, const float *reg_sums, float *d_feature, float *d_glo, void *stream) {
+                                float w_specular_reg, const float *reg_sums, float *d_feature, float *d_glo, int accumulate,
+                                void *stream) {
   int rc = color_check(h_model);
   if (rc != GS_OK) return rc;
   rc = color_check(h_grads);
@@ -743,11 +765,11 @@ extern "C" int gs_color_mlp_bwd(const gs_color_mlp *h_model, const gs_color_mlp 
     GS_CUDA(cudaFuncSetAttribute(k_color_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
-  int64_t chunks = (n + CM_CHUNK - 1) / CM_CHUNK;
+  int64_t chunks = (n + CMB_CHUNK - 1) / CMB_CHUNK;
   int grid = (int)(chunks < 148 ? chunks : 148);  // persistent, one CTA per SM (218 KB of shared memory)
   k_color_bwd<<<grid, CM_THREADS, smem, (cudaStream_t)stream>>>(m, gd, n, row_w, row_w_stride, feature, position, h_cam_pos[0],
                                                                 h_cam_pos[1], h_cam_pos[2], glo, specular_weight, d_rgb,
-                                                                d_rgb_stride, w_specular_reg, reg_sums, d_feature, d_glo);
+                                                                d_rgb_stride, w_specular_reg, reg_sums, d_feature, d_glo, accumulate);
   GS_LAUNCH_CHECK();
   return GS_OK;
 }

@@ -1,0 +1,108 @@
+"""ColorModule — the colour model of the reference's default scene (`scene: mlp`): GLO embedding table + the two MLPs
+of ColorModel (reference scene/color_model.py:11-46,88-170, sizes config/scene/mlp.yaml:33-43).
+
+The per-splat work (LayerNorm, SH, both MLPs forward and backward) is gs_color_mlp_fwd / gs_color_mlp_bwd
+(csrc/color_mlp.cu).  What lives here is the small dense state around it: ten weight arrays (10k floats), their Adam
+(reference ColorModel.optimizer, betas (0.9, 0.999)) and the per-image GLO rows with their sparse Adam
+(GLOTable.optimizer, betas (0.8, 0.95)) — a handful of elementwise torch ops on one flat tensor each."""
+import math
+
+import torch
+
+from . import ops
+
+SHAPES = dict(base_w1=(64, 48), base_b1=(64,), base_w2=(4, 32), base_b2=(4,), dir_wsh=(96, 36), dir_bsh=(96,),
+              dir_w1=(64, 48), dir_b1=(64,), dir_w2=(4, 32), dir_b2=(4,))
+POINT_FEATURES, GLO_FEATURES = 16, 32
+
+
+class ColorModule:
+  def __init__(self, num_images, device="cuda", seed=0, lr=1e-2, lr_glo=2.0, weights=None, specular_reg=1e-5):
+    """weights: optional dict of arrays shaped like SHAPES (e.g. a reference checkpoint's ColorModel state);
+    default = nn.Linear's initialisation (U(-1/sqrt(in), 1/sqrt(in)) for weight and bias)."""
+    self.device = torch.device(device)
+    total = sum(math.prod(s) for s in SHAPES.values())
+    self.flat = torch.zeros((total,), device=self.device)
+    self.grad = torch.zeros_like(self.flat)
+    self.exp_avg, self.exp_avg_sq = torch.zeros_like(self.flat), torch.zeros_like(self.flat)
+    self.w, self.g = {}, {}
+    o = 0
+    gen = torch.Generator(device="cpu").manual_seed(seed)
+    for k in ops.COLOR_WEIGHTS:
+      shape = SHAPES[k]
+      cnt = math.prod(shape)
+      self.w[k] = self.flat[o:o + cnt].view(shape)
+      self.g[k] = self.grad[o:o + cnt].view(shape)
+      if weights is not None:
+        self.w[k].copy_(torch.as_tensor(weights[k], dtype=torch.float32))
+      else:
+        fan_in = SHAPES[k.replace("_b", "_w")][1]
+        bound = 1.0 / math.sqrt(fan_in)
+        self.w[k].copy_((torch.rand(shape, generator=gen) * 2 - 1) * bound)
+      o += cnt
+    self.model = ops.color_model(self.w)
+    self.grads = ops.color_model(self.g)
+    # GLOTable: zero-initialised embeddings (reference scene/color_model.py:16), one row per training image
+    self.glo = torch.zeros((max(num_images, 1), GLO_FEATURES), device=self.device)
+    self.glo_grad = torch.zeros_like(self.glo)
+    self.glo_m, self.glo_v = torch.zeros_like(self.glo), torch.zeros_like(self.glo)
+    self.glo_steps = torch.zeros((self.glo.shape[0],), device=self.device)
+    self._zero_glo = torch.zeros((GLO_FEATURES,), device=self.device)
+    self._touched = set()
+    self.lr, self.lr_glo, self.specular_reg = lr, lr_glo, specular_reg
+    self.steps = 0
+
+  def glo_row(self, image_idx):
+    """the image's embedding (reference MLPScene.eval_colors, scene/mlp_scene.py:355-360: zeros for a view that is not a
+    training image)."""
+    return self._zero_glo if image_idx is None else self.glo[image_idx]
+
+  def glo_grad_row(self, image_idx):
+    if image_idx is None:
+      return torch.zeros_like(self._zero_glo)
+    self._touched.add(int(image_idx))
+    return self.glo_grad[image_idx]
+
+  def forward(self, feature, position, cam_pos, image_idx, in_view, rgb, specular=None, specular_weight=1.0):
+    return ops.color_mlp_fwd(self.model, feature, position, cam_pos, self.glo_row(image_idx), in_view=in_view,
+                             specular_weight=specular_weight, rgb=rgb, specular=specular)
+
+  def backward(self, feature, position, cam_pos, image_idx, row_w, d_rgb, d_feature, accumulate, reg_sums=None,
+               specular_weight=1.0):
+    ops.color_mlp_bwd(self.model, self.grads, feature, position, cam_pos, self.glo_row(image_idx), row_w, d_rgb, d_feature,
+                      self.glo_grad_row(image_idx), specular_weight=specular_weight,
+                      w_specular_reg=self.specular_reg if reg_sums is not None else 0.0, reg_sums=reg_sums,
+                      accumulate=accumulate)
+
+  def step(self):
+    """Adam on the MLP weights (betas (0.9, 0.999), eps 1e-8) and on the GLO rows touched since the last step
+    (betas (0.8, 0.95)); clears the gradients."""
+    self.steps += 1
+    b1, b2, eps = 0.9, 0.999, 1e-8
+    self.exp_avg.mul_(b1).add_(self.grad, alpha=1 - b1)
+    self.exp_avg_sq.mul_(b2).addcmul_(self.grad, self.grad, value=1 - b2)
+    denom = (self.exp_avg_sq / (1 - b2 ** self.steps)).sqrt_().add_(eps)
+    self.flat.addcdiv_(self.exp_avg, denom, value=-self.lr / (1 - b1 ** self.steps))
+    self.grad.zero_()
+    if self._touched:
+      rows = torch.tensor(sorted(self._touched), device=self.device)
+      b1, b2 = 0.8, 0.95
+      g = self.glo_grad[rows]
+      self.glo_steps[rows] += 1
+      t = self.glo_steps[rows].unsqueeze(1)
+      m = self.glo_m[rows] * b1 + g * (1 - b1)
+      v = self.glo_v[rows] * b2 + g * g * (1 - b2)
+      self.glo_m[rows], self.glo_v[rows] = m, v
+      self.glo[rows] -= self.lr_glo * (m / (1 - b1 ** t)) / ((v / (1 - b2 ** t)).sqrt() + eps)
+      self.glo_grad[rows] = 0
+      self._touched.clear()
+
+  def all_reduce(self, dist, group=None):
+    """camera-batch DP: the colour model is replicated; its (tiny) dense gradients are summed over the ranks."""
+    dist.all_reduce(self.grad, group=group)
+    dist.all_reduce(self.glo_grad, group=group)
+    touched = torch.zeros((self.glo.shape[0],), device=self.device)
+    if self._touched:
+      touched[torch.tensor(sorted(self._touched), device=self.device)] = 1
+    dist.all_reduce(touched, group=group)
+    self._touched = set(int(i) for i in touched.nonzero().flatten().tolist())

@@ -476,7 +476,7 @@ def color_mlp_fwd(model, feature, position, cam_pos, glo, in_view=None, specular
 
 
 def color_mlp_bwd(model, grads, feature, position, cam_pos, glo, row_w, d_rgb, d_feature, d_glo, specular_weight=1.0,
-                  w_specular_reg=0.0, reg_sums=None):
+                  w_specular_reg=0.0, reg_sums=None, accumulate=False):
   """gs_color_mlp_bwd.  grads: a color_model() over the gradient tensors (accumulated); row_w / d_rgb may be column
   views; d_feature (n, point_features) is written for the rows with row_w > 0, d_glo accumulated."""
   n = feature.shape[0]
@@ -485,4 +485,4 @@ def color_mlp_bwd(model, grads, feature, position, cam_pos, glo, row_w, d_rgb, d
   L.check(L.load().gs_color_mlp_bwd(C.byref(model), C.byref(grads), n, row_w.data_ptr(), row_w.stride(0),
                                     L.ptr(_f32(feature)), L.ptr(_f32(position)), _cam_pos3(cam_pos), L.ptr(_f32(glo)),
                                     float(specular_weight), d_rgb.data_ptr(), d_rgb.stride(0), float(w_specular_reg),
-                                    L.ptr(reg_sums), L.ptr(d_feature), L.ptr(d_glo), L.stream()))
+                                    L.ptr(reg_sums), L.ptr(d_feature), L.ptr(d_glo), int(accumulate), L.stream()))

@@ -45,6 +45,23 @@ class SceneConfig:
   # reg_weight (scale, opacity, aspect): reference config/scene/mlp.yaml:16-19 at t = 0 (the log_decay schedules are the
   # caller's: assign scene.config.reg_weights per step).  (0, 0, 0) disables the two regularisation sweeps.
   reg_weights: tuple = (0.01, 1.0, 1e-4)
+  # colour model: False = SH coefficients per splat (SHScene); True = the reference's default MLPScene colour path
+  # (per-splat feature 16 + per-image GLO embedding 32 -> ColorModel, scene/mlp_scene.py:352-368): the last attribute
+  # plane then holds the point features (n, 16) and `sh_degree` is unused
+  color_mlp: bool = False
+  num_images: int = 0            # rows of the GLO table (training images)
+  lr_feature: float = 0.02       # vector group (config/scene/mlp.yaml:14 names the group; value = Spec O like the others)
+  lr_color: float = 1e-2         # ColorModel Adam (lr_diffuse / lr_specular at t = 0, config/scene/mlp.yaml:40-41)
+  lr_glo: float = 2.0            # lr_glo_feature, config/scene/mlp.yaml:21
+  reg_specular: float = 1e-5     # reg_weight.specular, config/scene/mlp.yaml:19
+
+
+def camera_position(cam):
+  """camera centre in world coordinates from the world->camera transform: -R^T t."""
+  T = [cam.T[i] for i in range(16)]
+  R = [[T[4 * r + c] for c in range(3)] for r in range(3)]
+  t = [T[3], T[7], T[11]]
+  return [-(R[0][k] * t[0] + R[1][k] * t[1] + R[2][k] * t[2]) for k in range(3)]
 
 
 def _plane_offsets(n, dims):
@@ -57,7 +74,8 @@ def _plane_offsets(n, dims):
 
 class SplatScene:
   def __init__(self, gaussians, config=None, device="cuda"):
-    """gaussians: dict position (N,3), log_scaling (N,3), rotation (N,4) xyzw, alpha_logit (N,), sh (N,3,K)."""
+    """gaussians: dict position (N,3), log_scaling (N,3), rotation (N,4) xyzw, alpha_logit (N,), sh (N,3,K) — or,
+    with config.color_mlp, feature (N,16) instead of sh (kept in the plane named "sh")."""
     self.config = config or SceneConfig()
     self.device = torch.device(device)
     if self.device.type != "cuda":
@@ -65,10 +83,16 @@ class SplatScene:
     L.load()
     self.K = (self.config.sh_degree + 1) ** 2
     self.ocfg = L.make_optim_config(**self.config.optim)
+    self.color = None
+    if self.config.color_mlp:
+      from .color import ColorModule
+      c = self.config
+      self.color = ColorModule(c.num_images, self.device, lr=c.lr_color, lr_glo=c.lr_glo, specular_reg=c.reg_specular,
+                               weights=gaussians.get("color_weights"))
     self._alloc(int(gaussians["position"].shape[0]))
     for name in ATTRS:
-      src = gaussians[name]
-      if name == "sh":
+      src = gaussians["feature" if (name == "sh" and self.color is not None) else name]
+      if name == "sh" and self.color is None:
         src = src[:, :, :self.K]
       self.p[name].copy_(torch.as_tensor(src, dtype=torch.float32).reshape(self.p[name].shape))
     self._work = None
@@ -79,7 +103,7 @@ class SplatScene:
 
   # ---- storage ---------------------------------------------------------------------------------------
   def _dims(self):
-    return (3, 3, 4, 1, 3 * self.K)
+    return (3, 3, 4, 1, 16 if self.color is not None else 3 * self.K)
 
   def _alloc(self, n):
     dev = self.device
@@ -93,7 +117,8 @@ class SplatScene:
     sq_dims = (1, 3, 1, 1, 1)
     sq_offs, sq_total = _plane_offsets(n, sq_dims)
     self.exp_avg_sq_flat = torch.zeros((sq_total,), device=dev)
-    shapes = dict(position=(n, 3), log_scaling=(n, 3), rotation=(n, 4), alpha_logit=(n,), sh=(n, 3, self.K))
+    shapes = dict(position=(n, 3), log_scaling=(n, 3), rotation=(n, 4), alpha_logit=(n,),
+                  sh=(n, 16) if self.color is not None else (n, 3, self.K))
 
     def views(flat, offsets, dims_, shp):
       return {name: flat[o:o + n * d].view(shp[name]) for name, o, d in zip(ATTRS, offsets, dims_)}
@@ -170,13 +195,17 @@ class SplatScene:
       self.timer.mark(name)
 
   # ---- forward ---------------------------------------------------------------------------------------
-  def _forward(self, cam, median=False, visibility=None):
+  def _forward(self, cam, median=False, visibility=None, image_idx=None):
     w = self._buffers(cam)
     p = self.p
     self._mark("begin")
-    ops.project_fwd(cam, self.raster_cfg, p["position"], p["log_scaling"], p["rotation"], p["alpha_logit"], p["sh"],
-                    self.config.sh_degree, out=(w["g2d"], w["depth"], w["rgb"]), tile_info=w["tinfo"])
+    ops.project_fwd(cam, self.raster_cfg, p["position"], p["log_scaling"], p["rotation"], p["alpha_logit"],
+                    None if self.color is not None else p["sh"], self.config.sh_degree,
+                    out=(w["g2d"], w["depth"], w["rgb"]), tile_info=w["tinfo"])
     self._mark("project_fwd")
+    if self.color is not None:  # MLPScene.eval_colors for the in-view rows (reference scene/mlp_scene.py:415-417)
+      self.color.forward(p["sh"], p["position"], camera_position(cam), image_idx, w["g2d"][:, 5], w["rgb"])
+      self._mark("color_fwd")
     tb = self._tile_buffers(w, cam)
     ops.tile_map(self.raster_cfg, w["g2d"], w["depth"], cam.width, cam.height, buffers=tb, tile_info=w["tinfo"])
     self._mark("tile_map")
@@ -186,10 +215,11 @@ class SplatScene:
     self._mark("raster_fwd")
     return w, tb, vis, med
 
-  def render(self, cam, median_depth=False, compute_visibility=False):
+  def render(self, cam, median_depth=False, compute_visibility=False, image_idx=None):
     """Forward only (reference scene/mlp_scene.py:411-427): returns dict(image (H,W,3) clamped to [0,1] like the
     reference's post_activation scene/color_model.py:154-160, raw, weight, visibility, median_depth)."""
-    w, tb, vis, med = self._forward(cam, median=median_depth, visibility=True if compute_visibility else None)
+    w, tb, vis, med = self._forward(cam, median=median_depth, visibility=True if compute_visibility else None,
+                                    image_idx=image_idx)
     return dict(image=w["image"].clamp(0, 1), raw=w["image"], weight=1.0 - w["final_T"], visibility=vis,
                 median_depth=med, g2d=w["g2d"], depth=w["depth"])
 
@@ -234,7 +264,7 @@ class SplatScene:
     return split_mask, prune_mask
 
   # ---- one training image: forward + loss + backward + statistics ------------------------------------------
-  def forward_backward(self, cam, target, first=False, exchange=None, slot=0, target_ready=None):
+  def forward_backward(self, cam, target, first=False, exchange=None, slot=0, target_ready=None, image_idx=None):
     """Reference trainer/trainer.py:500-514 for one image (render → loss → backward → add_rendering), fused:
     gradients are ADDED into self.g (batch = sum), statistics into self.stats / self.visible.
     target: (H,W,3) float32 in [0,1] or uint8 on the device.  Returns loss_sums (device, 2): Σ|d|, Σd².
@@ -243,7 +273,7 @@ class SplatScene:
     exchange (an ImageExchange, camera-batch DP): the image's gradient rows and statistics are packed into record
     `slot` instead of being applied here; ImageExchange.fold() applies every rank's records in image order.
     target_ready: CUDA event of a side-stream upload of `target`; the stream waits for it right before the loss."""
-    w, tb, _, _ = self._forward(cam)
+    w, tb, _, _ = self._forward(cam, image_idx=image_idx)
     c = self.config
     if target_ready is not None:
       torch.cuda.current_stream().wait_event(target_ready)
@@ -265,10 +295,14 @@ class SplatScene:
       # formed per row inside the projection backward, which already holds everything they need
       ops.reg_loss(c.reg_weights, w["g2d"], w["depth"], p["log_scaling"], w["vis"], sums=w["reg_sums"], compute_sums=True)
       self._mark("reg")
-    ops.project_bwd(cam, self.raster_cfg, p["position"], p["log_scaling"], p["rotation"], p["alpha_logit"], p["sh"],
-                    c.sh_degree, w["g2d"], acc[:, 0:6], acc[:, 6:9], None, row_vis=w["vis"], grads=self.g,
-                    accumulate=not (first or exchange is not None),
-                    reg=(c.reg_weights, w["reg_sums"], w["depth"]) if reg else None)
+    accumulate = not (first or exchange is not None)
+    ops.project_bwd(cam, self.raster_cfg, p["position"], p["log_scaling"], p["rotation"], p["alpha_logit"],
+                    None if self.color is not None else p["sh"], c.sh_degree, w["g2d"], acc[:, 0:6],
+                    None if self.color is not None else acc[:, 6:9], None, row_vis=w["vis"], grads=self.g,
+                    accumulate=accumulate, reg=(c.reg_weights, w["reg_sums"], w["depth"]) if reg else None)
+    if self.color is not None:  # colour gradient of the blended rows -> point features, GLO row, MLP weights
+      self.color.backward(p["sh"], p["position"], camera_position(cam), image_idx, w["vis"], acc[:, 6:9], self.g["sh"],
+                          accumulate, reg_sums=w["reg_sums"] if reg else None)
     self._mark("project_bwd")
     if exchange is not None:
       # the dense gradient buffer holds this image's rows only (pack moves them out and zeroes them again)
@@ -299,12 +333,15 @@ class SplatScene:
       G(L.GS_GROUP_LOCAL_VECTOR, c.lr_position, p["position"], g["position"], m1["position"], m2["position"],
         basis_ls=p["log_scaling"], basis_q=p["rotation"]),
       G(L.GS_GROUP_SCALAR, c.lr_alpha_logit, p["alpha_logit"], g["alpha_logit"], m1["alpha_logit"], m2["alpha_logit"]),
-      G(L.GS_GROUP_VECTOR, c.lr_sh, p["sh"], g["sh"], m1["sh"], m2["sh"])], vis, rv, st, indexes=ix)
+      G(L.GS_GROUP_VECTOR, c.lr_feature if self.color is not None else c.lr_sh, p["sh"], g["sh"], m1["sh"], m2["sh"])],
+      vis, rv, st, indexes=ix)
     ops.optim_step_groups(o, self.n, [
       G(L.GS_GROUP_SCALAR, c.lr_log_scaling, p["log_scaling"], g["log_scaling"], m1["log_scaling"], m2["log_scaling"],
         post=L.GS_POST_CLAMP, post_lo=-8.0, post_hi=8.0),
       G(L.GS_GROUP_VECTOR, c.lr_rotation, p["rotation"], g["rotation"], m1["rotation"], m2["rotation"],
         post=L.GS_POST_NORMALIZE)], vis, rv, st, indexes=ix)
+    if self.color is not None:
+      self.color.step()
     self._mark("optim")
     vis.zero_()  # zero_grad(): gradient rows were cleared by the optimiser kernels (mlp_scene.py:155-161)
 

@@ -82,6 +82,8 @@ class Trainer:
   def exchange_gradients(self):
     """SUM (not mean: reference accumulates .grad over the batch, trainer/trainer.py:500-514) of the packed
     gradient buffer; the tail plane carries `visible` so one collective moves both."""
+    if self.world_size > 1 and getattr(self.scene, "color", None) is not None:
+      self.scene.color.all_reduce(dist)  # replicated colour model: its small dense gradients are summed
     if self.exchange is not None:
       self.exchange.fold()
       self.scene._mark("exchange")
@@ -140,10 +142,12 @@ class Trainer:
       self.exchange = ImageExchange(scene, e.world, e.rank, cap=e.cap, images_per_rank=e.k, transport=e.transport, group=e.group)
     if self.exchange is not None and len(mine) != self.exchange.k:
       raise L.GsError(f"the exchange was sized for {self.exchange.k} image(s) per rank, got {len(mine)}")
-    for k, (cam, image) in enumerate(mine):
+    for k, item in enumerate(mine):
+      cam, image = item[0], item[1]
+      extra = dict(image_idx=item[2]) if len(item) > 2 else {}  # MLP colour scenes: the image's GLO row
       target, ready = self._to_device(image)
       sums = scene.forward_backward(cam, target, first=(k == 0 and self._grads_clean), exchange=self.exchange, slot=k,
-                                    target_ready=None if ready is None else ready[0])
+                                    target_ready=None if ready is None else ready[0], **extra)
       if ready is not None:
         done = torch.cuda.Event()
         done.record()  # after this image's backward: its loss kernels are long finished with the target
