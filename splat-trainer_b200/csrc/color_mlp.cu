@@ -34,15 +34,16 @@ struct Stage {
   __half xh[32 * KP];  // LayerNorm output, fp16 (A operand of the base layer)
   __half yh[32 * KP];  // SH coefficients, fp16, zero padded to 48 (A operand of the direction encoder)
   float xf[32 * KP];   // LayerNorm output, fp32 (x = f * a + b multiplies the fp32 feature, color_model.py / torch_mlp.py:65)
-  float o[2][32 * 8];  // outputs of the two MLPs (4 valid columns)
+  // the outputs of the two MLPs (2 x 32 x 8 floats) reuse the bytes of xh once its fragments are in registers
 };
+constexpr int FW_THREADS = 384, FW_WARPS = FW_THREADS / 32;  // forward: 12 warps share one copy of the weights per SM
 
 __device__ __forceinline__ float hr(float v) { return __half2float(__float2half_rn(v)); }
 __device__ __forceinline__ uint32_t pack2(float a, float b) {
   __half2 h = __floats2half2_rn(a, b);
   return *reinterpret_cast<uint32_t *>(&h);
 }
-__device__ __forceinline__ float sigmoidf(float v) { return 1.0f / (1.0f + __expf(-v)); }
+__device__ __forceinline__ float sigmoidf(float v) { return __fdividef(1.0f, 1.0f + __expf(-v)); }
 
 __device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
   asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
@@ -103,24 +104,24 @@ __device__ __forceinline__ void rsh5(float x, float y, float z, float *Y) {
 
 __device__ __forceinline__ void load_weights(Weights &W, const ColorDev &m) {
   uint32_t *z = reinterpret_cast<uint32_t *>(&W);
-  for (int i = threadIdx.x; i < (int)(sizeof(Weights) / 4); i += CM_THREADS) z[i] = 0u;  // the pads must be zero
+  for (int i = threadIdx.x; i < (int)(sizeof(Weights) / 4); i += blockDim.x) z[i] = 0u;  // the pads must be zero
   __syncthreads();
-  for (int i = threadIdx.x; i < 2 * H * F; i += CM_THREADS) {
+  for (int i = threadIdx.x; i < 2 * H * F; i += blockDim.x) {
     int o = i / F, k = i - o * F;
     W.w1b[o * KP + k] = __float2half_rn(m.w[0][i]);
     W.w1d[o * KP + k] = __float2half_rn(m.w[6][i]);
   }
-  for (int i = threadIdx.x; i < 2 * F * S; i += CM_THREADS) {
+  for (int i = threadIdx.x; i < 2 * F * S; i += blockDim.x) {
     int o = i / S, k = i - o * S;
     W.wsh[o * KP + k] = __float2half_rn(m.w[4][i]);
   }
-  for (int i = threadIdx.x; i < 4 * H; i += CM_THREADS) {
+  for (int i = threadIdx.x; i < 4 * H; i += blockDim.x) {
     int o = i / H, k = i - o * H;
     W.w2b[o * HP + k] = __float2half_rn(m.w[2][i]);
     W.w2d[o * HP + k] = __float2half_rn(m.w[8][i]);
   }
-  for (int i = threadIdx.x; i < 2 * H; i += CM_THREADS) { W.b1b[i] = hr(m.w[1][i]); W.b1d[i] = hr(m.w[7][i]); }
-  for (int i = threadIdx.x; i < 2 * F; i += CM_THREADS) W.bsh[i] = hr(m.w[5][i]);
+  for (int i = threadIdx.x; i < 2 * H; i += blockDim.x) { W.b1b[i] = hr(m.w[1][i]); W.b1d[i] = hr(m.w[7][i]); }
+  for (int i = threadIdx.x; i < 2 * F; i += blockDim.x) W.bsh[i] = hr(m.w[5][i]);
   if (threadIdx.x < 4) { W.b2b[threadIdx.x] = hr(m.w[3][threadIdx.x]); W.b2d[threadIdx.x] = hr(m.w[9][threadIdx.x]); }
   __syncthreads();
 }
@@ -254,13 +255,105 @@ __device__ __forceinline__ void affine_tile(const Weights &W, StageT &st, int r0
   }
 }
 
+// The same two steps for BOTH 16-row tiles of a warp's 32 rows at once: every weight fragment is loaded once and feeds two
+// independent accumulator chains (half the shared-memory traffic, twice the MMAs in flight).
+__device__ __forceinline__ void mlp_tile2(const __half *__restrict__ w1, const float *__restrict__ b1,
+                                          const __half *__restrict__ w2, const float *__restrict__ b2, float *__restrict__ out,
+                                          int g, int t, const uint32_t (&A)[2][3][4]) {
+  uint32_t A2[2][2][4];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      int col = 8 * (2 * j + q) + 2 * t;
+      float ca[2][4], cb[2][4];
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt) {
+        ca[mt][0] = ca[mt][2] = b1[col]; ca[mt][1] = ca[mt][3] = b1[col + 1];
+        cb[mt][0] = cb[mt][2] = b1[H + col]; cb[mt][1] = cb[mt][3] = b1[H + col + 1];
+      }
+#pragma unroll
+      for (int ks = 0; ks < 3; ++ks) {
+        uint32_t b0, b1r, c0, c1r;
+        load_b(b0, b1r, w1, KP, 8 * (2 * j + q), 16 * ks, g, t);
+        load_b(c0, c1r, w1, KP, H + 8 * (2 * j + q), 16 * ks, g, t);
+        mma16816(ca[0], A[0][ks], b0, b1r);
+        mma16816(ca[1], A[1][ks], b0, b1r);
+        mma16816(cb[0], A[0][ks], c0, c1r);
+        mma16816(cb[1], A[1][ks], c0, c1r);
+      }
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt) {
+        A2[mt][j][2 * q] = pack2(hr(ca[mt][0]) * sigmoidf(hr(cb[mt][0])), hr(ca[mt][1]) * sigmoidf(hr(cb[mt][1])));
+        A2[mt][j][2 * q + 1] = pack2(hr(ca[mt][2]) * sigmoidf(hr(cb[mt][2])), hr(ca[mt][3]) * sigmoidf(hr(cb[mt][3])));
+      }
+    }
+  }
+  float co[2][4];
+#pragma unroll
+  for (int mt = 0; mt < 2; ++mt) { co[mt][0] = co[mt][2] = b2[2 * t]; co[mt][1] = co[mt][3] = b2[2 * t + 1]; }
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    uint32_t b0, b1r;
+    load_b(b0, b1r, w2, HP, 0, 16 * j, g, t);
+    mma16816(co[0], A2[0][j], b0, b1r);
+    mma16816(co[1], A2[1][j], b0, b1r);
+  }
+  if (t < 2) {
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt) {
+      *reinterpret_cast<float2 *>(out + (16 * mt + g) * 8 + 2 * t) = make_float2(hr(co[mt][0]), hr(co[mt][1]));
+      *reinterpret_cast<float2 *>(out + (16 * mt + g + 8) * 8 + 2 * t) = make_float2(hr(co[mt][2]), hr(co[mt][3]));
+    }
+  }
+}
+
+template <typename StageT>
+__device__ __forceinline__ void affine_tile2(const Weights &W, StageT &st, int g, int t, uint32_t (&AX)[2][3][4]) {
+  uint32_t AY[2][3][4];
+#pragma unroll
+  for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+    for (int ks = 0; ks < 3; ++ks) load_a(AY[mt][ks], st.yh, KP, 16 * mt, 16 * ks, g, t);
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      int col = 8 * (2 * j + q) + 2 * t;
+      float ca[2][4], cb[2][4];
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt) {
+        ca[mt][0] = ca[mt][2] = W.bsh[col]; ca[mt][1] = ca[mt][3] = W.bsh[col + 1];
+        cb[mt][0] = cb[mt][2] = W.bsh[F + col]; cb[mt][1] = cb[mt][3] = W.bsh[F + col + 1];
+      }
+#pragma unroll
+      for (int ks = 0; ks < 3; ++ks) {
+        uint32_t b0, b1r, c0, c1r;
+        load_b(b0, b1r, W.wsh, KP, 8 * (2 * j + q), 16 * ks, g, t);
+        load_b(c0, c1r, W.wsh, KP, F + 8 * (2 * j + q), 16 * ks, g, t);
+        mma16816(ca[0], AY[0][ks], b0, b1r);
+        mma16816(ca[1], AY[1][ks], b0, b1r);
+        mma16816(cb[0], AY[0][ks], c0, c1r);
+        mma16816(cb[1], AY[1][ks], c0, c1r);
+      }
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt) {
+        float2 lo = *reinterpret_cast<const float2 *>(st.xf + (16 * mt + g) * KP + col);
+        float2 hi = *reinterpret_cast<const float2 *>(st.xf + (16 * mt + g + 8) * KP + col);
+        AX[mt][j][2 * q] = pack2(lo.x * hr(ca[mt][0]) + hr(cb[mt][0]), lo.y * hr(ca[mt][1]) + hr(cb[mt][1]));
+        AX[mt][j][2 * q + 1] = pack2(hi.x * hr(ca[mt][2]) + hr(cb[mt][2]), hi.y * hr(ca[mt][3]) + hr(cb[mt][3]));
+      }
+    }
+  }
+}
+
 // block compaction of the rows of one chunk that have work (in view / blended), like k_project_bwd
 template <int CHUNK, typename T>
 __device__ __forceinline__ int compact_chunk(int64_t base, int64_t n, const float *__restrict__ mask, int mask_stride,
                                              T *s_list, int *s_count) {
   if (threadIdx.x == 0) *s_count = 0;
   __syncthreads();
-  for (int k = threadIdx.x; k < CHUNK; k += CM_THREADS) {
+  for (int k = threadIdx.x; k < CHUNK; k += blockDim.x) {
     int64_t i = base + k;
     if (i < n && (!mask || mask[(int64_t)mask_stride * i] > 0.f)) s_list[atomicAdd(s_count, 1)] = (T)k;
   }
@@ -268,7 +361,7 @@ __device__ __forceinline__ int compact_chunk(int64_t base, int64_t n, const floa
   return *s_count;
 }
 
-__global__ void __launch_bounds__(CM_THREADS) k_color_fwd(ColorDev m, int64_t n, const float *__restrict__ in_view,
+__global__ void __launch_bounds__(FW_THREADS, 1) k_color_fwd(ColorDev m, int64_t n, const float *__restrict__ in_view,
                                                           int in_view_stride, const float *__restrict__ feature,
                                                           const float *__restrict__ position, float cx, float cy, float cz,
                                                           const float *__restrict__ glo, float specular_weight,
@@ -276,7 +369,7 @@ __global__ void __launch_bounds__(CM_THREADS) k_color_fwd(ColorDev m, int64_t n,
   extern __shared__ __align__(16) unsigned char smem[];
   Weights &W = *reinterpret_cast<Weights *>(smem);
   Stage *stages = reinterpret_cast<Stage *>(smem + ((sizeof(Weights) + 15) & ~(size_t)15));
-  int *s_list = reinterpret_cast<int *>(stages + CM_WARPS);
+  int *s_list = reinterpret_cast<int *>(stages + FW_WARPS);
   float *s_glo = reinterpret_cast<float *>(s_list + CM_CHUNK);
   int *s_count = reinterpret_cast<int *>(s_glo + GF);
   load_weights(W, m);
@@ -285,27 +378,28 @@ __global__ void __launch_bounds__(CM_THREADS) k_color_fwd(ColorDev m, int64_t n,
   const float cam[3] = {cx, cy, cz};
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   Stage &st = stages[warp];
+  float *so = reinterpret_cast<float *>(st.xh);
   for (int64_t base = (int64_t)blockIdx.x * CM_CHUNK; base < n; base += (int64_t)gridDim.x * CM_CHUNK) {
     int cnt = compact_chunk<CM_CHUNK>(base, n, in_view, in_view_stride, s_list, s_count);
-    for (int k0 = warp * 32; k0 < cnt; k0 += CM_WARPS * 32) {
+    for (int k0 = warp * 32; k0 < cnt; k0 += FW_WARPS * 32) {
       bool valid = k0 + lane < cnt;
       int64_t i = valid ? base + s_list[k0 + lane] : 0;
       stage_row(st, lane, valid, i, feature, position, cam, s_glo);
       __syncwarp();
-#pragma unroll 1
-      for (int mt = 0; mt < 2; ++mt) {
-        int r0 = 16 * mt;
-        if (k0 + r0 >= cnt) break;
-        uint32_t A[3][4];
+      {
+        uint32_t A[2][3][4];
 #pragma unroll
-        for (int ks = 0; ks < 3; ++ks) load_a(A[ks], st.xh, KP, r0, 16 * ks, g, t);
-        mlp_tile(W.w1b, W.b1b, W.w2b, W.b2b, st.o[0], r0, g, t, A);
-        affine_tile<false>(W, st, r0, g, t, A);
-        mlp_tile(W.w1d, W.b1d, W.w2d, W.b2d, st.o[1], r0, g, t, A);
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+          for (int ks = 0; ks < 3; ++ks) load_a(A[mt][ks], st.xh, KP, 16 * mt, 16 * ks, g, t);
+        __syncwarp();  // xh is in registers: its bytes now take the MLP outputs
+        mlp_tile2(W.w1b, W.b1b, W.w2b, W.b2b, so, g, t, A);
+        affine_tile2(W, st, g, t, A);
+        mlp_tile2(W.w1d, W.b1d, W.w2d, W.b2d, so + 32 * 8, g, t, A);
       }
       __syncwarp();
       if (valid) {
-        const float *o = st.o[0] + lane * 8, *o2 = st.o[1] + lane * 8;
+        const float *o = so + lane * 8, *o2 = so + 32 * 8 + lane * 8;
         float lum = expf(o[0]), lum2 = expf(o2[0] - 2.0f);  // luminance_activation, intensity_bias -2 for the specular term
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
@@ -321,7 +415,7 @@ __global__ void __launch_bounds__(CM_THREADS) k_color_fwd(ColorDev m, int64_t n,
 }
 
 size_t color_smem_bytes() {
-  return ((sizeof(Weights) + 15) & ~(size_t)15) + CM_WARPS * sizeof(Stage) + CM_CHUNK * sizeof(int) + GF * sizeof(float) + 16;
+  return ((sizeof(Weights) + 15) & ~(size_t)15) + FW_WARPS * sizeof(Stage) + CM_CHUNK * sizeof(int) + GF * sizeof(float) + 16;
 }
 
 int color_check(const gs_color_mlp *m) {
@@ -737,8 +831,8 @@ extern "C" int gs_color_mlp_fwd(const gs_color_mlp *h_model, int64_t n, const fl
     configured = true;
   }
   int64_t chunks = (n + CM_CHUNK - 1) / CM_CHUNK;
-  int grid = (int)(chunks < 148 * 2 ? chunks : 148 * 2);  // persistent: 2 CTAs (97 KB of shared memory each) per SM
-  k_color_fwd<<<grid, CM_THREADS, smem, (cudaStream_t)stream>>>(m, n, in_view, in_view_stride, feature, position, h_cam_pos[0],
+  int grid = (int)(chunks < 148 ? chunks : 148);  // persistent: one CTA of 12 warps per SM (203 KB of shared memory)
+  k_color_fwd<<<grid, FW_THREADS, smem, (cudaStream_t)stream>>>(m, n, in_view, in_view_stride, feature, position, h_cam_pos[0],
                                                                 h_cam_pos[1], h_cam_pos[2], glo, specular_weight, rgb, specular);
   GS_LAUNCH_CHECK();
   return GS_OK;
