@@ -17,7 +17,7 @@ namespace {
 constexpr int PF = 16, GF = 32, F = PF + GF, H = 32, DEG = 5, S = (DEG + 1) * (DEG + 1);  // config/scene/mlp.yaml:33-43
 constexpr int KP = 56;  // row pitch (halfs) of 48-wide fp16 tiles: conflict-free fragment loads (28 words: 4-bank steps)
 constexpr int HP = 40;  // row pitch (halfs) of 32-wide fp16 tiles
-constexpr int CM_THREADS = 128, CM_WARPS = CM_THREADS / 32, CM_CHUNK = 1024;
+constexpr int CM_THREADS = 128, CM_WARPS = CM_THREADS / 32;  // backward CTA
 
 struct ColorDev {
   const float *w[10];  // base_w1 base_b1 base_w2 base_b2 dir_wsh dir_bsh dir_w1 dir_b1 dir_w2 dir_b2
@@ -35,7 +35,9 @@ struct Stage {
   __half yh[32 * KP];  // SH coefficients, fp16, zero padded to 48 (A operand of the direction encoder)
   float xf[32 * KP];   // LayerNorm output, fp32 (x = f * a + b multiplies the fp32 feature, color_model.py / torch_mlp.py:65)
   // the outputs of the two MLPs (2 x 32 x 8 floats) reuse the bytes of xh once its fragments are in registers
+  uint16_t list[512];  // the warp's compacted row offsets of its current 512-row slice
 };
+constexpr int FW_SLICE = 512;
 constexpr int FW_THREADS = 384, FW_WARPS = FW_THREADS / 32;  // forward: 12 warps share one copy of the weights per SM
 
 __device__ __forceinline__ float hr(float v) { return __half2float(__float2half_rn(v)); }
@@ -369,9 +371,7 @@ __global__ void __launch_bounds__(FW_THREADS, 1) k_color_fwd(ColorDev m, int64_t
   extern __shared__ __align__(16) unsigned char smem[];
   Weights &W = *reinterpret_cast<Weights *>(smem);
   Stage *stages = reinterpret_cast<Stage *>(smem + ((sizeof(Weights) + 15) & ~(size_t)15));
-  int *s_list = reinterpret_cast<int *>(stages + FW_WARPS);
-  float *s_glo = reinterpret_cast<float *>(s_list + CM_CHUNK);
-  int *s_count = reinterpret_cast<int *>(s_glo + GF);
+  float *s_glo = reinterpret_cast<float *>(stages + FW_WARPS);
   load_weights(W, m);
   if (threadIdx.x < GF) s_glo[threadIdx.x] = glo[threadIdx.x];
   __syncthreads();
@@ -379,11 +379,23 @@ __global__ void __launch_bounds__(FW_THREADS, 1) k_color_fwd(ColorDev m, int64_t
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   Stage &st = stages[warp];
   float *so = reinterpret_cast<float *>(st.xh);
-  for (int64_t base = (int64_t)blockIdx.x * CM_CHUNK; base < n; base += (int64_t)gridDim.x * CM_CHUNK) {
-    int cnt = compact_chunk<CM_CHUNK>(base, n, in_view, in_view_stride, s_list, s_count);
-    for (int k0 = warp * 32; k0 < cnt; k0 += FW_WARPS * 32) {
+  // Every warp works alone from here on (no CTA barrier): it compacts the in-view rows of its own 512-row slice by
+  // ballot and walks them 32 at a time, so warps never wait for each other's uneven slices.
+  int64_t stride = (int64_t)gridDim.x * FW_WARPS * FW_SLICE;
+  for (int64_t base = ((int64_t)blockIdx.x * FW_WARPS + warp) * FW_SLICE; base < n; base += stride) {
+    int cnt = 0;
+#pragma unroll 4
+    for (int k = 0; k < FW_SLICE; k += 32) {
+      int64_t r = base + k + lane;
+      bool on = r < n && (!in_view || in_view[(int64_t)in_view_stride * r] > 0.f);
+      unsigned bal = __ballot_sync(GS_FULL, on);
+      if (on) st.list[cnt + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)(k + lane);
+      cnt += __popc(bal);
+    }
+    __syncwarp();
+    for (int k0 = 0; k0 < cnt; k0 += 32) {
       bool valid = k0 + lane < cnt;
-      int64_t i = valid ? base + s_list[k0 + lane] : 0;
+      int64_t i = valid ? base + st.list[k0 + lane] : 0;
       stage_row(st, lane, valid, i, feature, position, cam, s_glo);
       __syncwarp();
       {
@@ -410,12 +422,11 @@ __global__ void __launch_bounds__(FW_THREADS, 1) k_color_fwd(ColorDev m, int64_t
       }
       __syncwarp();
     }
-    __syncthreads();
   }
 }
 
 size_t color_smem_bytes() {
-  return ((sizeof(Weights) + 15) & ~(size_t)15) + FW_WARPS * sizeof(Stage) + CM_CHUNK * sizeof(int) + GF * sizeof(float) + 16;
+  return ((sizeof(Weights) + 15) & ~(size_t)15) + FW_WARPS * sizeof(Stage) + GF * sizeof(float) + 16;
 }
 
 int color_check(const gs_color_mlp *m) {
@@ -830,8 +841,8 @@ extern "C" int gs_color_mlp_fwd(const gs_color_mlp *h_model, int64_t n, const fl
     GS_CUDA(cudaFuncSetAttribute(k_color_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
-  int64_t chunks = (n + CM_CHUNK - 1) / CM_CHUNK;
-  int grid = (int)(chunks < 148 ? chunks : 148);  // persistent: one CTA of 12 warps per SM (203 KB of shared memory)
+  int64_t chunks = (n + (int64_t)FW_WARPS * FW_SLICE - 1) / ((int64_t)FW_WARPS * FW_SLICE);
+  int grid = (int)(chunks < 148 ? chunks : 148);  // persistent: one CTA of 12 warps per SM (212 KB of shared memory)
   k_color_fwd<<<grid, FW_THREADS, smem, (cudaStream_t)stream>>>(m, n, in_view, in_view_stride, feature, position, h_cam_pos[0],
                                                                 h_cam_pos[1], h_cam_pos[2], glo, specular_weight, rgb, specular);
   GS_LAUNCH_CHECK();

@@ -64,5 +64,6 @@ def bwd():
 
 
 if __name__ == "__main__":
-  bwd()
+  if "fwd" not in sys.argv[1:]:
+    bwd()
   main()
