@@ -97,6 +97,18 @@ class ColorModule:
       self.glo_grad[rows] = 0
       self._touched.clear()
 
+  _STATE = ("flat", "exp_avg", "exp_avg_sq", "glo", "glo_m", "glo_v", "glo_steps")
+
+  def state_dict(self):
+    sd = {k: getattr(self, k).clone() for k in self._STATE}
+    sd["steps"] = self.steps
+    return sd
+
+  def load_state_dict(self, sd):
+    for k in self._STATE:
+      getattr(self, k).copy_(sd[k])  # in place: the kernels hold pointers into `flat`
+    self.steps = int(sd["steps"])
+
   def all_reduce(self, dist, group=None):
     """camera-batch DP: the colour model is replicated; its (tiny) dense gradients are summed over the ranks."""
     dist.all_reduce(self.grad, group=group)

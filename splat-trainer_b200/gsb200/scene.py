@@ -415,12 +415,21 @@ class SplatScene:
     sd.update({f"m1.{k}": v.clone() for k, v in self.m1.items()})
     sd.update({f"m2.{k}": v.clone() for k, v in self.m2.items()})
     sd.update(running_vis=self.running_vis.clone(), opt_step=self.opt_step.clone(), sh_degree=self.config.sh_degree)
+    if self.color is not None:  # colour model + GLO table + their optimiser state (reference all_parameters, mlp_scene.py:291-298)
+      sd.update({f"color.{k}": v for k, v in self.color.state_dict().items()})
     return sd
 
   @staticmethod
   def from_state_dict(sd, config=None, device="cuda"):
-    config = config or SceneConfig(sh_degree=int(sd["sh_degree"]))
-    scene = SplatScene({k: sd[f"p.{k}"] for k in ATTRS}, config, device)
+    mlp = "color.flat" in sd
+    config = config or SceneConfig(sh_degree=int(sd["sh_degree"]), color_mlp=mlp,
+                                   num_images=int(sd["color.glo"].shape[0]) if mlp else 0)
+    g = {k: sd[f"p.{k}"] for k in ATTRS}
+    if mlp:
+      g["feature"] = g["sh"]
+    scene = SplatScene(g, config, device)
+    if mlp:
+      scene.color.load_state_dict({k[len("color."):]: v for k, v in sd.items() if k.startswith("color.")})
     for k in ATTRS:
       scene.m1[k].copy_(sd[f"m1.{k}"]); scene.m2[k].copy_(sd[f"m2.{k}"])
     scene.running_vis.copy_(sd["running_vis"]); scene.opt_step.copy_(sd["opt_step"])

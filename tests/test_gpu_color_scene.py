@@ -108,3 +108,34 @@ def test_batch_accumulation_equals_sum_of_single_image_gradients():
   torch.testing.assert_close(both.g["sh"], singles[0][0] + singles[1][0], rtol=1e-4, atol=1e-9)
   torch.testing.assert_close(both.color.grad, singles[0][1] + singles[1][1], rtol=1e-3, atol=1e-8)
   torch.testing.assert_close(both.color.glo_grad, singles[0][2] + singles[1][2], rtol=1e-3, atol=1e-8)
+
+
+def test_densify_and_checkpoint_keep_the_feature_plane_and_colour_state():
+  scene = _scene(2, reg_weights=(0.0, 0.0, 0.0))
+  cams = _cams(2)
+  gen = torch.Generator(device="cuda").manual_seed(8)
+  target = torch.rand((H, W, 3), device="cuda", generator=gen)
+  tr = Trainer(scene)
+  for it in range(3):
+    tr.training_step([(cams[it % 2], target, it % 2)])
+  # split 50 rows, prune 100 others: children inherit the parent's feature row (reference gaussians/split.py:87-113)
+  keep = torch.ones((N,), device="cuda", dtype=torch.bool)
+  split_idx = torch.arange(200, 250, device="cuda")
+  keep[split_idx] = False
+  keep[1000:1100] = False
+  parents = scene.p["sh"][split_idx].clone()
+  survivor = scene.p["sh"][5].clone()
+  old_n, new_n = scene.split_and_prune(keep, split_idx)
+  assert new_n == N - 150 + 100 and scene.p["sh"].shape == (new_n, 16)
+  assert torch.equal(scene.p["sh"][5], survivor)
+  kids = scene.p["sh"][new_n - 100:].reshape(50, 2, 16)
+  assert torch.equal(kids[:, 0], parents) and torch.equal(kids[:, 1], parents)
+  tr.training_step([(cams[0], target, 0)])  # the resized scene trains on
+  assert torch.isfinite(scene.params).all()
+  # checkpoint round trip: same render, same colour-model state
+  sd = scene.state_dict()
+  clone = SplatScene.from_state_dict(sd)
+  assert clone.color is not None and torch.equal(clone.color.flat, scene.color.flat) and torch.equal(clone.color.glo, scene.color.glo)
+  a = scene.render(cams[1], image_idx=1)["raw"].clone()
+  b = clone.render(cams[1], image_idx=1)["raw"]
+  assert torch.equal(a, b)
