@@ -354,3 +354,19 @@ class Oracle:
                                self.p(position), self.p(cam_pos), self.p(glo), self.p(rw), C.c_int(1), C.c_int(int(half)),
                                self.p(dd), self.p(ds), self.p(d_feature), self.p(d_glo), dptrs)
     return d_feature, d_glo, dict(zip(self.COLOR_WEIGHTS, dW))
+
+  # -- (10) point clustering -------------------------------------------------------
+  def assign_clusters(self, x, centroids):
+    x, c = self.r(x), self.r(centroids)
+    labels = np.zeros(x.shape[0], np.int32)
+    self.lib.gso_assign_clusters(C.c_int64(x.shape[0]), C.c_int(x.shape[1]), C.c_int(c.shape[0]), self.p(x), self.p(c),
+                                 self.p(labels))
+    return labels
+
+  def kmeans(self, x, centroids, iters):
+    """-> (labels of the last assignment (n,) int32, centroids after the last update (k,d))."""
+    x, c = self.r(x), self.r(centroids).copy()
+    labels = np.zeros(x.shape[0], np.int32)
+    self.lib.gso_kmeans(C.c_int64(x.shape[0]), C.c_int(x.shape[1]), C.c_int(c.shape[0]), C.c_int(iters), self.p(x), self.p(c),
+                        self.p(labels))
+    return labels, c
