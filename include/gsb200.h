@@ -429,6 +429,20 @@ int gs_color_mlp_bwd(const gs_color_mlp *h_model, const gs_color_mlp *h_grads, i
                      float w_specular_reg, const float *reg_sums, float *d_feature, float *d_glo, int accumulate,
                      void *stream);
 
+/* ---------------------------------------------------------------------------------------
+ * (10) Point clustering for the view-similarity features: assign_clusters / kmeans_iter, reference
+ *      visibility/cluster.py:139-171 (pykeops argmin of squared distances), used by PointClusters.cluster (:22) on the
+ *      splat positions at every evaluation (trainer/trainer.py:327-370).  1 <= d <= 8, k*d*4 <= 48 KB.
+ *      gs_assign_clusters: labels[i] = argmin_j |x_i - c_j|^2 (ties: lowest j; a NaN centroid is never nearest).
+ *      gs_kmeans: `iters` rounds of (assign, centroid = mean of its points; an emptied cluster becomes NaN = 0/0 like
+ *      the reference).  centroids (k,d): initial values in, final values out; labels: the LAST assignment.
+ *      No host synchronisation; labels equal the CPU oracle's exactly for equal centroids, centroid sums are fp32
+ *      reductions in arbitrary order (as the reference's scatter_add_ on CUDA). */
+size_t gs_kmeans_workspace_bytes(int k, int d);
+int gs_assign_clusters(int64_t n, int d, int k, const float *x, const float *centroids, int32_t *labels, void *stream);
+int gs_kmeans(int64_t n, int d, int k, int iters, const float *x, float *centroids, int32_t *labels, void *workspace,
+              size_t workspace_bytes, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,127 @@
+// cluster.cu — point clustering for the view-similarity features: assign_clusters / kmeans_iter,
+// reference visibility/cluster.py:139-171 (pykeops LazyTensor argmin of ((x_i - c_j)^2).sum(-1)), called by
+// PointClusters.cluster (:22) on the splat positions (1024 clusters, 100 iterations) at every evaluation.
+//
+// assign: one thread per 4 points, all centroids in shared memory (12 KB at 1024 x 3), every centroid read is a
+// broadcast; the squared distance is summed in the reference's order with explicit round-to-nearest mul / add (no FMA
+// contraction), ties go to the lowest index, a NaN centroid is never nearest: labels equal the oracle's bit for bit.
+// update: per-cluster sums by fire-and-forget global fp32 reductions (RED.ADD; fp32 atomics on SHARED memory would be
+// CAS loops) into a k x (d+1) table, then centroid = sum / count (0/0 = NaN for an emptied cluster, like the reference).
+#include "common.cuh"
+
+namespace {
+
+constexpr int KM_THREADS = 256, KM_PTS = 4, KM_MAX_D = 8;
+
+template <int D>
+__global__ void __launch_bounds__(KM_THREADS) k_assign(int64_t n, int k, const float *__restrict__ x,
+                                                       const float *__restrict__ centroids, int32_t *__restrict__ labels,
+                                                       float *__restrict__ sums) {
+  extern __shared__ float sc[];
+  for (int i = threadIdx.x; i < k * D; i += KM_THREADS) sc[i] = centroids[i];
+  __syncthreads();
+  for (int64_t i0 = ((int64_t)blockIdx.x * KM_THREADS + threadIdx.x) * KM_PTS; i0 < n;
+       i0 += (int64_t)gridDim.x * KM_THREADS * KM_PTS) {
+    float p[KM_PTS][D], best[KM_PTS];
+    int bj[KM_PTS];
+#pragma unroll
+    for (int a = 0; a < KM_PTS; ++a) {
+      best[a] = INFINITY; bj[a] = 0;
+#pragma unroll
+      for (int q = 0; q < D; ++q) p[a][q] = (i0 + a < n) ? x[(i0 + a) * D + q] : 0.f;
+    }
+    for (int j = 0; j < k; ++j) {
+      float c[D];
+#pragma unroll
+      for (int q = 0; q < D; ++q) c[q] = sc[j * D + q];
+#pragma unroll
+      for (int a = 0; a < KM_PTS; ++a) {
+        float s = 0.f;
+#pragma unroll
+        for (int q = 0; q < D; ++q) {
+          float t = __fsub_rn(p[a][q], c[q]);
+          s = __fadd_rn(s, __fmul_rn(t, t));
+        }
+        if (s < best[a]) { best[a] = s; bj[a] = j; }
+      }
+    }
+#pragma unroll
+    for (int a = 0; a < KM_PTS; ++a) {
+      if (i0 + a >= n) continue;
+      labels[i0 + a] = bj[a];
+      if (sums) {
+        float *dst = sums + (int64_t)bj[a] * (D + 1);
+#pragma unroll
+        for (int q = 0; q < D; ++q) atomicAdd(dst + q, p[a][q]);
+        atomicAdd(dst + D, 1.0f);
+      }
+    }
+  }
+}
+
+__global__ void k_update(int k, int d, float *__restrict__ centroids, float *__restrict__ sums) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= k) return;
+  float cnt = sums[(int64_t)j * (d + 1) + d];
+  for (int q = 0; q < d; ++q) {
+    centroids[(int64_t)j * d + q] = __fdiv_rn(sums[(int64_t)j * (d + 1) + q], cnt);  // 0/0 = NaN: emptied cluster
+    sums[(int64_t)j * (d + 1) + q] = 0.f;
+  }
+  sums[(int64_t)j * (d + 1) + d] = 0.f;
+}
+
+template <int D>
+int launch_assign(int64_t n, int k, const float *x, const float *centroids, int32_t *labels, float *sums, cudaStream_t st) {
+  int64_t want = (n + KM_THREADS * KM_PTS - 1) / (KM_THREADS * KM_PTS);
+  int grid = (int)(want < 148 * 8 ? want : 148 * 8);
+  k_assign<D><<<grid, KM_THREADS, (size_t)k * D * sizeof(float), st>>>(n, k, x, centroids, labels, sums);
+  return 0;
+}
+
+int dispatch_assign(int64_t n, int d, int k, const float *x, const float *centroids, int32_t *labels, float *sums,
+                    cudaStream_t st) {
+  switch (d) {
+    case 1: return launch_assign<1>(n, k, x, centroids, labels, sums, st);
+    case 2: return launch_assign<2>(n, k, x, centroids, labels, sums, st);
+    case 3: return launch_assign<3>(n, k, x, centroids, labels, sums, st);
+    case 4: return launch_assign<4>(n, k, x, centroids, labels, sums, st);
+    case 5: return launch_assign<5>(n, k, x, centroids, labels, sums, st);
+    case 6: return launch_assign<6>(n, k, x, centroids, labels, sums, st);
+    case 7: return launch_assign<7>(n, k, x, centroids, labels, sums, st);
+    default: return launch_assign<8>(n, k, x, centroids, labels, sums, st);
+  }
+}
+
+}  // namespace
+
+extern "C" size_t gs_kmeans_workspace_bytes(int k, int d) { return gs_align256((size_t)k * (d + 1) * sizeof(float)); }
+
+extern "C" int gs_assign_clusters(int64_t n, int d, int k, const float *x, const float *centroids, int32_t *labels,
+                                  void *stream) {
+  GS_REQUIRE(x && centroids && labels, "null argument");
+  GS_REQUIRE(d >= 1 && d <= KM_MAX_D && k >= 1 && (size_t)k * d * sizeof(float) <= 48 * 1024, "1 <= d <= 8, k*d*4 <= 48 KB");
+  if (n <= 0) return GS_OK;
+  dispatch_assign(n, d, k, x, centroids, labels, nullptr, (cudaStream_t)stream);
+  GS_LAUNCH_CHECK();
+  return GS_OK;
+}
+
+extern "C" int gs_kmeans(int64_t n, int d, int k, int iters, const float *x, float *centroids, int32_t *labels,
+                         void *workspace, size_t workspace_bytes, void *stream) {
+  GS_REQUIRE(x && centroids && labels && workspace, "null argument");
+  GS_REQUIRE(d >= 1 && d <= KM_MAX_D && k >= 1 && (size_t)k * d * sizeof(float) <= 48 * 1024, "1 <= d <= 8, k*d*4 <= 48 KB");
+  if (workspace_bytes < gs_kmeans_workspace_bytes(k, d)) {
+    gs_set_error("gs_kmeans: workspace too small");
+    return GS_ERR_WORKSPACE;
+  }
+  if (n <= 0 || iters <= 0) return GS_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  float *sums = (float *)workspace;
+  GS_CUDA(cudaMemsetAsync(sums, 0, (size_t)k * (d + 1) * sizeof(float), st));
+  for (int it = 0; it < iters; ++it) {  // stream-ordered, no host synchronisation between iterations
+    dispatch_assign(n, d, k, x, centroids, labels, sums, st);
+    k_update<<<gs_div_up(k, 128), 128, 0, st>>>(k, d, centroids, sums);
+  }
+  GS_LAUNCH_CHECK();
+  return GS_OK;
+}

@@ -93,6 +93,9 @@ SIGNATURES = {
   "gs_color_mlp_fwd": (_I, [C.POINTER(ColorMLP), _L, _P, _I, _P, _P, C.POINTER(C.c_float), _P, _F, _P, _P, _P]),
   "gs_color_mlp_bwd": (_I, [C.POINTER(ColorMLP), C.POINTER(ColorMLP), _L, _P, _I, _P, _P, C.POINTER(C.c_float), _P, _F, _P, _I,
                              _F, _P, _P, _P, _I, _P]),
+  "gs_kmeans_workspace_bytes": (_Z, [_I, _I]),
+  "gs_assign_clusters": (_I, [_L, _I, _I, _P, _P, _P, _P]),
+  "gs_kmeans": (_I, [_L, _I, _I, _I, _P, _P, _P, _P, _Z, _P]),
   "gs_optim_step_groups": (_I, [_OPT, _L, _P, _P, _I, C.POINTER(OptimGroup), _P, _P, _P, _I, _P]),
   "gs_optim_step": (_I, [_OPT, _I, _L, _P, _P, _I, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _F, _F, _I, _P]),
   "gs_accumulate_stats": (_I, [_L, _P, _P, _P, _I, _P, _I, _F, _F, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P]),

@@ -486,3 +486,28 @@ def color_mlp_bwd(model, grads, feature, position, cam_pos, glo, row_w, d_rgb, d
                                     L.ptr(_f32(feature)), L.ptr(_f32(position)), _cam_pos3(cam_pos), L.ptr(_f32(glo)),
                                     float(specular_weight), d_rgb.data_ptr(), d_rgb.stride(0), float(w_specular_reg),
                                     L.ptr(reg_sums), L.ptr(d_feature), L.ptr(d_glo), int(accumulate), L.stream()))
+
+
+# ---- point clustering (include/gsb200.h section 10) -----------------------------------------------------------------
+def assign_clusters(x, centroids):
+  """reference visibility/cluster.py:139-148: nearest centroid of every point -> (n,) int32."""
+  n, d = x.shape
+  labels = torch.empty((n,), device=x.device, dtype=torch.int32)
+  L.check(L.load().gs_assign_clusters(n, d, centroids.shape[0], L.ptr(_f32(x)), L.ptr(_f32(centroids)), L.ptr(labels),
+                                      L.stream()))
+  return labels
+
+
+def kmeans(x, k=None, iters=100, centroids=None, generator=None):
+  """reference visibility/cluster.py:150-180: kmeans(x, k, iters) -> (labels (n,) int32, centroids (k,d)).
+  centroids: initial values (copied); None draws k distinct points with torch.randperm like the reference."""
+  n, d = x.shape
+  if centroids is None:
+    centroids = x[torch.randperm(n, device=x.device, generator=generator)[:k]]
+  centroids = _f32(centroids).clone().contiguous()
+  k = centroids.shape[0]
+  labels = torch.empty((n,), device=x.device, dtype=torch.int32)
+  nbytes = int(L.load().gs_kmeans_workspace_bytes(k, d))
+  ws = torch.empty((nbytes,), device=x.device, dtype=torch.uint8)
+  L.check(L.load().gs_kmeans(n, d, k, iters, L.ptr(_f32(x)), L.ptr(centroids), L.ptr(labels), L.ptr(ws), nbytes, L.stream()))
+  return labels, centroids
