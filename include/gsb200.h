@@ -443,6 +443,15 @@ int gs_assign_clusters(int64_t n, int d, int k, const float *x, const float *cen
 int gs_kmeans(int64_t n, int d, int k, int iters, const float *x, float *centroids, int32_t *labels, void *workspace,
               size_t workspace_bytes, void *stream);
 
+/* estimate_scale (reference gaussians/loading.py:45-61, pykeops Kmin over all N x N distances): scales[i] = mean
+ * distance from points[i] to its num_neighbors (1..8) nearest neighbours, computed as the reference does (the
+ * num_neighbors + 1 smallest squared distances to ALL points, the smallest — self — dropped, sqrt, mean).  Uniform grid +
+ * growing shell search; results equal the brute-force oracle bit for bit.  One host read (the bounding box): an
+ * initialisation-time call (initial log_scaling, gaussians/loading.py:23-34). */
+size_t gs_knn_scale_workspace_bytes(int64_t n);
+int gs_knn_scale(int64_t n, const float *points, int num_neighbors, float *scales, void *workspace,
+                 size_t workspace_bytes, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

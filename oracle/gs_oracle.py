@@ -370,3 +370,10 @@ class Oracle:
     self.lib.gso_kmeans(C.c_int64(x.shape[0]), C.c_int(x.shape[1]), C.c_int(c.shape[0]), C.c_int(iters), self.p(x), self.p(c),
                         self.p(labels))
     return labels, c
+
+  # -- (11) estimate_scale ----------------------------------------------------------
+  def knn_scale(self, points, num_neighbors=3):
+    pts = self.r(points)
+    out = np.zeros(pts.shape[0], self.real)
+    self.lib.gso_knn_scale(C.c_int64(pts.shape[0]), self.p(pts), C.c_int(num_neighbors), self.p(out))
+    return out

@@ -511,3 +511,14 @@ def kmeans(x, k=None, iters=100, centroids=None, generator=None):
   ws = torch.empty((nbytes,), device=x.device, dtype=torch.uint8)
   L.check(L.load().gs_kmeans(n, d, k, iters, L.ptr(_f32(x)), L.ptr(centroids), L.ptr(labels), L.ptr(ws), nbytes, L.stream()))
   return labels, centroids
+
+
+def estimate_scale(points, num_neighbors=3):
+  """reference gaussians/loading.py:45-61: mean distance to the num_neighbors nearest neighbours -> (n,) float32."""
+  n = points.shape[0]
+  assert points.shape[1] == 3
+  scales = torch.empty((n,), device=points.device, dtype=torch.float32)
+  nbytes = int(L.load().gs_knn_scale_workspace_bytes(n))
+  ws = torch.empty((nbytes,), device=points.device, dtype=torch.uint8)
+  L.check(L.load().gs_knn_scale(n, L.ptr(_f32(points)), num_neighbors, L.ptr(scales), L.ptr(ws), nbytes, L.stream()))
+  return scales

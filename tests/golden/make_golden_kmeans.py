@@ -37,6 +37,9 @@ class LazyTensor:
   def argmin(self, dim):
     return self.f().argmin(dim=dim)
 
+  def Kmin(self, k, dim):
+    return torch.topk(self.f(), k, dim=dim, largest=False, sorted=True).values
+
 
 def extract(path, names, env):
   tree = ast.parse(open(os.path.join(REF, path)).read())
@@ -69,6 +72,16 @@ def main():
   probe = torch.randn((500, 3), generator=gen) * 4
   good = torch.from_numpy(out["centroids_10"])
   out.update(probe=probe.numpy(), probe_labels=env["assign_clusters"](probe, good).numpy().astype(np.int32), probe_centroids=good.numpy())
+  # estimate_scale (gaussians/loading.py:45-61) on a clumpy cloud with a duplicate and an outlier
+  env2 = extract("gaussians/loading.py", {"estimate_scale"}, dict(torch=torch, LazyTensor=LazyTensor))
+  pts = x[:1500].clone()
+  pts[1499] = torch.tensor([60.0, -45.0, 30.0])
+
+  class Cloud:
+    points = pts
+  for nn in (3, 5):
+    out[f"knn_scale_{nn}"] = env2["estimate_scale"](Cloud, nn).numpy()
+  out["knn_points"] = pts.numpy()
   np.savez_compressed(os.path.join(OUT, "kmeans.npz"), **out)
   print({k_: v.shape for k_, v in out.items()}, "empty clusters:", int(np.isnan(out["centroids_10"]).any(axis=1).sum()))
 

@@ -78,3 +78,45 @@ def test_bad_arguments_are_refused():
   x = torch.zeros((10, 9), device="cuda")
   with pytest.raises(L.GsError):
     ops.assign_clusters(x, torch.zeros((4, 9), device="cuda"))
+
+
+def test_estimate_scale_matches_reference_golden():
+  for nn in (3, 5):
+    ours = npy(ops.estimate_scale(cu(G["knn_points"]), nn))
+    np.testing.assert_allclose(ours, G[f"knn_scale_{nn}"], rtol=2e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("n,kind", [(2, "uniform"), (5, "uniform"), (4000, "uniform"), (6000, "clumps"), (3000, "plane"),
+                                    (2500, "outliers"), (3000, "duplicates")])
+def test_estimate_scale_bit_exact_vs_brute_force_oracle(n, kind):
+  rng = np.random.default_rng(n)
+  if kind == "uniform":
+    p = rng.uniform(-3, 3, (n, 3))
+  elif kind == "clumps":
+    p = rng.normal(0, 4, (10, 3))[rng.integers(0, 10, n)] + rng.normal(0, 0.05, (n, 3))
+  elif kind == "plane":
+    p = np.concatenate([rng.uniform(-5, 5, (n, 2)), np.zeros((n, 1))], axis=1)
+  elif kind == "outliers":
+    p = rng.normal(0, 1, (n, 3)); p[:5] = rng.uniform(200, 400, (5, 3)) * np.array([1, -1, 1])
+  else:
+    p = rng.uniform(-2, 2, (n, 3)); p[n // 2:] = p[:n - n // 2]
+  p = p.astype(np.float32)
+  ours = npy(ops.estimate_scale(cu(p), 3))
+  ref = go.Oracle("f32").knn_scale(p, 3)
+  # the k+1 smallest squared distances are the same multiset; sqrt/mean on the GPU are correctly rounded like libm's
+  np.testing.assert_allclose(ours, ref, rtol=3e-7, atol=0)
+  if n > 10:
+    assert (ours == ref).mean() > 0.99
+
+
+def test_estimate_scale_at_scale_sanity():
+  gen = torch.Generator(device="cuda").manual_seed(1)
+  n = 1_000_000
+  p = torch.rand((n, 3), device="cuda", generator=gen)
+  s = ops.estimate_scale(p, 3)
+  # uniform density n per unit volume: mean distance to the 3 nearest neighbours ~ 0.74 * n^(-1/3)
+  assert torch.isfinite(s).all()
+  assert 0.6 < s.mean().item() * n ** (1 / 3) < 0.9
+  sub = torch.arange(0, n, 5000, device="cuda")
+  d = torch.cdist(p[sub], p, compute_mode="donot_use_mm_for_euclid_dist").topk(4, dim=1, largest=False).values[:, 1:].mean(dim=1)
+  torch.testing.assert_close(s[sub], d, rtol=1e-4, atol=1e-6)

@@ -29,3 +29,12 @@ def test_emptied_cluster_is_nan_and_never_nearest():
   labels, cent = orc.kmeans(G["x"], init, 3)
   assert np.isnan(cent[5]).all() and not (labels == 5).any()
   assert np.isfinite(np.delete(cent, 5, axis=0)).all()
+
+
+def test_knn_scale_matches_reference_estimate_scale():
+  orc = go.Oracle("f32")
+  for nn in (3, 5):
+    ours = orc.knn_scale(G["knn_points"], nn)
+    # the reference's dense expression sums (x-y)^2 over the last axis with torch's reduction; same values up to 1 ulp
+    np.testing.assert_allclose(ours, G[f"knn_scale_{nn}"], rtol=2e-6, atol=1e-7)
+  assert ours[7] < 1e-3 or ours[100] < ours.mean(), "the duplicated point has a zero-distance neighbour"
