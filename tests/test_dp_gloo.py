@@ -156,3 +156,43 @@ def test_record_pointers_follow_image_order():
       return 500
   ex.gathered = G()
   assert ex.record_ptrs() == [500, 500 + 2000, 500 + 4000, 500 + 1000, 500 + 3000, 500 + 5000]
+
+
+def _color_grads(rank, step):
+  """rank-specific gradients of the replicated colour model: dense weight gradient + one GLO row per rank."""
+  g = torch.Generator().manual_seed(100 + rank + 10 * step)
+  return torch.randn((10088,), generator=g) * 1e-2, rank + 1, torch.randn((32,), generator=g) * 1e-2
+
+
+def color_worker(rank, world, port, out):
+  os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+  dist.init_process_group("gloo", rank=rank, world_size=world)
+  from gsb200.color import ColorModule
+  cm = ColorModule(4, device="cpu", seed=3)
+  for step in range(2):
+    dense, row, glo = _color_grads(rank, step)
+    cm.grad.copy_(dense)
+    cm.glo_grad_row(row).copy_(glo)
+    cm.all_reduce(dist)
+    cm.step()
+  torch.save(dict(flat=cm.flat, glo=cm.glo), os.path.join(out, f"color{rank}.pt"))
+  dist.destroy_process_group()
+
+
+def test_replicated_colour_model_stays_identical_under_dp(tmp_path):
+  """Trainer.exchange_gradients sums the colour model's dense gradients and GLO rows over the ranks (SUM, like the
+  splat gradients): every replica then takes the same Adam step as one process holding the summed gradients."""
+  world = 2
+  mp.spawn(color_worker, args=(world, free_port(), str(tmp_path)), nprocs=world, join=True)
+  r = [torch.load(os.path.join(tmp_path, f"color{k}.pt")) for k in range(world)]
+  assert torch.equal(r[0]["flat"], r[1]["flat"]) and torch.equal(r[0]["glo"], r[1]["glo"])
+  from gsb200.color import ColorModule
+  cm = ColorModule(4, device="cpu", seed=3)
+  for step in range(2):
+    for rank in range(world):
+      dense, row, glo = _color_grads(rank, step)
+      cm.grad.add_(dense)
+      cm.glo_grad_row(row).add_(glo)
+    cm.step()
+  assert torch.allclose(r[0]["flat"], cm.flat, rtol=0, atol=1e-5) and torch.allclose(r[0]["glo"], cm.glo, rtol=0, atol=1e-5)
+  assert r[0]["glo"][1].abs().max() > 0 and r[0]["glo"][2].abs().max() > 0 and not r[0]["glo"][0].any() and not r[0]["glo"][3].any()
