@@ -49,7 +49,7 @@ def parse():
 def measured_traffic(stage):
   """dram__bytes_read.sum + dram__bytes_write.sum of the stage's kernels per image from the committed ncu --set full
   capture of this same command (profiles/: cold-cache, serialised launches), or None."""
-  path = os.path.join(ROOT, "profiles", "r1k_traffic.json")
+  path = os.path.join(ROOT, "profiles", "r1p_traffic.json")
   try:
     with open(path) as f:
       return json.load(f)["dram_bytes_per_image"].get(stage)
@@ -367,7 +367,7 @@ def run_b200(args):
       "stages_ms": stages, "host_enqueue_ms_per_step": host_enqueue_ms,
       "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
                    "traffic": measured_traffic(dom) if args.workload == "c2" and not args.points else None,
-                   "traffic_source": "profiles/r1k_traffic.json (ncu --set full of the c2 command)",
+                   "traffic_source": "profiles/r1p_traffic.json (ncu --set full of the c2 command)",
                    "peak_source": which, "algorithmic_bytes": bytes_[dom],
                    "iteration": {"algorithmic_bytes": iter_bytes, "achieved": iter_bytes / (ms_step * 1e-3) / 1e9,
                                  "frac": iter_bytes / (ms_step * 1e-3) / 1e9 / hbm}},

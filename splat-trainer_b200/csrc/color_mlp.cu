@@ -182,45 +182,6 @@ __device__ __forceinline__ float stage_row(StageT &st, int lane, bool valid, int
   return inv;
 }
 
-// GLU layer + output layer of one MLP for one 16-row tile: A = input fragments (3 k-steps of 16).
-// Leaves the fp16-rounded outputs (4 valid columns) in st.o[which].
-__device__ __forceinline__ void mlp_tile(const __half *__restrict__ w1, const float *__restrict__ b1,
-                                         const __half *__restrict__ w2, const float *__restrict__ b2, float *__restrict__ out,
-                                         int r0, int g, int t, const uint32_t (&A)[3][4]) {
-  uint32_t A2[2][4];
-#pragma unroll
-  for (int j = 0; j < 2; ++j) {
-#pragma unroll
-    for (int q = 0; q < 2; ++q) {
-      int col = 8 * (2 * j + q) + 2 * t;
-      float ca[4] = {b1[col], b1[col + 1], b1[col], b1[col + 1]};
-      float cb[4] = {b1[H + col], b1[H + col + 1], b1[H + col], b1[H + col + 1]};
-#pragma unroll
-      for (int ks = 0; ks < 3; ++ks) {
-        uint32_t b0, b1r;
-        load_b(b0, b1r, w1, KP, 8 * (2 * j + q), 16 * ks, g, t);
-        mma16816(ca, A[ks], b0, b1r);
-        load_b(b0, b1r, w1, KP, H + 8 * (2 * j + q), 16 * ks, g, t);
-        mma16816(cb, A[ks], b0, b1r);
-      }
-      // nn.GLU on the fp16 layer output: first half * sigmoid(second half), rounded to fp16
-      A2[j][2 * q] = pack2(hr(ca[0]) * sigmoidf(hr(cb[0])), hr(ca[1]) * sigmoidf(hr(cb[1])));
-      A2[j][2 * q + 1] = pack2(hr(ca[2]) * sigmoidf(hr(cb[2])), hr(ca[3]) * sigmoidf(hr(cb[3])));
-    }
-  }
-  float co[4] = {b2[2 * t], b2[2 * t + 1], b2[2 * t], b2[2 * t + 1]};  // b2 is zero padded to 8
-#pragma unroll
-  for (int j = 0; j < 2; ++j) {
-    uint32_t b0, b1r;
-    load_b(b0, b1r, w2, HP, 0, 16 * j, g, t);
-    mma16816(co, A2[j], b0, b1r);
-  }
-  if (t < 2) {
-    *reinterpret_cast<float2 *>(out + (r0 + g) * 8 + 2 * t) = make_float2(hr(co[0]), hr(co[1]));
-    *reinterpret_cast<float2 *>(out + (r0 + g + 8) * 8 + 2 * t) = make_float2(hr(co[2]), hr(co[3]));
-  }
-}
-
 // direction encoder + affine modulation for one 16-row tile: AX = fragments of x = f * a + b, (a, b) = Wsh Y + bsh
 template <bool SAVE, typename StageT>
 __device__ __forceinline__ void affine_tile(const Weights &W, StageT &st, int r0, int g, int t, uint32_t (&AX)[3][4],
@@ -257,8 +218,10 @@ __device__ __forceinline__ void affine_tile(const Weights &W, StageT &st, int r0
   }
 }
 
-// The same two steps for BOTH 16-row tiles of a warp's 32 rows at once: every weight fragment is loaded once and feeds two
-// independent accumulator chains (half the shared-memory traffic, twice the MMAs in flight).
+// GLU layer + output layer of one MLP (and, below, the affine step) for BOTH 16-row tiles of a warp's 32 rows at once:
+// every weight fragment is loaded once and feeds two independent accumulator chains (half the shared-memory traffic,
+// twice the MMAs in flight).  A = input fragments (3 k-steps of 16 per tile); the fp16-rounded outputs (4 valid columns)
+// go to `out` (32 x 8 floats).
 __device__ __forceinline__ void mlp_tile2(const __half *__restrict__ w1, const float *__restrict__ b1,
                                           const __half *__restrict__ w2, const float *__restrict__ b2, float *__restrict__ out,
                                           int g, int t, const uint32_t (&A)[2][3][4]) {
@@ -671,16 +634,16 @@ __global__ void __launch_bounds__(CM_THREADS, 1) k_color_bwd(ColorDev m, ColorGr
         }
       }
       __syncwarp();
-      // forward (outputs only)
-#pragma unroll 1
-      for (int mt = 0; mt < 2; ++mt) {
-        int r0 = 16 * mt;
-        uint32_t A[3][4];
+      // forward (outputs only), both 16-row tiles at once like k_color_fwd
+      {
+        uint32_t A[2][3][4];
 #pragma unroll
-        for (int ks = 0; ks < 3; ++ks) load_a(A[ks], st.xh, KP, r0, 16 * ks, g, t);
-        mlp_tile(W.w1b, W.b1b, W.w2b, W.b2b, st.o[0], r0, g, t, A);
-        affine_tile<false>(W, st, r0, g, t, A);
-        mlp_tile(W.w1d, W.b1d, W.w2d, W.b2d, st.o[1], r0, g, t, A);
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+          for (int ks = 0; ks < 3; ++ks) load_a(A[mt][ks], st.xh, KP, 16 * mt, 16 * ks, g, t);
+        mlp_tile2(W.w1b, W.b1b, W.w2b, W.b2b, st.o[0], g, t, A);
+        affine_tile2(W, st, g, t, A);
+        mlp_tile2(W.w1d, W.b1d, W.w2d, W.b2d, st.o[1], g, t, A);
       }
       __syncwarp();
       // lane = row: gradient at the MLP outputs through luminance_activation
