@@ -45,6 +45,9 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
   __half2 h = __floats2half2_rn(a, b);
   return *reinterpret_cast<uint32_t *>(&h);
 }
+// two values rounded to fp16 and back with ONE packed conversion each way (the scalar conversions issue on the quarter-rate
+// conversion pipe; the packed forms do not)
+__device__ __forceinline__ float2 hr2(float a, float b) { return __half22float2(__floats2half2_rn(a, b)); }
 __device__ __forceinline__ float sigmoidf(float v) { return __fdividef(1.0f, 1.0f + __expf(-v)); }
 
 __device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
@@ -249,8 +252,10 @@ __device__ __forceinline__ void mlp_tile2(const __half *__restrict__ w1, const f
       }
 #pragma unroll
       for (int mt = 0; mt < 2; ++mt) {
-        A2[mt][j][2 * q] = pack2(hr(ca[mt][0]) * sigmoidf(hr(cb[mt][0])), hr(ca[mt][1]) * sigmoidf(hr(cb[mt][1])));
-        A2[mt][j][2 * q + 1] = pack2(hr(ca[mt][2]) * sigmoidf(hr(cb[mt][2])), hr(ca[mt][3]) * sigmoidf(hr(cb[mt][3])));
+        float2 a01 = hr2(ca[mt][0], ca[mt][1]), a23 = hr2(ca[mt][2], ca[mt][3]);
+        float2 b01 = hr2(cb[mt][0], cb[mt][1]), b23 = hr2(cb[mt][2], cb[mt][3]);
+        A2[mt][j][2 * q] = pack2(a01.x * sigmoidf(b01.x), a01.y * sigmoidf(b01.y));
+        A2[mt][j][2 * q + 1] = pack2(a23.x * sigmoidf(b23.x), a23.y * sigmoidf(b23.y));
       }
     }
   }
@@ -267,8 +272,8 @@ __device__ __forceinline__ void mlp_tile2(const __half *__restrict__ w1, const f
   if (t < 2) {
 #pragma unroll
     for (int mt = 0; mt < 2; ++mt) {
-      *reinterpret_cast<float2 *>(out + (16 * mt + g) * 8 + 2 * t) = make_float2(hr(co[mt][0]), hr(co[mt][1]));
-      *reinterpret_cast<float2 *>(out + (16 * mt + g + 8) * 8 + 2 * t) = make_float2(hr(co[mt][2]), hr(co[mt][3]));
+      *reinterpret_cast<float2 *>(out + (16 * mt + g) * 8 + 2 * t) = hr2(co[mt][0], co[mt][1]);
+      *reinterpret_cast<float2 *>(out + (16 * mt + g + 8) * 8 + 2 * t) = hr2(co[mt][2], co[mt][3]);
     }
   }
 }
@@ -305,8 +310,10 @@ __device__ __forceinline__ void affine_tile2(const Weights &W, StageT &st, int g
       for (int mt = 0; mt < 2; ++mt) {
         float2 lo = *reinterpret_cast<const float2 *>(st.xf + (16 * mt + g) * KP + col);
         float2 hi = *reinterpret_cast<const float2 *>(st.xf + (16 * mt + g + 8) * KP + col);
-        AX[mt][j][2 * q] = pack2(lo.x * hr(ca[mt][0]) + hr(cb[mt][0]), lo.y * hr(ca[mt][1]) + hr(cb[mt][1]));
-        AX[mt][j][2 * q + 1] = pack2(hi.x * hr(ca[mt][2]) + hr(cb[mt][2]), hi.y * hr(ca[mt][3]) + hr(cb[mt][3]));
+        float2 a01 = hr2(ca[mt][0], ca[mt][1]), a23 = hr2(ca[mt][2], ca[mt][3]);
+        float2 b01 = hr2(cb[mt][0], cb[mt][1]), b23 = hr2(cb[mt][2], cb[mt][3]);
+        AX[mt][j][2 * q] = pack2(lo.x * a01.x + b01.x, lo.y * a01.y + b01.y);
+        AX[mt][j][2 * q + 1] = pack2(hi.x * a23.x + b23.x, hi.y * a23.y + b23.y);
       }
     }
   }

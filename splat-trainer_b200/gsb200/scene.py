@@ -147,7 +147,11 @@ class SplatScene:
     return self.n
 
   def gaussians(self):
-    return {k: v.clone() for k, v in self.p.items()}
+    """copies of the parameter planes; the last one is named `feature` for an MLP colour scene (gsb200.io with_sh=False)."""
+    out = {k: v.clone() for k, v in self.p.items()}
+    if self.color is not None:
+      out["feature"] = out.pop("sh")
+    return out
 
   # ---- per-image work buffers --------------------------------------------------------------------------
   def _buffers(self, cam):
