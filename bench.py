@@ -40,6 +40,9 @@ def parse():
   ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
   ap.add_argument("--points", type=int, default=0, help="override the splat count (testing only)")
   ap.add_argument("--no-cpu-baseline", action="store_true")
+  ap.add_argument("--scene", default="sh", choices=["sh", "mlp"],
+                  help="sh: SH colour per splat (BASELINE.json's configuration); mlp: the reference's default `scene: mlp` "
+                       "colour path (point feature 16 + GLO 32 -> ColorModel), same geometry (SURVEY 8f-2; no CPU baseline)")
   ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl", "dense", "local"],
                   help="N>1 gradient/statistics exchange: per-image records over peer memory (auto/peer), records "
                        "all-gathered by NCCL, or the dense SUM all-reduce of the packed gradient buffer")
@@ -243,7 +246,12 @@ def run_b200(args):
   del tgt_scene
   torch.cuda.empty_cache()
   dev_targets = [t.cuda() for t in host_targets]
-  scene = SplatScene(g, SceneConfig(sh_degree=deg))
+  if args.scene == "mlp":
+    gm = {k: v for k, v in g.items() if k != "sh"}
+    gm["feature"] = np.random.default_rng(7).normal(0, 1, (n, 16)).astype(np.float32)
+    scene = SplatScene(gm, SceneConfig(sh_degree=deg, color_mlp=True, num_images=VIEWS_PER_RANK * world))
+  else:
+    scene = SplatScene(g, SceneConfig(sh_degree=deg))
   if args.exchange == "local":  # N=1 only: run the pack/fold kernels of the DP exchange on one GPU (for profiling them)
     from gsb200.exchange import ImageExchange
     local_k = int(os.environ.get("GS_LOCAL_IMAGES", "1"))  # K different images per step packed + folded on one GPU
@@ -257,6 +265,8 @@ def run_b200(args):
       return [(lcams[(i + q) % len(lcams)], targets[(i + q) % len(targets)]) for q in range(trainer.exchange.k)]
     b = [None] * world
     b[rank] = (lcams[i % len(lcams)], targets[i % len(targets)])
+    if args.scene == "mlp":  # the image's GLO row
+      b[rank] = b[rank] + (rank + world * (i % len(lcams)),)
     return b
 
   def step(i, targets, read_loss=False):
@@ -333,7 +343,7 @@ def run_b200(args):
   O = int(counters[0])
   V = int((w["g2d"][:, 5] > 0).sum().item())
   v_opt = int(scene._vis_idx.count.item())  # rows the last optimiser step touched (device-side visible.nonzero())
-  P, T, D = W * H, ((W + 15) // 16) * ((H + 15) // 16), 11 + 3 * (deg + 1) ** 2
+  P, T, D = W * H, ((W + 15) // 16) * ((H + 15) // 16), 11 + (16 if args.scene == "mlp" else 3 * (deg + 1) ** 2)
   bytes_ = algorithmic_bytes(n, D, V, O, P, T, v_opt)
   hbm, which = peaks()
   dom = max(("raster_fwd", "raster_bwd", "tile_map", "project_fwd", "project_bwd", "optim"), key=lambda k: stages.get(k, 0.0))
@@ -360,13 +370,13 @@ def run_b200(args):
       "raster_fwd_bwd_mpix_per_sec": world * P / ((stages["raster_fwd"] + stages["raster_bwd"]) * 1e-3) / 1e6,
       "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
       "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-      "config": {"workload": f"{args.workload}: {n} splats SH{deg} {W}x{H}, camera batch = {world} (1 image per GPU per step), "
+      "config": {"workload": f"{args.workload}: {n} splats {'MLP colour (feature 16 + GLO 32)' if args.scene == 'mlp' else f'SH{deg}'} {W}x{H}, camera batch = {world} (1 image per GPU per step), "
                              "fwd + loss (MSE 10 + 3-level SSIM 1.0 + reg) + bwd + fused visibility-aware LaProp step", "images_per_step": world,
                  "l2": f"inputs larger than L2 (params+grads+moments {4 * 4 * D * n / 1e9:.1f} GB, overlap list {4 * O / 1e6:.0f} MB)",
                  "parallelism": f"dp{world}", "V_in_view": V, "O_overlaps": O, "V_optimised": v_opt, "overflow": overflow},
       "stages_ms": stages, "host_enqueue_ms_per_step": host_enqueue_ms,
       "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                   "traffic": measured_traffic(dom) if args.workload == "c2" and not args.points else None,
+                   "traffic": measured_traffic(dom) if args.workload == "c2" and not args.points and args.scene == "sh" else None,
                    "traffic_source": "profiles/r1p_traffic.json (ncu --set full of the c2 command)",
                    "peak_source": which, "algorithmic_bytes": bytes_[dom],
                    "iteration": {"algorithmic_bytes": iter_bytes, "achieved": iter_bytes / (ms_step * 1e-3) / 1e9,
@@ -381,7 +391,7 @@ def run_b200(args):
       if trainer.exchange is not None:
         exchange_info["overflow"] = any(o for _, o in trainer.exchange.counts())
       line["exchange"] = exchange_info
-    if world == 1 and not args.no_cpu_baseline:
+    if world == 1 and not args.no_cpu_baseline and args.scene == "sh":
       cpu = CpuIteration(g, views[:1], [host_targets[0].numpy()], deg)
       cpu.iteration(0)  # warm-up (page faults, OpenMP pool)
       t0 = time.perf_counter()

@@ -452,6 +452,13 @@ size_t gs_knn_scale_workspace_bytes(int64_t n);
 int gs_knn_scale(int64_t n, const float *points, int num_neighbors, float *scales, void *workspace,
                  size_t workspace_bytes, void *stream);
 
+/* torch.optim.Adam's update on a dense fp32 array in one launch (the colour MLP's weights, reference
+ * scene/color_model.py:162-170, betas (0.9, 0.999); a GLO row an image touched, :37-44, betas (0.8, 0.95)):
+ * m = b1 m + (1-b1) g; v = b2 v + (1-b2) g^2; p -= lr/(1-b1^step) * m / (sqrt(v/(1-b2^step)) + eps); step >= 1.
+ * zero_grad != 0 clears grad. */
+int gs_adam_step(int64_t n, float *param, float *grad, float *exp_avg, float *exp_avg_sq, float lr, float beta1,
+                 float beta2, float eps, int step, int zero_grad, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -848,3 +848,33 @@ extern "C" int gs_color_mlp_bwd(const gs_color_mlp *h_model, const gs_color_mlp 
   GS_LAUNCH_CHECK();
   return GS_OK;
 }
+
+// Dense Adam for the small replicated state around the colour path (ten weight arrays = 10 088 floats, one GLO row = 32
+// floats): torch.optim.Adam's update (reference ColorModel.optimizer, scene/color_model.py:162-170, and the GLO table's
+// SparseAdam on the rows an image touched, :37-44) in ONE launch instead of ~10 elementwise ones.
+namespace {
+__global__ void __launch_bounds__(256) k_adam(int64_t n, float *__restrict__ p, float *__restrict__ g, float *__restrict__ m,
+                                              float *__restrict__ v, float lr_over_bc1, float b1, float b2, float inv_bc2,
+                                              float eps, int zero_grad) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float gi = g[i];
+  float mi = b1 * m[i] + (1.0f - b1) * gi;
+  float vi = b2 * v[i] + (1.0f - b2) * gi * gi;
+  m[i] = mi; v[i] = vi;
+  p[i] -= lr_over_bc1 * mi / (sqrtf(vi * inv_bc2) + eps);
+  if (zero_grad) g[i] = 0.f;
+}
+}  // namespace
+
+extern "C" int gs_adam_step(int64_t n, float *param, float *grad, float *exp_avg, float *exp_avg_sq, float lr, float beta1,
+                            float beta2, float eps, int step, int zero_grad, void *stream) {
+  GS_REQUIRE(param && grad && exp_avg && exp_avg_sq, "null argument");
+  GS_REQUIRE(step >= 1, "step counts from 1");
+  if (n <= 0) return GS_OK;
+  double bc1 = 1.0 - pow((double)beta1, step), bc2 = 1.0 - pow((double)beta2, step);
+  k_adam<<<gs_div_up(n, 256), 256, 0, (cudaStream_t)stream>>>(n, param, grad, exp_avg, exp_avg_sq, (float)(lr / bc1), beta1, beta2,
+                                                            (float)(1.0 / bc2), eps, zero_grad);
+  GS_LAUNCH_CHECK();
+  return GS_OK;
+}

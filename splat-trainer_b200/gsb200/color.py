@@ -46,7 +46,7 @@ class ColorModule:
     self.glo = torch.zeros((max(num_images, 1), GLO_FEATURES), device=self.device)
     self.glo_grad = torch.zeros_like(self.glo)
     self.glo_m, self.glo_v = torch.zeros_like(self.glo), torch.zeros_like(self.glo)
-    self.glo_steps = torch.zeros((self.glo.shape[0],), device=self.device)
+    self.glo_steps = [0] * self.glo.shape[0]  # per-row step counts (host side: they only feed the bias corrections)
     self._zero_glo = torch.zeros((GLO_FEATURES,), device=self.device)
     self._touched = set()
     self.lr, self.lr_glo, self.specular_reg = lr, lr_glo, specular_reg
@@ -76,38 +76,41 @@ class ColorModule:
 
   def step(self):
     """Adam on the MLP weights (betas (0.9, 0.999), eps 1e-8) and on the GLO rows touched since the last step
-    (betas (0.8, 0.95)); clears the gradients."""
+    (betas (0.8, 0.95)); clears the gradients.  One launch for the weights, one per touched GLO row."""
     self.steps += 1
-    b1, b2, eps = 0.9, 0.999, 1e-8
-    self.exp_avg.mul_(b1).add_(self.grad, alpha=1 - b1)
-    self.exp_avg_sq.mul_(b2).addcmul_(self.grad, self.grad, value=1 - b2)
-    denom = (self.exp_avg_sq / (1 - b2 ** self.steps)).sqrt_().add_(eps)
-    self.flat.addcdiv_(self.exp_avg, denom, value=-self.lr / (1 - b1 ** self.steps))
-    self.grad.zero_()
-    if self._touched:
-      rows = torch.tensor(sorted(self._touched), device=self.device)
-      b1, b2 = 0.8, 0.95
-      g = self.glo_grad[rows]
-      self.glo_steps[rows] += 1
-      t = self.glo_steps[rows].unsqueeze(1)
-      m = self.glo_m[rows] * b1 + g * (1 - b1)
-      v = self.glo_v[rows] * b2 + g * g * (1 - b2)
-      self.glo_m[rows], self.glo_v[rows] = m, v
-      self.glo[rows] -= self.lr_glo * (m / (1 - b1 ** t)) / ((v / (1 - b2 ** t)).sqrt() + eps)
-      self.glo_grad[rows] = 0
-      self._touched.clear()
+    if self.flat.is_cuda:
+      ops.adam_step(self.flat, self.grad, self.exp_avg, self.exp_avg_sq, self.lr, self.steps)
+      for r in sorted(self._touched):
+        self.glo_steps[r] += 1
+        ops.adam_step(self.glo[r], self.glo_grad[r], self.glo_m[r], self.glo_v[r], self.lr_glo, self.glo_steps[r],
+                      betas=(0.8, 0.95))
+    else:  # host-side replica (the gloo tests): the same update in torch ops
+      for p, g, m, v, lr, t, (b1, b2) in [(self.flat, self.grad, self.exp_avg, self.exp_avg_sq, self.lr, self.steps, (0.9, 0.999))] + [
+          (self.glo[r], self.glo_grad[r], self.glo_m[r], self.glo_v[r], self.lr_glo, self._bump(r), (0.8, 0.95))
+          for r in sorted(self._touched)]:
+        m.mul_(b1).add_(g, alpha=1 - b1)
+        v.mul_(b2).addcmul_(g, g, value=1 - b2)
+        p.addcdiv_(m, (v / (1 - b2 ** t)).sqrt_().add_(1e-8), value=-lr / (1 - b1 ** t))
+        g.zero_()
+    self._touched.clear()
 
-  _STATE = ("flat", "exp_avg", "exp_avg_sq", "glo", "glo_m", "glo_v", "glo_steps")
+  def _bump(self, r):
+    self.glo_steps[r] += 1
+    return self.glo_steps[r]
+
+  _STATE = ("flat", "exp_avg", "exp_avg_sq", "glo", "glo_m", "glo_v")
 
   def state_dict(self):
     sd = {k: getattr(self, k).clone() for k in self._STATE}
     sd["steps"] = self.steps
+    sd["glo_steps"] = torch.tensor(self.glo_steps, dtype=torch.int64)
     return sd
 
   def load_state_dict(self, sd):
     for k in self._STATE:
       getattr(self, k).copy_(sd[k])  # in place: the kernels hold pointers into `flat`
     self.steps = int(sd["steps"])
+    self.glo_steps = [int(x) for x in sd["glo_steps"].tolist()]
 
   def all_reduce(self, dist, group=None):
     """camera-batch DP: the colour model is replicated; its (tiny) dense gradients are summed over the ranks."""

@@ -522,3 +522,10 @@ def estimate_scale(points, num_neighbors=3):
   ws = torch.empty((nbytes,), device=points.device, dtype=torch.uint8)
   L.check(L.load().gs_knn_scale(n, L.ptr(_f32(points)), num_neighbors, L.ptr(scales), L.ptr(ws), nbytes, L.stream()))
   return scales
+
+
+def adam_step(param, grad, exp_avg, exp_avg_sq, lr, step, betas=(0.9, 0.999), eps=1e-8, zero_grad=True):
+  """gs_adam_step on contiguous fp32 CUDA tensors of equal size (views into larger buffers are fine)."""
+  assert param.is_contiguous() and grad.is_contiguous() and exp_avg.is_contiguous() and exp_avg_sq.is_contiguous()
+  L.check(L.load().gs_adam_step(param.numel(), L.ptr(_f32(param)), L.ptr(_f32(grad)), L.ptr(exp_avg), L.ptr(exp_avg_sq),
+                                float(lr), float(betas[0]), float(betas[1]), float(eps), int(step), int(zero_grad), L.stream()))

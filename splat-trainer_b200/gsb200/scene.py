@@ -305,9 +305,12 @@ class SplatScene:
                     None if self.color is not None else acc[:, 6:9], None, row_vis=w["vis"], grads=self.g,
                     accumulate=accumulate, reg=(c.reg_weights, w["reg_sums"], w["depth"]) if reg else None)
     if self.color is not None:  # colour gradient of the blended rows -> point features, GLO row, MLP weights
+      self._mark("project_bwd")
       self.color.backward(p["sh"], p["position"], camera_position(cam), image_idx, w["vis"], acc[:, 6:9], self.g["sh"],
                           accumulate, reg_sums=w["reg_sums"] if reg else None)
-    self._mark("project_bwd")
+      self._mark("color_bwd")
+    else:
+      self._mark("project_bwd")
     if exchange is not None:
       # the dense gradient buffer holds this image's rows only (pack moves them out and zeroes them again)
       exchange.pack(slot, w, acc)

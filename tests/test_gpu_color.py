@@ -159,3 +159,18 @@ def test_backward_all_rows_equals_reference_autograd_and_specular_reg():
   _bwd_close(npy(d_feature2), df0, "diffuse-only d_feature")
   assert not npy(grads["dir_w1"]).any() and not npy(grads["dir_wsh"]).any(), "no gradient reaches the directional MLP"
   _bwd_close(npy(grads["base_w1"]), dW0["base_w1"], "diffuse-only base_w1")
+
+
+def test_adam_step_equals_torch_adam():
+  gen = torch.Generator(device="cuda").manual_seed(0)
+  p = torch.randn((10088,), device="cuda", generator=gen)
+  ref = p.clone().requires_grad_(True)
+  opt = torch.optim.Adam([ref], lr=1e-2, betas=(0.8, 0.95), eps=1e-8)
+  m, v = torch.zeros_like(p), torch.zeros_like(p)
+  for step in range(1, 4):
+    g = torch.randn((10088,), device="cuda", generator=gen) * 10.0 ** (-step)
+    ref.grad = g.clone()
+    opt.step()
+    ops.adam_step(p, g, m, v, 1e-2, step, betas=(0.8, 0.95))
+    assert not g.any(), "the consumed gradient is cleared"
+    torch.testing.assert_close(p, ref.detach(), rtol=1e-5, atol=1e-6)
