@@ -459,6 +459,13 @@ int gs_knn_scale(int64_t n, const float *points, int num_neighbors, float *scale
 int gs_adam_step(int64_t n, float *param, float *grad, float *exp_avg, float *exp_avg_sq, float lr, float beta1,
                  float beta2, float eps, int step, int zero_grad, void *stream);
 
+/* The same update on the rows r of a (rows, dim) table with touched[r] > 0 (the GLO embeddings an image used since the
+ * last step; SparseAdam semantics: other rows keep parameters AND moments).  steps (rows) int32 and touched (rows) float
+ * live on the device: steps[r] is incremented, grad row and touched[r] are cleared.  No host read-back; under camera-batch
+ * DP `touched` is summed over the ranks together with the gradients. */
+int gs_adam_rows(int rows, int dim, float *param, float *grad, float *exp_avg, float *exp_avg_sq, int32_t *steps,
+                 float *touched, float lr, float beta1, float beta2, float eps, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

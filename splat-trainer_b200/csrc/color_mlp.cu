@@ -867,6 +867,39 @@ __global__ void __launch_bounds__(256) k_adam(int64_t n, float *__restrict__ p, 
 }
 }  // namespace
 
+namespace {
+// Adam on the rows of a small table that were touched since the last step (the GLO embeddings, reference GLOTable's
+// SparseAdam, scene/color_model.py:37-44): per-row step counts and the touched flags live on the device, so neither a
+// host-built index list nor a read-back is needed (under DP the flags are all-reduced with the gradients).
+__global__ void __launch_bounds__(64) k_adam_rows(int dim, float *__restrict__ p, float *__restrict__ g, float *__restrict__ m,
+                                                  float *__restrict__ v, int32_t *__restrict__ steps, float *__restrict__ touched,
+                                                  float lr, float b1, float b2, float eps) {
+  int r = blockIdx.x;
+  if (!(touched[r] > 0.f)) return;
+  int t = steps[r] + 1;
+  float lr_over_bc1 = lr / (1.0f - powf(b1, (float)t)), inv_bc2 = 1.0f / (1.0f - powf(b2, (float)t));
+  for (int k = threadIdx.x; k < dim; k += blockDim.x) {
+    int64_t i = (int64_t)r * dim + k;
+    float gi = g[i];
+    float mi = b1 * m[i] + (1.0f - b1) * gi, vi = b2 * v[i] + (1.0f - b2) * gi * gi;
+    m[i] = mi; v[i] = vi;
+    p[i] -= lr_over_bc1 * mi / (sqrtf(vi * inv_bc2) + eps);
+    g[i] = 0.f;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) { steps[r] = t; touched[r] = 0.f; }
+}
+}  // namespace
+
+extern "C" int gs_adam_rows(int rows, int dim, float *param, float *grad, float *exp_avg, float *exp_avg_sq, int32_t *steps,
+                            float *touched, float lr, float beta1, float beta2, float eps, void *stream) {
+  GS_REQUIRE(param && grad && exp_avg && exp_avg_sq && steps && touched, "null argument");
+  if (rows <= 0 || dim <= 0) return GS_OK;
+  k_adam_rows<<<rows, 64, 0, (cudaStream_t)stream>>>(dim, param, grad, exp_avg, exp_avg_sq, steps, touched, lr, beta1, beta2, eps);
+  GS_LAUNCH_CHECK();
+  return GS_OK;
+}
+
 extern "C" int gs_adam_step(int64_t n, float *param, float *grad, float *exp_avg, float *exp_avg_sq, float lr, float beta1,
                             float beta2, float eps, int step, int zero_grad, void *stream) {
   GS_REQUIRE(param && grad && exp_avg && exp_avg_sq, "null argument");

@@ -22,8 +22,11 @@ class ColorModule:
     default = nn.Linear's initialisation (U(-1/sqrt(in), 1/sqrt(in)) for weight and bias)."""
     self.device = torch.device(device)
     total = sum(math.prod(s) for s in SHAPES.values())
+    rows = max(num_images, 1)
     self.flat = torch.zeros((total,), device=self.device)
-    self.grad = torch.zeros_like(self.flat)
+    # everything a DP step has to sum over the ranks sits in ONE buffer: weight gradients, GLO gradients, touched flags
+    self.exchange = torch.zeros((total + rows * GLO_FEATURES + rows,), device=self.device)
+    self.grad = self.exchange[:total]
     self.exp_avg, self.exp_avg_sq = torch.zeros_like(self.flat), torch.zeros_like(self.flat)
     self.w, self.g = {}, {}
     o = 0
@@ -43,12 +46,12 @@ class ColorModule:
     self.model = ops.color_model(self.w)
     self.grads = ops.color_model(self.g)
     # GLOTable: zero-initialised embeddings (reference scene/color_model.py:16), one row per training image
-    self.glo = torch.zeros((max(num_images, 1), GLO_FEATURES), device=self.device)
-    self.glo_grad = torch.zeros_like(self.glo)
+    self.glo = torch.zeros((rows, GLO_FEATURES), device=self.device)
+    self.glo_grad = self.exchange[total:total + rows * GLO_FEATURES].view(rows, GLO_FEATURES)
+    self.touched = self.exchange[total + rows * GLO_FEATURES:]  # > 0: the row was used since the last step
     self.glo_m, self.glo_v = torch.zeros_like(self.glo), torch.zeros_like(self.glo)
-    self.glo_steps = [0] * self.glo.shape[0]  # per-row step counts (host side: they only feed the bias corrections)
+    self.glo_steps = torch.zeros((rows,), device=self.device, dtype=torch.int32)
     self._zero_glo = torch.zeros((GLO_FEATURES,), device=self.device)
-    self._touched = set()
     self.lr, self.lr_glo, self.specular_reg = lr, lr_glo, specular_reg
     self.steps = 0
 
@@ -60,7 +63,7 @@ class ColorModule:
   def glo_grad_row(self, image_idx):
     if image_idx is None:
       return torch.zeros_like(self._zero_glo)
-    self._touched.add(int(image_idx))
+    self.touched[image_idx] = 1.0
     return self.glo_grad[image_idx]
 
   def forward(self, feature, position, cam_pos, image_idx, in_view, rgb, specular=None, specular_weight=1.0):
@@ -76,48 +79,37 @@ class ColorModule:
 
   def step(self):
     """Adam on the MLP weights (betas (0.9, 0.999), eps 1e-8) and on the GLO rows touched since the last step
-    (betas (0.8, 0.95)); clears the gradients.  One launch for the weights, one per touched GLO row."""
+    (betas (0.8, 0.95), SparseAdam semantics); clears gradients and flags.  Two launches, no host read-back."""
     self.steps += 1
     if self.flat.is_cuda:
       ops.adam_step(self.flat, self.grad, self.exp_avg, self.exp_avg_sq, self.lr, self.steps)
-      for r in sorted(self._touched):
-        self.glo_steps[r] += 1
-        ops.adam_step(self.glo[r], self.glo_grad[r], self.glo_m[r], self.glo_v[r], self.lr_glo, self.glo_steps[r],
-                      betas=(0.8, 0.95))
-    else:  # host-side replica (the gloo tests): the same update in torch ops
-      for p, g, m, v, lr, t, (b1, b2) in [(self.flat, self.grad, self.exp_avg, self.exp_avg_sq, self.lr, self.steps, (0.9, 0.999))] + [
-          (self.glo[r], self.glo_grad[r], self.glo_m[r], self.glo_v[r], self.lr_glo, self._bump(r), (0.8, 0.95))
-          for r in sorted(self._touched)]:
-        m.mul_(b1).add_(g, alpha=1 - b1)
-        v.mul_(b2).addcmul_(g, g, value=1 - b2)
-        p.addcdiv_(m, (v / (1 - b2 ** t)).sqrt_().add_(1e-8), value=-lr / (1 - b1 ** t))
-        g.zero_()
-    self._touched.clear()
+      ops.adam_rows(self.glo, self.glo_grad, self.glo_m, self.glo_v, self.glo_steps, self.touched, self.lr_glo)
+      return
+    # host-side replica (the gloo tests): the same update in torch ops
+    def adam(p, g, m, v, lr, t, b1, b2):
+      m.mul_(b1).add_(g, alpha=1 - b1)
+      v.mul_(b2).addcmul_(g, g, value=1 - b2)
+      p.addcdiv_(m, (v / (1 - b2 ** t)).sqrt_().add_(1e-8), value=-lr / (1 - b1 ** t))
+      g.zero_()
+    adam(self.flat, self.grad, self.exp_avg, self.exp_avg_sq, self.lr, self.steps, 0.9, 0.999)
+    for r in (self.touched > 0).nonzero().flatten().tolist():
+      self.glo_steps[r] += 1
+      adam(self.glo[r], self.glo_grad[r], self.glo_m[r], self.glo_v[r], self.lr_glo, int(self.glo_steps[r]), 0.8, 0.95)
+    self.touched.zero_()
 
-  def _bump(self, r):
-    self.glo_steps[r] += 1
-    return self.glo_steps[r]
-
-  _STATE = ("flat", "exp_avg", "exp_avg_sq", "glo", "glo_m", "glo_v")
+  _STATE = ("flat", "exp_avg", "exp_avg_sq", "glo", "glo_m", "glo_v", "glo_steps")
 
   def state_dict(self):
     sd = {k: getattr(self, k).clone() for k in self._STATE}
     sd["steps"] = self.steps
-    sd["glo_steps"] = torch.tensor(self.glo_steps, dtype=torch.int64)
     return sd
 
   def load_state_dict(self, sd):
     for k in self._STATE:
       getattr(self, k).copy_(sd[k])  # in place: the kernels hold pointers into `flat`
     self.steps = int(sd["steps"])
-    self.glo_steps = [int(x) for x in sd["glo_steps"].tolist()]
 
   def all_reduce(self, dist, group=None):
-    """camera-batch DP: the colour model is replicated; its (tiny) dense gradients are summed over the ranks."""
-    dist.all_reduce(self.grad, group=group)
-    dist.all_reduce(self.glo_grad, group=group)
-    touched = torch.zeros((self.glo.shape[0],), device=self.device)
-    if self._touched:
-      touched[torch.tensor(sorted(self._touched), device=self.device)] = 1
-    dist.all_reduce(touched, group=group)
-    self._touched = set(int(i) for i in touched.nonzero().flatten().tolist())
+    """camera-batch DP: the colour model is replicated; its (tiny) dense gradients, the GLO gradients and the touched
+    flags are summed over the ranks in one collective."""
+    dist.all_reduce(self.exchange, group=group)

@@ -98,6 +98,7 @@ SIGNATURES = {
   "gs_kmeans": (_I, [_L, _I, _I, _I, _P, _P, _P, _P, _Z, _P]),
   "gs_knn_scale_workspace_bytes": (_Z, [_L]),
   "gs_knn_scale": (_I, [_L, _P, _I, _P, _P, _Z, _P]),
+  "gs_adam_rows": (_I, [_I, _I, _P, _P, _P, _P, _P, _P, _F, _F, _F, _F, _P]),
   "gs_adam_step": (_I, [_L, _P, _P, _P, _P, _F, _F, _F, _F, _I, _I, _P]),
   "gs_optim_step_groups": (_I, [_OPT, _L, _P, _P, _I, C.POINTER(OptimGroup), _P, _P, _P, _I, _P]),
   "gs_optim_step": (_I, [_OPT, _I, _L, _P, _P, _I, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _F, _F, _I, _P]),

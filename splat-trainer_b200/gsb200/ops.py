@@ -529,3 +529,12 @@ def adam_step(param, grad, exp_avg, exp_avg_sq, lr, step, betas=(0.9, 0.999), ep
   assert param.is_contiguous() and grad.is_contiguous() and exp_avg.is_contiguous() and exp_avg_sq.is_contiguous()
   L.check(L.load().gs_adam_step(param.numel(), L.ptr(_f32(param)), L.ptr(_f32(grad)), L.ptr(exp_avg), L.ptr(exp_avg_sq),
                                 float(lr), float(betas[0]), float(betas[1]), float(eps), int(step), int(zero_grad), L.stream()))
+
+
+def adam_rows(param, grad, exp_avg, exp_avg_sq, steps, touched, lr, betas=(0.8, 0.95), eps=1e-8):
+  """gs_adam_rows on a contiguous (rows, dim) table; steps int32 (rows,), touched float32 (rows,) on the device."""
+  rows, dim = param.shape
+  assert steps.dtype == torch.int32 and touched.dtype == torch.float32 and param.is_contiguous() and grad.is_contiguous()
+  L.check(L.load().gs_adam_rows(rows, dim, L.ptr(_f32(param)), L.ptr(_f32(grad)), L.ptr(exp_avg), L.ptr(exp_avg_sq),
+                                L.ptr(steps), L.ptr(touched), float(lr), float(betas[0]), float(betas[1]), float(eps),
+                                L.stream()))
