@@ -468,14 +468,20 @@ __global__ void __launch_bounds__(256) k_accumulate_stats(int64_t m, const int64
   float scale_px = sqrtf(fmaxf(lam, 0.f));
   if (scale_px > max_scale_px[i]) max_scale_px[i] = scale_px;
   float v = vis[(int64_t)vis_stride * r];
-  float h_prune = heur[(int64_t)heur_stride * r], h_split = heur[(int64_t)heur_stride * r + 1];
+  // fused path (clear_acc given: heur IS the raster accumulator): the heuristics of a row no pixel blended are exactly
+  // zero (the raster backward is their only writer and the projection zeroed the row), so that sector is not fetched
+  // for the ~97 % of in-view rows that were not blended
+  float h_prune = 0.f, h_split = 0.f;
+  if (v > 0.f || !clear_acc) { h_prune = heur[(int64_t)heur_stride * r]; h_split = heur[(int64_t)heur_stride * r + 1]; }
   if (v > 0.f) {
     points_in_view[i] += 1;
     visibility[i] += v;
     if (scene_visible) scene_visible[i] += v;
   }
-  split_score[i] = gs_exp_lerp(split_alpha, split_score[i], h_split);
-  prune_cost[i] = gs_exp_lerp(prune_alpha, prune_cost[i], h_prune);
+  float s_old = split_score[i], p_old = prune_cost[i];
+  float s_new = gs_exp_lerp(split_alpha, s_old, h_split), p_new = gs_exp_lerp(prune_alpha, p_old, h_prune);
+  if (s_new != s_old) split_score[i] = s_new;  // a never-blended row stays 0: do not dirty its sector
+  if (p_new != p_old) prune_cost[i] = p_new;
   if (v > 0.f) {
     if (clear_acc) {
       float *a = clear_acc + (int64_t)clear_stride * r;
