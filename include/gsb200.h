@@ -90,12 +90,14 @@ const char *gs_last_error(void);
  *     tile_info (nullable, gs_tile_info_bytes(n, W, H) bytes, 256-B aligned): what the cull learns about each row's
  *     tile footprint (16-B record with the exact hit mask, tile count, per-tile totals); gs_tile_map(tile_info_in =
  *     tile_info) then skips its own footprint pass.  Opaque to the caller.
+ *     records (nullable, (n, GS_REC_FLOATS), needs sh): the rasteriser's staged splat record of every in-view row
+ *     (gs_raster_aux.records), written here so no later pass re-reads g2d / rgb to build it.
  * ------------------------------------------------------------------------------------- */
 int gs_project_fwd(const gs_camera *h_cam, const gs_raster_config *h_cfg, int64_t n,
                    const float *position, const float *log_scaling, const float *rotation,
                    const float *alpha_logit, const float *sh, int sh_degree,
                    float *g2d, float *depth, float *rgb,
-                   float *acc, int acc_stride, void *tile_info, void *stream);
+                   float *acc, int acc_stride, void *tile_info, float *records, void *stream);
 size_t gs_tile_info_bytes(int64_t n, int width, int height);
 
 /* Backward of gs_project_fwd.  d_g2d (row stride d_g2d_stride floats, 6 used),
@@ -170,12 +172,43 @@ int gs_radix_sort_pairs(uint32_t *keys_in, uint32_t *vals_in, uint32_t *keys_out
  *       median_depth (H,W, nullable) depth of the splat that takes T below ½ (0 if none).
  *     channels ∈ {1,3,4}.
  * ------------------------------------------------------------------------------------- */
+/* Optional fast-path inputs of the rasteriser (host struct, every member nullable; NULL aux = plain path).
+ *   records    (m, GS_REC_FLOATS) staged splat records written by gs_raster_records (or by gs_project_fwd's `records`
+ *              output): {mean.x, mean.y, A', B' | C', opacity, pcut, row id | r, g, b, y half-extent} with the conic
+ *              pre-scaled for exp2 and pcut = log2(thr/opacity).  With records (channels == 3 only) a tile's batch of
+ *              64 splats is gathered by asynchronous 16-byte copies (cp.async, completion on an mbarrier), double
+ *              buffered: batch k+1 lands while batch k is composited.
+ *   tile_order (T) tile ids, heaviest first (gs_tile_order) + ticket: the kernels then run as persistent CTAs that pull
+ *              tiles from this queue (longest-processing-time-first), so one long tile cannot form the tail.
+ *   tile_work  (T) forward: OUT, the tile's largest n_contrib (= the backward's trip count for the tile).
+ *   counters   (8 x uint64, zeroed by the caller) forward only: [0] (warp, splat) candidate iterations, [1] iterations in
+ *              which at least one pixel blended, [2] (pixel, splat) pairs blended, [3] splat records staged.
+ *              Instrumented build of the kernel: slower, never used by the training path. */
+#define GS_REC_FLOATS 12
+typedef struct gs_raster_aux {
+  const float *records;
+  const int32_t *tile_order;
+  uint32_t *ticket;
+  int32_t *tile_work;
+  unsigned long long *counters;
+} gs_raster_aux;
+
 int gs_raster_fwd(const gs_raster_config *h_cfg, int channels, int64_t m,
                   const float *g2d, const float *features, const float *depth,
                   const int32_t *overlap_to_point, const int32_t *tile_ranges,
                   int width, int height,
                   float *image, float *final_T, int32_t *n_contrib,
-                  float *visibility, float *median_depth, void *stream);
+                  float *visibility, float *median_depth, const gs_raster_aux *aux, void *stream);
+
+/* records[i] for every row with opacity > 0 (3 feature channels).  Rows with opacity 0 are skipped (never listed). */
+int gs_raster_records(const gs_raster_config *h_cfg, int64_t m, const float *g2d, const float *features,
+                      float *records, void *stream);
+
+/* Processing order of the T tiles, heaviest first, by a single-CTA counting sort on the work estimate:
+ *   work_stride == 2: work = tile_ranges (T,2), estimate = end - begin (forward);
+ *   work_stride == 1: work = tile_work (T) written by gs_raster_fwd (backward).
+ * Also zeroes *ticket (the queue head the persistent kernels advance). */
+int gs_tile_order(int tiles, const int32_t *work, int work_stride, int32_t *order, uint32_t *ticket, void *stream);
 
 /* (4) Backward rasterisation: back-to-front re-composite, per-thread 2×2 pixels, warp
  *     transpose-reduction, one vector of atomics per (warp, splat).  acc row layout
@@ -190,7 +223,7 @@ int gs_raster_bwd(const gs_raster_config *h_cfg, int channels, int64_t m,
                   const int32_t *overlap_to_point, const int32_t *tile_ranges,
                   int width, int height,
                   const float *final_T, const int32_t *n_contrib, const float *d_image,
-                  float *acc, int acc_stride, float *vis_plane, void *stream);
+                  float *acc, int acc_stride, float *vis_plane, const gs_raster_aux *aux, void *stream);
 
 /* L1 + MSE photometric loss against a target, fused with the reference's post-activation
  * clamp(image,0,1) (scene/color_model.py:154-160; trainer/trainer.py:465-476):

@@ -244,7 +244,7 @@ __device__ __forceinline__ void optim_row(const OptDev &c, int64_t i, int l, boo
       bc1 = 1.0f - powf(c.beta1, ts);
       bc2 = 1.0f - powf(c.beta2, ts);
     }
-    lam = w / (rv + c.vis_smooth);
+    lam = fminf(w / (rv + c.vis_smooth), 1.0f);  // Spec O: a row seen less than usual takes a smaller step, never a larger one
     inv_w = 1.0f / (w + c.vis_smooth);
   }
   float g[EPL], gt[EPL], p[EPL], m1[EPL];

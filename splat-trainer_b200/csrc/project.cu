@@ -8,6 +8,7 @@
 #include "common.cuh"
 #include "footprint.cuh"
 #include "reg.cuh"
+#include "raster_common.cuh"  // make_record: the rasteriser's staged splat record
 
 // ---- SH basis: reference scene/mlp/rsh.py:110-157 (rsh_cart_3) ------------------------------------
 template <int DEG>
@@ -173,7 +174,8 @@ __global__ void __launch_bounds__(128) k_project_fwd(CamDev cam, CfgDev cfg, int
                                                      const float *__restrict__ alpha_logit, const float *__restrict__ sh,
                                                      float *__restrict__ g2d, float *__restrict__ depth,
                                                      float *__restrict__ rgb, float *__restrict__ acc, int acc_stride,
-                                                     uint4 *__restrict__ tile_recs, int32_t *__restrict__ tile_counts) {
+                                                     uint4 *__restrict__ tile_recs, int32_t *__restrict__ tile_counts,
+                                                     float *__restrict__ records) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   float px = position[3 * i], py = position[3 * i + 1], pz = position[3 * i + 2];
@@ -208,6 +210,11 @@ __global__ void __launch_bounds__(128) k_project_fwd(CamDev cam, CfgDev cfg, int
     float c[3];
     sh_color<DEG>(sh + (int64_t)3 * K * i, px, py, pz, cam.cam_pos, c);
     rgb[3 * i] = c[0]; rgb[3 * i + 1] = c[1]; rgb[3 * i + 2] = c[2];
+    if (records) {  // the rasteriser's staged record of this row: written once here, gathered per tile by cp.async
+      SplatRec R = make_record(t.u, t.v, t.ca, t.cb, t.cc, t.op, cfg.thr, (int)i, c[0], c[1], c[2]);
+      float4 *dst = reinterpret_cast<float4 *>(records + (int64_t)GS_REC_FLOATS * i);
+      dst[0] = R.w0; dst[1] = R.w1; dst[2] = R.w2;
+    }
   }
   if (acc) {
     float4 *a = reinterpret_cast<float4 *>(acc + (int64_t)acc_stride * i);
@@ -486,9 +493,10 @@ __global__ void __launch_bounds__(128) k_sh_eval_bwd(int64_t nv, const int64_t *
 extern "C" int gs_project_fwd(const gs_camera *h_cam, const gs_raster_config *h_cfg, int64_t n, const float *position,
                               const float *log_scaling, const float *rotation, const float *alpha_logit, const float *sh,
                               int sh_degree, float *g2d, float *depth, float *rgb, float *acc, int acc_stride,
-                              void *tile_info, void *stream) {
+                              void *tile_info, float *records, void *stream) {
   GS_REQUIRE(h_cam && h_cfg, "null camera/config");
   GS_REQUIRE(h_cfg->tile_size == GS_TILE, "tile_size must be 16");
+  GS_REQUIRE(records == nullptr || (sh && rgb), "staged records need the SH colour (use gs_raster_records otherwise)");
   GS_REQUIRE(acc == nullptr || (acc_stride > 0 && acc_stride % 4 == 0), "acc_stride must be a multiple of 4");
   if (n <= 0) return GS_OK;
   CamDev cam = gs_make_cam(h_cam, h_cfg);
@@ -499,7 +507,7 @@ extern "C" int gs_project_fwd(const gs_camera *h_cam, const gs_raster_config *h_
   if (tile_info) ti = gs_tile_info_carve(tile_info, n, h_cam->width, h_cam->height);
   GS_DISPATCH_DEG(sh_degree, (k_project_fwd<D><<<blocks, 128, 0, st>>>(cam, cfg, n, position, log_scaling, rotation,
                                                                         alpha_logit, sh, g2d, depth, rgb, acc, acc_stride,
-                                                                        ti.recs, ti.counts)));
+                                                                        ti.recs, ti.counts, records)));
   GS_LAUNCH_CHECK();
   return GS_OK;
 }

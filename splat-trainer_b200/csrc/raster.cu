@@ -10,18 +10,15 @@
 // are summed in registers, then a 13-shuffle transpose-reduction leaves the 12 per-splat sums on
 // 12 lanes, which issue one coalesced vector of fp32 reductions (RED) per (warp, splat) — instead
 // of 12 x 5 butterfly shuffles and 12 separate atomics.  No tensor cores: FMA/SFU/LSU bound.
-#include "common.cuh"
-#include "footprint.cuh"  // det_logf
+#include "raster_common.cuh"
 
-constexpr int RT = 64;  // threads per tile
-constexpr float LOG2E = 1.4426950408889634f;
-constexpr float LN2 = 0.6931471805599453f;
-
-__device__ __forceinline__ float ex2_approx(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
+// raster_rec.cu: the record-staged asynchronous kernels (taken when aux->records is given)
+int gs_raster_fwd_rec(const gs_raster_config *h_cfg, const gs_raster_aux *aux, const float *depth, const int32_t *o2p,
+                      const int32_t *ranges, int W, int H, float *image, float *final_T, int32_t *n_contrib, float *visibility,
+                      float *median, cudaStream_t st);
+int gs_raster_bwd_rec(const gs_raster_config *h_cfg, const gs_raster_aux *aux, const int32_t *o2p, const int32_t *ranges,
+                      int W, int H, const float *final_T, const int32_t *n_contrib, const float *d_image, float *acc,
+                      int acc_stride, float *vis_plane, cudaStream_t st);
 
 struct TileCtx {
   int begin, n;
@@ -179,66 +176,6 @@ __global__ void __launch_bounds__(RT) k_raster_fwd(CfgDev cfg, const float *__re
   }
 }
 
-// ---- warp transpose-reductions: NV per-lane values -> NV totals spread over lanes --------------------
-// 12 values, 13 shuffles.  On return lane L (even, !(b2&&b1)) holds the total of value `index`.
-__device__ __forceinline__ float multi_reduce12(const float *v, int lane, int &index, bool &valid) {
-  bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
-  float a[6];
-#pragma unroll
-  for (int i = 0; i < 6; ++i) {
-    float keep = b4 ? v[6 + i] : v[i], send = b4 ? v[i] : v[6 + i];
-    a[i] = keep + __shfl_xor_sync(GS_FULL, send, 16);
-  }
-  float b[3];
-#pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    float keep = b3 ? a[3 + i] : a[i], send = b3 ? a[i] : a[3 + i];
-    b[i] = keep + __shfl_xor_sync(GS_FULL, send, 8);
-  }
-  float c0, c1;
-  {
-    float keep = b2 ? b[2] : b[0], send = b2 ? b[0] : b[2];
-    c0 = keep + __shfl_xor_sync(GS_FULL, send, 4);
-    float keep1 = b2 ? 0.f : b[1], send1 = b2 ? b[1] : 0.f;
-    c1 = keep1 + __shfl_xor_sync(GS_FULL, send1, 4);
-  }
-  float keep = b1 ? c1 : c0, send = b1 ? c0 : c1;
-  float d = keep + __shfl_xor_sync(GS_FULL, send, 2);
-  d += __shfl_xor_sync(GS_FULL, d, 1);
-  index = (b4 ? 6 : 0) + (b3 ? 3 : 0) + (b2 ? 2 : (b1 ? 1 : 0));
-  valid = !(b2 && b1) && !(lane & 1);
-  return d;
-}
-
-// 16 values, 16 shuffles; lane L (even) holds the total of value index = lane >> 1.
-__device__ __forceinline__ float multi_reduce16(const float *v, int lane, int &index, bool &valid) {
-  bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
-  float a[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    float keep = b4 ? v[8 + i] : v[i], send = b4 ? v[i] : v[8 + i];
-    a[i] = keep + __shfl_xor_sync(GS_FULL, send, 16);
-  }
-  float b[4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    float keep = b3 ? a[4 + i] : a[i], send = b3 ? a[i] : a[4 + i];
-    b[i] = keep + __shfl_xor_sync(GS_FULL, send, 8);
-  }
-  float c[2];
-#pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    float keep = b2 ? b[2 + i] : b[i], send = b2 ? b[i] : b[2 + i];
-    c[i] = keep + __shfl_xor_sync(GS_FULL, send, 4);
-  }
-  float keep = b1 ? c[1] : c[0], send = b1 ? c[0] : c[1];
-  float d = keep + __shfl_xor_sync(GS_FULL, send, 2);
-  d += __shfl_xor_sync(GS_FULL, d, 1);
-  index = (b4 ? 8 : 0) + (b3 ? 4 : 0) + (b2 ? 2 : 0) + (b1 ? 1 : 0);
-  valid = !(lane & 1);
-  return d;
-}
-
 template <int C>
 __global__ void __launch_bounds__(RT) k_raster_bwd(CfgDev cfg, const float *__restrict__ g2d, const float *__restrict__ feat,
                                                    const int32_t *__restrict__ o2p, const int32_t *__restrict__ ranges,
@@ -387,12 +324,18 @@ static int launch_fwd(const gs_raster_config *h_cfg, const float *g2d, const flo
 extern "C" int gs_raster_fwd(const gs_raster_config *h_cfg, int channels, int64_t m, const float *g2d, const float *features,
                              const float *depth, const int32_t *overlap_to_point, const int32_t *tile_ranges, int width,
                              int height, float *image, float *final_T, int32_t *n_contrib, float *visibility,
-                             float *median_depth, void *stream) {
+                             float *median_depth, const gs_raster_aux *aux, void *stream) {
   (void)m;
   GS_REQUIRE(h_cfg && h_cfg->tile_size == GS_TILE, "tile_size must be 16");
   GS_REQUIRE(width > 0 && height > 0, "bad image size");
   GS_REQUIRE(median_depth == nullptr || depth != nullptr, "median depth needs depth");
   cudaStream_t st = (cudaStream_t)stream;
+  if (aux && aux->records) {
+    GS_REQUIRE(channels == 3, "staged records carry 3 channels");
+    return gs_raster_fwd_rec(h_cfg, aux, depth, overlap_to_point, tile_ranges, width, height, image, final_T, n_contrib,
+                             visibility, median_depth, st);
+  }
+  GS_REQUIRE(!aux || (!aux->tile_order && !aux->counters), "tile_order / counters need staged records");
   switch (channels) {
     case 1: return launch_fwd<1>(h_cfg, g2d, features, depth, overlap_to_point, tile_ranges, width, height, image, final_T, n_contrib, visibility, median_depth, st);
     case 3: return launch_fwd<3>(h_cfg, g2d, features, depth, overlap_to_point, tile_ranges, width, height, image, final_T, n_contrib, visibility, median_depth, st);
@@ -404,11 +347,17 @@ extern "C" int gs_raster_fwd(const gs_raster_config *h_cfg, int channels, int64_
 extern "C" int gs_raster_bwd(const gs_raster_config *h_cfg, int channels, int64_t m, const float *g2d, const float *features,
                              const int32_t *overlap_to_point, const int32_t *tile_ranges, int width, int height,
                              const float *final_T, const int32_t *n_contrib, const float *d_image, float *acc,
-                             int acc_stride, float *vis_plane, void *stream) {
+                             int acc_stride, float *vis_plane, const gs_raster_aux *aux, void *stream) {
   (void)m;
   GS_REQUIRE(h_cfg && h_cfg->tile_size == GS_TILE, "tile_size must be 16");
   GS_REQUIRE(acc_stride >= 9 + channels, "acc_stride too small");
   cudaStream_t st = (cudaStream_t)stream;
+  if (aux && aux->records) {
+    GS_REQUIRE(channels == 3, "staged records carry 3 channels");
+    return gs_raster_bwd_rec(h_cfg, aux, overlap_to_point, tile_ranges, width, height, final_T, n_contrib, d_image, acc,
+                             acc_stride, vis_plane, st);
+  }
+  GS_REQUIRE(!aux || !aux->tile_order, "tile_order needs staged records");
   CfgDev cfg = gs_make_cfg(h_cfg);
   int TX = (width + GS_TILE - 1) / GS_TILE, TY = (height + GS_TILE - 1) / GS_TILE;
   int tiles = TX * TY;

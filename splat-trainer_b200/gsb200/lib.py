@@ -60,17 +60,25 @@ class RegFuse(C.Structure):  # gs_reg_fuse
               ("depth", C.c_void_p)]
 
 
+class RasterAux(C.Structure):  # gs_raster_aux
+  _fields_ = [("records", C.c_void_p), ("tile_order", C.c_void_p), ("ticket", C.c_void_p), ("tile_work", C.c_void_p),
+              ("counters", C.c_void_p)]
+
+
+GS_REC_FLOATS = 12
+
 _P, _I, _L, _F, _Z = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t
 _CAM, _CFG, _OPT = C.POINTER(Camera), C.POINTER(RasterConfig), C.POINTER(OptimConfig)
 _XG = C.POINTER(ExchangeGroups)
 _REG = C.POINTER(RegFuse)
+_AUX = C.POINTER(RasterAux)
 
 # name -> (restype, argtypes); one entry per symbol declared in include/gsb200.h
 SIGNATURES = {
   "gs_default_raster_config": (None, [_CFG]),
   "gs_version": (_I, []),
   "gs_last_error": (C.c_char_p, []),
-  "gs_project_fwd": (_I, [_CAM, _CFG, _L, _P, _P, _P, _P, _P, _I, _P, _P, _P, _P, _I, _P, _P]),
+  "gs_project_fwd": (_I, [_CAM, _CFG, _L, _P, _P, _P, _P, _P, _I, _P, _P, _P, _P, _I, _P, _P, _P]),
   "gs_project_bwd": (_I, [_CAM, _CFG, _L, _P, _P, _P, _P, _P, _I, _P, _P, _I, _P, _I, _P, _P, _I, _REG,
                           _P, _P, _P, _P, _P, _I, _P]),
   "gs_sh_eval_fwd": (_I, [_L, _P, _P, _I, _P, C.POINTER(C.c_float), _P, _P]),
@@ -81,9 +89,11 @@ SIGNATURES = {
   "gs_tile_count": (_I, [_CFG, _L, _P, _P, _I, _I, _P, _P, _P]),
   "gs_radix_sort_workspace_bytes": (_Z, [_L]),
   "gs_radix_sort_pairs": (_I, [_P, _P, _P, _P, _L, _P, _I, _I, _P, _Z, _P]),
-  "gs_raster_fwd": (_I, [_CFG, _I, _L, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, _P, _P]),
+  "gs_raster_fwd": (_I, [_CFG, _I, _L, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, _P, _AUX, _P]),
+  "gs_raster_records": (_I, [_CFG, _L, _P, _P, _P, _P]),
+  "gs_tile_order": (_I, [_I, _P, _I, _P, _P, _P]),
   "gs_raster_acc_stride": (_I, [_I]),
-  "gs_raster_bwd": (_I, [_CFG, _I, _L, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, _I, _P, _P]),
+  "gs_raster_bwd": (_I, [_CFG, _I, _L, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, _I, _P, _AUX, _P]),
   "gs_loss_l1_mse": (_I, [_L, _P, _P, _P, _F, _F, _P, _P, _P]),
   "gs_optim_begin_workspace_bytes": (_Z, [_L]),
   "gs_optim_begin": (_I, [_OPT, _L, _P, _P, _P, _P, _P, _P, _Z, _P]),

@@ -21,7 +21,7 @@ def tiles_of(width, height):
 
 # ---- (1) projection + SH ---------------------------------------------------------------------------
 def project_fwd(cam, cfg, position, log_scaling, rotation, alpha_logit, sh=None, sh_degree=0, acc=None,
-                out=None, tile_info=None):
+                out=None, tile_info=None, records=None):
   """gs_project_fwd.  Returns (g2d (n,6), depth (n), rgb (n,3)); row i belongs to Gaussian i.
   tile_info: a TileInfo (filled for gs_tile_map(tile_info=...))."""
   n = position.shape[0]
@@ -35,7 +35,8 @@ def project_fwd(cam, cfg, position, log_scaling, rotation, alpha_logit, sh=None,
   L.check(L.load().gs_project_fwd(C.byref(cam), C.byref(cfg), n, L.ptr(_f32(position)), L.ptr(_f32(log_scaling)),
                                   L.ptr(_f32(rotation)), L.ptr(_f32(alpha_logit)), L.ptr(sh), sh_degree,
                                   L.ptr(g2d), L.ptr(depth), L.ptr(rgb), L.ptr(acc),
-                                  0 if acc is None else acc.shape[1], None if tile_info is None else L.ptr(tile_info.buffer), L.stream()))
+                                  0 if acc is None else acc.shape[1], None if tile_info is None else L.ptr(tile_info.buffer),
+                                  L.ptr(records), L.stream()))
   return g2d, depth, rgb
 
 
@@ -176,8 +177,50 @@ def acc_stride(channels):
   return L.load().gs_raster_acc_stride(channels)
 
 
+class RasterAux:
+  """fast-path buffers of the rasteriser for one image size (gs_raster_aux): staged splat records, the heaviest-first
+  tile queue of the forward and of the backward, the per-tile work the forward measures."""
+
+  def __init__(self, m, width, height, device, persistent=True):
+    tx, ty = tiles_of(width, height)
+    self.m, self.tiles = m, tx * ty
+    self.records = torch.empty((m, L.GS_REC_FLOATS), device=device, dtype=torch.float32)
+    self.tile_work = torch.zeros((self.tiles,), device=device, dtype=torch.int32)
+    self.order = torch.empty((2, self.tiles), device=device, dtype=torch.int32) if persistent else None
+    self.ticket = torch.zeros((2,), device=device, dtype=torch.int32) if persistent else None
+    self.counters = None
+
+  def struct(self, which, counters=None):
+    """which: 0 = forward (queue sorted by list length), 1 = backward (queue sorted by the forward's tile_work)."""
+    a = L.RasterAux()
+    a.records = L.ptr(self.records)
+    a.tile_work = L.ptr(self.tile_work)
+    if self.order is not None:
+      a.tile_order = L.ptr(self.order[which])
+      a.ticket = self.ticket[which:].data_ptr()
+    a.counters = L.ptr(counters)
+    return a
+
+  def order_forward(self, tile_ranges):
+    if self.order is not None:
+      L.check(L.load().gs_tile_order(self.tiles, L.ptr(tile_ranges), 2, L.ptr(self.order[0]), self.ticket.data_ptr(),
+                                     L.stream()))
+
+  def order_backward(self):
+    if self.order is not None:
+      L.check(L.load().gs_tile_order(self.tiles, L.ptr(self.tile_work), 1, L.ptr(self.order[1]),
+                                     self.ticket[1:].data_ptr(), L.stream()))
+
+
+def raster_records(cfg, g2d, features, records):
+  """gs_raster_records: staged 48-byte records of every in-view row (3 feature channels)."""
+  L.check(L.load().gs_raster_records(C.byref(cfg), g2d.shape[0], L.ptr(g2d), L.ptr(_f32(features)), L.ptr(records), L.stream()))
+  return records
+
+
 def raster_fwd(cfg, g2d, features, depth, overlap_to_point, tile_ranges, width, height, visibility=False,
-               median=False, out=None):
+               median=False, out=None, aux=None, counters=None):
+  """aux: a RasterAux whose records are current for (g2d, features) -> record-staged asynchronous kernels."""
   m, ch = g2d.shape[0], features.shape[1]
   dev = g2d.device
   if out is None:
@@ -193,22 +236,30 @@ def raster_fwd(cfg, g2d, features, depth, overlap_to_point, tile_ranges, width, 
   else:
     vis = visibility  # caller's accumulator (+=)
   med = torch.empty((height, width), device=dev, dtype=torch.float32) if median else None
+  ax = None
+  if aux is not None:
+    aux.order_forward(tile_ranges)
+    ax = C.byref(aux.struct(0, counters))
   L.check(L.load().gs_raster_fwd(C.byref(cfg), ch, m, L.ptr(g2d), L.ptr(_f32(features)), L.ptr(depth),
                                  L.ptr(overlap_to_point), L.ptr(tile_ranges), width, height, L.ptr(image),
-                                 L.ptr(final_T), L.ptr(n_contrib), L.ptr(vis), L.ptr(med), L.stream()))
+                                 L.ptr(final_T), L.ptr(n_contrib), L.ptr(vis), L.ptr(med), ax, L.stream()))
   return image, final_T, n_contrib, vis, med
 
 
 def raster_bwd(cfg, g2d, features, overlap_to_point, tile_ranges, width, height, final_T, n_contrib, d_image,
-               acc=None, vis_plane=None):
+               acc=None, vis_plane=None, aux=None):
   """gs_raster_bwd; acc (m, acc_stride) must be zero on entry (allocated zeroed if None).
   vis_plane (m,): receives the visibility sums instead of acc[:, 8+C] (must be zero on entry too)."""
   m, ch = g2d.shape[0], features.shape[1]
   if acc is None:
     acc = torch.zeros((m, acc_stride(ch)), device=g2d.device, dtype=torch.float32)
+  ax = None
+  if aux is not None:
+    aux.order_backward()
+    ax = C.byref(aux.struct(1))
   L.check(L.load().gs_raster_bwd(C.byref(cfg), ch, m, L.ptr(g2d), L.ptr(features), L.ptr(overlap_to_point),
                                  L.ptr(tile_ranges), width, height, L.ptr(final_T), L.ptr(n_contrib),
-                                 L.ptr(_f32(d_image)), L.ptr(acc), acc.shape[1], L.ptr(vis_plane), L.stream()))
+                                 L.ptr(_f32(d_image)), L.ptr(acc), acc.shape[1], L.ptr(vis_plane), ax, L.stream()))
   return acc
 
 

@@ -25,12 +25,13 @@ ATTRS = ("position", "log_scaling", "rotation", "alpha_logit", "sh")
 @dataclasses.dataclass
 class SceneConfig:
   sh_degree: int = 3
-  # per-group learning rates and kinds (reference config/scene/mlp.yaml:8-14 names the groups/kinds; the values
-  # here are ours — the reference's optimiser arithmetic is unpinned, DESIGN.md "Spec O")
-  lr_position: float = 0.05      # local_vector: in units of the splat's own R·S basis
-  lr_log_scaling: float = 0.02   # scalar
+  # per-group learning rates = the reference's config/scene/mlp.yaml:8-14 (position .3 local_vector, log_scaling .08,
+  # rotation .01 vector, alpha_logit .1, feature 5.0 vector).  `sh` is this repo's SH colour group (the reference's
+  # scene has MLP point features instead): its rate is ours.
+  lr_position: float = 0.3       # local_vector: in units of the splat's own R·S basis
+  lr_log_scaling: float = 0.08   # scalar
   lr_rotation: float = 0.01      # vector
-  lr_alpha_logit: float = 0.05   # scalar
+  lr_alpha_logit: float = 0.1    # scalar
   lr_sh: float = 0.01            # vector
   optim: dict = dataclasses.field(default_factory=dict)  # overrides of make_optim_config (LaProp, .8/.95, ...)
   w_l1: float = 0.0              # reference trainer/config.py:67-70, config/trainer/default.yaml:52-55
@@ -48,9 +49,12 @@ class SceneConfig:
   # colour model: False = SH coefficients per splat (SHScene); True = the reference's default MLPScene colour path
   # (per-splat feature 16 + per-image GLO embedding 32 -> ColorModel, scene/mlp_scene.py:352-368): the last attribute
   # plane then holds the point features (n, 16) and `sh_degree` is unused
+  # rasteriser of the training path: "async" = staged records gathered by cp.async with the heaviest-first persistent
+  # tile queue (csrc/raster_rec.cu); "gather" = the plain gather-staged kernels (csrc/raster.cu)
+  raster: str = "async"
   color_mlp: bool = False
   num_images: int = 0            # rows of the GLO table (training images)
-  lr_feature: float = 0.02       # vector group (config/scene/mlp.yaml:14 names the group; value = Spec O like the others)
+  lr_feature: float = 5.0        # vector group, config/scene/mlp.yaml:14
   lr_color: float = 1e-2         # ColorModel Adam (lr_diffuse / lr_specular at t = 0, config/scene/mlp.yaml:40-41)
   lr_glo: float = 2.0            # lr_glo_feature, config/scene/mlp.yaml:21
   reg_specular: float = 1e-5     # reg_weight.specular, config/scene/mlp.yaml:19
@@ -167,7 +171,7 @@ class SplatScene:
              image=torch.empty((H, W, 3), device=dev), final_T=torch.empty((H, W), device=dev),
              n_contrib=torch.empty((H, W), device=dev, dtype=torch.int32), d_image=torch.empty((H, W, 3), device=dev),
              loss_sums=torch.zeros((2,), device=dev), reg_sums=torch.zeros((4,), device=dev),
-             tile=None,
+             tile=None, aux=ops.RasterAux(n, W, H, dev) if self.config.raster == "async" else None,
              ssim_sums=torch.zeros((max(self.config.ssim_levels, 1),), device=dev),
              ssim_ws=ops.ssim_workspace(H, W, 3, max(self.config.ssim_levels, 1), dev) if self.config.w_ssim != 0.0 else None)
     self._work = w
@@ -205,17 +209,20 @@ class SplatScene:
     self._mark("begin")
     ops.project_fwd(cam, self.raster_cfg, p["position"], p["log_scaling"], p["rotation"], p["alpha_logit"],
                     None if self.color is not None else p["sh"], self.config.sh_degree,
-                    out=(w["g2d"], w["depth"], w["rgb"]), tile_info=w["tinfo"])
+                    out=(w["g2d"], w["depth"], w["rgb"]), tile_info=w["tinfo"],
+                    records=w["aux"].records if (w["aux"] is not None and self.color is None) else None)
     self._mark("project_fwd")
     if self.color is not None:  # MLPScene.eval_colors for the in-view rows (reference scene/mlp_scene.py:415-417)
       self.color.forward(p["sh"], p["position"], camera_position(cam), image_idx, w["g2d"][:, 5], w["rgb"])
+      if w["aux"] is not None:
+        ops.raster_records(self.raster_cfg, w["g2d"], w["rgb"], w["aux"].records)
       self._mark("color_fwd")
     tb = self._tile_buffers(w, cam)
     ops.tile_map(self.raster_cfg, w["g2d"], w["depth"], cam.width, cam.height, buffers=tb, tile_info=w["tinfo"])
     self._mark("tile_map")
     _, _, _, vis, med = ops.raster_fwd(self.raster_cfg, w["g2d"], w["rgb"], w["depth"], tb.overlap_to_point,
                                        tb.tile_ranges, cam.width, cam.height, visibility=visibility, median=median,
-                                       out=(w["image"], w["final_T"], w["n_contrib"]))
+                                       out=(w["image"], w["final_T"], w["n_contrib"]), aux=w["aux"])
     self._mark("raster_fwd")
     return w, tb, vis, med
 
@@ -289,7 +296,7 @@ class SplatScene:
     self._mark("loss")
     acc = w["acc"]
     ops.raster_bwd(self.raster_cfg, w["g2d"], w["rgb"], tb.overlap_to_point, tb.tile_ranges, cam.width, cam.height,
-                   w["final_T"], w["n_contrib"], w["d_image"], acc=acc, vis_plane=w["vis"])
+                   w["final_T"], w["n_contrib"], w["d_image"], acc=acc, vis_plane=w["vis"], aux=w["aux"])
     self._mark("raster_bwd")
     p = self.p
     reg = any(x != 0.0 for x in c.reg_weights)

@@ -84,6 +84,54 @@ def garden_scene(n, sh_degree=3, seed=0, scale_mult=0.7, shell_min=6.0, max_px=1
   return dict(position=f32(pos), log_scaling=f32(ls), rotation=f32(q), alpha_logit=f32(al), sh=f32(sh))
 
 
+def knn_mean_distance_cpu(points, k=3):
+  """mean distance to the k nearest neighbours by a k-d tree on the host (scipy) — the same quantity as the library's
+  gs_knn_scale / the reference's estimate_scale (gaussians/loading.py:45-61); used where no GPU may be touched (the CPU
+  arm of bench.py, CPU tests)."""
+  from scipy.spatial import cKDTree
+  pts = np.asarray(points, np.float64)
+  d, _ = cKDTree(pts).query(pts, k=k + 1, workers=-1)
+  return d[:, 1:].mean(axis=1).astype(np.float32)
+
+
+def spec_scene(n, sh_degree=3, seed=0, knn=None, opacity=(0.05, 0.95)):
+  """The scene exactly as SURVEY.md §8(d) writes it: 70 % of the splats in a central blob N(0, diag(1.5,1.5,0.6)²), 30 %
+  in a far shell of radius U(4,20); log_scaling ~ N(log(0.7·knn3 distance), 0.5²) clamped to [-8, 8]; quaternion =
+  normalize(N(0,I4)) xyzw; alpha_logit = logit(U(0.05,0.95)); SH DC = rgb_to_sh(U(0,1)), higher bands N(0, 0.05²).
+  knn: callable (n,3) float32 -> (n,) mean distance to the 3 nearest neighbours (default: the host k-d tree; bench.py's
+  GPU arm passes the library's own gs_knn_scale)."""
+  rng = np.random.default_rng(seed)
+  K = (sh_degree + 1) ** 2
+  n_blob = int(0.7 * n)
+  n_shell = n - n_blob
+  blob = rng.normal(0, 1, (n_blob, 3)) * np.array([1.5, 1.5, 0.6])
+  r = rng.uniform(4.0, 20.0, n_shell)
+  dirs = rng.normal(0, 1, (n_shell, 3)); dirs /= np.linalg.norm(dirs, axis=1, keepdims=True)
+  pos = np.concatenate([blob, dirs * r[:, None]]).astype(np.float32)
+  perm = rng.permutation(n)
+  pos = np.ascontiguousarray(pos[perm])
+  d3 = np.asarray((knn or knn_mean_distance_cpu)(pos), np.float64)
+  ls = np.clip(np.log(0.7 * np.maximum(d3, 1e-12))[:, None] + rng.normal(0, 0.5, (n, 3)), -8, 8)
+  q = rng.normal(0, 1, (n, 4)); q /= np.linalg.norm(q, axis=1, keepdims=True)
+  op = rng.uniform(opacity[0], opacity[1], n)
+  al = np.log(op / (1 - op))
+  sh = rng.normal(0, 0.05, (n, 3, K))
+  sh[:, :, 0] = (rng.uniform(0, 1, (n, 3)) - 0.5) / SH0
+  f32 = lambda a: np.ascontiguousarray(a, np.float32)
+  return dict(position=pos, log_scaling=f32(ls), rotation=f32(q), alpha_logit=f32(al), sh=f32(sh))
+
+
+def trained_scene(n, sh_degree=3, seed=0, focal=1390.7):
+  """A scene shaped like one the reference's controller has trained: the sparse generator's geometry, but translucent
+  splats (opacity U(0.02, 0.3), so a pixel blends many layers before it saturates) and only the controller's own size
+  rule (nothing larger than 200 px, config/controller/target.yaml max_scale_px) instead of the 10-px cap."""
+  g = garden_scene(n, sh_degree, seed=seed, max_px=200.0, focal=focal)
+  rng = np.random.default_rng(seed + 77)
+  op = rng.uniform(0.02, 0.3, n)
+  g["alpha_logit"] = np.ascontiguousarray(np.log(op / (1 - op)), np.float32)
+  return g
+
+
 def perturbed(g, seed=1, pos_sigma=0.01, sh_sigma=0.2, alpha_sigma=0.5):
   """a second scene for the training TARGET images: same splats, perturbed colour/opacity/position."""
   rng = np.random.default_rng(seed)
@@ -92,3 +140,34 @@ def perturbed(g, seed=1, pos_sigma=0.01, sh_sigma=0.2, alpha_sigma=0.5):
   out["sh"] += (rng.normal(0, sh_sigma, g["sh"].shape) * (np.arange(g["sh"].shape[2]) == 0)).astype(np.float32)
   out["alpha_logit"] += rng.normal(0, alpha_sigma, g["alpha_logit"].shape).astype(np.float32)
   return out
+
+
+# ---- the BASELINE.json workloads ---------------------------------------------------------------------------------------
+WORKLOADS = {
+  # name: (points, sh_degree, width, height, scene generator, target)
+  "c1": (100_000, 0, 640, 480, "spec", "independent"),            # configs[0]: the CPU-runnable case
+  "c2": (3_000_000, 3, 1297, 840, "spec", "independent"),         # configs[1], generated exactly as SURVEY 8(d) writes it
+  "c2-sparse": (3_000_000, 3, 1297, 840, "sparse", "perturbed"),  # round 1's generator: opaque small splats, ~3 % of rows blend
+  "c2-trained": (3_000_000, 3, 1297, 840, "trained", "perturbed"),  # translucent splats: most in-view rows blend
+  "c4": (6_000_000, 3, 3840, 2160, "sparse", "perturbed"),        # configs[3]: high-res stress
+}
+
+
+def workload(name, points=0, knn=None, seed=0):
+  """-> dict(n, sh_degree, width, height, gaussians, target_gaussians, cameras (185 ring views), description)."""
+  n, deg, W, H, kind, tgt = WORKLOADS[name]
+  if points:
+    n = points
+  focal = 0.5 * W / math.tan(math.radians(25.0))
+  make = dict(spec=lambda s: spec_scene(n, deg, seed=s, knn=knn),
+              sparse=lambda s: garden_scene(n, deg, seed=s, focal=focal),
+              trained=lambda s: trained_scene(n, deg, seed=s, focal=focal))[kind]
+  g = make(seed)
+  target = make(seed + 1) if tgt == "independent" else perturbed(g, seed=seed + 1)
+  what = dict(spec="scene as SURVEY 8(d): blob + shell U(4,20), knn3 scales, opacity U(.05,.95)",
+              sparse="opaque small splats (10 px cap): few rows blend",
+              trained="translucent splats (opacity U(.02,.3), 200 px cap): most in-view rows blend")[kind]
+  return dict(n=n, sh_degree=deg, width=W, height=H, gaussians=g, target_gaussians=target,
+              cameras=ring_cameras(185, W, H, seed=seed),
+              description=f"{name}: {n} splats SH{deg} {W}x{H}, {what}; target = "
+                          f"{'independent seed+1 scene' if tgt == 'independent' else 'perturbed copy'}")
