@@ -43,10 +43,13 @@ def project_fwd(cam, cfg, position, log_scaling, rotation, alpha_logit, sh=None,
 class TileInfo:
   """Opaque per-row tile-footprint buffer written by gs_project_fwd and consumed by gs_tile_map."""
 
-  def __init__(self, n, width, height, device):
+  def __init__(self, n, width, height, device, buffer=None):
+    """buffer: an existing uint8 allocation of at least gs_tile_info_bytes(n, W, H) bytes to lay the info out in."""
     self.n, self.width, self.height = n, width, height
     nbytes = L.load().gs_tile_info_bytes(n, width, height)
-    self.buffer = torch.empty((nbytes,), device=device, dtype=torch.uint8)
+    if buffer is not None and buffer.numel() < nbytes:
+      raise L.GsError("tile info buffer too small")
+    self.buffer = buffer if buffer is not None else torch.empty((nbytes,), device=device, dtype=torch.uint8)
 
   @property
   def counts(self):

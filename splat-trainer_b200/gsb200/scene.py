@@ -43,6 +43,7 @@ class SceneConfig:
   antialias: bool = False        # reference trainer/trainer.py:308-310: blur_cov = 0.0 if antialias else 0.3
   blur_cov: float = 0.3
   max_overlaps: int = 0          # capacity of the tile-overlap list; 0 = calibrate on first use
+  capacity: int = 0              # rows the buffers are laid out for (0 = the initial count; grown ×1.5 when exceeded)
   # reg_weight (scale, opacity, aspect): reference config/scene/mlp.yaml:16-19 at t = 0 (the log_decay schedules are the
   # caller's: assign scene.config.reg_weights per step).  (0, 0, 0) disables the two regularisation sweeps.
   reg_weights: tuple = (0.01, 1.0, 1e-4)
@@ -93,6 +94,7 @@ class SplatScene:
       c = self.config
       self.color = ColorModule(c.num_images, self.device, lr=c.lr_color, lr_glo=c.lr_glo, specular_reg=c.reg_specular,
                                weights=gaussians.get("color_weights"))
+    self._work = None
     self._alloc(int(gaussians["position"].shape[0]))
     for name in ATTRS:
       src = gaussians["feature" if (name == "sh" and self.color is not None) else name]
@@ -109,34 +111,44 @@ class SplatScene:
   def _dims(self):
     return (3, 3, 4, 1, 16 if self.color is not None else 3 * self.K)
 
-  def _alloc(self, n):
+  def _alloc(self, n, capacity=0):
+    """One fp32 allocation per buffer kind, planes laid out for `capacity` rows (>= n) so the scene can grow to it
+    without re-allocating: densification compacts into the second copy of each buffer (ping-pong) and swaps.
+    capacity 0 = SceneConfig.capacity, else n."""
     dev = self.device
+    cap = max(int(capacity or self.config.capacity or 0), n)
+    self.n, self.capacity = n, cap
+    dims = self._dims()
+    offs, total = _plane_offsets(cap, dims)
+    self._offs, self._total = offs, total
+    sq_offs, sq_total = _plane_offsets(cap, (1, 3, 1, 1, 1))
+    self._sq_offs = sq_offs
+    self.params = torch.zeros((total,), device=dev)
+    self.grads = torch.zeros((total + (cap + 63) // 64 * 64,), device=dev)  # + visible at the tail
+    self.exp_avg = torch.zeros((total,), device=dev)
+    self.exp_avg_sq_flat = torch.zeros((sq_total,), device=dev)
+    self._spare = None  # (params, exp_avg, exp_avg_sq) compaction targets, allocated by the first densification
+    self.running_vis = torch.zeros((cap,), device=dev)[:n]
+    self.opt_step = torch.zeros((cap,), device=dev)[:n]
+    self.stats = self.new_point_state(n)
+    self._view(n)
+
+  def _view(self, n):
+    """row views [0, n) of the capacity-sized planes"""
     self.n = n
     dims = self._dims()
-    offs, total = _plane_offsets(n, dims)
-    self._offs, self._total = offs, total
-    self.params = torch.zeros((total,), device=dev)
-    self.grads = torch.zeros((total + (n + 63) // 64 * 64,), device=dev)  # + visible at the tail
-    self.exp_avg = torch.zeros((total,), device=dev)
-    sq_dims = (1, 3, 1, 1, 1)
-    sq_offs, sq_total = _plane_offsets(n, sq_dims)
-    self.exp_avg_sq_flat = torch.zeros((sq_total,), device=dev)
     shapes = dict(position=(n, 3), log_scaling=(n, 3), rotation=(n, 4), alpha_logit=(n,),
                   sh=(n, 16) if self.color is not None else (n, 3, self.K))
 
     def views(flat, offsets, dims_, shp):
       return {name: flat[o:o + n * d].view(shp[name]) for name, o, d in zip(ATTRS, offsets, dims_)}
 
-    self.p = views(self.params, offs, dims, shapes)
-    self.g = views(self.grads, offs, dims, shapes)
-    self.m1 = views(self.exp_avg, offs, dims, shapes)
+    self.p = views(self.params, self._offs, dims, shapes)
+    self.g = views(self.grads, self._offs, dims, shapes)
+    self.m1 = views(self.exp_avg, self._offs, dims, shapes)
     sq_shapes = dict(position=(n,), log_scaling=(n, 3), rotation=(n,), alpha_logit=(n,), sh=(n,))
-    self.m2 = views(self.exp_avg_sq_flat, sq_offs, sq_dims, sq_shapes)
-    self.visible = self.grads[total:total + n]
-    self.running_vis = torch.zeros((n,), device=dev)
-    self.opt_step = torch.zeros((n,), device=dev)
-    self.stats = self.new_point_state(n)
-    self._work = None
+    self.m2 = views(self.exp_avg_sq_flat, self._sq_offs, (1, 3, 1, 1, 1), sq_shapes)
+    self.visible = self.grads[self._total:self._total + n]
     self._vis_idx = None
 
   def new_point_state(self, n):
@@ -159,21 +171,32 @@ class SplatScene:
 
   # ---- per-image work buffers --------------------------------------------------------------------------
   def _buffers(self, cam):
+    """per-image work buffers: allocated once for (image size, row capacity); a densification only re-slices them"""
     W, H = cam.width, cam.height
     w = self._work
     if w is not None and w["W"] == W and w["H"] == H and w["n"] == self.n:
       return w
-    dev, n = self.device, self.n
+    dev, n, cap = self.device, self.n, self.capacity
     stride = ops.acc_stride(3)
-    w = dict(W=W, H=H, n=n,
-             g2d=torch.empty((n, 6), device=dev), depth=torch.empty((n,), device=dev), rgb=torch.empty((n, 3), device=dev),
-             acc=torch.zeros((n, stride), device=dev), vis=torch.zeros((n,), device=dev), tinfo=ops.TileInfo(n, W, H, dev),
-             image=torch.empty((H, W, 3), device=dev), final_T=torch.empty((H, W), device=dev),
-             n_contrib=torch.empty((H, W), device=dev, dtype=torch.int32), d_image=torch.empty((H, W, 3), device=dev),
-             loss_sums=torch.zeros((2,), device=dev), reg_sums=torch.zeros((4,), device=dev),
-             tile=None, aux=ops.RasterAux(n, W, H, dev) if self.config.raster == "async" else None,
-             ssim_sums=torch.zeros((max(self.config.ssim_levels, 1),), device=dev),
-             ssim_ws=ops.ssim_workspace(H, W, 3, max(self.config.ssim_levels, 1), dev) if self.config.w_ssim != 0.0 else None)
+    base = w["base"] if (w is not None and w["W"] == W and w["H"] == H and w["base"]["cap"] == cap) else None
+    if base is None:
+      levels = max(self.config.ssim_levels, 1)
+      base = dict(cap=cap, g2d=torch.empty((cap, 6), device=dev), depth=torch.empty((cap,), device=dev),
+                  rgb=torch.empty((cap, 3), device=dev), acc=torch.zeros((cap, stride), device=dev),
+                  vis=torch.zeros((cap,), device=dev),
+                  tinfo=torch.empty((L.load().gs_tile_info_bytes(cap, W, H),), device=dev, dtype=torch.uint8),
+                  image=torch.empty((H, W, 3), device=dev), final_T=torch.empty((H, W), device=dev),
+                  n_contrib=torch.empty((H, W), device=dev, dtype=torch.int32), d_image=torch.empty((H, W, 3), device=dev),
+                  loss_sums=torch.zeros((2,), device=dev), reg_sums=torch.zeros((4,), device=dev),
+                  ssim_sums=torch.zeros((levels,), device=dev),
+                  ssim_ws=ops.ssim_workspace(H, W, 3, levels, dev) if self.config.w_ssim != 0.0 else None,
+                  aux=ops.RasterAux(cap, W, H, dev) if self.config.raster == "async" else None,
+                  tile=w["tile"] if (w is not None and w["W"] == W and w["H"] == H and w["tile"] is not None
+                                     and w["tile"].m >= n) else None)
+    w = dict(W=W, H=H, n=n, base=base, g2d=base["g2d"][:n], depth=base["depth"][:n], rgb=base["rgb"][:n], acc=base["acc"][:n],
+             vis=base["vis"][:n], tinfo=ops.TileInfo(n, W, H, dev, buffer=base["tinfo"]), tile=base["tile"], aux=base["aux"])
+    for k in ("image", "final_T", "n_contrib", "d_image", "loss_sums", "reg_sums", "ssim_sums", "ssim_ws"):
+      w[k] = base[k]
     self._work = w
     return w
 
@@ -184,7 +207,7 @@ class SplatScene:
       cap = self.config.max_overlaps
       if cap <= 0:
         cap = int(int(w["tinfo"].counts.sum(dtype=torch.int64).item()) * 1.5) + 65536
-      w["tile"] = ops.TileMapBuffers(self.n, cap, cam.width, cam.height, self.device)
+      w["tile"] = w["base"]["tile"] = ops.TileMapBuffers(self.capacity, cap, cam.width, cam.height, self.device)
     return w["tile"]
 
   def overflowed(self):
@@ -196,7 +219,7 @@ class SplatScene:
     w = self._work
     if w and w["tile"] is not None:
       cap = int(w["tile"].max_overlaps * factor)
-      w["tile"] = ops.TileMapBuffers(self.n, cap, w["W"], w["H"], self.device)
+      w["tile"] = w["base"]["tile"] = ops.TileMapBuffers(self.capacity, cap, w["W"], w["H"], self.device)
 
   def _mark(self, name):
     if self.timer is not None:
@@ -367,16 +390,33 @@ class SplatScene:
     """points = points[keep_mask] (parameters AND optimiser state) then append 2 children per split_idx row with
     zero optimiser state.  keep_mask: (N,) bool; split_idx: (S,) int64 rows of the OLD numbering.
     uniform: (S,) U[0,1) draws for the split axis (random_axis=True); None draws them from torch's CUDA generator.
-    The number of kept rows is read back once (densification is off the per-iteration path; the reference
-    reads four scalars here, controller/point_state.py:83-91)."""
+    The kept rows are compacted into the spare copy of each buffer (allocated once, at capacity) and the copies are
+    swapped: no per-densification allocation of the 59·4·N-byte buffers (the allocator churn of the reference,
+    controller/target_controller.py:125-126).  The number of kept rows is read back once (densification is off the
+    per-iteration path; the reference reads four scalars here, controller/point_state.py:83-91)."""
     old_n = self.n
     s = 0 if split_idx is None else int(split_idx.shape[0])
     slots, count = ops.compact_slots(keep_mask)
     kept = int(count.item())
     new_n = kept + 2 * s
-    old = dict(p=self.p, m1=self.m1, m2=self.m2, running_vis=self.running_vis, opt_step=self.opt_step, stats=self.stats,
-               flats=(self.params, self.grads, self.exp_avg, self.exp_avg_sq_flat))
-    self._alloc(new_n)  # zero-initialised: children get zero state, PointState rows of children are zero
+    old = dict(p=self.p, m1=self.m1, m2=self.m2, running_vis=self.running_vis, opt_step=self.opt_step, stats=self.stats)
+    if new_n > self.capacity:  # grow: fresh buffers laid out for 1.5x the rows (the old ones stay alive through `old`)
+      self._alloc(new_n, capacity=max(int(1.5 * new_n), self.capacity))
+    else:
+      if self._spare is None:
+        self._spare = (torch.zeros_like(self.params), torch.zeros_like(self.exp_avg), torch.zeros_like(self.exp_avg_sq_flat))
+      spare = self._spare
+      self._spare = (self.params, self.exp_avg, self.exp_avg_sq_flat)
+      self.params, self.exp_avg, self.exp_avg_sq_flat = spare
+      cap = self.capacity
+      self.running_vis = torch.zeros((cap,), device=self.device)[:new_n]
+      self.opt_step = torch.zeros((cap,), device=self.device)[:new_n]
+      self.stats = self.new_point_state(new_n)
+      self._view(new_n)
+      if s > 0:  # children start with zero optimiser state: clear their rows of the recycled moment buffers
+        for name in ATTRS:
+          self.m1[name][kept:].zero_()
+          self.m2[name][kept:].zero_()
     for name in ATTRS:
       ops.compact_rows(old["p"][name], slots, self.p[name])
       ops.compact_rows(old["m1"][name], slots, self.m1[name])
@@ -414,37 +454,82 @@ class SplatScene:
     both = split_mask & prune_mask
     return split_mask ^ both, prune_mask ^ both
 
-  def densify(self, t, target_points, uniform=None, **kw):
-    """densify_and_prune (reference controller/point_state.py:76-110) + new PointState (target_controller.py:122)."""
+  def densify(self, t, target_points, uniform=None, uniform_rows=None, **kw):
+    """densify_and_prune (reference controller/point_state.py:76-110) + new PointState (target_controller.py:122).
+    uniform: (S,) split-axis draws in split order; uniform_rows: (N,) one draw per OLD row (the split rows take theirs —
+    what replicated ranks use, so identical statistics give identical children)."""
     split_mask, prune_mask = self.find_split_prune(t, target_points, **kw)
     split_idx = split_mask.nonzero().squeeze(1)
+    if uniform is None and uniform_rows is not None:
+      uniform = uniform_rows[split_idx].contiguous()
     keep = ~(split_mask | prune_mask)
     out = self.split_and_prune(keep, split_idx, uniform=uniform)
     self.stats = self.new_point_state(self.n)
     return out
 
+  # ---- checkpoint: the reference's nested layout (trainer/trainer.py:188-194, scene/mlp_scene.py:316-322) -----------
+  _CKPT = dict(position="position", log_scaling="log_scaling", rotation="rotation", alpha_logit="alpha_logit", sh="feature")
+
+  def learning_rates(self):
+    c = self.config
+    return dict(position=c.lr_position, log_scaling=c.lr_log_scaling, rotation=c.lr_rotation, alpha_logit=c.lr_alpha_logit,
+                feature=c.lr_feature if self.color is not None else c.lr_sh)
+
   def state_dict(self):
-    """plain tensors / scalars only (reference checkpoints load with weights_only=True, trainer/checkpoint.py:38)."""
-    sd = {f"p.{k}": v.clone() for k, v in self.p.items()}
-    sd.update({f"m1.{k}": v.clone() for k, v in self.m1.items()})
-    sd.update({f"m2.{k}": v.clone() for k, v in self.m2.items()})
-    sd.update(running_vis=self.running_vis.clone(), opt_step=self.opt_step.clone(), sh_degree=self.config.sh_degree)
+    """dict(points=dict(tensors, parameter_groups, state, shared)[, color=...]) — the layout of the reference's
+    MLPScene.state_dict (`points` = ParameterClass.state_dict()), plain tensors / scalars only (reference checkpoints
+    load with weights_only=True, trainer/checkpoint.py:38).  gsb200.plugin.SHScene reads and writes the same layout."""
+    n = self.n
+    kinds = dict(position="local_vector", log_scaling="scalar", rotation="vector", alpha_logit="scalar", feature="vector")
+    lrs = self.learning_rates()
+    tensors = {self._CKPT[k]: v.clone() for k, v in self.p.items()}
+    tensors["alpha_logit"] = tensors["alpha_logit"].reshape(n, 1)
+    tensors["visible"] = self.visible.clone()
+    state = {self._CKPT[k]: dict(exp_avg=self.m1[k].clone().reshape(tensors[self._CKPT[k]].shape), exp_avg_sq=self.m2[k].clone())
+             for k in ATTRS}
+    o = self.ocfg
+    points = dict(tensors=tensors, parameter_groups={k: dict(lr=float(lrs[k]), type=kinds[k]) for k in kinds},
+                  state=state, shared=dict(step=self.opt_step.clone(), running_vis=self.running_vis.clone()),
+                  optim=dict(mode=int(o.mode), beta1=float(o.beta1), beta2=float(o.beta2), eps=float(o.eps),
+                             vis_beta=float(o.vis_beta), vis_smooth=float(o.vis_smooth), grad_clip=float(o.grad_clip),
+                             bias_correction=int(o.bias_correction)))
+    c = self.config
+    sd = dict(points=points, sh_degree=int(c.sh_degree), reg_weights=[float(x) for x in c.reg_weights],
+              loss=dict(w_l1=float(c.w_l1), w_mse=float(c.w_mse), w_ssim=float(c.w_ssim), ssim_levels=int(c.ssim_levels)))
     if self.color is not None:  # colour model + GLO table + their optimiser state (reference all_parameters, mlp_scene.py:291-298)
-      sd.update({f"color.{k}": v for k, v in self.color.state_dict().items()})
+      sd["color"] = self.color.state_dict()
     return sd
 
   @staticmethod
   def from_state_dict(sd, config=None, device="cuda"):
-    mlp = "color.flat" in sd
-    config = config or SceneConfig(sh_degree=int(sd["sh_degree"]), color_mlp=mlp,
-                                   num_images=int(sd["color.glo"].shape[0]) if mlp else 0)
-    g = {k: sd[f"p.{k}"] for k in ATTRS}
-    if mlp:
-      g["feature"] = g["sh"]
+    pts = sd["points"]
+    t = pts["tensors"]
+    mlp = "color" in sd
+    if config is None:
+      lr = {k: float(g["lr"]) for k, g in pts["parameter_groups"].items()}
+      loss = sd.get("loss", {})
+      config = SceneConfig(sh_degree=int(sd.get("sh_degree", round(t["feature"].shape[-1] ** 0.5) - 1 if not mlp else 3)),
+                           color_mlp=mlp, num_images=int(sd["color"]["glo"].shape[0]) if mlp else 0,
+                           lr_position=lr["position"], lr_log_scaling=lr["log_scaling"], lr_rotation=lr["rotation"],
+                           lr_alpha_logit=lr["alpha_logit"], optim=dict(pts.get("optim", {})),
+                           reg_weights=tuple(sd.get("reg_weights", (0.01, 1.0, 1e-4))), **loss)
+      if mlp:
+        config.lr_feature = lr["feature"]
+      else:
+        config.lr_sh = lr["feature"]
+    g = dict(position=t["position"], log_scaling=t["log_scaling"], rotation=t["rotation"],
+             alpha_logit=t["alpha_logit"].reshape(-1))
+    g["feature" if mlp else "sh"] = t["feature"]
     scene = SplatScene(g, config, device)
     if mlp:
-      scene.color.load_state_dict({k[len("color."):]: v for k, v in sd.items() if k.startswith("color.")})
+      scene.color.load_state_dict(sd["color"])
     for k in ATTRS:
-      scene.m1[k].copy_(sd[f"m1.{k}"]); scene.m2[k].copy_(sd[f"m2.{k}"])
-    scene.running_vis.copy_(sd["running_vis"]); scene.opt_step.copy_(sd["opt_step"])
+      st = pts.get("state", {}).get(SplatScene._CKPT[k])
+      if st:
+        scene.m1[k].copy_(st["exp_avg"].reshape(scene.m1[k].shape)); scene.m2[k].copy_(st["exp_avg_sq"].reshape(scene.m2[k].shape))
+    shared = pts.get("shared", {})
+    if "step" in shared:
+      scene.opt_step.copy_(shared["step"]); scene.running_vis.copy_(shared["running_vis"])
+    if "visible" in t:
+      scene.visible.copy_(t["visible"])
     return scene
