@@ -3,14 +3,21 @@
 
   python bench.py --gpus N --steps K --warmup W            our arm (libgsb200 on B200)
   python bench.py --impl reference --steps K --warmup W    CPU arm: the oracle restatement on the host cores
+  python bench.py --workload c5 [--gpus N]                 configs[4]: 500k -> 5M growth with densification in the loop
 
-A step = one optimiser iteration of the hot path: per rank one 1297x840 image of the C2 workload
-(3M splats, SH degree 3): project+SH -> tile map/sort -> raster fwd -> L1/MSE loss -> raster bwd -> project/SH
-bwd -> statistics, then (N>1) NCCL all-reduce of the packed gradients, then the fused visibility-aware
-optimiser.  Weak scaling: every rank renders a different camera of the batch (batch = N images).
-Prints ONE JSON line on rank 0.
+A step = one optimiser iteration of the hot path: per rank ONE image of the workload — project + SH -> tile map / sort ->
+raster forward -> loss (MSE 10 + 3-level SSIM 1.0 + reg_loss, the reference's defaults) -> raster backward -> projection /
+SH backward -> statistics — then, for N > 1, the exchange of the per-image gradient records over NVLink peer memory
+(folded in image order on every rank), then the fused visibility-aware LaProp step.  Weak scaling: every rank renders a
+different camera of the batch (batch = N images).  The timed window of K steps is repeated `--windows` times inside the
+run; `value` is the median window.  Prints ONE JSON line on rank 0.
+
+Workloads (gsb200.synthetic.WORKLOADS): c2 = BASELINE.json configs[1] generated exactly as SURVEY.md 8(d) writes it (the
+default); c2-sparse = round 1's generator (opaque small splats: ~3 % of the in-view rows blend); c2-trained = translucent
+splats (most in-view rows blend); c1, c4 = configs[0], configs[3]; c5 = configs[4].
 """
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -22,13 +29,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(ROOT, "splat-trainer_b200"))
 sys.path.insert(0, ROOT)
 
-WORKLOADS = {
-  # name: (points, sh_degree, width, height)
-  "c1": (100_000, 0, 640, 480),       # BASELINE.json configs[0]: the CPU-runnable case
-  "c2": (3_000_000, 3, 1297, 840),    # configs[1]: the configuration the metric is quoted on
-  "c4": (6_000_000, 3, 3840, 2160),   # configs[3]: high-res stress
-}
 VIEWS_PER_RANK = 4
+LOSS = "fwd + loss (MSE 10 + 3-level SSIM 1.0 + reg) + bwd + fused visibility-aware LaProp step"
 
 
 def parse():
@@ -36,8 +38,9 @@ def parse():
   ap.add_argument("--gpus", type=int, default=1)
   ap.add_argument("--steps", type=int, default=20)
   ap.add_argument("--warmup", type=int, default=3)
+  ap.add_argument("--windows", type=int, default=5, help="the --steps window is timed this many times; value = the median window")
   ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-  ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+  ap.add_argument("--workload", default="c2", choices=["c1", "c2", "c2-sparse", "c2-trained", "c4", "c5"])
   ap.add_argument("--points", type=int, default=0, help="override the splat count (testing only)")
   ap.add_argument("--no-cpu-baseline", action="store_true")
   ap.add_argument("--scene", default="sh", choices=["sh", "mlp"],
@@ -46,16 +49,29 @@ def parse():
   ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl", "dense", "local"],
                   help="N>1 gradient/statistics exchange: per-image records over peer memory (auto/peer), records "
                        "all-gathered by NCCL, or the dense SUM all-reduce of the packed gradient buffer")
+  ap.add_argument("--raster", default="async", choices=["async", "gather"])
+  ap.add_argument("--c5-steps", type=int, default=2000, help="c5: optimiser steps of the whole 500k -> 5M run")
   return ap.parse_args()
 
 
-def measured_traffic(stage):
-  """dram__bytes_read.sum + dram__bytes_write.sum of the stage's kernels per image from the committed ncu --set full
-  capture of this same command (profiles/: cold-cache, serialised launches), or None."""
-  path = os.path.join(ROOT, "profiles", "r1p_traffic.json")
+def build_id():
+  """hash of the CUDA sources: ties a committed ncu capture to the build it was taken from"""
+  h = hashlib.sha1()
+  d = os.path.join(ROOT, "splat-trainer_b200", "csrc")
+  for f in sorted(os.listdir(d)):
+    if f.endswith((".cu", ".cuh")):
+      h.update(open(os.path.join(d, f), "rb").read())
+  return h.hexdigest()[:12]
+
+
+def measured_traffic(workload):
+  """dram__bytes_read.sum + dram__bytes_write.sum per image and per stage from the committed `ncu --set full` capture
+  of this command (profiles/r2_traffic_<workload>.json), used only when it was taken from THIS build."""
+  path = os.path.join(ROOT, "profiles", f"r2_traffic_{workload}.json")
   try:
     with open(path) as f:
-      return json.load(f)["dram_bytes_per_image"].get(stage)
+      t = json.load(f)
+    return t if t.get("build_id") == build_id() else None
   except Exception:
     return None
 
@@ -86,7 +102,7 @@ class ClockSampler:
           self.samples.append([x.strip() for x in out.split(",")])
       except Exception:
         pass
-      time.sleep(0.1)
+      time.sleep(0.05)
 
   def __enter__(self):
     self.thread.start()
@@ -105,116 +121,146 @@ class ClockSampler:
                 samples=len(self.samples))
 
 
+def workload_string(args, wl, world):
+  colour = "MLP colour (feature 16 + GLO 32)" if args.scene == "mlp" else f"SH{wl['sh_degree']}"
+  return f"{wl['description']}; {colour}; 1 image per step per arm unit; {LOSS}"
+
+
 # ---- CPU arm: the oracle (test infrastructure) timed as the reported baseline ------------------------------------
-class CpuIteration:
-  """One full hot-path iteration of the workload in the CPU oracle (oracle/gs_oracle.c, OpenMP)."""
-
-  def __init__(self, g, cams, targets_u8, sh_degree):
-    import numpy as np
-    from oracle import gs_oracle as go
-    self.np, self.go = np, go
-    self.orc = go.Oracle("f32")
-    self.g = {k: v.copy() for k, v in g.items()}
-    self.cams = [go.make_camera(c["T"], c["fx"], c["fy"], c["cx"], c["cy"], c["width"], c["height"], c["near"], c["far"])
-                 for c in cams]
-    self.targets, self.deg = targets_u8, sh_degree
-    self.cfg = go.make_config()
-    self.ocfg = go.make_optim_config()
-    n = g["position"].shape[0]
-    z = lambda *s: np.zeros(s, np.float32)
-    self.m1 = dict(position=z(n, 3), log_scaling=z(n, 3), rotation=z(n, 4), alpha_logit=z(n), sh=np.zeros_like(g["sh"]))
-    self.m2 = dict(position=z(n), log_scaling=z(n, 3), rotation=z(n), alpha_logit=z(n), sh=z(n))
-    self.running, self.step = z(n), z(n)
-    self.stats = dict(prune_cost=z(n), split_score=z(n), max_scale_px=z(n), points_in_view=np.zeros(n, np.int16),
-                      visibility=z(n), scene_visible=z(n))
-
-  def iteration(self, i):
-    o, g, cfg, np = self.orc, self.g, self.cfg, self.np
-    cam = self.cams[i % len(self.cams)]
-    W, H = cam.width, cam.height
-    g2d, depth, rgb = o.project_fwd(cam, cfg, g["position"], g["log_scaling"], g["rotation"], g["alpha_logit"], g["sh"], self.deg)
-    o2p, ranges, total, _ = o.tile_map(cfg, g2d, depth, W, H)
-    image, fT, nc, _, _ = o.raster_fwd(cfg, g2d, rgb, depth, o2p, ranges, W, H, visibility=False)
-    tu8 = self.targets[i % len(self.targets)]
-    dimg, sums = o.loss_l1_mse(image, None, 0.0, 10.0, target_u8=tu8)
-    # multi-scale SSIM with the reference's default weights (ssim 1.0, 3 levels), like SplatScene.forward_backward
-    _, dssim, _ = o.ssim_loss(np.clip(image, 0, 1), tu8.astype(np.float32) / 255.0, levels=3, weight=1.0)
-    dimg = dimg + np.where((image >= 0) & (image <= 1), dssim, 0).astype(np.float32)
-    acc = o.raster_bwd(cfg, g2d, rgb, o2p, ranges, W, H, fT, nc, dimg)
-    # reg_loss with the reference's yaml weights, like SplatScene.forward_backward
-    vis = np.ascontiguousarray(acc[:, 11]); d_op = np.ascontiguousarray(acc[:, 5])
-    d_depth = np.zeros_like(vis); d_ls = np.zeros((vis.shape[0], 3), np.float32)
-    o.reg_loss((0.01, 1.0, 1e-4), g2d, depth, g["log_scaling"], vis, d_op, d_depth, d_ls)
-    acc[:, 5] = d_op
-    grads = o.project_bwd(cam, cfg, g["position"], g["log_scaling"], g["rotation"], g["alpha_logit"], g["sh"], self.deg,
-                          g2d, acc[:, 0:6], acc[:, 6:9], d_depth, row_vis=acc[:, 11])
-    grads["log_scaling"] = grads["log_scaling"] + d_ls
-    st = self.stats
-    o.accumulate_stats(None, g2d, np.ascontiguousarray(acc[:, 11]), np.ascontiguousarray(acc[:, 9:11]), 0.01, 0.1, st)
-    vis = st["scene_visible"]
-    o.optim_vis_update(self.ocfg, vis, self.running, self.step)
-    lr = dict(position=0.05, log_scaling=0.02, rotation=0.01, alpha_logit=0.05, sh=0.01)
-    kind = dict(position=2, log_scaling=0, rotation=1, alpha_logit=0, sh=1)
-    post = dict(position=(0, 0, 0), log_scaling=(2, -8.0, 8.0), rotation=(1, 0, 0), alpha_logit=(0, 0, 0), sh=(0, 0, 0))
-    bls, bq = g["log_scaling"].copy(), g["rotation"].copy()
-    for name in ("position", "log_scaling", "rotation", "alpha_logit", "sh"):
-      o.optim_step(self.ocfg, kind[name], lr[name], g[name], grads[name], self.m1[name], self.m2[name], vis, self.running,
-                   self.step, bls, bq, post[name][0], post[name][1], post[name][2], 1)
-    vis[:] = 0
-    return float(sums[1])
+def host_threads():
+  return len(os.sched_getaffinity(0))
 
 
-def make_workload(args):
-  from gsb200 import synthetic as syn
-  n, deg, W, H = WORKLOADS[args.workload]
-  if args.points:
-    n = args.points
-  g = syn.garden_scene(n, deg, seed=0)
-  cams = syn.ring_cameras(185, W, H, seed=0)  # garden has 185 views
-  return n, deg, W, H, g, cams
+def make_cpu_scene(wl):
+  """the workload in the CPU oracle (oracle/gs_train.py, OpenMP over all the host cores this process may use —
+  set explicitly: torchrun exports OMP_NUM_THREADS=1)."""
+  from gsb200.scene import SceneConfig
+  from oracle import gs_oracle as go
+  from oracle import gs_train as gt
+  cfg = SceneConfig(sh_degree=wl["sh_degree"])
+  lrs = dict(position=cfg.lr_position, log_scaling=cfg.lr_log_scaling, rotation=cfg.lr_rotation,
+             alpha_logit=cfg.lr_alpha_logit, sh=cfg.lr_sh)
+  sc = gt.OracleScene(wl["gaussians"], wl["sh_degree"], lrs, w_l1=cfg.w_l1, w_mse=cfg.w_mse, w_ssim=cfg.w_ssim,
+                      ssim_levels=cfg.ssim_levels, reg_weights=cfg.reg_weights, blur_cov=cfg.blur_cov)
+  sc.orc.set_threads(host_threads())
+  return sc, go, gt
 
 
-def algorithmic_bytes(n, d, v, o, p, t, v_opt):
-  """SURVEY.md §8(d) byte model per training image (+ the optimiser over the rows it touches)."""
-  return dict(project_fwd=12 * n + 4 * (d - 3) * v + 44 * v,
-              tile_map=28 * v + 4 * v + 12 * o + 8 * t + 6 * 24 * o + 8 * o,  # map + 6-pass 64-bit-key sort model
-              raster_fwd=40 * o + 16 * p,
-              raster_bwd=40 * o + 28 * p + 36 * v,
-              project_bwd=36 * v + 8 * d * v,
-              stats=40 * v,
-              optim=7 * 4 * d * v_opt)
+def oracle_cameras(go, cams, W, H):
+  return [go.make_camera(c["T"], c["fx"], c["fy"], c["cx"], c["cy"], W, H, c["near"], c["far"]) for c in cams]
 
 
 def run_reference(args):
   """--impl reference: the path's CPU implementation on the host cores.  The reference's own kernels live in the
-  absent taichi-splatting package (unbuildable here: DESIGN.md "Oracle"), so this is the oracle port."""
+  absent taichi-splatting package (unbuildable here: DESIGN.md "Oracle"), so this is the oracle port — same workload,
+  same targets (rendered from the workload's target scene, stored as uint8), visibility on, every host core."""
   import numpy as np
   rank = int(os.environ.get("RANK", "0"))
   if rank != 0:
     return
-  n, deg, W, H, g, cams = make_workload(args)
-  rng = np.random.default_rng(1)
-  views = cams[:VIEWS_PER_RANK]
-  targets = [rng.integers(0, 256, (H, W, 3), dtype=np.uint8) for _ in views]
-  cpu = CpuIteration(g, views, targets, deg)
+  from gsb200 import synthetic as syn
+  wl = syn.workload("c2" if args.workload == "c5" else args.workload, points=args.points)
+  W, H = wl["width"], wl["height"]
+  sc, go, gt = make_cpu_scene(wl)
+  views = wl["cameras"][:VIEWS_PER_RANK]
+  ocams = oracle_cameras(go, views, W, H)
+  tgt = gt.OracleScene(wl["target_gaussians"], wl["sh_degree"], sc.lrs)
+  tgt.orc.set_threads(host_threads())
+  targets = [np.clip(tgt.render(oc) * 255.0 + 0.5, 0, 255).astype(np.uint8) for oc in ocams]
+  del tgt
   for i in range(args.warmup):
-    cpu.iteration(i)
+    sc.training_step([(ocams[i % len(ocams)], targets[i % len(ocams)])])
   t0 = time.perf_counter()
   for i in range(args.steps):
-    cpu.iteration(args.warmup + i)
+    k = (args.warmup + i) % len(ocams)
+    sc.training_step([(ocams[k], targets[k])])
   dt = time.perf_counter() - t0
-  cores = len(os.sched_getaffinity(0))
+  cores = host_threads()
   value = args.steps / dt
   unit = "iters/s"
+  world = int(os.environ.get("WORLD_SIZE", "1"))
   line = {"impl": "reference", "metric": "train_iters_per_sec", "value": value, "unit": unit, "n_gpus": args.gpus,
           "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
           "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-          "config": {"workload": f"{args.workload}: {n} splats SH{deg} {W}x{H}, 1 image/step on the host CPU",
-                     "images_per_step": 1},
+          "config": {"workload": workload_string(args, wl, world), "images_per_step": 1},
           "cpu_baseline": {"value": value, "unit": unit, "cores": cores, "kind": "port",
-                           "sample": f"{args.steps} full iterations of the same workload (random uint8 targets)"},
+                           "sample": f"{args.steps} full iterations of the same workload, same targets, after {args.warmup} warm-up, "
+                                     f"OpenMP oracle on {sc.orc.get_threads()} threads"},
           "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
   emit(line)
+
+
+def algorithmic_bytes(n, d, v, o, p, t, v_blend):
+  """SURVEY.md §8(d) byte model per training image.  The backward / statistics / optimiser terms are charged for the
+  rows a pixel actually blended (v_blend), not for every in-view row: the kernels legitimately never touch the others."""
+  return dict(project_fwd=12 * n + 4 * (d - 3) * v + 44 * v,
+              tile_map=28 * v + 4 * v + 12 * o + 8 * t + 6 * 24 * o + 8 * o,  # map + 6-pass 64-bit-key sort model
+              raster_fwd=40 * o + 16 * p,
+              raster_bwd=40 * o + 28 * p + 36 * v_blend,
+              project_bwd=36 * v_blend + 8 * d * v_blend,
+              stats=40 * v_blend,
+              optim=7 * 4 * d * v_blend)
+
+
+def median(xs):
+  s = sorted(xs)
+  return s[len(s) // 2]
+
+
+def setup_b200(args, workload_name):
+  """process group, library, workload, scene, targets, trainer — shared by the steady-state bench and the c5 run"""
+  import numpy as np
+  import torch
+  import torch.distributed as dist
+  from gsb200 import lib as L
+  from gsb200 import ops
+  from gsb200 import synthetic as syn
+  from gsb200.scene import SceneConfig, SplatScene
+
+  world = int(os.environ.get("WORLD_SIZE", "1"))
+  rank = int(os.environ.get("RANK", "0"))
+  local = int(os.environ.get("LOCAL_RANK", "0"))
+  torch.cuda.set_device(local)
+  if world > 1 and not dist.is_initialized():
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+  L.load()
+  # the knn3-derived scales of the SURVEY 8(d) scene come from the library's own k-NN kernel (gs_knn_scale)
+  knn = lambda p: ops.estimate_scale(torch.as_tensor(p, device="cuda"), 3).cpu().numpy()
+  wl = syn.workload(workload_name, points=args.points, knn=knn)
+  W, H = wl["width"], wl["height"]
+  cams = wl["cameras"]
+  views = [cams[(rank + world * j) % len(cams)] for j in range(VIEWS_PER_RANK)]
+  lcams = [L.make_camera(c["T"], c["fx"], c["fy"], c["cx"], c["cy"], W, H, c["near"], c["far"]) for c in views]
+  # targets: renders of the workload's target scene, stored as uint8 like the reference's dataset
+  tgt_scene = SplatScene(wl["target_gaussians"], SceneConfig(sh_degree=wl["sh_degree"]))
+  host_targets = []
+  for cam in lcams:
+    for _ in range(4):
+      img = tgt_scene.render(cam)["image"]
+      if not tgt_scene.overflowed():
+        break
+      tgt_scene.grow_overlaps(2.0)
+    host_targets.append((img * 255.0 + 0.5).to(torch.uint8).cpu().pin_memory())
+  del tgt_scene
+  torch.cuda.empty_cache()
+  return dict(world=world, rank=rank, local=local, wl=wl, W=W, H=H, views=views, lcams=lcams, host_targets=host_targets,
+              dev_targets=[t.cuda() for t in host_targets])
+
+
+def replicas_identical(scene, world):
+  """outside the timed region: every rank holds bit-identical parameters and moments (MIN == MAX of a 64-bit digest)"""
+  import torch
+  import torch.distributed as dist
+  if world <= 1:
+    return None
+  digest = []
+  for t in (scene.params[:scene._total], scene.exp_avg[:scene._total], scene.exp_avg_sq_flat, scene.running_vis):
+    digest.append(t.view(torch.int32).to(torch.int64).sum())
+  lo = torch.stack(digest).clone()
+  hi = lo.clone()
+  dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+  dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+  return bool(torch.equal(lo, hi))
 
 
 def run_b200(args):
@@ -225,39 +271,22 @@ def run_b200(args):
   from gsb200.scene import SceneConfig, SplatScene
   from gsb200.trainer import StageTimer, Trainer
 
-  world = int(os.environ.get("WORLD_SIZE", "1"))
-  rank = int(os.environ.get("RANK", "0"))
-  local = int(os.environ.get("LOCAL_RANK", "0"))
-  torch.cuda.set_device(local)
-  if world > 1:
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-  L.load()
-  n, deg, W, H, g, cams = make_workload(args)
-  from gsb200 import synthetic as syn
-  # this rank's views of every step's batch (batch = world images, rank r renders batch[r::world])
-  views = [cams[(rank + world * j) % len(cams)] for j in range(VIEWS_PER_RANK)]
-  lcams = [L.make_camera(c["T"], c["fx"], c["fy"], c["cx"], c["cy"], W, H, c["near"], c["far"]) for c in views]
-  # targets: renders of a perturbed copy of the scene (seed 1), stored as uint8 like the reference's dataset
-  tgt_scene = SplatScene(syn.perturbed(g, seed=1), SceneConfig(sh_degree=deg))
-  host_targets = []
-  for cam in lcams:
-    img = (tgt_scene.render(cam)["image"] * 255.0 + 0.5).to(torch.uint8)
-    host_targets.append(img.cpu().pin_memory())
-  del tgt_scene
-  torch.cuda.empty_cache()
-  dev_targets = [t.cuda() for t in host_targets]
+  S = setup_b200(args, args.workload)
+  world, rank, local, wl, W, H = S["world"], S["rank"], S["local"], S["wl"], S["W"], S["H"]
+  lcams, host_targets, dev_targets = S["lcams"], S["host_targets"], S["dev_targets"]
+  n, deg, g = wl["n"], wl["sh_degree"], wl["gaussians"]
   if args.scene == "mlp":
     gm = {k: v for k, v in g.items() if k != "sh"}
     gm["feature"] = np.random.default_rng(7).normal(0, 1, (n, 16)).astype(np.float32)
-    scene = SplatScene(gm, SceneConfig(sh_degree=deg, color_mlp=True, num_images=VIEWS_PER_RANK * world))
+    scene = SplatScene(gm, SceneConfig(sh_degree=deg, color_mlp=True, num_images=VIEWS_PER_RANK * world, raster=args.raster))
   else:
-    scene = SplatScene(g, SceneConfig(sh_degree=deg))
+    scene = SplatScene(g, SceneConfig(sh_degree=deg, raster=args.raster))
   if args.exchange == "local":  # N=1 only: run the pack/fold kernels of the DP exchange on one GPU (for profiling them)
     from gsb200.exchange import ImageExchange
     local_k = int(os.environ.get("GS_LOCAL_IMAGES", "1"))  # K different images per step packed + folded on one GPU
-    trainer = Trainer(scene, 1, 0, exchange=ImageExchange(scene, 1, 0, transport="local", images_per_rank=local_k))
+    trainer = Trainer(scene, 1, 0, exchange=ImageExchange(scene, 1, 0, transport="local", images_per_rank=local_k), check_every=0)
   else:
-    trainer = Trainer(scene, world, rank, exchange=args.exchange)
+    trainer = Trainer(scene, world, rank, exchange=args.exchange, check_every=0)  # overflow is checked around the timed region
 
   def batch_for(i, targets):
     # the step's full batch has `world` images; only this rank's entry is materialised (others are None-padded)
@@ -277,12 +306,11 @@ def run_b200(args):
       dist.barrier()
     torch.cuda.synchronize()
 
-  for i in range(max(args.warmup, 3)):
+  warm = max(args.warmup, 3)
+  for i in range(warm + len(lcams)):  # every view of the rotation once: capacities see the largest of them
     step(i, dev_targets)
-  torch.cuda.synchronize()
-  if scene.overflowed():
-    scene.grow_overlaps(2.0)
-    step(0, dev_targets)
+    torch.cuda.synchronize()
+    trainer.check_overflow()
   exchange_info = None
   if trainer.exchange is not None:
     # size the records from the rows the warm-up images really blended (one host read at start-up, all ranks agree)
@@ -299,67 +327,88 @@ def run_b200(args):
   elif world > 1:
     exchange_info = {"transport": "dense-allreduce", "dense_allreduce_bytes": int(scene.grads.numel() * 4)}
 
-  # ---- device-resident throughput (value) with per-stage CUDA events ----------------------------------------------
+  # ---- device-resident throughput (value): R windows of K steps, no stage events inside ---------------------------
+  scene.timer = None
+  lib = L.load()
+  window_ms, launches_per_step = [], None
+  with ClockSampler(local) as clocks:
+    for r in range(args.windows):
+      barrier()
+      e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+      l0 = lib.gs_launch_count()
+      e0.record()
+      h0 = time.perf_counter()
+      for i in range(args.steps):
+        step(warm + i, dev_targets)
+      host_enqueue_ms = 1e3 * (time.perf_counter() - h0) / args.steps  # CPU time to enqueue one step (no sync inside)
+      e1.record()
+      barrier()
+      launches_per_step = (lib.gs_launch_count() - l0) / args.steps
+      t = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
+      if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+      window_ms.append(float(t.item()))
+  ms = median(window_ms)
+  overflow = scene.overflowed()
+
+  # ---- per-stage CUDA events (a separate loop: one event per stage perturbs the enqueue) --------------------------
   timer = StageTimer()
   scene.timer = timer
   barrier()
-  e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-  with ClockSampler(local) as clocks:
-    e0.record()
-    h0 = time.perf_counter()
-    for i in range(args.steps):
-      step(args.warmup + i, dev_targets)
-    host_enqueue_ms = 1e3 * (time.perf_counter() - h0) / args.steps  # CPU time to enqueue one step (no sync inside)
-    e1.record()
-    barrier()
-  ms = e0.elapsed_time(e1)
+  for i in range(args.steps):
+    step(warm + i, dev_targets)
   stages = {k: float(np.mean(v)) for k, v in timer.collect().items()}
   scene.timer = None
-  overflow = scene.overflowed()
 
   # ---- end to end through the public API with HOST buffers --------------------------------------------------------
   for i in range(3):  # untimed: first use of the upload stream and its two device buffers
     step(i, host_targets, read_loss=True)
-  barrier()
-  t0 = time.perf_counter()
-  per_step = []
-  for i in range(args.steps):
-    loss = step(args.warmup + i, host_targets, read_loss=True)
-    per_step.append(time.perf_counter())
-  torch.cuda.synchronize()
-  if world > 1:
-    dist.barrier()
-  e2e_s = time.perf_counter() - t0
+  e2e_windows = []
+  loss = None
+  for r in range(args.windows):
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+      loss = step(warm + i, host_targets, read_loss=True)
+    torch.cuda.synchronize()
+    if world > 1:
+      dist.barrier()
+    t = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
+    if world > 1:
+      dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_windows.append(float(t.item()))
+  e2e_s = median(e2e_windows)
+  identical = replicas_identical(scene, world)
 
-  if os.environ.get("GS_BENCH_DEBUG"):
-    print("e2e per-step ms:", [round(1e3 * (b - a), 3) for a, b in zip([t0] + per_step[:-1], per_step)], file=sys.stderr)
-  if world > 1:
-    t = torch.tensor([ms, e2e_s], device="cuda", dtype=torch.float64)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, e2e_s = float(t[0].item()), float(t[1].item())
-
+  # ---- what the last image did (outside every timed region) -----------------------------------------------------------
   w = scene._work
   counters = w["tile"].counters.cpu().tolist()
   O = int(counters[0])
   V = int((w["g2d"][:, 5] > 0).sum().item())
   v_opt = int(scene._vis_idx.count.item())  # rows the last optimiser step touched (device-side visible.nonzero())
-  P, T, D = W * H, ((W + 15) // 16) * ((H + 15) // 16), 11 + (16 if args.scene == "mlp" else 3 * (deg + 1) ** 2)
-  bytes_ = algorithmic_bytes(n, D, V, O, P, T, v_opt)
+  blend = None
+  if w["aux"] is not None:  # instrumented forward of the same image: pairs actually evaluated / blended
+    from gsb200 import ops
+    cnt = torch.zeros((8,), device="cuda", dtype=torch.int64)
+    tb = w["tile"]
+    ops.raster_fwd(scene.raster_cfg, w["g2d"], w["rgb"], w["depth"], tb.overlap_to_point, tb.tile_ranges, W, H,
+                   out=(w["image"], w["final_T"], w["n_contrib"]), aux=w["aux"], counters=cnt)
+    c = cnt.cpu().tolist()
+    blend = dict(records_staged=c[3], warp_splat_iterations=c[0], iterations_with_a_blend=c[1], blend_pairs=c[2])
+  P, T = W * H, ((W + 15) // 16) * ((H + 15) // 16)
+  D = 11 + (16 if args.scene == "mlp" else 3 * (deg + 1) ** 2)
+  # under DP the optimiser visits the union of the batch's rows; the per-image terms use this rank's own image
+  rows_image = int(trainer.exchange.counts()[0][0]) if (trainer.exchange is not None and world > 1) else v_opt
+  bytes_ = algorithmic_bytes(n, D, V, O, P, T, rows_image)
+  bytes_["optim"] = 7 * 4 * D * v_opt
   hbm, which = peaks()
   dom = max(("raster_fwd", "raster_bwd", "tile_map", "project_fwd", "project_bwd", "optim"), key=lambda k: stages.get(k, 0.0))
   dom_ms = stages[dom]
   achieved = bytes_[dom] / (dom_ms * 1e-3) / 1e9
   iter_bytes = sum(bytes_.values())
   ms_step = ms / args.steps
-  # kernels of libgsb200 per image: project_fwd, tile map (live compaction, depth sort = histogram + 4 passes,
-  # super-tile pairs, their sort = histogram + passes, segment tables, expand count, chunk prefix, expand write),
-  # raster_fwd, loss, raster_bwd, project_bwd, statistics; per step: optimiser begin + 5 parameter groups
-  n_super = ((W + 127) // 128) * ((H + 127) // 128)
-  super_passes = (max(1, (n_super - 1).bit_length()) + 7) // 8
-  launches_image = 1 + (1 + 5 + 1 + 1 + super_passes + 4) + 5
-  launches = launches_image + 6
-  if trainer.exchange is not None:
-    launches += 1 + 2  # pack = 2 kernels in place of the statistics pass; fold = 2 kernels (NCCL's own not counted)
+  traffic = measured_traffic(args.workload) if (not args.points and args.scene == "sh" and world == 1) else None
+  dram_step = traffic["dram_bytes_per_step"] if traffic else None
 
   if rank == 0:
     line = {
@@ -368,39 +417,116 @@ def run_b200(args):
       "metric": "train_iters_per_sec", "value": world * args.steps / (ms * 1e-3), "unit": "iters/s",
       "optimizer_steps_per_sec": args.steps / (ms * 1e-3),
       "raster_fwd_bwd_mpix_per_sec": world * P / ((stages["raster_fwd"] + stages["raster_bwd"]) * 1e-3) / 1e6,
-      "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
+      "n_gpus": world, "steps": args.steps, "warmup": warm, "ms_per_step": ms_step,
+      "windows": {"count": args.windows, "ms_per_step": [x / args.steps for x in window_ms],
+                  "min": min(window_ms) / args.steps, "median": ms_step, "max": max(window_ms) / args.steps},
       "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-      "config": {"workload": f"{args.workload}: {n} splats {'MLP colour (feature 16 + GLO 32)' if args.scene == 'mlp' else f'SH{deg}'} {W}x{H}, camera batch = {world} (1 image per GPU per step), "
-                             "fwd + loss (MSE 10 + 3-level SSIM 1.0 + reg) + bwd + fused visibility-aware LaProp step", "images_per_step": world,
+      "config": {"workload": workload_string(args, wl, world), "images_per_step": world,
                  "l2": f"inputs larger than L2 (params+grads+moments {4 * 4 * D * n / 1e9:.1f} GB, overlap list {4 * O / 1e6:.0f} MB)",
-                 "parallelism": f"dp{world}", "V_in_view": V, "O_overlaps": O, "V_optimised": v_opt, "overflow": overflow},
+                 "parallelism": f"dp{world}", "raster": args.raster, "V_in_view": V, "O_overlaps": O, "rows_blended": rows_image,
+                 "V_optimised": v_opt, "blend": blend, "overflow": overflow, "build_id": build_id()},
       "stages_ms": stages, "host_enqueue_ms_per_step": host_enqueue_ms,
       "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                   "traffic": measured_traffic(dom) if args.workload == "c2" and not args.points and args.scene == "sh" else None,
-                   "traffic_source": "profiles/r1p_traffic.json (ncu --set full of the c2 command)",
+                   "traffic": traffic["dram_bytes_per_image"].get(dom) if traffic else None,
+                   "traffic_source": f"profiles/r2_traffic_{args.workload}.json (ncu --set full of this command, build {build_id()})" if traffic else None,
                    "peak_source": which, "algorithmic_bytes": bytes_[dom],
                    "iteration": {"algorithmic_bytes": iter_bytes, "achieved": iter_bytes / (ms_step * 1e-3) / 1e9,
-                                 "frac": iter_bytes / (ms_step * 1e-3) / 1e9 / hbm}},
+                                 "frac": iter_bytes / (ms_step * 1e-3) / 1e9 / hbm, "dram_bytes_per_step": dram_step,
+                                 "iteration_measured_frac": dram_step / (ms_step * 1e-3) / 1e9 / hbm if dram_step else None}},
       "e2e": {"value": world * args.steps / e2e_s, "unit": "iters/s", "h2d_bytes_per_step": int(host_targets[0].numel()),
-              "d2h_bytes_per_step": 8},
-      "gpu_launches": launches * args.steps,
+              "d2h_bytes_per_step": 8, "windows_s": e2e_windows},
+      "gpu_launches": int(round(launches_per_step * args.steps)), "gpu_launches_per_step": launches_per_step,
       "clocks": clocks.summary(),
       "last_loss_mse": loss[1] / (P * 3),
     }
+    if identical is not None:
+      line["replicas_identical"] = identical
     if exchange_info:
       if trainer.exchange is not None:
         exchange_info["overflow"] = any(o for _, o in trainer.exchange.counts())
       line["exchange"] = exchange_info
     if world == 1 and not args.no_cpu_baseline and args.scene == "sh":
-      cpu = CpuIteration(g, views[:1], [host_targets[0].numpy()], deg)
-      cpu.iteration(0)  # warm-up (page faults, OpenMP pool)
+      sc, go, gt = make_cpu_scene(wl)
+      ocam = oracle_cameras(go, S["views"][:1], W, H)[0]
+      tu8 = host_targets[0].numpy()
+      sc.training_step([(ocam, tu8)])  # warm-up (page faults, OpenMP pool)
       t0 = time.perf_counter()
       reps = 2
       for i in range(reps):
-        cpu.iteration(i)
+        sc.training_step([(ocam, tu8)])
       dt = (time.perf_counter() - t0) / reps
-      line["cpu_baseline"] = {"value": 1.0 / dt, "unit": "iters/s", "cores": len(os.sched_getaffinity(0)), "kind": "port",
-                              "sample": f"{reps} full iterations of the same workload (after 1 warm-up) in the OpenMP oracle"}
+      line["cpu_baseline"] = {"value": 1.0 / dt, "unit": "iters/s", "cores": host_threads(), "kind": "port",
+                              "sample": f"{reps} full iterations of the same workload and target (after 1 warm-up) in the "
+                                        f"OpenMP oracle on {sc.orc.get_threads()} threads"}
+    emit(line)
+  if world > 1:
+    dist.destroy_process_group()
+
+
+def run_c5(args):
+  """BASELINE.json configs[4]: 500k -> 5M growth with split / clone / prune compaction in the training loop, following
+  the reference's TargetController schedule (controller/target_controller.py:73-126, config/controller/target.yaml) over
+  `--c5-steps` optimiser steps.  Under N > 1 the statistics are synchronised and every rank densifies redundantly."""
+  import numpy as np
+  import torch
+  import torch.distributed as dist
+  from gsb200.controller import TargetConfig, TargetController
+  from gsb200.scene import SceneConfig, SplatScene
+  from gsb200.trainer import Trainer
+
+  args.points = args.points or 500_000
+  S = setup_b200(args, "c2")
+  world, rank, local, wl, W, H = S["world"], S["rank"], S["local"], S["wl"], S["W"], S["H"]
+  lcams, dev_targets = S["lcams"], S["dev_targets"]
+  target_points = 10 * wl["n"]
+  total_images = args.c5_steps * world  # the reference's schedule counts images (trainer/trainer.py:532)
+  scene = SplatScene(wl["gaussians"], SceneConfig(sh_degree=wl["sh_degree"], raster=args.raster, capacity=int(1.02 * target_points)))
+  trainer = Trainer(scene, world, rank, exchange=args.exchange, check_every=25)
+  controller = TargetController(TargetConfig(), scene, target_points, total_images, trainer=trainer, seed=0)
+  controller.record_events = True
+  trainer.controller = controller
+
+  def batch_for(i):
+    b = [None] * world
+    b[rank] = (lcams[i % len(lcams)], dev_targets[i % len(dev_targets)])
+    return b
+
+  for i in range(max(args.warmup, 3)):  # untimed: capacities, exchange, first-use allocations (no densify before step 50)
+    trainer.training_step(batch_for(i))
+  torch.cuda.synchronize()
+  if world > 1:
+    dist.barrier()
+  torch.cuda.reset_peak_memory_stats()
+  e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+  with ClockSampler(local) as clocks:
+    e0.record()
+    t0 = time.perf_counter()
+    for i in range(args.c5_steps):
+      trainer.training_step(batch_for(i))
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+      dist.barrier()
+    wall = time.perf_counter() - t0
+  t = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
+  if world > 1:
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+  ms = float(t.item())
+  dens = [a.elapsed_time(b) for a, b in controller.events]
+  identical = replicas_identical(scene, world)
+  if rank == 0:
+    line = {"metric": "train_iters_per_sec", "value": world * args.c5_steps / (ms * 1e-3), "unit": "iters/s",
+            "n_gpus": world, "steps": args.c5_steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.c5_steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"c5: {wl['n']} -> {target_points} splats SH{wl['sh_degree']} {W}x{H}, TargetController schedule over "
+                                   f"{total_images} images (densify every 50/100/200 images x1), camera batch = {world}; {LOSS}",
+                       "parallelism": f"dp{world}", "final_points": scene.num_points, "capacity": scene.capacity},
+            "densify": {"count": len(dens), "ms_mean": float(np.mean(dens)) if dens else None, "ms_max": max(dens) if dens else None,
+                        "ms_total": float(np.sum(dens)) if dens else 0.0, "points": [h[2] for h in controller.history]},
+            "wall_s": wall, "peak_memory_gb": torch.cuda.max_memory_allocated() / 1e9,
+            "overflow_events": trainer.overflow_events, "clocks": clocks.summary()}
+    if identical is not None:
+      line["replicas_identical"] = identical
     emit(line)
   if world > 1:
     dist.destroy_process_group()
@@ -422,5 +548,7 @@ if __name__ == "__main__":
   a = parse()
   if a.impl == "reference":
     run_reference(a)
+  elif a.workload == "c5":
+    run_c5(a)
   else:
     run_b200(a)

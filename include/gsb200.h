@@ -76,6 +76,8 @@ typedef struct gs_reg_fuse {
 void gs_default_raster_config(gs_raster_config *cfg);
 int gs_version(void);
 const char *gs_last_error(void);
+/* Diagnostics: number of kernels this library has launched in this process (what bench.py reports as gpu_launches). */
+unsigned long long gs_launch_count(void);
 
 /* ---------------------------------------------------------------------------------------
  * (1) 3D→2D projection + SH colour.   Serves taichi_splatting.project_to_image

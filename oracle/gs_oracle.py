@@ -82,6 +82,12 @@ class Oracle:
     self.lib.gso_exp_lerp.restype = C.c_float if precision == "f32" else C.c_double
     self.lib.gso_exp_lerp.argtypes = [self.lib.gso_exp_lerp.restype] * 3
 
+  def set_threads(self, n):
+    self.lib.gso_set_threads(C.c_int(int(n)))
+
+  def get_threads(self):
+    return int(self.lib.gso_get_threads())
+
   # -- helpers -------------------------------------------------------------------------------
   def r(self, a):
     return np.ascontiguousarray(a, dtype=self.real)

@@ -4,11 +4,14 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <atomic>
+
 #include "../../include/gsb200.h"
 
 #define GS_FULL 0xffffffffu
 
 void gs_set_error(const char *fmt, ...);
+extern std::atomic<unsigned long long> g_gs_launches;  // gs_launch_count(): diagnostics, bumped by GS_LAUNCH_CHECK
 
 #define GS_REQUIRE(cond, msg)                 \
   do {                                        \
@@ -20,6 +23,7 @@ void gs_set_error(const char *fmt, ...);
 
 #define GS_LAUNCH_CHECK()                                                             \
   do {                                                                                \
+    g_gs_launches.fetch_add(1, std::memory_order_relaxed);                            \
     cudaError_t e__ = cudaGetLastError();                                             \
     if (e__ != cudaSuccess) {                                                         \
       gs_set_error("%s: CUDA error %s (%s:%d)", __func__, cudaGetErrorString(e__), __FILE__, __LINE__); \

@@ -193,7 +193,7 @@ __global__ void __launch_bounds__(PB_THREADS) k_pack_base(int64_t words, int64_t
 // and rank planes; clears the consumed raster accumulator rows like gs_accumulate_stats does.  A thread scans 4 rows.
 __global__ void __launch_bounds__(256) k_pack_list(int64_t n, int64_t cap, const float *__restrict__ vis, int vis_stride,
                                                    const float *__restrict__ heur, int heur_stride, float *__restrict__ clear_acc,
-                                                   int clear_stride, float *__restrict__ clear_vis, RecView rv) {
+                                                   int clear_stride, float *__restrict__ clear_vis, RecView rv, GroupsDev gd) {
   int64_t r0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (r0 >= n) return;
   unsigned vb = rv.visbits[r0 >> 5];
@@ -211,6 +211,14 @@ __global__ void __launch_bounds__(256) k_pack_list(int64_t n, int64_t cap, const
     if (pos < (uint32_t)cap) {
       rv.idx[pos] = (int32_t)r;
       rv.aux[pos] = make_float4(v, hp, hs, 0.f);
+    } else {
+      // the record is full (header[1] reports it; the Trainer regrows the record): this row is dropped from the step.
+      // Clear its gradient at the source so it cannot leak into a later step's fold.
+      for (int e = 0; e < gd.total; ++e) {
+        int k, dim; float *plane;
+        group_of(gd, e, k, dim, plane);
+        plane[r * dim + k] = 0.f;
+      }
     }
     if (clear_acc) {
       float *a = clear_acc + (int64_t)clear_stride * r;
@@ -468,7 +476,7 @@ extern "C" int gs_exchange_pack(int64_t n, const float *g2d, const float *vis, i
   GS_LAUNCH_CHECK();
   k_pack_base<<<tiles, PB_THREADS, 0, st>>>(words, cap, rv, status, ticket);
   GS_LAUNCH_CHECK();
-  k_pack_list<<<gs_div_up((n + 3) / 4, 256), 256, 0, st>>>(n, cap, vis, vis_stride, heur, heur_stride, clear_acc, clear_stride, clear_vis, rv);
+  k_pack_list<<<gs_div_up((n + 3) / 4, 256), 256, 0, st>>>(n, cap, vis, vis_stride, heur, heur_stride, clear_acc, clear_stride, clear_vis, rv, gd);
   GS_LAUNCH_CHECK();
   {  // one warp per record row where the machine has room for them (the count is only known on the device)
     int64_t want = (cap + 7) / 8;

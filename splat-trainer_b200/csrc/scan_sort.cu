@@ -19,6 +19,9 @@ void gs_set_error(const char *fmt, ...) {
   va_end(ap);
 }
 extern "C" const char *gs_last_error(void) { return g_err; }
+// diagnostics only: kernels this library launched in this process (every launch site passes through GS_LAUNCH_CHECK)
+std::atomic<unsigned long long> g_gs_launches{0};
+extern "C" unsigned long long gs_launch_count(void) { return g_gs_launches.load(std::memory_order_relaxed); }
 extern "C" int gs_version(void) { return GSB200_VERSION; }
 extern "C" void gs_default_raster_config(gs_raster_config *c) {
   c->tile_size = GS_TILE;

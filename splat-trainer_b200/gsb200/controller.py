@@ -49,6 +49,7 @@ class TargetController:
     self.generator = torch.Generator(device=scene.device).manual_seed(seed)
     self.next_densify = self.find_next_densify(step)
     self.history = []
+    self.record_events, self.events = False, []  # bench.py: CUDA events around every densification
 
   def interval(self, step):
     v = self.config.densify_prune_interval
@@ -67,6 +68,10 @@ class TargetController:
     """call once per optimiser step with the trainer's image counter; returns (old_n, new_n) when it densified."""
     if self.next_densify is None or step < self.next_densify:
       return None
+    ev0 = None
+    if self.record_events:
+      ev0 = torch.cuda.Event(enable_timing=True)
+      ev0.record()
     if self.trainer is not None:
       self.trainer.sync_statistics()
     scene, c = self.scene, self.config
@@ -77,6 +82,10 @@ class TargetController:
                         max_scale_px=c.max_scale_px, min_split_px=c.min_split_px)
     self.next_densify = self.find_next_densify(step)
     self.history.append((step,) + tuple(out))
+    if ev0 is not None:
+      ev1 = torch.cuda.Event(enable_timing=True)
+      ev1.record()
+      self.events.append((ev0, ev1))
     return out
 
   def state_dict(self):

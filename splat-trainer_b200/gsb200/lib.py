@@ -78,6 +78,7 @@ SIGNATURES = {
   "gs_default_raster_config": (None, [_CFG]),
   "gs_version": (_I, []),
   "gs_last_error": (C.c_char_p, []),
+  "gs_launch_count": (C.c_ulonglong, []),
   "gs_project_fwd": (_I, [_CAM, _CFG, _L, _P, _P, _P, _P, _P, _I, _P, _P, _P, _P, _I, _P, _P, _P]),
   "gs_project_bwd": (_I, [_CAM, _CFG, _L, _P, _P, _P, _P, _P, _I, _P, _P, _I, _P, _I, _P, _P, _I, _REG,
                           _P, _P, _P, _P, _P, _I, _P]),

@@ -278,10 +278,17 @@ class SplatScene:
     return (wts[0] * s[0] + wts[1] * s[1] + wts[2] * s[2]) / s[3].clamp_min(1.0)
 
   # ---- MCMC controller (reference controller/mcmc_controller.py:69-100) ---------------------------------------------
+  stats_partial = None  # set by the Trainer under data parallelism while each rank holds only a slice of the statistics
+
+  def _require_full_stats(self):
+    if self.stats_partial:
+      raise L.GsError(f"scene statistics are incomplete on this rank: {self.stats_partial}")
+
   def mcmc_noise(self, noise_level, min_views=5, opacity_threshold=0.1, randn=None):
     """noise branch (:91-100).  randn: (N,3) N(0,1) draws (None: torch's CUDA generator; seed it identically on every
     rank).  The reference writes through a boolean-masked TensorDict copy; the intended effect — the noise is added to
     the positions — is what is implemented."""
+    self._require_full_stats()
     if randn is None:
       randn = torch.randn((self.n, 3), device=self.device)
     ops.mcmc_noise(self.p["alpha_logit"], self.p["log_scaling"], self.p["rotation"], self.stats["points_in_view"], min_views,
@@ -289,6 +296,7 @@ class SplatScene:
 
   def mcmc_find_prune_split(self, opacity_threshold=0.1, max_scale_px=200.0, min_split_px=0.0):
     """prune / respawn branch (:76-89): prune large or transparent splats and split as many by top split_score."""
+    self._require_full_stats()
     st = self.stats
     opacity = torch.sigmoid(self.p["alpha_logit"])
     prune_mask = (st["max_scale_px"] > max_scale_px) | (opacity < opacity_threshold)
@@ -438,6 +446,7 @@ class SplatScene:
   def find_split_prune(self, t, target_points, prune_rate=0.025, min_views=5, max_scale_px=200.0, min_split_px=0.0):
     """TargetController.find_split_prune_indexes (reference controller/target_controller.py:73-96) with the two
     full argsorts replaced by radix selects.  Returns (split_mask, prune_mask)."""
+    self._require_full_stats()
     st = self.stats
     n = self.n
     exceeds = st["max_scale_px"] > max_scale_px

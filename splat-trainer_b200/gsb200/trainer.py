@@ -36,13 +36,26 @@ class StageTimer:
 
 
 class Trainer:
-  def __init__(self, scene, world_size=1, rank=0, exchange="auto", exchange_cap=0, images_per_rank=1):
+  def __init__(self, scene, world_size=1, rank=0, exchange="auto", exchange_cap=0, images_per_rank=1, controller=None,
+               check_every=50, strict_overflow=False):
     """exchange: "auto" (sparse per-image records over peer memory when world_size > 1), "peer", "nccl" (records
-    all-gathered with NCCL), "dense" (SUM all-reduce of the whole packed gradient buffer; statistics stay per rank)
-    or an ImageExchange instance."""
+    all-gathered with NCCL), "dense" (SUM all-reduce of the whole packed gradient buffer; statistics stay per rank:
+    a bench arm only, densification raises) or an ImageExchange instance.
+    controller: a gsb200.controller.TargetController stepped after every optimiser step (reference
+    trainer/trainer.py:672-689).  check_every: the two device-side overflow flags (tile list, exchange record) are read
+    every that many steps and right after a densification — one 8-byte read; on overflow the buffer is regrown for the
+    following steps and the event is counted in `overflow_events` (strict_overflow: raise GsError instead)."""
     self.scene = scene
     self.world_size, self.rank = world_size, rank
     self.step_count = 0
+    self.steps_done = 0
+    self.controller = controller
+    if controller is not None and controller.trainer is None:
+      controller.trainer = self
+    self.check_every, self.strict_overflow = int(check_every), bool(strict_overflow)
+    self.overflow_events = []
+    self._check_now = True  # first step: the capacities were calibrated from one camera only
+    self.dense = isinstance(exchange, str) and exchange == "dense" and world_size > 1
     self._copy_stream, self._target_flip = None, 0
     self._grads_clean = False  # unknown history of scene.grads until the first step has run
     self.exchange = None
@@ -86,9 +99,12 @@ class Trainer:
       self.scene.color.all_reduce(dist)  # replicated colour model: its small dense gradients are summed
     if self.exchange is not None:
       self.exchange.fold()
+      if self.world_size > 1 and getattr(self.exchange, "stats_rows", None) not in (None, (0, getattr(self.scene, "n", 0))):
+        self.scene.stats_partial = "each rank holds its own row slice of the statistics: call Trainer.sync_statistics() first"
       self.scene._mark("exchange")
     elif self.world_size > 1:
       dist.all_reduce(self.scene.grads, op=dist.ReduceOp.SUM)
+      self.scene.stats_partial = "exchange='dense' keeps the statistics per rank (bench arm only): densification would diverge the replicas"
       self.scene._mark("exchange")
 
   def calibrate_exchange(self, margin=1.5):
@@ -113,9 +129,12 @@ class Trainer:
     slices.  Afterwards scene.stats is complete and identical on every rank."""
     if self.world_size <= 1:
       return
+    if self.dense:
+      raise L.GsError("exchange='dense' keeps split_score / prune_cost per rank; use the record exchange to densify")
     st = self.scene.stats
     dist.all_reduce(st["max_scale_px"], op=dist.ReduceOp.MAX)
     ex = self.exchange
+    self.scene.stats_partial = None
     if ex is None or ex.stats_rows == (0, self.scene.n):
       return
     b, e = ex.stats_rows
@@ -127,6 +146,56 @@ class Trainer:
       out = torch.empty((self.world_size * ex.slice_len,), device=t.device, dtype=dt)
       dist.all_gather_into_tensor(out, send, group=ex.group)
       t.copy_(out[:self.scene.n].to(t.dtype))
+
+  def check_overflow(self):
+    """read the device-side overflow flags of the last step (tile-overlap list; exchange record) — one small host read,
+    never on the per-step path.  An overflowed buffer silently truncated that step's lists / dropped rows: grow it for the
+    steps to come and report."""
+    self._check_now = False
+    scene = self.scene
+    grew = []
+    if hasattr(scene, "overflowed") and scene.overflowed():
+      scene.grow_overlaps(2.0)
+      grew.append("tile_overlaps")
+    ex = self.exchange
+    if ex is not None and hasattr(ex, "counts") and not ex.stale():
+      flag = torch.tensor([1.0 if any(o for _, o in ex.counts()) else 0.0], device=scene.device)
+      if self.world_size > 1:
+        dist.all_reduce(flag, op=dist.ReduceOp.MAX, group=ex.group)  # every rank must resize together
+      if float(flag.item()) > 0:
+        from .exchange import ImageExchange
+        scene.zero_grad()  # rows a full record dropped are still in the dense buffer
+        self.exchange = ImageExchange(scene, ex.world, ex.rank, cap=min(scene.n, 2 * ex.cap), images_per_rank=ex.k,
+                                      transport=ex.transport, group=ex.group)
+        grew.append("exchange_record")
+    if grew:
+      self.overflow_events.append((self.steps_done, grew))
+      self._check_now = True
+      if self.strict_overflow:
+        raise L.GsError(f"step {self.steps_done}: capacity exceeded ({', '.join(grew)}); the step's lists were truncated")
+    return grew
+
+  def state_dict(self):
+    """the reference's checkpoint layout (trainer/trainer.py:188-194): dict(step, scene, controller)."""
+    ctrl = self.controller.state_dict() if self.controller is not None else dict(
+        points={k: v.clone() for k, v in self.scene.stats.items()}, start_points=self.scene.num_points)
+    return dict(step=int(self.step_count), scene=self.scene.state_dict(), controller=ctrl)
+
+  @staticmethod
+  def from_state_dict(state, controller_config=None, target_points=0, total_steps=0, device="cuda", **kw):
+    from .scene import SplatScene
+    scene = SplatScene.from_state_dict(state["scene"], device=device)
+    controller = None
+    if controller_config is not None:
+      from .controller import TargetController
+      controller = TargetController(controller_config, scene, target_points, total_steps, step=int(state["step"]))
+      controller.load_state_dict(state["controller"])
+    else:
+      for k, v in state["controller"]["points"].items():
+        scene.stats[k].copy_(v)
+    tr = Trainer(scene, controller=controller, **kw)
+    tr.step_count = int(state["step"])
+    return tr
 
   def training_step(self, batch, read_loss=False):
     """batch: list of (camera, target image) for the WHOLE step (all ranks pass the same list); this rank
@@ -157,6 +226,11 @@ class Trainer:
     self.exchange_gradients()
     scene.step()
     self._grads_clean = True  # scene.step() cleared every gradient row it consumed
+    self.steps_done += 1
+    if self._check_now or (self.check_every > 0 and self.steps_done % self.check_every == 0):
+      self.check_overflow()
+    if self.controller is not None and self.controller.step(self.step_count) is not None:
+      self._check_now = True  # the scene changed size: capacities are re-checked after the next step
     if read_loss:
       return [float(x) for x in total.cpu().tolist()] if total is not None else [0.0, 0.0]
     return total

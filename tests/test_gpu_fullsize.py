@@ -1,18 +1,16 @@
-"""BASELINE.json's full-size configurations through size-independent properties (the CPU oracle needs minutes per image
-at these sizes, so it checks the small cases; here the invariants of the path are checked at full scale):
+"""BASELINE.json's full-size configurations through size-independent properties (the oracle comparison at C2 itself is
+tests/test_gpu_parity_configs.py; here the invariants of the path are checked at full scale, C4 included):
   C2  3M splats SH3 1297x840   (configs[1], the bench workload)
   C4  6M splats SH3 3840x2160  (configs[3], high-res stress: large overlap counts through the sort and the backward)
 Invariants: the overlap list is the stable (tile, depth) order and partitions [0, O); O equals the independent count
 pass; forward is idempotent bit for bit; Σ visibility over splats == Σ (1 - final_T) over pixels (every blended
 alpha·T is counted once on each side); a training step touches exactly the rows a pixel blended and leaves the gradient
 buffer clear."""
-import argparse
-
 import pytest
 import torch
 
-import bench
 from gsb200 import lib as L
+from gsb200 import synthetic as syn
 from gsb200 import ops
 from gsb200.scene import SceneConfig, SplatScene
 from gsb200.trainer import Trainer
@@ -21,7 +19,8 @@ pytestmark = pytest.mark.gpu
 
 
 def _scene(workload):
-  n, deg, W, H, g, cams = bench.make_workload(argparse.Namespace(workload=workload, points=0))
+  wl = syn.workload(workload)
+  deg, W, H, g, cams = wl["sh_degree"], wl["width"], wl["height"], wl["gaussians"], wl["cameras"]
   scene = SplatScene(g, SceneConfig(sh_degree=deg))
   lcams = [L.make_camera(c["T"], c["fx"], c["fy"], c["cx"], c["cy"], W, H, c["near"], c["far"]) for c in cams[:2]]
   return scene, lcams, W, H
