@@ -478,6 +478,17 @@ int gs_assign_clusters(int64_t n, int d, int k, const float *x, const float *cen
 int gs_kmeans(int64_t n, int d, int k, int iters, const float *x, float *centroids, int32_t *labels, void *workspace,
               size_t workspace_bytes, void *stream);
 
+/* Per-view cluster features (PointClusters.view_features, reference visibility/cluster.py:40-55, called per training view
+ * from trainer/trainer.py:337-340,356-359): features[labels[row]] += vis over the entries with vis > threshold.
+ * indexes == NULL: vis is the (n) visibility plane of one render (row = entry); else vis / indexes are the (v) compacted
+ * (idx, visibility) lists of query_visibility.  features (num_clusters) is zeroed here. */
+int gs_view_features(int64_t n, const float *vis, const int64_t *indexes, int64_t v, const int32_t *labels, float threshold,
+                     int num_clusters, float *features, void *stream);
+/* point_visibility (reference visibility/query_points.py:62-92, used to crop the initial cloud, trainer/init.py): counts[i] =
+ * number of cameras in which point i projects inside the image with near < depth < far.  cameras: (num_cameras, 20) floats
+ * = image_t_world (4x4 row-major, K·T_camera_world) | width, height, near, far. */
+int gs_point_visibility(int64_t n, const float *points, int num_cameras, const float *cameras, int32_t *counts, void *stream);
+
 /* estimate_scale (reference gaussians/loading.py:45-61, pykeops Kmin over all N x N distances): scales[i] = mean
  * distance from points[i] to its num_neighbors (1..8) nearest neighbours, computed as the reference does (the
  * num_neighbors + 1 smallest squared distances to ALL points, the smallest — self — dropped, sqrt, mean).  Uniform grid +

@@ -383,3 +383,19 @@ class Oracle:
     out = np.zeros(pts.shape[0], self.real)
     self.lib.gso_knn_scale(C.c_int64(pts.shape[0]), self.p(pts), C.c_int(num_neighbors), self.p(out))
     return out
+
+  # -- (12) per-view cluster features / frustum counts ----------------------------------
+  def view_features(self, labels, num_clusters, vis, indexes=None, threshold=0.01):
+    vis = self.r(vis)
+    labels = np.ascontiguousarray(labels, np.int32)
+    idx = None if indexes is None else np.ascontiguousarray(indexes, np.int64)
+    out = np.zeros(num_clusters, self.real)
+    self.lib.gso_view_features(C.c_int64(vis.shape[0]), self.p(vis), self.p(idx), self.p(labels), self.creal(threshold),
+                               C.c_int(num_clusters), self.p(out))
+    return out
+
+  def point_visibility(self, points, cameras):
+    pts, cams = self.r(points), self.r(cameras)
+    counts = np.zeros(pts.shape[0], np.int32)
+    self.lib.gso_point_visibility(C.c_int64(pts.shape[0]), self.p(pts), C.c_int(cams.shape[0]), self.p(cams), self.p(counts))
+    return counts

@@ -125,3 +125,91 @@ extern "C" int gs_kmeans(int64_t n, int d, int k, int iters, const float *x, flo
   GS_LAUNCH_CHECK();
   return GS_OK;
 }
+
+// ---- per-view cluster features + frustum visibility counts (SURVEY §8f-3 remainder) ---------------------------------
+// PointClusters.view_features (reference visibility/cluster.py:40-55): features[label[i]] += vis[i] over the rows with
+// vis[i] > threshold.  A segmented reduction over the visibility plane of one render: block-local partial sums in shared
+// memory (one fp32 slot per cluster), one global RED per non-empty (block, cluster).
+constexpr int VF_THREADS = 256;
+constexpr int VF_ITEMS = 16;
+
+__global__ void __launch_bounds__(VF_THREADS) k_view_features(int64_t n, const float *__restrict__ vis, const int64_t *__restrict__ idx,
+                                                              int64_t v, const int32_t *__restrict__ labels, float threshold,
+                                                              int k, float *__restrict__ out) {
+  extern __shared__ float s_feat[];
+  for (int c = threadIdx.x; c < k; c += VF_THREADS) s_feat[c] = 0.f;
+  __syncthreads();
+  const int64_t count = idx ? v : n;
+  int64_t base = (int64_t)blockIdx.x * VF_THREADS * VF_ITEMS;
+  for (int it = 0; it < VF_ITEMS; ++it) {
+    int64_t j = base + (int64_t)it * VF_THREADS + threadIdx.x;
+    if (j >= count) break;
+    float w = vis[j];
+    if (w > threshold) {
+      int64_t row = idx ? idx[j] : j;
+      atomicAdd(&s_feat[labels[row]], w);
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < k; c += VF_THREADS) {
+    float s = s_feat[c];
+    if (s != 0.f) atomicAdd(out + c, s);
+  }
+}
+
+extern "C" int gs_view_features(int64_t n, const float *vis, const int64_t *indexes, int64_t v, const int32_t *labels,
+                                float threshold, int num_clusters, float *features, void *stream) {
+  GS_REQUIRE(vis && labels && features, "null argument");
+  GS_REQUIRE(num_clusters >= 1 && num_clusters <= 12288, "1 <= num_clusters <= 12288");
+  cudaStream_t st = (cudaStream_t)stream;
+  GS_CUDA(cudaMemsetAsync(features, 0, (size_t)num_clusters * sizeof(float), st));
+  int64_t count = indexes ? v : n;
+  if (count <= 0) return GS_OK;
+  k_view_features<<<gs_div_up(count, VF_THREADS * VF_ITEMS), VF_THREADS, (size_t)num_clusters * sizeof(float), st>>>(
+      n, vis, indexes, v, labels, threshold, num_clusters, features);
+  GS_LAUNCH_CHECK();
+  return GS_OK;
+}
+
+// point_visibility (reference visibility/query_points.py:62-92): in how many cameras does a point project inside the
+// image with near < depth < far.  cameras: (C, 20) floats per camera = image_t_world (row-major 4x4 = K·T_camera_world)
+// | width, height, near, far.  A thread per point, the camera table in shared memory.
+constexpr int PV_THREADS = 256;
+constexpr int PV_CAM_FLOATS = 20;
+
+__global__ void __launch_bounds__(PV_THREADS) k_point_visibility(int64_t n, const float *__restrict__ points, int num_cameras,
+                                                                 const float *__restrict__ cameras, int32_t *__restrict__ counts) {
+  extern __shared__ float s_cam[];
+  int64_t i = (int64_t)blockIdx.x * PV_THREADS + threadIdx.x;
+  float x = 0.f, y = 0.f, z = 0.f;
+  if (i < n) { x = points[3 * i]; y = points[3 * i + 1]; z = points[3 * i + 2]; }
+  int total = 0;
+  const int chunk = 512;  // cameras per shared-memory refill (40 KB)
+  for (int c0 = 0; c0 < num_cameras; c0 += chunk) {
+    int cn = min(chunk, num_cameras - c0);
+    __syncthreads();
+    for (int t = threadIdx.x; t < cn * PV_CAM_FLOATS; t += PV_THREADS) s_cam[t] = cameras[(size_t)c0 * PV_CAM_FLOATS + t];
+    __syncthreads();
+    for (int c = 0; c < cn; ++c) {
+      const float *M = s_cam + c * PV_CAM_FLOATS;
+      // the reference's matrix-vector product, term by term in row order (no contraction)
+      float px = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(M[0], x), __fmul_rn(M[1], y)), __fmul_rn(M[2], z)), M[3]);
+      float py = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(M[4], x), __fmul_rn(M[5], y)), __fmul_rn(M[6], z)), M[7]);
+      float d = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(M[8], x), __fmul_rn(M[9], y)), __fmul_rn(M[10], z)), M[11]);
+      float u = __fdiv_rn(px, d), w = __fdiv_rn(py, d);
+      total += (u >= 0.f) && (u < M[16]) && (w >= 0.f) && (w < M[17]) && (d > M[18]) && (d < M[19]);
+    }
+  }
+  if (i < n) counts[i] = total;
+}
+
+extern "C" int gs_point_visibility(int64_t n, const float *points, int num_cameras, const float *cameras, int32_t *counts,
+                                   void *stream) {
+  GS_REQUIRE(points && cameras && counts && num_cameras >= 0, "null argument");
+  if (n <= 0) return GS_OK;
+  int cn = num_cameras < 512 ? (num_cameras > 0 ? num_cameras : 1) : 512;
+  k_point_visibility<<<gs_div_up(n, PV_THREADS), PV_THREADS, (size_t)cn * PV_CAM_FLOATS * sizeof(float), (cudaStream_t)stream>>>(
+      n, points, num_cameras, cameras, counts);
+  GS_LAUNCH_CHECK();
+  return GS_OK;
+}

@@ -107,6 +107,8 @@ SIGNATURES = {
   "gs_kmeans_workspace_bytes": (_Z, [_I, _I]),
   "gs_assign_clusters": (_I, [_L, _I, _I, _P, _P, _P, _P]),
   "gs_kmeans": (_I, [_L, _I, _I, _I, _P, _P, _P, _P, _Z, _P]),
+  "gs_view_features": (_I, [_L, _P, _P, _L, _P, _F, _I, _P, _P]),
+  "gs_point_visibility": (_I, [_L, _P, _I, _P, _P, _P]),
   "gs_knn_scale_workspace_bytes": (_Z, [_L]),
   "gs_knn_scale": (_I, [_L, _P, _I, _P, _P, _Z, _P]),
   "gs_adam_rows": (_I, [_I, _I, _P, _P, _P, _P, _P, _P, _F, _F, _F, _F, _P]),

@@ -567,6 +567,41 @@ def kmeans(x, k=None, iters=100, centroids=None, generator=None):
   return labels, centroids
 
 
+def view_features(labels, num_clusters, vis, indexes=None, threshold=0.01):
+  """PointClusters.view_features (reference visibility/cluster.py:40-55): (num_clusters,) Σ of the visibilities > threshold
+  per cluster.  vis: the (n,) visibility plane of a render, or — with indexes (v,) int64 — the compacted (idx, visibility)
+  lists of query_visibility."""
+  out = torch.empty((num_clusters,), device=labels.device, dtype=torch.float32)
+  n = labels.shape[0]
+  v = 0 if indexes is None else indexes.shape[0]
+  assert labels.dtype == torch.int32 and (indexes is None or indexes.dtype == torch.int64)
+  L.check(L.load().gs_view_features(n, L.ptr(_f32(vis)), L.ptr(indexes), v, L.ptr(labels), float(threshold), int(num_clusters),
+                                    L.ptr(out), L.stream()))
+  return out
+
+
+def camera_table(cameras):
+  """list of lib cameras (gs_camera) -> (C, 20) float32 host tensor: image_t_world = K·T_camera_world | W, H, near, far."""
+  rows = []
+  for c in cameras:
+    T = torch.tensor([c.T[i] for i in range(16)], dtype=torch.float32).reshape(4, 4)
+    K = torch.zeros((4, 4), dtype=torch.float32)
+    K[0, 0], K[1, 1], K[0, 2], K[1, 2], K[2, 2], K[3, 3] = c.fx, c.fy, c.cx, c.cy, 1.0, 1.0
+    rows.append(torch.cat([(K @ T).reshape(-1), torch.tensor([c.width, c.height, c.near_plane, c.far_plane], dtype=torch.float32)]))
+  return torch.stack(rows)
+
+
+def point_visibility(points, cameras):
+  """reference visibility/query_points.py:89-92: (n,) int32 number of cameras that see each point.  cameras: (C,20) table
+  (camera_table) or a list of lib cameras."""
+  if not isinstance(cameras, torch.Tensor):
+    cameras = camera_table(cameras)
+  cams = cameras.to(points.device, torch.float32).contiguous()
+  counts = torch.empty((points.shape[0],), device=points.device, dtype=torch.int32)
+  L.check(L.load().gs_point_visibility(points.shape[0], L.ptr(_f32(points)), cams.shape[0], L.ptr(cams), L.ptr(counts), L.stream()))
+  return counts
+
+
 def estimate_scale(points, num_neighbors=3):
   """reference gaussians/loading.py:45-61: mean distance to the num_neighbors nearest neighbours -> (n,) float32."""
   n = points.shape[0]

@@ -265,6 +265,19 @@ class SplatScene:
     idx = (vis > 0).nonzero().squeeze(1)
     return idx, vis[idx]
 
+  def evaluate(self, cam, target, image_idx=None):
+    """Evaluation.metrics (reference trainer/evaluation.py:29-46, util/colors.py compute_psnr): psnr / l1 / ssim of the
+    clamped render against `target` ((H,W,3) uint8 or float32 on the device), as one (3,) device tensor — forward only,
+    the loss kernels' sums, no gradient."""
+    w, _, _, _ = self._forward(cam, image_idx=image_idx)
+    H, W = w["H"], w["W"]
+    _, sums = ops.loss_l1_mse(w["image"], target, 0.0, 0.0, d_pred=w["d_image"])
+    ss = ops.ssim_loss(w["image"], target, levels=1, weight=0.0, workspace=w["ssim_ws"])
+    npx = float(H * W * 3)
+    mse = sums[1] / npx
+    return torch.stack([10.0 * torch.log10(1.0 / mse.clamp_min(1e-20)), sums[0] / npx,
+                        ss[0] / float(max(ops.ssim_counts(H, W, 3, 1)[0], 1))])
+
   def ssim_value(self):
     """(weighted multi-scale SSIM loss, SSIM of level 0) of the last forward_backward image — device scalars."""
     w, c = self._work, self.config
