@@ -10,7 +10,8 @@ raster forward -> loss (MSE 10 + 3-level SSIM 1.0 + reg_loss, the reference's de
 SH backward -> statistics — then, for N > 1, the exchange of the per-image gradient records over NVLink peer memory
 (folded in image order on every rank), then the fused visibility-aware LaProp step.  Weak scaling: every rank renders a
 different camera of the batch (batch = N images).  The timed window of K steps is repeated `--windows` times inside the
-run; `value` is the median window.  Prints ONE JSON line on rank 0.
+run, every window starting from the same training state (restored outside the timed region); `value` is the median
+window.  Prints ONE JSON line on rank 0.
 
 Workloads (gsb200.synthetic.WORKLOADS): c2 = BASELINE.json configs[1] generated exactly as SURVEY.md 8(d) writes it (the
 default); c2-sparse = round 1's generator (opaque small splats: ~3 % of the in-view rows blend); c2-trained = translucent
@@ -327,12 +328,32 @@ def run_b200(args):
   elif world > 1:
     exchange_info = {"transport": "dense-allreduce", "dense_allreduce_bytes": int(scene.grads.numel() * 4)}
 
+  # every timed window starts from the SAME training state (parameters, moments, statistics restored outside the timed
+  # region): the scene trains while it is timed, so without this later windows measure a different scene
+  def snapshot():
+    snap = [t.clone() for t in (scene.params, scene.exp_avg, scene.exp_avg_sq_flat, scene.running_vis, scene.opt_step)]
+    snap += [v.clone() for v in scene.stats.values()]
+    if scene.color is not None:
+      snap.append({k: (v.clone() if torch.is_tensor(v) else v) for k, v in scene.color.state_dict().items()})
+    return snap
+
+  def restore(snap):
+    live = [scene.params, scene.exp_avg, scene.exp_avg_sq_flat, scene.running_vis, scene.opt_step] + list(scene.stats.values())
+    for dst, src in zip(live, snap):
+      dst.copy_(src)
+    if scene.color is not None:
+      scene.color.load_state_dict(snap[-1])
+    torch.cuda.synchronize()
+
+  state0 = snapshot()
+
   # ---- device-resident throughput (value): R windows of K steps, no stage events inside ---------------------------
   scene.timer = None
   lib = L.load()
   window_ms, launches_per_step = [], None
   with ClockSampler(local) as clocks:
     for r in range(args.windows):
+      restore(state0)
       barrier()
       e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
       l0 = lib.gs_launch_count()
@@ -353,6 +374,7 @@ def run_b200(args):
 
   # ---- per-stage CUDA events (a separate loop: one event per stage perturbs the enqueue) --------------------------
   timer = StageTimer()
+  restore(state0)
   scene.timer = timer
   barrier()
   for i in range(args.steps):
@@ -366,6 +388,7 @@ def run_b200(args):
   e2e_windows = []
   loss = None
   for r in range(args.windows):
+    restore(state0)
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
@@ -379,6 +402,7 @@ def run_b200(args):
     e2e_windows.append(float(t.item()))
   e2e_s = median(e2e_windows)
   identical = replicas_identical(scene, world)
+  del state0
 
   # ---- what the last image did (outside every timed region) -----------------------------------------------------------
   w = scene._work
@@ -418,7 +442,7 @@ def run_b200(args):
       "optimizer_steps_per_sec": args.steps / (ms * 1e-3),
       "raster_fwd_bwd_mpix_per_sec": world * P / ((stages["raster_fwd"] + stages["raster_bwd"]) * 1e-3) / 1e6,
       "n_gpus": world, "steps": args.steps, "warmup": warm, "ms_per_step": ms_step,
-      "windows": {"count": args.windows, "ms_per_step": [x / args.steps for x in window_ms],
+      "windows": {"count": args.windows, "each_from_the_same_training_state": True, "ms_per_step": [x / args.steps for x in window_ms],
                   "min": min(window_ms) / args.steps, "median": ms_step, "max": max(window_ms) / args.steps},
       "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
       "config": {"workload": workload_string(args, wl, world), "images_per_step": world,

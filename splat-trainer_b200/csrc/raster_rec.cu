@@ -50,8 +50,10 @@ __device__ __forceinline__ void issue_batch(const float *__restrict__ records, i
     cp_async16(smem_u32(&S->w0[stage][threadIdx.x]), src);
     cp_async16(smem_u32(&S->w1[stage][threadIdx.x]), src + 4);
     cp_async16(smem_u32(&S->w2[stage][threadIdx.x]), src + 8);
+    cp_async_arrive(bar);  // arrives once the three copies have landed
+  } else {
+    mbar_arrive(bar);      // nothing to copy: a plain arrival
   }
-  cp_async_arrive(bar);
 }
 
 // this warp's candidates among the `cnt` staged records: bit k set iff record k can reach the warp's 8 pixel rows
@@ -196,7 +198,7 @@ __global__ void __launch_bounds__(RT) k_raster_fwd_rec(CfgDev cfg, const float *
   __shared__ RecStages S;
   __shared__ __align__(8) unsigned long long s_bar[2];
   __shared__ int s_next[2];
-  __shared__ int s_wmax[RT / 32];
+  __shared__ int s_wmax[2][RT / 32];
   const int wid = threadIdx.x >> 5;
   const uint32_t bar0 = smem_u32(&s_bar[0]);
   if (threadIdx.x == 0) { mbar_init(bar0, RT); mbar_init(bar0 + 8u, RT); }
@@ -240,7 +242,11 @@ __global__ void __launch_bounds__(RT) k_raster_fwd_rec(CfgDev cfg, const float *
         unsigned long long cand = warp_candidates(&S, s, cnt, row_lo);
         bool all_done = done[0] && done[1] && done[2] && done[3];
         while (cand) {
-          if (!VIS && all_done) break;
+          if (COUNT) {  // the counters use warp-wide votes: leave the loop together (finished lanes blend nothing anyway)
+            if (!VIS && __all_sync(GS_FULL, all_done)) break;
+          } else if (!VIS && all_done) {
+            break;
+          }
           int k = __ffsll((long long)cand) - 1;
           cand &= cand - 1;
           float4 A = S.w0[s][k], B = S.w1[s][k], F = S.w2[s][k];
@@ -303,10 +309,10 @@ __global__ void __launch_bounds__(RT) k_raster_fwd_rec(CfgDev cfg, const float *
       if (MEDIAN) median[pix] = med[p];
     }
     tmax = __reduce_max_sync(GS_FULL, tmax);
-    if ((threadIdx.x & 31) == 0) s_wmax[wid] = tmax;
     queue_publish(Q, s_next);
+    if ((threadIdx.x & 31) == 0) s_wmax[Q.flip][wid] = tmax;
     __syncthreads();
-    if (tile_work && threadIdx.x == 0) tile_work[tile] = max(s_wmax[0], s_wmax[1]);
+    if (tile_work && threadIdx.x == 0) tile_work[tile] = max(s_wmax[Q.flip][0], s_wmax[Q.flip][1]);
     queue_advance(Q, s_next);
   }
   if (COUNT && (threadIdx.x & 31) == 0) {

@@ -373,8 +373,19 @@ extern "C" size_t gs_radix_sort_workspace_bytes(int64_t n) {
 }
 
 // internal: ping-pong sort; returns (via *result_in_b) which buffer pair holds the result
+// zero the sort's header (digit histograms, tickets) and look-back status words.  A caller that fills the digit
+// histograms itself (ghist[p*256 + digit], p = pass over bits [begin_bit + 8p, ...)) calls this first, then its own
+// kernel, then gs_radix_sort_pingpong(hist_ready = true).
+int gs_radix_sort_prepare(void *workspace, int64_t n, int begin_bit, int end_bit, cudaStream_t st) {
+  if (n <= 0 || end_bit <= begin_bit) return GS_OK;
+  int nblk = gs_div_up(n, OS_TILE);
+  int passes = (end_bit - begin_bit + 7) / 8;
+  GS_CUDA(cudaMemsetAsync(workspace, 0, os_header_bytes() + (size_t)passes * nblk * 256 * sizeof(uint32_t), st));
+  return GS_OK;
+}
+
 int gs_radix_sort_pingpong(uint32_t *ka, uint32_t *va, uint32_t *kb, uint32_t *vb, int64_t n, const int32_t *n_dev,
-                           int begin_bit, int end_bit, void *workspace, int *result_in_b, cudaStream_t st) {
+                           int begin_bit, int end_bit, void *workspace, int *result_in_b, cudaStream_t st, bool hist_ready) {
   *result_in_b = 0;
   if (n <= 0 || end_bit <= begin_bit) return GS_OK;
   if (n >= ((int64_t)1 << 30)) { gs_set_error("radix sort: n must be < 2^30"); return GS_ERR_INVALID; }
@@ -383,7 +394,10 @@ int gs_radix_sort_pingpong(uint32_t *ka, uint32_t *va, uint32_t *kb, uint32_t *v
   uint32_t *ghist = (uint32_t *)workspace;
   uint32_t *tickets = ghist + OS_MAX_PASSES * 256;
   uint32_t *status = (uint32_t *)((char *)workspace + os_header_bytes());
-  GS_CUDA(cudaMemsetAsync(workspace, 0, os_header_bytes() + (size_t)passes * nblk * 256 * sizeof(uint32_t), st));
+  if (!hist_ready) {
+    int rc0 = gs_radix_sort_prepare(workspace, n, begin_bit, end_bit, st);
+    if (rc0 != GS_OK) return rc0;
+  }
   int hgrid = gs_div_up(n, OH_BLOCK_ITEMS);
   size_t hsm = (size_t)OH_WARPS * passes * 256 * 32;
 #define GS_HIST(NP)                                                                                            \
@@ -391,11 +405,13 @@ int gs_radix_sort_pingpong(uint32_t *ka, uint32_t *va, uint32_t *kb, uint32_t *v
     GS_CUDA(cudaFuncSetAttribute(k_os_hist<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hsm));       \
     k_os_hist<NP><<<hgrid, OH_THREADS, hsm, st>>>(ka, n, n_dev, begin_bit, end_bit, ghist);                     \
   } while (0)
-  switch (passes) {
-    case 1: GS_HIST(1); break;
-    case 2: GS_HIST(2); break;
-    case 3: GS_HIST(3); break;
-    default: GS_HIST(4); break;
+  if (!hist_ready) {
+    switch (passes) {
+      case 1: GS_HIST(1); break;
+      case 2: GS_HIST(2); break;
+      case 3: GS_HIST(3); break;
+      default: GS_HIST(4); break;
+    }
   }
 #undef GS_HIST
   uint32_t *ks = ka, *vs = va, *kd = kb, *vd = vb;
@@ -435,7 +451,7 @@ extern "C" int gs_radix_sort_pairs(uint32_t *keys_in, uint32_t *vals_in, uint32_
   }
   cudaStream_t st = (cudaStream_t)stream;
   int in_b = 0;
-  int rc = gs_radix_sort_pingpong(keys_in, vals_in, keys_out, vals_out, n, n_dev, begin_bit, end_bit, workspace, &in_b, st);
+  int rc = gs_radix_sort_pingpong(keys_in, vals_in, keys_out, vals_out, n, n_dev, begin_bit, end_bit, workspace, &in_b, st, false);
   if (rc != GS_OK) return rc;
   if (!in_b && n > 0) {  // even number of passes (or none): result sits in the input pair
     GS_CUDA(cudaMemcpyAsync(keys_out, keys_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));

@@ -14,8 +14,9 @@
 #include "common.cuh"
 #include "footprint.cuh"
 
+int gs_radix_sort_prepare(void *workspace, int64_t n, int begin_bit, int end_bit, cudaStream_t st);
 int gs_radix_sort_pingpong(uint32_t *ka, uint32_t *va, uint32_t *kb, uint32_t *vb, int64_t n, const int32_t *n_dev,
-                           int begin_bit, int end_bit, void *workspace, int *result_in_b, cudaStream_t st);
+                           int begin_bit, int end_bit, void *workspace, int *result_in_b, cudaStream_t st, bool hist_ready);
 
 // ---- tile info: what the cull knows about every row ------------------------------------------------------
 TileInfo gs_tile_info_carve(void *base, int64_t n, int width, int height) {
@@ -106,11 +107,14 @@ constexpr int LC_TILE = LC_THREADS * LC_ITEMS;
 __global__ void __launch_bounds__(LC_THREADS) k_live_compact(const int32_t *__restrict__ counts, const float *__restrict__ depth,
                                                              int64_t m, uint32_t *__restrict__ status, uint32_t *__restrict__ ticket,
                                                              uint32_t *__restrict__ depth_keys, uint32_t *__restrict__ rows,
-                                                             int32_t *__restrict__ live_out) {
+                                                             int32_t *__restrict__ live_out, uint32_t *__restrict__ ghist) {
   __shared__ int s_warp[8];
   __shared__ int s_tile;
   __shared__ uint32_t s_prefix;
+  __shared__ uint32_t s_hist[4][256];  // digit histograms of this tile's live depth keys (the depth sort's 4 passes)
   if (threadIdx.x == 0) s_tile = (int)atomicAdd(ticket, 1u);
+#pragma unroll
+  for (int p = 0; p < 4; ++p) s_hist[p][threadIdx.x] = 0u;
   __syncthreads();
   const int tile = s_tile;
   int64_t base = (int64_t)tile * LC_TILE + (int64_t)threadIdx.x * LC_ITEMS;
@@ -142,10 +146,23 @@ __global__ void __launch_bounds__(LC_THREADS) k_live_compact(const int32_t *__re
 #pragma unroll
   for (int i = 0; i < LC_ITEMS; ++i) {
     if (c[i] > 0) {
-      depth_keys[pos] = __float_as_uint(depth[base + i]);
+      uint32_t key = __float_as_uint(depth[base + i]);
+      depth_keys[pos] = key;
       rows[pos] = (uint32_t)(base + i);
       ++pos;
+      // the key is in a register anyway: count its four digits here instead of re-reading every key in a histogram
+      // kernel of the sort (one launch and one sweep of the keys less)
+      atomicAdd(&s_hist[0][key & 255u], 1u);
+      atomicAdd(&s_hist[1][(key >> 8) & 255u], 1u);
+      atomicAdd(&s_hist[2][(key >> 16) & 255u], 1u);
+      atomicAdd(&s_hist[3][key >> 24], 1u);
     }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int p = 0; p < 4; ++p) {
+    uint32_t h = s_hist[p][threadIdx.x];
+    if (h) atomicAdd(ghist + p * 256 + threadIdx.x, h);
   }
 }
 
@@ -161,11 +178,14 @@ __global__ void __launch_bounds__(EM_THREADS) k_super_emit(const float *__restri
                                                            const uint32_t *__restrict__ sorted_rows, int64_t cap,
                                                            uint32_t *__restrict__ status, uint32_t *__restrict__ ticket,
                                                            uint32_t *__restrict__ skeys, uint32_t *__restrict__ svals,
-                                                           int32_t *__restrict__ scounters) {
+                                                           int32_t *__restrict__ scounters, int NS,
+                                                           uint32_t *__restrict__ ghist, int32_t *__restrict__ scount) {
+  extern __shared__ uint32_t s_cnt[];  // NS: pairs of this tile per super-tile
   __shared__ int s_warp[8];
   __shared__ int s_tile;
   __shared__ uint32_t s_prefix;
   if (threadIdx.x == 0) s_tile = (int)atomicAdd(ticket, 1u);
+  for (int i = threadIdx.x; i < NS; i += EM_THREADS) s_cnt[i] = 0u;
   __syncthreads();
   const int tile = s_tile;
   int64_t live = min((int64_t)*live_dev, m);
@@ -197,14 +217,15 @@ __global__ void __launch_bounds__(EM_THREADS) k_super_emit(const float *__restri
     }
   }
   __syncthreads();
-  if (ns <= 0) return;
   int64_t o = (int64_t)s_prefix + ex;
-  int sx0, sx1, sy0, sy1;
+  int sx0 = 0, sx1 = -1, sy0 = 0, sy1 = -1;
+  if (ns > 0) {
   if (v.big) {
     Footprint fp = load_footprint(g2d, depth, row, thr, W, H);
     sx0 = fp.tx0 / GS_SUPER; sx1 = fp.tx1 / GS_SUPER; sy0 = fp.ty0 / GS_SUPER; sy1 = fp.ty1 / GS_SUPER;
   } else {
     sx0 = v.tx0 / GS_SUPER; sx1 = (v.tx0 + v.w - 1) / GS_SUPER; sy0 = v.ty0 / GS_SUPER; sy1 = (v.ty0 + v.h - 1) / GS_SUPER;
+  }
   }
   for (int sy = sy0; sy <= sy1; ++sy)
     for (int sx = sx0; sx <= sx1; ++sx) {
@@ -212,9 +233,21 @@ __global__ void __launch_bounds__(EM_THREADS) k_super_emit(const float *__restri
       if (o < cap) {
         skeys[o] = (uint32_t)sid;
         svals[o] = (uint32_t)row;
+        atomicAdd(&s_cnt[sid], 1u);
       }
       ++o;
     }
+  // per-super-tile totals (the segment table of the sorted list is their scan: no search over the sorted keys) and the
+  // digit histograms of the super-tile sort (its histogram kernel and sweep of the keys are gone)
+  __syncthreads();
+  for (int i = threadIdx.x; i < NS; i += EM_THREADS) {
+    uint32_t c = s_cnt[i];
+    if (c) {
+      atomicAdd((unsigned *)scount + i, c);
+      atomicAdd(ghist + (i & 255), c);
+      if (NS > 256) atomicAdd(ghist + 256 + (i >> 8), c);
+    }
+  }
 }
 
 
@@ -225,53 +258,50 @@ constexpr int EX_ITEMS = 2;                       // super-items per thread
 constexpr int EX_CHUNK = EX_THREADS * EX_ITEMS;   // super-items per CTA
 constexpr int EX_MAX_SUPER = 4096;                // super-tiles whose tables fit shared memory (image up to ~8K x 8K)
 
-// Segment tables of the sorted super-tile list (one block): stab[0..NS] = seg_begin (first index whose key >= s, by
-// binary search over the sorted keys — no atomics), stab[NS+1 .. 2NS+1] = chunk_begin (exclusive scan of
-// ceil(segment / chunk)); both end with their grand total.
-__global__ void __launch_bounds__(1024) k_seg_tables(const uint32_t *__restrict__ skeys, const int32_t *__restrict__ scounters,
-                                                     int NS, int32_t *__restrict__ stab) {
+// Segment tables of the sorted super-tile list (one block): stab[0..NS] = seg_begin = exclusive scan of the per-super-tile
+// pair counts k_super_emit accumulated (no search over the sorted keys), stab[NS+1 .. 2NS+1] = chunk_begin (exclusive scan
+// of ceil(segment / chunk)); both end with their grand total.
+__global__ void __launch_bounds__(1024) k_seg_tables(const int32_t *__restrict__ scount, int NS, int32_t *__restrict__ stab) {
   __shared__ int s_warp[33];
-  __shared__ int s_carry;
-  const int n = scounters[2];
-  for (int s = threadIdx.x; s <= NS; s += 1024) {
-    int lo = 0, hi = n;  // first index with key >= s
-    while (lo < hi) {
-      int mid = (lo + hi) >> 1;
-      if (skeys[mid] < (uint32_t)s) lo = mid + 1; else hi = mid;
-    }
-    stab[s] = lo;
-  }
-  if (threadIdx.x == 0) s_carry = 0;
+  __shared__ int s_carry[2];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (threadIdx.x < 2) s_carry[threadIdx.x] = 0;
   __syncthreads();
   for (int base = 0; base < NS; base += 1024) {
     int s = base + threadIdx.x;
-    int v = s < NS ? (stab[s + 1] - stab[s] + EX_CHUNK - 1) / EX_CHUNK : 0;
-    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    int inc = v;
+    int cnt = s < NS ? scount[s] : 0;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      int t = __shfl_up_sync(GS_FULL, inc, o);
-      if (lane >= o) inc += t;
-    }
-    if (lane == 31) s_warp[w] = inc;
-    __syncthreads();
-    if (w == 0) {
-      int x = s_warp[lane], xi = x;
+    for (int which = 0; which < 2; ++which) {  // 0: pairs per super-tile, 1: chunks per super-tile
+      int v = which == 0 ? cnt : (cnt + EX_CHUNK - 1) / EX_CHUNK;
+      int inc = v;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
-        int t = __shfl_up_sync(GS_FULL, xi, o);
-        if (lane >= o) xi += t;
+        int t = __shfl_up_sync(GS_FULL, inc, o);
+        if (lane >= o) inc += t;
       }
-      s_warp[lane] = xi - x;
-      if (lane == 31) s_warp[32] = xi;
+      if (lane == 31) s_warp[w] = inc;
+      __syncthreads();
+      if (w == 0) {
+        int x = s_warp[lane], xi = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          int t = __shfl_up_sync(GS_FULL, xi, o);
+          if (lane >= o) xi += t;
+        }
+        s_warp[lane] = xi - x;
+        if (lane == 31) s_warp[32] = xi;
+      }
+      __syncthreads();
+      if (s < NS) stab[which * (NS + 1) + s] = s_carry[which] + s_warp[w] + inc - v;
+      __syncthreads();
+      if (threadIdx.x == 0) s_carry[which] += s_warp[32];
+      __syncthreads();
     }
-    __syncthreads();
-    if (s < NS) stab[NS + 1 + s] = s_carry + s_warp[w] + inc - v;
-    __syncthreads();
-    if (threadIdx.x == 0) s_carry += s_warp[32];
-    __syncthreads();
   }
-  if (threadIdx.x == 0) stab[2 * NS + 1] = s_carry;
+  if (threadIdx.x == 0) {
+    stab[NS] = s_carry[0];
+    stab[2 * NS + 1] = s_carry[1];
+  }
 }
 
 // 32x32 bit-matrix transpose across the warp: on return bit i of lane L = bit L of lane i on entry (5 shuffles)
@@ -532,7 +562,7 @@ static TileWs carve(void *base, int64_t m, int64_t maxo, int width, int height) 
   w.chunk_counts = (int32_t *)take((size_t)w.ex_chunks * 64 * 4);
   w.totals = (int32_t *)take((size_t)TX * TY * 4);
   w.stab = (int32_t *)take((size_t)(2 * w.ns + 2) * 4);
-  w.zero_bytes = ((size_t)64 + 4 + w.lc_tiles + w.em_tiles) * 4;
+  w.zero_bytes = ((size_t)64 + 4 + w.lc_tiles + w.em_tiles + w.ns) * 4;
   w.zero = (uint32_t *)take(w.zero_bytes);
   int64_t big = m > maxo ? m : maxo;
   w.sort_ws = take(gs_radix_sort_workspace_bytes(big));
@@ -593,26 +623,34 @@ extern "C" int gs_tile_map(const gs_raster_config *h_cfg, int64_t m, const float
   int32_t *scounters = (int32_t *)(w.zero + 64);
   uint32_t *lc_status = w.zero + 68;
   uint32_t *em_status = lc_status + w.lc_tiles;
+  int32_t *scount = (int32_t *)(em_status + w.em_tiles);  // pairs per super-tile
   // (a) compact the live rows (>= 1 tile) in row order, then sort them by depth: stable 32-bit LSD sort, ties keep
   //     row order.  Culled / off-screen rows never enter the sort.
   int32_t *live = counters + 3;
-  k_live_compact<<<w.lc_tiles, LC_THREADS, 0, st>>>(info.counts, depth, m, lc_status, tickets + 0, w.dk[0], w.dv[0], live);
+  int rc = gs_radix_sort_prepare(w.sort_ws, m, 0, 32, st);
+  if (rc != GS_OK) return rc;
+  k_live_compact<<<w.lc_tiles, LC_THREADS, 0, st>>>(info.counts, depth, m, lc_status, tickets + 0, w.dk[0], w.dv[0], live,
+                                                    (uint32_t *)w.sort_ws);
   GS_LAUNCH_CHECK();
   int in_b = 0;
-  int rc = gs_radix_sort_pingpong(w.dk[0], w.dv[0], w.dk[1], w.dv[1], m, live, 0, 32, w.sort_ws, &in_b, st);
+  rc = gs_radix_sort_pingpong(w.dk[0], w.dv[0], w.dk[1], w.dv[1], m, live, 0, 32, w.sort_ws, &in_b, st, true);
   if (rc != GS_OK) return rc;
   uint32_t *srows = w.dv[in_b];
   // (b) one (super-tile, row) pair per super-tile a row hits, in depth order; stable sort by super-tile id
   int SXN = (TX + GS_SUPER - 1) / GS_SUPER;
-  k_super_emit<<<w.em_tiles, EM_THREADS, 0, st>>>(g2d, depth, info.recs, live, m, thr, width, height, SXN, srows,
-                                                  max_overlaps, em_status, tickets + 1, w.sk[0], w.sv[0], scounters);
-  GS_LAUNCH_CHECK();
   int bits = 1;
   while ((1 << bits) < w.ns) ++bits;
-  rc = gs_radix_sort_pingpong(w.sk[0], w.sv[0], w.sk[1], w.sv[1], max_overlaps, scounters + 2, 0, bits, w.sort_ws, &in_b, st);
+  rc = gs_radix_sort_prepare(w.sort_ws, max_overlaps, 0, bits, st);  // after the depth sort: the two sorts share the workspace
+  if (rc != GS_OK) return rc;
+  k_super_emit<<<w.em_tiles, EM_THREADS, (size_t)w.ns * sizeof(uint32_t), st>>>(
+      g2d, depth, info.recs, live, m, thr, width, height, SXN, srows, max_overlaps, em_status, tickets + 1, w.sk[0], w.sv[0],
+      scounters, w.ns, (uint32_t *)w.sort_ws, scount);
+  GS_LAUNCH_CHECK();
+  rc = gs_radix_sort_pingpong(w.sk[0], w.sv[0], w.sk[1], w.sv[1], max_overlaps, scounters + 2, 0, bits, w.sort_ws, &in_b, st,
+                              max_overlaps > 0);
   if (rc != GS_OK) return rc;
   // (c) segment / chunk tables, per-chunk sub-tile counts, their prefixes + tile ranges, then the final lists
-  k_seg_tables<<<1, 1024, 0, st>>>(w.sk[in_b], scounters, w.ns, w.stab);
+  k_seg_tables<<<1, 1024, 0, st>>>(scount, w.ns, w.stab);
   GS_LAUNCH_CHECK();
   size_t ex_smem = (size_t)(w.ns + 1) * sizeof(int32_t);
   k_expand<false><<<w.ex_chunks, EX_THREADS, ex_smem, st>>>(g2d, depth, info.recs, thr, width, height, SXN, w.ns, w.sv[in_b],

@@ -182,9 +182,11 @@ def acc_stride(channels):
 
 class RasterAux:
   """fast-path buffers of the rasteriser for one image size (gs_raster_aux): staged splat records, the heaviest-first
-  tile queue of the forward and of the backward, the per-tile work the forward measures."""
+  tile queue of the forward and of the backward, the per-tile work the forward measures.
+  persistent=False (default): one CTA per tile in tile order — measured faster on the BASELINE scenes than the
+  heaviest-first queue (neighbouring tiles run together and share their splat records in L2; profiles/README.md r2a)."""
 
-  def __init__(self, m, width, height, device, persistent=True):
+  def __init__(self, m, width, height, device, persistent=False):
     tx, ty = tiles_of(width, height)
     self.m, self.tiles = m, tx * ty
     self.records = torch.empty((m, L.GS_REC_FLOATS), device=device, dtype=torch.float32)

@@ -43,6 +43,8 @@ def _grad_check(name, a, r, q=0.999, tol=1e-4, cap=1e-2):
   a, r = a.reshape(r.shape[0], -1), r.reshape(r.shape[0], -1)
   scale = np.abs(r).max(axis=0) + 1e-20
   e = np.abs(a - r) / scale
+  print(f"grad {name}: rows {r.shape[0]}, entries above {tol:g} of the column max: {int((e > tol).sum())} of {e.size} "
+        f"({(e > tol).mean():.2e}), max {e.max():.2e}, p99.9 {np.quantile(e, 0.999):.2e}")
   assert np.quantile(e, q) <= tol, (name, np.quantile(e, [0.5, 0.99, 0.999, 1.0]).tolist())
   assert e.max() <= cap, (name, float(e.max()))
 

@@ -74,6 +74,39 @@ def main():
         good = d < 2e-2
         ok &= good
         print(f"[{mode}] vs sequential {k}: max rel diff {d:.3e} {'ok' if good else 'FAIL'}")
+  # 3. densification under DP (reference controller/target_controller.py:111-126): synchronised statistics, every rank
+  #    densifies redundantly with the controller's shared split-axis draws, then trains on; replicas must stay identical
+  if mode != "dense":
+    from gsb200.controller import TargetConfig, TargetController, piecewise
+    ctrl = TargetController(TargetConfig(min_views=1, densify_prune_interval=piecewise(world, [])), scene, int(1.3 * n),
+                            total_steps=100 * world, step=tr.step_count, trainer=tr, seed=3)
+    tr.controller = ctrl
+    more = [[(cams[(7 * s + r) % len(cams)], targets[(s * world + r) % len(targets)]) for r in range(world)] for s in range(3)]
+    for b in more:
+      tr.training_step(b)
+    tr.sync_statistics()
+    torch.cuda.synchronize()
+    grew = len(ctrl.history) >= 2 and scene.num_points > n
+    ok &= grew
+    if rank == 0:
+      print(f"[{mode}] densified under DP: {[h[1:] for h in ctrl.history]} {'ok' if grew else 'FAIL'}")
+    cnt = torch.tensor([scene.num_points], device="cuda")
+    lo, hi = cnt.clone(), cnt.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    same_n = bool(torch.equal(lo, hi))
+    ok &= same_n
+    if same_n:
+      post = dict(params=scene.params[:scene._total], exp_avg=scene.exp_avg[:scene._total], running_vis=scene.running_vis,
+                  opt_step=scene.opt_step, **{k: v.float() for k, v in scene.stats.items()})
+      for name, t in post.items():
+        lo, hi = t.clone(), t.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        same = bool(torch.equal(lo, hi))
+        ok &= same
+        if rank == 0:
+          print(f"[{mode}] after densify: replicas identical {name}: {same}")
+    elif rank == 0:
+      print(f"[{mode}] after densify: point counts differ across ranks FAIL")
   flag = torch.tensor([0 if ok else 1], device="cuda")
   dist.all_reduce(flag)
   dist.destroy_process_group()

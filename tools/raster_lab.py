@@ -60,7 +60,14 @@ def main():
   V = int((g2d[:, 5] > 0).sum().item())
   flush = torch.empty((256 << 20,), device=dev, dtype=torch.uint8)
   target = torch.rand((H, W, 3), device=dev)
-  out = dict(scene=a.scene, n=n, W=W, H=H, V=V, O=O)
+  class Out(dict):
+    def __setitem__(self, k, v):  # partial results go to stderr at once: a hang later on must not lose them
+      dict.__setitem__(self, k, v)
+      print(json.dumps({k: v}), file=sys.stderr, flush=True)
+
+  out = Out()
+  for k, v in dict(scene=a.scene, n=n, W=W, H=H, V=V, O=O).items():
+    out[k] = v
 
   # ---- gather-staged kernels (raster.cu) ------------------------------------------------------------------------------
   image, fT, nc, _, _ = ops.raster_fwd(cfg, g2d, rgb, depth, o2p, ranges, W, H)
