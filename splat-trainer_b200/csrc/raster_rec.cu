@@ -11,6 +11,18 @@
 //   * every warp builds its own candidate mask from the staged records (no cross-warp publish, one barrier per batch).
 #include "raster_common.cuh"
 
+// Pixel ownership inside a tile: warp w covers the 16x8 pixel rows [8w, 8w+8) of the tile; lane (lx = lane & 7, ly = lane >> 3)
+// owns the FOUR pixels (lx + 8a, 8w + ly + 4b), a, b in {0,1} — one pixel in each 8x4 quarter of the warp's region — instead
+// of a compact 2x2 quad.  Pixel index p = a + 2b is therefore "quarter p" for every lane of the warp: a splat that misses a
+// quarter leaves NO lane active in that p-block and the warp skips the block, where compact quads would run all four
+// blocks with idle lanes.  The lane still shares two dx and two dy values over its pixels, and a lane row is 8
+// consecutive pixels (coalesced image / gradient accesses).
+#ifndef GS_QUARTERS
+#define GS_QUARTERS 1  // 0 = compact 2x2 quads per lane (the layout of raster.cu), kept for A/B measurements
+#endif
+constexpr int QX = GS_QUARTERS ? 8 : 1, QY = GS_QUARTERS ? 4 : 1;  // distance between a lane's pixels
+constexpr int LSX = GS_QUARTERS ? 1 : 2, LSY = GS_QUARTERS ? 1 : 2;  // distance between neighbouring lanes' first pixels
+
 struct TileGeo {
   int begin, n;
   float fx0, fy0, row0;
@@ -21,19 +33,23 @@ struct TileGeo {
 __device__ __forceinline__ TileGeo tile_geo(int tile, const int32_t *__restrict__ ranges, int W, int H, int TX) {
   TileGeo c;
   int tx = tile % TX, ty = tile / TX;
-  int lx = threadIdx.x & 7, ly = threadIdx.x >> 3;
-  c.px0 = tx * GS_TILE + 2 * lx;
-  c.py0 = ty * GS_TILE + 2 * ly;
+  int lx = threadIdx.x & 7, ly = (threadIdx.x >> 3) & 3, w = threadIdx.x >> 5;
+  c.px0 = tx * GS_TILE + LSX * lx;
+  c.py0 = ty * GS_TILE + 8 * w + LSY * ly;
   c.fx0 = (float)c.px0 + 0.5f;
   c.fy0 = (float)c.py0 + 0.5f;
   c.row0 = (float)(ty * GS_TILE);
   c.in[0] = c.px0 < W && c.py0 < H;
-  c.in[1] = c.px0 + 1 < W && c.py0 < H;
-  c.in[2] = c.px0 < W && c.py0 + 1 < H;
-  c.in[3] = c.px0 + 1 < W && c.py0 + 1 < H;
+  c.in[1] = c.px0 + QX < W && c.py0 < H;
+  c.in[2] = c.px0 < W && c.py0 + QY < H;
+  c.in[3] = c.px0 + QX < W && c.py0 + QY < H;
   c.begin = ranges[2 * tile];
   c.n = ranges[2 * tile + 1] - c.begin;
   return c;
+}
+
+__device__ __forceinline__ int64_t geo_pixel(const TileGeo &c, int p, int W) {
+  return (int64_t)(c.py0 + QY * (p >> 1)) * W + c.px0 + QX * (p & 1);
 }
 
 // two stages of 64 records, as three planes of 16-byte words
@@ -222,7 +238,7 @@ __global__ void __launch_bounds__(RT) k_raster_fwd_rec(CfgDev cfg, const float *
       done[p] = !tc.in[p];
       col[p][0] = col[p][1] = col[p][2] = 0.f;
     }
-    const float fx[2] = {tc.fx0, tc.fx0 + 1.0f}, fy[2] = {tc.fy0, tc.fy0 + 1.0f};
+    const float fx[2] = {tc.fx0, tc.fx0 + (float)QX}, fy[2] = {tc.fy0, tc.fy0 + (float)QY};
     const int nb = (tc.n + RT - 1) / RT;
     if (nb > 0) {
       int id = ((int)threadIdx.x < tc.n) ? o2p[tc.begin + threadIdx.x] : -1;
@@ -302,7 +318,7 @@ __global__ void __launch_bounds__(RT) k_raster_fwd_rec(CfgDev cfg, const float *
     for (int p = 0; p < 4; ++p) {
       tmax = max(tmax, last[p]);
       if (!tc.in[p]) continue;
-      int64_t pix = (int64_t)(tc.py0 + (p >> 1)) * W + tc.px0 + (p & 1);
+      int64_t pix = geo_pixel(tc, p, W);
       image[pix * 3] = col[p][0]; image[pix * 3 + 1] = col[p][1]; image[pix * 3 + 2] = col[p][2];
       final_T[pix] = Tr[p];
       n_contrib[pix] = last[p];
@@ -355,7 +371,7 @@ __global__ void __launch_bounds__(RT) k_raster_bwd_rec(CfgDev cfg, const float *
       Tr[p] = 1.f; nc[p] = 0; R[p] = 0.f;
       dC[p][0] = dC[p][1] = dC[p][2] = 0.f;
       if (tc.in[p]) {
-        int64_t pix = (int64_t)(tc.py0 + (p >> 1)) * W + tc.px0 + (p & 1);
+        int64_t pix = geo_pixel(tc, p, W);
         Tr[p] = final_T[pix];
         nc[p] = n_contrib[pix];
         dC[p][0] = d_image[pix * 3]; dC[p][1] = d_image[pix * 3 + 1]; dC[p][2] = d_image[pix * 3 + 2];
@@ -366,7 +382,7 @@ __global__ void __launch_bounds__(RT) k_raster_bwd_rec(CfgDev cfg, const float *
     if (lane == 0) s_max[Q.flip][wid] = wmax;
     __syncthreads();
     const int top = min(max(s_max[Q.flip][0], s_max[Q.flip][1]), tc.n);
-    const float fx[2] = {tc.fx0, tc.fx0 + 1.0f}, fy[2] = {tc.fy0, tc.fy0 + 1.0f};
+    const float fx[2] = {tc.fx0, tc.fx0 + (float)QX}, fy[2] = {tc.fy0, tc.fy0 + (float)QY};
     const int nb = (top + RT - 1) / RT;
     if (nb > 0) {
       // batch b covers list positions [lo_b, hi_b), hi_b = top - b·RT, lo_b = max(0, hi_b - RT); slot j <-> lo_b + j

@@ -9,7 +9,8 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "libgsb200.so")
+# GSB200_LIB: another build of the same library (A/B measurements of kernel variants); default = the in-tree build
+LIB_PATH = os.environ.get("GSB200_LIB") or os.path.join(os.path.dirname(_HERE), "libgsb200.so")
 
 GS_GROUP_SCALAR, GS_GROUP_VECTOR, GS_GROUP_LOCAL_VECTOR = 0, 1, 2
 GS_POST_NONE, GS_POST_NORMALIZE, GS_POST_CLAMP = 0, 1, 2

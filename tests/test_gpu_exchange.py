@@ -164,7 +164,8 @@ def test_emulated_ranks_match_sequential_training_step():
     assert not a.grads.any() and not b.grads.any(), "the optimiser clears every consumed row"
     for name in ("position", "log_scaling", "rotation", "alpha_logit", "sh"):
       d = (a.p[name] - b.p[name]).abs().max().item()
-      assert d < 2e-4, (name, d)  # LaProp normalises tiny gradients: a last-bit gradient change can move an update by ~lr
+      # LaProp normalises tiny gradients: a last-bit gradient change can move an update by a fraction of lr (lr 0.3 ... 0.01)
+      assert d < 2e-3, (name, d)
     assert torch.equal(a.stats["points_in_view"], b.stats["points_in_view"])
     mx = torch.stack([s.stats["max_scale_px"] for s in reps]).amax(dim=0)
     if step == 0:  # identical parameters on both sides during the first step
