@@ -171,6 +171,8 @@ __global__ void __launch_bounds__(LC_THREADS) k_live_compact(const int32_t *__re
 // hits, at its scanned offset.
 // The last live tile publishes scounters: [0] total pairs, [1] overflow flag, [2] min(total, capacity).
 constexpr int EM_THREADS = 256;
+constexpr int EM_ITEMS = 4;                       // live rows per thread: a quarter of the CTAs in the look-back chain, four
+constexpr int EM_TILE = EM_THREADS * EM_ITEMS;    // independent record gathers in flight per thread
 
 __global__ void __launch_bounds__(EM_THREADS) k_super_emit(const float *__restrict__ g2d, const float *__restrict__ depth,
                                                            const uint4 *__restrict__ recs, const int32_t *__restrict__ live_dev,
@@ -189,26 +191,30 @@ __global__ void __launch_bounds__(EM_THREADS) k_super_emit(const float *__restri
   __syncthreads();
   const int tile = s_tile;
   int64_t live = min((int64_t)*live_dev, m);
-  int64_t tbase = (int64_t)tile * EM_THREADS;
+  int64_t tbase = (int64_t)tile * EM_TILE;
   if (tbase >= live) return;
-  int64_t j = tbase + threadIdx.x;
-  int64_t row = -1;
-  uint4 rec = make_uint4(0u, 0u, 0u, 0u);
-  if (j < live) {
-    row = (int64_t)sorted_rows[j];
-    rec = recs[row];
+  const int64_t j0 = tbase + (int64_t)threadIdx.x * EM_ITEMS;
+  int64_t row[EM_ITEMS];
+  uint4 rec[EM_ITEMS];
+  int ns[EM_ITEMS], sum = 0;
+#pragma unroll
+  for (int i = 0; i < EM_ITEMS; ++i) row[i] = (j0 + i < live) ? (int64_t)sorted_rows[j0 + i] : -1;
+#pragma unroll
+  for (int i = 0; i < EM_ITEMS; ++i) rec[i] = row[i] >= 0 ? recs[row[i]] : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+  for (int i = 0; i < EM_ITEMS; ++i) {
+    ns[i] = row[i] >= 0 ? rec_view(rec[i]).nsuper : 0;
+    sum += ns[i];
   }
-  RecView v = rec_view(rec);
-  int ns = row >= 0 ? v.nsuper : 0;
   int tot;
-  int ex = block_scan_256(ns, s_warp, tot);
+  int ex = block_scan_256(sum, s_warp, tot);
   if (threadIdx.x == 0) gs_st_status(status + tile, (uint32_t)tot | (tile == 0 ? GS_LB_INCL : GS_LB_LOCAL));
   if (threadIdx.x < 32) {
     uint32_t prefix = gs_lookback_warp(status, tile);
     if (threadIdx.x == 0) {
       if (tile > 0) gs_st_status(status + tile, (prefix + (uint32_t)tot) | GS_LB_INCL);
       s_prefix = prefix;
-      if (tbase + EM_THREADS >= live) {  // last live tile
+      if (tbase + EM_TILE >= live) {  // last live tile
         int64_t o = (int64_t)prefix + tot;
         scounters[0] = (int32_t)o;
         scounters[1] = (o > cap) ? 1 : 0;
@@ -218,25 +224,54 @@ __global__ void __launch_bounds__(EM_THREADS) k_super_emit(const float *__restri
   }
   __syncthreads();
   int64_t o = (int64_t)s_prefix + ex;
-  int sx0 = 0, sx1 = -1, sy0 = 0, sy1 = -1;
-  if (ns > 0) {
-  if (v.big) {
-    Footprint fp = load_footprint(g2d, depth, row, thr, W, H);
-    sx0 = fp.tx0 / GS_SUPER; sx1 = fp.tx1 / GS_SUPER; sy0 = fp.ty0 / GS_SUPER; sy1 = fp.ty1 / GS_SUPER;
-  } else {
-    sx0 = v.tx0 / GS_SUPER; sx1 = (v.tx0 + v.w - 1) / GS_SUPER; sy0 = v.ty0 / GS_SUPER; sy1 = (v.ty0 + v.h - 1) / GS_SUPER;
-  }
-  }
-  for (int sy = sy0; sy <= sy1; ++sy)
-    for (int sx = sx0; sx <= sx1; ++sx) {
-      int sid = sy * SXN + sx;
-      if (o < cap) {
-        skeys[o] = (uint32_t)sid;
-        svals[o] = (uint32_t)row;
-        atomicAdd(&s_cnt[sid], 1u);
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int i = 0; i < EM_ITEMS; ++i) {
+    int sx0 = 0, sx1 = -1, sy0 = 0, sy1 = -1;
+    if (ns[i] > 0) {
+      RecView v = rec_view(rec[i]);
+      if (v.big) {
+        Footprint fp = load_footprint(g2d, depth, row[i], thr, W, H);
+        sx0 = fp.tx0 / GS_SUPER; sx1 = fp.tx1 / GS_SUPER; sy0 = fp.ty0 / GS_SUPER; sy1 = fp.ty1 / GS_SUPER;
+      } else {
+        sx0 = v.tx0 / GS_SUPER; sx1 = (v.tx0 + v.w - 1) / GS_SUPER; sy0 = v.ty0 / GS_SUPER; sy1 = (v.ty0 + v.h - 1) / GS_SUPER;
       }
-      ++o;
     }
+    // a row that spans many super-tiles (a splat filling the screen emits one pair per super-tile) is written by the whole
+    // warp together, 32 pairs per round, instead of by its own lane alone while the other 31 wait
+    const bool wide = ns[i] >= 16;
+    if (ns[i] > 0 && !wide) {
+      int64_t oo = o;
+      for (int sy = sy0; sy <= sy1; ++sy)
+        for (int sx = sx0; sx <= sx1; ++sx) {
+          int sid = sy * SXN + sx;
+          if (oo < cap) {
+            skeys[oo] = (uint32_t)sid;
+            svals[oo] = (uint32_t)row[i];
+            atomicAdd(&s_cnt[sid], 1u);
+          }
+          ++oo;
+        }
+    }
+    unsigned todo = __ballot_sync(GS_FULL, wide);
+    while (todo) {
+      const int src = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const uint32_t r = __shfl_sync(GS_FULL, (uint32_t)row[i], src);
+      const int x0 = __shfl_sync(GS_FULL, sx0, src), y0 = __shfl_sync(GS_FULL, sy0, src);
+      const int nx = __shfl_sync(GS_FULL, sx1 - sx0 + 1, src), count = __shfl_sync(GS_FULL, ns[i], src);
+      const long long base = __shfl_sync(GS_FULL, (long long)o, src);
+      for (int t = lane; t < count; t += 32) {
+        int sid = (y0 + t / nx) * SXN + x0 + t % nx;
+        if (base + t < cap) {
+          skeys[base + t] = (uint32_t)sid;
+          svals[base + t] = r;
+          atomicAdd(&s_cnt[sid], 1u);
+        }
+      }
+    }
+    o += ns[i];
+  }
   // per-super-tile totals (the segment table of the sorted list is their scan: no search over the sorted keys) and the
   // digit histograms of the super-tile sort (its histogram kernel and sweep of the keys are gone)
   __syncthreads();
@@ -320,11 +355,14 @@ struct ChunkCtx {
 };
 
 // which super-tile segment a chunk belongs to: last s with chunk_begin[s] <= chunk (table staged in shared memory)
-__device__ __forceinline__ bool chunk_ctx(const int32_t *__restrict__ stab, int NS, int SXN, int32_t *cb_smem, ChunkCtx &c) {
+__device__ __forceinline__ void chunk_table(const int32_t *__restrict__ stab, int NS, int32_t *cb_smem) {
   for (int i = threadIdx.x; i <= NS; i += EX_THREADS) cb_smem[i] = stab[NS + 1 + i];
   __syncthreads();
-  c.chunk = blockIdx.x;
-  if (c.chunk >= cb_smem[NS]) return false;
+}
+
+__device__ __forceinline__ void chunk_ctx(const int32_t *__restrict__ stab, int NS, int SXN, const int32_t *cb_smem, int chunk,
+                                          ChunkCtx &c) {
+  c.chunk = chunk;
   int lo = 0, hi = NS;
   while (hi - lo > 1) {
     int mid = (lo + hi) >> 1;
@@ -334,7 +372,6 @@ __device__ __forceinline__ bool chunk_ctx(const int32_t *__restrict__ stab, int 
   c.sx = lo % SXN; c.sy = lo / SXN;
   c.seg_end = stab[lo + 1];
   c.item0 = stab[lo] + (c.chunk - cb_smem[lo]) * EX_CHUNK + (threadIdx.x >> 5) * (32 * EX_ITEMS);
-  return true;
 }
 
 // COUNT pass (WRITE = false): each thread turns its super-items into 64-bit masks of sub-tiles hit (stored for the
@@ -352,9 +389,14 @@ __global__ void __launch_bounds__(EX_THREADS) k_expand(const float *__restrict__
   __shared__ uint32_t sT[EX_WARPS][EX_ITEMS][64];    // transposed hit words: [s] = lanes of the warp hitting sub-tile s
   __shared__ uint32_t sPos[EX_WARPS][EX_ITEMS][64];  // hits of (warp, sub-tile) in earlier rounds
   __shared__ uint32_t sCnt[EX_WARPS][64];
-  ChunkCtx cc;
-  if (!chunk_ctx(stab, NS, SXN, ex_smem, cc)) return;
+  // persistent CTAs: the grid is sized for the machine, not for the list capacity (a launch with one CTA per POSSIBLE chunk
+  // spent most of its time starting CTAs that found nothing to do); the chunk table is staged once per CTA
+  chunk_table(stab, NS, ex_smem);
+  const int total_chunks = ex_smem[NS];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int chunk = blockIdx.x; chunk < total_chunks; chunk += gridDim.x) {
+  ChunkCtx cc;
+  chunk_ctx(stab, NS, SXN, ex_smem, chunk, cc);
   unsigned long long m[EX_ITEMS];
   uint32_t row[EX_ITEMS];
   uint32_t c0 = 0, c1 = 0;
@@ -409,7 +451,7 @@ __global__ void __launch_bounds__(EX_THREADS) k_expand(const float *__restrict__
       for (int i = 0; i < EX_WARPS; ++i) sCnt[i][s] = base + wo[i];
     }
   }
-  if (!WRITE) return;
+  if (WRITE) {
   __syncthreads();
   const unsigned lt = (1u << lane) - 1u;
 #pragma unroll
@@ -421,6 +463,9 @@ __global__ void __launch_bounds__(EX_THREADS) k_expand(const float *__restrict__
       uint32_t pos = sCnt[w][s] + sPos[w][r][s] + __popc(sT[w][r][s] & lt);
       if ((int64_t)pos < max_overlaps) out[pos] = (int32_t)row[r];
     }
+  }
+  }
+  __syncthreads();  // the shared arrays are reused by the next chunk
   }
 }
 
@@ -557,7 +602,7 @@ static TileWs carve(void *base, int64_t m, int64_t maxo, int width, int height) 
   int TX = (width + GS_TILE - 1) / GS_TILE, TY = (height + GS_TILE - 1) / GS_TILE;
   w.ns = ((TX + GS_SUPER - 1) / GS_SUPER) * ((TY + GS_SUPER - 1) / GS_SUPER);
   w.lc_tiles = (int)((mm + LC_TILE - 1) / LC_TILE);
-  w.em_tiles = (int)((mm + EM_THREADS - 1) / EM_THREADS);
+  w.em_tiles = (int)((mm + EM_TILE - 1) / EM_TILE);
   w.ex_chunks = (int)((oo + EX_CHUNK - 1) / EX_CHUNK) + w.ns;
   w.chunk_counts = (int32_t *)take((size_t)w.ex_chunks * 64 * 4);
   w.totals = (int32_t *)take((size_t)TX * TY * 4);
@@ -653,14 +698,18 @@ extern "C" int gs_tile_map(const gs_raster_config *h_cfg, int64_t m, const float
   k_seg_tables<<<1, 1024, 0, st>>>(scount, w.ns, w.stab);
   GS_LAUNCH_CHECK();
   size_t ex_smem = (size_t)(w.ns + 1) * sizeof(int32_t);
-  k_expand<false><<<w.ex_chunks, EX_THREADS, ex_smem, st>>>(g2d, depth, info.recs, thr, width, height, SXN, w.ns, w.sv[in_b],
+  int ex_grid = w.ex_chunks < 148 * 6 ? w.ex_chunks : 148 * 6;
+  // the write pass measured faster with one CTA per possible chunk (77 vs 89 us at C2-sparse: its scattered 4-byte stores
+  // want every resident CTA slot refilled at once), the count pass with persistent CTAs (56 -> 39 us)
+  int ex_grid_w = w.ex_chunks;
+  k_expand<false><<<ex_grid, EX_THREADS, ex_smem, st>>>(g2d, depth, info.recs, thr, width, height, SXN, w.ns, w.sv[in_b],
                                                             w.stab, w.masks, w.chunk_counts, nullptr, max_overlaps, nullptr);
   GS_LAUNCH_CHECK();
   k_chunk_prefix<<<w.ns, CP_THREADS, 0, st>>>(w.stab, w.ns, SXN, TX, TY, w.chunk_counts, w.totals, tickets + 2, max_overlaps,
                                       scounters, tile_ranges, counters);
   GS_LAUNCH_CHECK();
   if (max_overlaps == 0) return GS_OK;
-  k_expand<true><<<w.ex_chunks, EX_THREADS, ex_smem, st>>>(g2d, depth, info.recs, thr, width, height, SXN, w.ns, w.sv[in_b],
+  k_expand<true><<<ex_grid_w, EX_THREADS, ex_smem, st>>>(g2d, depth, info.recs, thr, width, height, SXN, w.ns, w.sv[in_b],
                                                            w.stab, w.masks, w.chunk_counts, w.totals, max_overlaps,
                                                            overlap_to_point);
   GS_LAUNCH_CHECK();

@@ -227,7 +227,8 @@ def test_plugin_scene_matches_the_fused_scene():
     big = float(sb.abs().max())
     assert big > 0 and float(((sa - sb).abs() / big).quantile(0.99)) < 1e-2, theirs
     # the same rows are stepped (a step below one ulp of the parameter leaves it unchanged on either side: < 2 % of rows)
-    assert int(((sa != 0).any(dim=1) != (sb != 0).any(dim=1)).sum()) < 0.02 * n
+    # (the plugin re-normalises every quaternion like the reference does, the fused step only the rows it moved: ignore ulps)
+    assert int(((sa.abs() > 1e-6).any(dim=1) != (sb.abs() > 1e-6).any(dim=1)).sum()) < 0.02 * n, theirs
   assert not ps.points.visible.any()
   # conversion between the two carries parameters and optimiser state
   conv = ps.to_splat_scene(w_ssim=0.0)
