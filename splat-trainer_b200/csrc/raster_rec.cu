@@ -423,6 +423,11 @@ __global__ void __launch_bounds__(RT) k_raster_bwd_rec(CfgDev cfg, const float *
 #pragma unroll
           for (int i = 0; i < 12; ++i) v[i] = 0.f;
           bool touched = false;
+          // per-splat and per-row factors of the position gradient, hoisted out of the pixels:
+          //   dL/dmean = -dp·(2A'·dx + B'·dy, 2C'·dy + B'·dx) = ndp·(tx, ty),  split_score += |dp|·(|tx| + |ty|)
+          const float nopl = -(B.y * LN2);  // dp = dL/dp' = opacity·ln2·(G·dL/dalpha); ndp = -dp
+          const float A2 = 2.0f * A.z;
+          const float bdy[2] = {A.w * dy[0], A.w * dy[1]}, c2dy[2] = {2.0f * B.x * dy[0], 2.0f * B.x * dy[1]};
 #pragma unroll
           for (int p = 0; p < 4; ++p) {
             float pw = __fmaf_rn(bx[p & 1], dy[p >> 1], __fadd_rn(ax[p & 1], cy[p >> 1]));
@@ -436,25 +441,26 @@ __global__ void __launch_bounds__(RT) k_raster_bwd_rec(CfgDev cfg, const float *
               Tr[p] = Tp;
               float w = a * Tp;
               float q = F.x * dC[p][0] + F.y * dC[p][1] + F.z * dC[p][2];
-              v[6] += w * dC[p][0]; v[7] += w * dC[p][1]; v[8] += w * dC[p][2];
+              v[6] = fmaf(w, dC[p][0], v[6]); v[7] = fmaf(w, dC[p][1], v[7]); v[8] = fmaf(w, dC[p][2], v[8]);
               float dLda = (q - R[p]) * Tp;
-              R[p] = a * q + (1.0f - a) * R[p];
+              R[p] = fmaf(a, q - R[p], R[p]);  // a·q + (1-a)·R
               v[11] += w;
               v[9] += fabsf(a * dLda);
               if (!clamped) {
                 float ddx = dx[p & 1], ddy = dy[p >> 1];
-                float dp = B.y * dLda * G * LN2;  // dL/dp', p' = log2(e)·power
-                float gx = -dp * (2.0f * A.z * ddx + A.w * ddy);
-                float gy = -dp * (2.0f * B.x * ddy + A.w * ddx);
-                v[0] += gx; v[1] += gy;
-                v[2] += dp * ddx * ddx; v[3] += dp * ddx * ddy; v[4] += dp * ddy * ddy;
-                v[5] += G * dLda;
-                v[10] += fabsf(gx) + fabsf(gy);
+                float GdL = G * dLda;
+                float ndp = GdL * nopl;
+                float tx = fmaf(A2, ddx, bdy[p >> 1]), ty = fmaf(A.w, ddx, c2dy[p >> 1]);
+                v[0] = fmaf(ndp, tx, v[0]); v[1] = fmaf(ndp, ty, v[1]);
+                float ndx = ndp * ddx, ndy = ndp * ddy;  // v[2..4] accumulate -dp·(dx², dx·dy, dy²): sign folded in below
+                v[2] = fmaf(ndx, ddx, v[2]); v[3] = fmaf(ndx, ddy, v[3]); v[4] = fmaf(ndy, ddy, v[4]);
+                v[5] += GdL;
+                v[10] = fmaf(fabsf(ndp), fabsf(tx) + fabsf(ty), v[10]);
               }
             }
           }
           if (__any_sync(GS_FULL, touched)) {
-            v[2] *= -0.5f * LOG2E; v[3] *= -LOG2E; v[4] *= -0.5f * LOG2E;
+            v[2] *= 0.5f * LOG2E; v[3] *= LOG2E; v[4] *= 0.5f * LOG2E;  // d/dconic from d/d(conic pre-scaled by -log2e/2, -log2e)
             int index; bool valid;
             float tot = multi_reduce12(v, lane, index, valid);
             if (valid && tot != 0.f) {

@@ -132,8 +132,13 @@ class Trainer:
     if self.dense:
       raise L.GsError("exchange='dense' keeps split_score / prune_cost per rank; use the record exchange to densify")
     st = self.scene.stats
-    dist.all_reduce(st["max_scale_px"], op=dist.ReduceOp.MAX)
     ex = self.exchange
+    if ex is not None and hasattr(ex, "stale") and ex.stale():
+      # the scene was resized by a densification since the last fold: its statistics are the fresh all-zero PointState on
+      # every rank (reference controller/target_controller.py:122), nothing to gather
+      self.scene.stats_partial = None
+      return
+    dist.all_reduce(st["max_scale_px"], op=dist.ReduceOp.MAX)
     self.scene.stats_partial = None
     if ex is None or ex.stats_rows == (0, self.scene.n):
       return
