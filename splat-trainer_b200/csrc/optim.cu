@@ -334,6 +334,100 @@ __device__ __forceinline__ void optim_row(const OptDev &c, int64_t i, int l, boo
   }
 }
 
+// VECTOR groups with wide rows (dim a multiple of 4, >= 16: the 48 SH coefficients, the 16 point features): four lanes
+// share a row and move it as 16-byte words (lane l owns words l, l+4, ...), so a warp has 8 rows and up to
+// 9 x 512 B of loads in flight instead of 2 rows / 9 x 128 B — the sweep is bound by memory-level parallelism.
+// Same arithmetic per element as optim_row<1, ...>; only the partition of the mean-square sum over lanes differs.
+template <int EPL4>
+__device__ __forceinline__ void optim_row_v4(const OptDev &c, int64_t i, int l, bool row_ok, int dim, float lr,
+                                             float *__restrict__ param, float *__restrict__ grad, float *__restrict__ exp_avg,
+                                             float *__restrict__ exp_avg_sq, const float *__restrict__ visible,
+                                             const float *__restrict__ running_vis, const float *__restrict__ step,
+                                             int post, float post_lo, float post_hi, int zero_grad) {
+  float w = row_ok ? visible[i] : 0.f;
+  bool active = row_ok && (w > 0.f);
+  float bc1 = 1.f, bc2 = 1.f, lam = 0.f, inv_w = 0.f;
+  if (active) {
+    float ts = step[i];
+    float rv = running_vis[i];
+    if (c.bias_correction) {
+      rv = rv / (1.0f - powf(c.vis_beta, ts));
+      bc1 = 1.0f - powf(c.beta1, ts);
+      bc2 = 1.0f - powf(c.beta2, ts);
+    }
+    lam = fminf(w / (rv + c.vis_smooth), 1.0f);
+    inv_w = 1.0f / (w + c.vis_smooth);
+  }
+  const int words = dim >> 2;
+  float4 *gp = reinterpret_cast<float4 *>(grad + i * dim), *pp = reinterpret_cast<float4 *>(param + i * dim);
+  float4 *mp = reinterpret_cast<float4 *>(exp_avg + i * dim);
+  float4 g[EPL4], p[EPL4], m1[EPL4];
+#pragma unroll
+  for (int j = 0; j < EPL4; ++j) {
+    int k = l + 4 * j;
+    bool ok = active && k < words;
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    g[j] = ok ? gp[k] : z;
+    p[j] = ok ? pp[k] : z;
+    m1[j] = ok ? mp[k] : z;
+  }
+  auto clipf = [&](float x) { x *= inv_w; return c.grad_clip > 0.f ? fminf(fmaxf(x, -c.grad_clip), c.grad_clip) : x; };
+  float ms = 0.f;
+#pragma unroll
+  for (int j = 0; j < EPL4; ++j) {
+    g[j].x = clipf(g[j].x); g[j].y = clipf(g[j].y); g[j].z = clipf(g[j].z); g[j].w = clipf(g[j].w);
+    ms += g[j].x * g[j].x + g[j].y * g[j].y + g[j].z * g[j].z + g[j].w * g[j].w;  // words past dim hold 0
+  }
+  ms += __shfl_xor_sync(GS_FULL, ms, 2);
+  ms += __shfl_xor_sync(GS_FULL, ms, 1);
+  ms /= (float)dim;
+  float v2 = 0.f;
+  if (active) {
+    v2 = c.beta2 * exp_avg_sq[i] + (1.0f - c.beta2) * ms;
+    if (l == 0) exp_avg_sq[i] = v2;
+  }
+  const float denom = sqrtf(v2 / bc2) + c.eps;
+  const float sc = lr * lam;
+  auto upd = [&](float &m, float gt, float &pv) {
+    float u;
+    if (c.mode == 0) {
+      m = c.beta1 * m + (1.0f - c.beta1) * gt;
+      u = (m / bc1) / denom;
+    } else {
+      m = c.beta1 * m + (1.0f - c.beta1) * gt / denom;
+      u = m / bc1;
+    }
+    pv -= sc * u;
+  };
+#pragma unroll
+  for (int j = 0; j < EPL4; ++j) {
+    upd(m1[j].x, g[j].x, p[j].x); upd(m1[j].y, g[j].y, p[j].y); upd(m1[j].z, g[j].z, p[j].z); upd(m1[j].w, g[j].w, p[j].w);
+  }
+  if (post == GS_POST_NORMALIZE) {
+    float ss = 0.f;
+#pragma unroll
+    for (int j = 0; j < EPL4; ++j) ss += p[j].x * p[j].x + p[j].y * p[j].y + p[j].z * p[j].z + p[j].w * p[j].w;
+    ss += __shfl_xor_sync(GS_FULL, ss, 2);
+    ss += __shfl_xor_sync(GS_FULL, ss, 1);
+    float inv = 1.0f / fmaxf(sqrtf(ss), 1e-12f);
+#pragma unroll
+    for (int j = 0; j < EPL4; ++j) { p[j].x *= inv; p[j].y *= inv; p[j].z *= inv; p[j].w *= inv; }
+  } else if (post == GS_POST_CLAMP) {
+    auto cl = [&](float x) { return fminf(fmaxf(x, post_lo), post_hi); };
+#pragma unroll
+    for (int j = 0; j < EPL4; ++j) { p[j].x = cl(p[j].x); p[j].y = cl(p[j].y); p[j].z = cl(p[j].z); p[j].w = cl(p[j].w); }
+  }
+#pragma unroll
+  for (int j = 0; j < EPL4; ++j) {
+    int k = l + 4 * j;
+    if (active && k < words) {
+      mp[k] = m1[j];
+      pp[k] = p[j];
+      if (zero_grad) gp[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+}
+
 // Grid-stride over rows.  Dense mode (indexes == NULL): row r is Gaussian r, rows with visible <= 0 idle.
 // Indexed mode: row r is Gaussian indexes[r], r < *count_dev (the device-side `visible.nonzero()` of the
 // reference, scene/mlp_scene.py:217, with no host read-back) — only the rows the step touches are ever read.
@@ -363,14 +457,33 @@ __device__ __forceinline__ void optim_sweep(const OptDev &c, int64_t n, const in
   }
 }
 
+template <int EPL4>
+__device__ __forceinline__ void optim_sweep_v4(const OptDev &c, int64_t n, const int32_t *__restrict__ indexes,
+                                               const int32_t *__restrict__ count_dev, const OptGroupDev &g,
+                                               const float *__restrict__ visible, const float *__restrict__ running_vis,
+                                               const float *__restrict__ step, int zero_grad) {
+  int64_t rows = indexes ? min((int64_t)*count_dev, n) : n;
+  int64_t total = rows * 4;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  int lane = threadIdx.x & 31;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t - lane < total; t += stride) {  // warp-uniform trip count
+    int64_t r = t >> 2;
+    bool row_ok = r < rows;
+    int64_t i = row_ok ? (indexes ? (int64_t)indexes[r] : r) : 0;
+    optim_row_v4<EPL4>(c, i, (int)(t & 3), row_ok, g.dim, g.lr, g.param, g.grad, g.exp_avg, g.exp_avg_sq, visible, running_vis,
+                       step, g.post, g.post_lo, g.post_hi, zero_grad);
+  }
+}
+
 // variant = the (KIND, LANES, EPL) instantiation a group runs with
 __host__ __device__ inline int optim_variant(int kind, int dim) {
   if (kind == GS_GROUP_LOCAL_VECTOR) return 0;
+  if (kind == GS_GROUP_VECTOR && dim >= 16 && dim % 4 == 0) return 7 + (dim <= 16 ? 0 : (dim <= 32 ? 1 : (dim <= 48 ? 2 : 3)));
   int w = dim <= 4 ? 0 : (dim <= 16 ? 1 : 2);
   return 1 + (kind == GS_GROUP_SCALAR ? 0 : 3) + w;
 }
 __host__ inline int optim_variant_lanes(int variant) {
-  const int lanes[7] = {1, 1, 4, 16, 1, 4, 16};
+  const int lanes[11] = {1, 1, 4, 16, 1, 4, 16, 4, 4, 4, 4};
   return lanes[variant];
 }
 
@@ -391,6 +504,21 @@ __global__ void __launch_bounds__(256) k_optim_groups(OptDev c, int64_t n, const
   }
 }
 
+// the wide-row VECTOR groups (variants 7..10) in their own kernel: they hold a row in twelve 16-byte registers per array
+// and would cost the narrow sweeps above their occupancy
+__global__ void __launch_bounds__(256) k_optim_groups_v4(OptDev c, int64_t n, const int32_t *__restrict__ indexes,
+                                                         const int32_t *__restrict__ count_dev, OptGroupsDev gs,
+                                                         const float *__restrict__ visible, const float *__restrict__ running_vis,
+                                                         const float *__restrict__ step, int zero_grad) {
+  const OptGroupDev &g = gs.g[blockIdx.y];
+  switch (g.variant) {
+    case 7: optim_sweep_v4<1>(c, n, indexes, count_dev, g, visible, running_vis, step, zero_grad); break;
+    case 8: optim_sweep_v4<2>(c, n, indexes, count_dev, g, visible, running_vis, step, zero_grad); break;
+    case 9: optim_sweep_v4<3>(c, n, indexes, count_dev, g, visible, running_vis, step, zero_grad); break;
+    default: optim_sweep_v4<4>(c, n, indexes, count_dev, g, visible, running_vis, step, zero_grad); break;
+  }
+}
+
 static int optim_check_group(const gs_optim_group &q) {
   GS_REQUIRE(q.param && q.grad && q.exp_avg && q.exp_avg_sq, "null argument");
   GS_REQUIRE(q.dim >= 1 && q.dim <= 64, "dim must be 1..64");
@@ -405,8 +533,9 @@ extern "C" int gs_optim_step_groups(const gs_optim_config *h, int64_t n, const i
   GS_REQUIRE(h && groups && visible && running_vis && step, "null argument");
   GS_REQUIRE(n_groups >= 1 && n_groups <= GS_OPTIM_MAX_GROUPS, "1..GS_OPTIM_MAX_GROUPS groups per call");
   GS_REQUIRE((indexes == nullptr) == (count_dev == nullptr), "indexes and count_dev go together");
-  OptGroupsDev gs;
-  int64_t want = 1;
+  OptGroupsDev gs[2];  // [0] narrow sweeps, [1] wide-row vector sweeps
+  int cnt[2] = {0, 0};
+  int64_t want[2] = {1, 1};
   for (int k = 0; k < n_groups; ++k) {
     const gs_optim_group &q = groups[k];
     int rc = optim_check_group(q);
@@ -415,22 +544,33 @@ extern "C" int gs_optim_step_groups(const gs_optim_config *h, int64_t n, const i
     for (int j = 0; j < n_groups; ++j)
       GS_REQUIRE(!(j != k && groups[j].kind == GS_GROUP_LOCAL_VECTOR && (groups[j].basis_ls == q.param || groups[j].basis_q == q.param)),
                  "a group of the call updates the basis of another one: put it in a later call");
-    OptGroupDev &d = gs.g[k];
-    d.variant = optim_variant(q.kind, q.dim);
+    int variant = optim_variant(q.kind, q.dim);
+    if (variant >= 7 && ((((uintptr_t)q.param | (uintptr_t)q.grad | (uintptr_t)q.exp_avg) & 15u) != 0))
+      variant = 1 + 3 + (q.dim <= 4 ? 0 : (q.dim <= 16 ? 1 : 2));  // rows not 16-byte aligned: the scalar-lane sweep
+    const int wsel = variant >= 7 ? 1 : 0;
+    OptGroupDev &d = gs[wsel].g[cnt[wsel]++];
+    d.variant = variant;
     d.dim = q.dim; d.post = q.post; d.lr = q.lr; d.post_lo = q.post_lo; d.post_hi = q.post_hi;
     d.param = q.param; d.grad = q.grad; d.exp_avg = q.exp_avg; d.exp_avg_sq = q.exp_avg_sq;
     d.basis_ls = q.basis_ls; d.basis_q = q.basis_q;
     int64_t w = (n * optim_variant_lanes(d.variant) + 255) / 256;
-    want = w > want ? w : want;
+    want[wsel] = w > want[wsel] ? w : want[wsel];
   }
   if (n <= 0) return GS_OK;
   OptDev c = {h->mode, h->beta1, h->beta2, h->eps, h->vis_beta, h->vis_smooth, h->grad_clip, h->bias_correction};
   // grid: per group enough CTAs to fill the machine (148 SMs x 8 resident CTAs of 256 threads), never more than the
   // work; the sweeps are latency bound (scattered rows), so the widest group sets the pace and the CTAs of narrow
   // groups that find no rows leave at once
-  dim3 grid((unsigned)(want < 148 * 8 ? want : 148 * 8), (unsigned)n_groups);
-  k_optim_groups<<<grid, 256, 0, (cudaStream_t)stream>>>(c, n, indexes, count_dev, gs, visible, running_vis, step, zero_grad);
-  GS_LAUNCH_CHECK();
+  if (cnt[0] > 0) {
+    dim3 grid((unsigned)(want[0] < 148 * 8 ? want[0] : 148 * 8), (unsigned)cnt[0]);
+    k_optim_groups<<<grid, 256, 0, (cudaStream_t)stream>>>(c, n, indexes, count_dev, gs[0], visible, running_vis, step, zero_grad);
+    GS_LAUNCH_CHECK();
+  }
+  if (cnt[1] > 0) {
+    dim3 grid((unsigned)(want[1] < 148 * 8 ? want[1] : 148 * 8), (unsigned)cnt[1]);
+    k_optim_groups_v4<<<grid, 256, 0, (cudaStream_t)stream>>>(c, n, indexes, count_dev, gs[1], visible, running_vis, step, zero_grad);
+    GS_LAUNCH_CHECK();
+  }
   return GS_OK;
 }
 
