@@ -236,6 +236,31 @@ class Trainer:
       self.check_overflow()
     if self.controller is not None and self.controller.step(self.step_count) is not None:
       self._check_now = True  # the scene changed size: capacities are re-checked after the next step
+    if read_loss == "pipelined":
+      # the loss of EVERY step is read back, one step late: this step's sums start an asynchronous 8-byte copy into pinned
+      # host memory and the previous step's (landed long ago) are returned — no host sync on the step's critical path
+      # (the reference itself reads its losses only on logging steps, trainer/trainer.py:485-494); flush_loss() returns the
+      # last one
+      prev = self.flush_loss()
+      if total is not None:
+        if self._loss_host is None:
+          self._loss_host = [torch.empty((2,), dtype=torch.float32).pin_memory() for _ in range(2)]
+        slot = self._loss_host[self.steps_done & 1]
+        slot.copy_(total, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        self._loss_pending = (slot, ev)
+      return prev
     if read_loss:
       return [float(x) for x in total.cpu().tolist()] if total is not None else [0.0, 0.0]
     return total
+
+  _loss_host, _loss_pending = None, None
+
+  def flush_loss(self):
+    """the (Σ|d|, Σd²) of the last step started with read_loss="pipelined" (waits for its copy), or None."""
+    pend, self._loss_pending = self._loss_pending, None
+    if pend is None:
+      return None
+    pend[1].synchronize()
+    return [float(x) for x in pend[0].tolist()]
