@@ -50,6 +50,8 @@ def parse():
   ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl", "dense", "local"],
                   help="N>1 gradient/statistics exchange: per-image records over peer memory (auto/peer), records "
                        "all-gathered by NCCL, or the dense SUM all-reduce of the packed gradient buffer")
+  ap.add_argument("--shard", default="auto", choices=["auto", "rows", "replicated"],
+                  help="N>1: optimiser sharded by row slice (each rank steps N/W rows and pushes them to its peers) or replicated")
   ap.add_argument("--raster", default="async", choices=["async", "gather"])
   ap.add_argument("--c5-steps", type=int, default=2000, help="c5: optimiser steps of the whole 500k -> 5M run")
   return ap.parse_args()
@@ -248,12 +250,16 @@ def setup_b200(args, workload_name):
               dev_targets=[t.cuda() for t in host_targets])
 
 
-def replicas_identical(scene, world):
-  """outside the timed region: every rank holds bit-identical parameters and moments (MIN == MAX of a 64-bit digest)"""
+def replicas_identical(scene, world, trainer=None):
+  """outside the timed region: every rank holds bit-identical parameters and moments (MIN == MAX of a 64-bit digest).
+  Row-sharded optimiser: the moments of a row live on its owner, so the slices are gathered first — the parameters
+  were pushed to every replica by the steps themselves."""
   import torch
   import torch.distributed as dist
   if world <= 1:
     return None
+  if trainer is not None and trainer.sharded:
+    trainer.sync_statistics()
   digest = []
   for t in (scene.params[:scene._total], scene.exp_avg[:scene._total], scene.exp_avg_sq_flat, scene.running_vis):
     digest.append(t.view(torch.int32).to(torch.int64).sum())
@@ -287,7 +293,7 @@ def run_b200(args):
     local_k = int(os.environ.get("GS_LOCAL_IMAGES", "1"))  # K different images per step packed + folded on one GPU
     trainer = Trainer(scene, 1, 0, exchange=ImageExchange(scene, 1, 0, transport="local", images_per_rank=local_k), check_every=0)
   else:
-    trainer = Trainer(scene, world, rank, exchange=args.exchange, check_every=0)  # overflow is checked around the timed region
+    trainer = Trainer(scene, world, rank, exchange=args.exchange, check_every=0, shard=args.shard)  # overflow is checked around the timed region
 
   def batch_for(i, targets):
     # the step's full batch has `world` images; only this rank's entry is materialised (others are None-padded)
@@ -320,7 +326,8 @@ def run_b200(args):
       step(i, dev_targets)
     torch.cuda.synchronize()
     ex = trainer.exchange
-    exchange_info = {"transport": ex.transport, "record_capacity_rows": ex.cap, "rows_per_image": rows,
+    exchange_info = {"transport": ex.transport, "optimizer_shard": getattr(ex, "shard", "replicated"),
+                     "record_capacity_rows": ex.cap, "rows_per_image": rows,
                      "bytes_read_per_peer_image": ex.bytes_per_image(rows),
                      "dense_allreduce_bytes": int(scene.grads.numel() * 4)}
     if getattr(ex, "fallback_reason", None):
@@ -403,7 +410,7 @@ def run_b200(args):
       dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_windows.append(float(t.item()))
   e2e_s = median(e2e_windows)
-  identical = replicas_identical(scene, world)
+  identical = replicas_identical(scene, world, trainer)
   del state0
 
   # ---- what the last image did (outside every timed region) -----------------------------------------------------------
@@ -511,7 +518,7 @@ def run_c5(args):
   target_points = 10 * wl["n"]
   total_images = args.c5_steps * world  # the reference's schedule counts images (trainer/trainer.py:532)
   scene = SplatScene(wl["gaussians"], SceneConfig(sh_degree=wl["sh_degree"], raster=args.raster, capacity=int(1.02 * target_points)))
-  trainer = Trainer(scene, world, rank, exchange=args.exchange, check_every=25)
+  trainer = Trainer(scene, world, rank, exchange=args.exchange, check_every=25, shard=args.shard)
   controller = TargetController(TargetConfig(), scene, target_points, total_images, trainer=trainer, seed=0)
   controller.record_events = True
   trainer.controller = controller
@@ -543,7 +550,7 @@ def run_c5(args):
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
   ms = float(t.item())
   dens = [a.elapsed_time(b) for a, b in controller.events]
-  identical = replicas_identical(scene, world)
+  identical = replicas_identical(scene, world, trainer)
   if rank == 0:
     line = {"metric": "train_iters_per_sec", "value": world * args.c5_steps / (ms * 1e-3), "unit": "iters/s",
             "n_gpus": world, "steps": args.c5_steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.c5_steps,

@@ -359,6 +359,7 @@ int gs_gather_rows(const void *src, void *dst, int64_t s, const int64_t *idx, in
  * ------------------------------------------------------------------------------------- */
 #define GS_EXCHANGE_MAX_GROUPS 8
 #define GS_EXCHANGE_MAX_IMAGES 64
+#define GS_EXCHANGE_MAX_PEERS 16
 typedef struct gs_exchange_groups {
   int32_t count;                          /* parameter groups, in record-plane order            */
   int32_t dim[GS_EXCHANGE_MAX_GROUPS];    /* floats per row of each group                       */
@@ -377,15 +378,25 @@ int gs_exchange_pack(int64_t n, const float *g2d, const float *vis, int vis_stri
                      float *clear_vis, const gs_exchange_groups *groups, void *record, int64_t cap,
                      void *workspace, size_t workspace_bytes, void *stream);
 /* records: HOST array of n_images device (or peer) pointers, in image order.  Adds every record's rows into the
- * gradient planes and their visibility into scene_visible (every rank needs both in full for the optimiser), and folds
+ * gradient planes and their visibility into scene_visible for rows [grad_begin, grad_end) (32-row aligned; all rows for the
+ * replicated optimiser, this rank's slice for the row-sharded one), and folds
  * the controller statistics of rows [stats_begin, stats_end) (4-row aligned; the whole scene on one GPU, this rank's
  * slice under DP — the statistics are only read at a densification, where the slices are all-gathered):
  * split_score / prune_cost by exp_lerp over in-view rows (0 for rows no pixel blended), points_in_view += 1,
  * visibility += vis for blended rows. */
 int gs_exchange_fold(int64_t n, int n_images, const void *const *records, int64_t cap,
-                     const gs_exchange_groups *groups, float split_alpha, float prune_alpha,
-                     float *prune_cost, float *split_score, int16_t *points_in_view, float *visibility,
-                     int64_t stats_begin, int64_t stats_end, float *scene_visible, void *stream);
+                     const gs_exchange_groups *groups, float split_alpha, float prune_alpha, float *prune_cost,
+                     float *split_score, int16_t *points_in_view, float *visibility, int64_t stats_begin,
+                     int64_t stats_end, int64_t grad_begin, int64_t grad_end, float *scene_visible, void *stream);
+/* Row-sharded optimiser under DP (reduce by row slice, step 1/W of the rows, all-gather the updated
+ * rows): gs_exchange_fold with [grad_begin, grad_end) = this rank's 32-row-aligned slice sums only those gradient rows
+ * (and their `visible`); after the optimiser step on the slice, gs_exchange_publish writes the parameter rows it
+ * touched — indexes[0 .. count[0]) relative to row_begin, the list gs_optim_begin produced — into every peer's copy of
+ * the parameter planes (peer_bases[q] = peer q's mapping of the buffer that starts at local_base here; param_groups:
+ * .grad[g] = this rank's PARAMETER plane of group g).  A barrier across ranks must follow before the planes are read. */
+int gs_exchange_publish(const int32_t *indexes, const int32_t *count, int64_t max_rows, int64_t row_begin,
+                        const gs_exchange_groups *param_groups, const void *local_base, int n_peers,
+                        void *const *peer_bases, void *stream);
 
 /* ---------------------------------------------------------------------------------------
  * (7) Per-step controller / scene passes over every splat.
@@ -423,6 +434,13 @@ size_t gs_ssim_workspace_bytes(int height, int width, int channels, int levels);
 int gs_ssim_loss(int height, int width, int channels, int levels, const float *pred, const float *target,
                  const uint8_t *target_u8, float weight, float *d_pred, float *ssim_sums, void *workspace,
                  size_t workspace_bytes, void *stream);
+/* The whole image loss of Trainer.compute_losses in one call (reference trainer/trainer.py:465-498: l1 / mse terms +
+ * compute_ssim_loss): gs_loss_l1_mse followed by gs_ssim_loss, with the L1/MSE arithmetic done by the level-0 SSIM
+ * forward on the pixels it already holds (no separate sweep of the image) and the pooled levels running on a helper
+ * stream beside it.  d_pred is WRITTEN; l1_mse_sums[2] = Σ|d|, Σd² and ssim_sums[levels] are zeroed here. */
+int gs_photometric_loss(int height, int width, int channels, int levels, const float *pred, const float *target,
+                        const uint8_t *target_u8, float w_l1, float w_mse, float w_ssim, float *d_pred,
+                        float *l1_mse_sums, float *ssim_sums, void *workspace, size_t workspace_bytes, void *stream);
 
 /* ---------------------------------------------------------------------------------------
  * (9) Colour MLP path of MLPScene: MLPScene.eval_colors -> ColorModel.forward, reference

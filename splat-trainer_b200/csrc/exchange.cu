@@ -72,6 +72,12 @@ __device__ __forceinline__ void group_of(const GroupsDev &gd, int e, int &k_in, 
   k_in = e - start;
 }
 
+struct PeersDev {
+  int count;
+  char *base[GS_EXCHANGE_MAX_PEERS];
+  size_t plane_offset[GS_EXCHANGE_MAX_GROUPS];
+};
+
 struct RecordsDev {
   int count;
   const void *rec[GS_EXCHANGE_MAX_IMAGES];
@@ -338,7 +344,8 @@ __global__ void __launch_bounds__(256) k_fold_stats(int64_t n, int64_t cap, Reco
 // round trip for all images), then for every row some image blended each lane keeps two elements of the dense
 // gradient row in registers and adds the images' record rows in image order — no barrier, no atomics.  A record row
 // is one coalesced 8-B-per-lane warp load (256 B for SH3), the unit NVLink moves efficiently.
-__global__ void __launch_bounds__(256, 8) k_fold_rows(int64_t n, int64_t cap, RecordsDev recs, GroupsDev gd) {
+__global__ void __launch_bounds__(256, 8) k_fold_rows(int64_t n, int64_t cap, RecordsDev recs, GroupsDev gd, int64_t word_begin,
+                                                      int64_t word_end) {
   const int lane = threadIdx.x & 31;
   const int64_t words = (n + 31) / 32;
   const size_t plane = al256((size_t)words * 4);
@@ -355,7 +362,7 @@ __global__ void __launch_bounds__(256, 8) k_fold_rows(int64_t n, int64_t cap, Re
     if (e < gd.total) group_of(gd, e, hk[q], hdim[q], hplane[q]);
     else if (e == gd.total) { hdim[q] = 1; hplane[q] = gd.vis; }
   }
-  for (int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < words; w += warps) {
+  for (int64_t w = word_begin + (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5); w < word_end; w += warps) {
     unsigned vb0 = 0u, bs0 = 0u, vb1 = 0u, bs1 = 0u;  // images lane and lane + 32
     if (lane < recs.count) {
       const char *rec = (const char *)recs.rec[lane] + 256;
@@ -489,12 +496,14 @@ extern "C" int gs_exchange_pack(int64_t n, const float *g2d, const float *vis, i
 extern "C" int gs_exchange_fold(int64_t n, int n_images, const void *const *records, int64_t cap,
                                 const gs_exchange_groups *groups, float split_alpha, float prune_alpha, float *prune_cost,
                                 float *split_score, int16_t *points_in_view, float *visibility, int64_t stats_begin,
-                                int64_t stats_end, float *scene_visible, void *stream) {
+                                int64_t stats_end, int64_t grad_begin, int64_t grad_end, float *scene_visible, void *stream) {
   GS_REQUIRE(n > 0 && n < ((int64_t)1 << 30), "n must be in [1, 2^30)");
   GS_REQUIRE(n_images >= 1 && n_images <= GS_EXCHANGE_MAX_IMAGES, "n_images must be 1..GS_EXCHANGE_MAX_IMAGES");
   GS_REQUIRE(records && prune_cost && split_score && points_in_view && visibility, "null argument");
   GS_REQUIRE(stats_begin >= 0 && stats_begin <= stats_end && stats_end <= n, "bad statistics row range");
   GS_REQUIRE(stats_begin % 4 == 0 && (stats_end % 4 == 0 || stats_end == n), "statistics row range must be 4-row aligned");
+  GS_REQUIRE(grad_begin >= 0 && grad_begin <= grad_end && grad_end <= n, "bad gradient row range");
+  GS_REQUIRE(grad_begin % 32 == 0 && (grad_end % 32 == 0 || grad_end == n), "gradient row range must be 32-row aligned");
   GroupsDev gd;
   GS_REQUIRE(make_groups(groups, &gd) == 0, "bad parameter groups");
   gd.vis = scene_visible;
@@ -511,10 +520,61 @@ extern "C" int gs_exchange_fold(int64_t n, int n_images, const void *const *reco
                                                           points_in_view, visibility, stats_begin, stats_end);
     GS_LAUNCH_CHECK();
   }
-  {
-    int64_t words = (n + 31) / 32, want = (words + 7) / 8;
-    k_fold_rows<<<(int)(want < 148 * 64 ? want : 148 * 64), 256, 0, st>>>(n, cap, rd, gd);
+  if (grad_end > grad_begin) {
+    int64_t wb = grad_begin / 32, we = (grad_end + 31) / 32, want = (we - wb + 7) / 8;
+    k_fold_rows<<<(int)(want < 148 * 64 ? want : 148 * 64), 256, 0, st>>>(n, cap, rd, gd, wb, we);
+    GS_LAUNCH_CHECK();
   }
+  return GS_OK;
+}
+
+// Row-sharded optimiser: the rank that owns a row slice has stepped it; the rows it touched are
+// written into every peer's copy of the parameter planes over NVLink.  One grid row per parameter group: thread t of a
+// group handles element t % dim of the (t / dim)-th touched row, so runs of neighbouring rows leave as full sectors.
+__global__ void __launch_bounds__(256) k_publish_rows(const int32_t *__restrict__ indexes, const int32_t *__restrict__ count,
+                                                      int64_t row_begin, GroupsDev gd, PeersDev peers) {
+  const int g = blockIdx.y;
+  if (g >= gd.count) return;
+  const int dim = gd.dim[g];
+  const float *src = gd.grad[g];  // (here: the PARAMETER plane of the group)
+  const int64_t total = (int64_t)count[0] * dim;
+  const size_t plane_off = peers.plane_offset[g];
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t i = t / dim;
+    const int k = (int)(t - i * dim);
+    const int64_t at = (row_begin + indexes[i]) * dim + k;
+    const float v = src[at];
+#pragma unroll 1
+    for (int q = 0; q < peers.count; ++q) reinterpret_cast<float *>(peers.base[q] + plane_off)[at] = v;
+  }
+}
+
+extern "C" int gs_exchange_publish(const int32_t *indexes, const int32_t *count, int64_t max_rows, int64_t row_begin,
+                                   const gs_exchange_groups *param_groups, const void *local_base, int n_peers,
+                                   void *const *peer_bases, void *stream) {
+  GS_REQUIRE(indexes && count && param_groups && local_base && peer_bases, "null argument");
+  GS_REQUIRE(n_peers >= 0 && n_peers <= GS_EXCHANGE_MAX_PEERS, "n_peers must be 0..GS_EXCHANGE_MAX_PEERS");
+  GS_REQUIRE(max_rows >= 0 && row_begin >= 0, "bad row range");
+  if (n_peers == 0 || max_rows == 0) return GS_OK;
+  GroupsDev gd;
+  GS_REQUIRE(make_groups(param_groups, &gd) == 0, "bad parameter groups");
+  PeersDev pd;
+  pd.count = n_peers;
+  for (int q = 0; q < GS_EXCHANGE_MAX_PEERS; ++q) {
+    pd.base[q] = q < n_peers ? (char *)peer_bases[q] : nullptr;
+    GS_REQUIRE(q >= n_peers || peer_bases[q], "null peer base");
+  }
+  for (int g = 0; g < GS_EXCHANGE_MAX_GROUPS; ++g) {
+    pd.plane_offset[g] = 0;
+    if (g < gd.count) {
+      ptrdiff_t off = (const char *)gd.grad[g] - (const char *)local_base;
+      GS_REQUIRE(off >= 0, "a parameter plane lies before local_base");
+      pd.plane_offset[g] = (size_t)off;
+    }
+  }
+  int64_t want = (max_rows * 48 + 255) / 256;
+  dim3 grid((unsigned)(want < 148 * 4 ? (want > 0 ? want : 1) : 148 * 4), (unsigned)gd.count);
+  k_publish_rows<<<grid, 256, 0, (cudaStream_t)stream>>>(indexes, count, row_begin, gd, pd);
   GS_LAUNCH_CHECK();
   return GS_OK;
 }

@@ -25,6 +25,21 @@ struct Win { float g[11]; };
 
 __device__ __forceinline__ float clamp01(float v) { return fminf(fmaxf(v, 0.f), 1.f); }
 
+// x / 255 for the integer values a uint8 target holds, correctly rounded like the IEEE division the oracle does, without
+// the division's slow-path check: one multiply by RN(1/255) and one exact-remainder correction (Markstein)
+__device__ __forceinline__ float u8_unit(float x) {
+  const float r = 1.0f / 255.0f;
+  float q = x * r;
+  return fmaf(fmaf(-q, 255.0f, x), r, q);
+}
+
+// 1 / x for x well inside the normal range (here x >= C1 * C2): MUFU.RCP refined by one Newton step
+__device__ __forceinline__ float rcp_newton(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return fmaf(r, fmaf(-x, r, 1.0f), r);
+}
+
 constexpr int SG = 4;             // outputs per thread along the filtered axis (register tiling: 14 loads feed 4 outputs)
 
 // 4 outputs of an 11-tap filter from 14 consecutive inputs
@@ -43,11 +58,13 @@ template <int C>
 __global__ void __launch_bounds__(ST * ST) k_ssim_fwd(Win win, int H, int W, const float *__restrict__ pred, int clamp_pred,
                                                       const float *__restrict__ target, const uint8_t *__restrict__ target_u8,
                                                       float *__restrict__ dm1, float *__restrict__ dm2, float *__restrict__ dm3,
-                                                      float *__restrict__ sum_out) {
+                                                      float *__restrict__ sum_out, float w_l1, float w_mse, float inv_n,
+                                                      float *__restrict__ lm_dpred, float *__restrict__ lm_sums) {
   extern __shared__ float ssim_smem[];
   float *sP = ssim_smem, *sT = sP + SH * SH * C, *sHz = sT + SH * SH * C;
   constexpr int HZ = SH * ST * C;  // one horizontally filtered plane
   __shared__ float s_red[ST * ST / 32];
+  float lm1 = 0.f, lm2 = 0.f;  // fused L1 / MSE photometric loss of the tile's own pixels (lm_sums != NULL, level 0)
   const int tid = threadIdx.x;
   const int tx0 = blockIdx.x * ST, ty0 = blockIdx.y * ST;
   {  // halo tile load, fully unrolled so that every global load is in flight before the first use (the tile is a
@@ -71,7 +88,20 @@ __global__ void __launch_bounds__(ST * ST) k_ssim_fwd(Win win, int H, int W, con
       int i = tid + it * ST * ST;
       if (i < SH * SH * C) {
         sP[i] = clamp_pred ? clamp01(pl[it]) : pl[it];
-        sT[i] = target_u8 ? tl[it] / 255.0f : tl[it];
+        sT[i] = target_u8 ? u8_unit(tl[it]) : tl[it];
+        // gs_loss_l1_mse's arithmetic for the 16x16 pixels this tile owns: the values are in registers anyway, so the
+        // separate loss kernel and its sweep of the image are gone
+        int c = i % C, rx = (i / C) % SH, ry = i / (C * SH);
+        int gx = tx0 - SR + rx, gy = ty0 - SR + ry;
+        if (lm_sums && rx >= SR && rx < SR + ST && ry >= SR && ry < SR + ST && gx < W && gy < H) {
+          float pr = pl[it];
+          bool ins = (pr >= 0.f) && (pr <= 1.f);
+          float dd = clamp01(pr) - sT[i];
+          lm1 += fabsf(dd);
+          lm2 += dd * dd;
+          float sg = dd > 0.f ? 1.f : (dd < 0.f ? -1.f : 0.f);
+          if (lm_dpred) lm_dpred[((int64_t)gy * W + gx) * C + c] = ins ? (w_l1 * sg + w_mse * 2.0f * dd) * inv_n : 0.f;
+        }
       }
     }
   }
@@ -131,15 +161,17 @@ __global__ void __launch_bounds__(ST * ST) k_ssim_fwd(Win win, int H, int W, con
       float m1 = q[0][o], m2 = q[1][o];
       float s1 = q[2][o] - m1 * m1, s2 = q[3][o] - m2 * m2, s12 = q[4][o] - m1 * m2;
       float A = 2.f * m1 * m2 + C1, B = 2.f * s12 + C2, Cc = m1 * m1 + m2 * m2 + C1, D = s1 + s2 + C2;
-      float icd = 1.0f / (Cc * D);
+      // one reciprocal for the three quotients of the map and its partial derivatives
+      float icd = rcp_newton(Cc * D);
+      float rC = D * icd, rD = Cc * icd;  // 1 / Cc, 1 / D
       float map = A * B * icd;
       if (valid) local += map;
       if (inside) {
         int64_t gi = ((int64_t)gy * W + gx) * C + c;
         float w = valid ? 1.f : 0.f;
         // d map / d mu1 with E[pp], E[pt] fixed (s1, s12 depend on mu1), d map / d E[pp], d map / d E[pt]
-        dm1[gi] = w * (2.f * m2 * (B - A) * icd - 2.f * m1 * map / Cc + 2.f * m1 * map / D);
-        dm2[gi] = w * (-map / D);
+        dm1[gi] = w * (2.f * m2 * (B - A) * icd + 2.f * m1 * map * (rD - rC));
+        dm2[gi] = w * (-map * rD);
         dm3[gi] = w * (2.f * A * icd);
       }
     }
@@ -151,6 +183,18 @@ __global__ void __launch_bounds__(ST * ST) k_ssim_fwd(Win win, int H, int W, con
     float t = 0.f;
     for (int k = 0; k < ST * ST / 32; ++k) t += s_red[k];
     if (t != 0.f) atomicAdd(sum_out, t);
+  }
+  if (lm_sums) {
+    __shared__ float s_lm[2][ST * ST / 32];
+    lm1 = warp_sum(lm1);
+    lm2 = warp_sum(lm2);
+    if ((tid & 31) == 0) { s_lm[0][tid >> 5] = lm1; s_lm[1][tid >> 5] = lm2; }
+    __syncthreads();
+    if (tid < 2) {
+      float t = 0.f;
+      for (int k = 0; k < ST * ST / 32; ++k) t += s_lm[tid][k];
+      atomicAdd(lm_sums + tid, t);
+    }
   }
 }
 
@@ -220,7 +264,7 @@ __global__ void __launch_bounds__(ST * ST) k_ssim_bwd(Win win, int H, int W, con
       int64_t gi = ((int64_t)gy * W + gx) * C + c;
       float raw = pred[gi];
       float p = clamp_pred ? clamp01(raw) : raw;
-      float t = target_u8 ? (float)target_u8[gi] / 255.0f : target[gi];
+      float t = target_u8 ? u8_unit((float)target_u8[gi]) : target[gi];
       float d = scale * (q[0][o] + 2.f * p * q[1][o] + t * q[2][o]);
       // transpose of the 2x2 average pooling: a quarter of the next coarser level's gradient (already complete: the
       // backward runs coarse to fine), for pixels inside the pooled area (floor sizes)
@@ -247,7 +291,7 @@ __global__ void __launch_bounds__(256) k_pool2(int h, int w, int C, int Wf, cons
       int64_t j = ((int64_t)(2 * y + dy) * Wf + 2 * x + dx) * C + c;
       float p = p_in[j];
       ps += clamp_pred ? clamp01(p) : p;
-      ts += t_u8 ? (float)t_u8[j] / 255.0f : t_in[j];
+      ts += t_u8 ? u8_unit((float)t_u8[j]) : t_in[j];
     }
   p_out[i] = 0.25f * ps;
   t_out[i] = 0.25f * ts;
@@ -278,7 +322,7 @@ extern "C" size_t gs_ssim_workspace_bytes(int height, int width, int channels, i
 
 template <int C>
 static int ssim_run(int H, int W, int levels, const float *pred, const float *target, const uint8_t *target_u8, float weight,
-                    float *d_pred, float *ssim_sums, void *workspace, cudaStream_t st) {
+                    float *d_pred, float *ssim_sums, void *workspace, cudaStream_t st, float w_l1, float w_mse, float *lm_sums) {
   Win win = make_window();
   const size_t fwd_smem = (size_t)(2 * SH * SH + 5 * SH * ST) * C * sizeof(float);
   const size_t bwd_smem = (size_t)(3 * SH * SH + 3 * SH * ST) * C * sizeof(float);
@@ -294,54 +338,88 @@ static int ssim_run(int H, int W, int levels, const float *pred, const float *ta
     size_t nl = gs_align256(level_floats(H, W, C, l) * 4);
     for (int q = 0; q < 3; ++q) { dm[l][q] = (float *)a; a += nl; }
     if (l > 0) {
-      float *pl = (float *)a, *tl = (float *)(a + nl);
+      p[l] = (float *)a; t[l] = (float *)(a + nl);
       d[l] = (float *)(a + 2 * nl);
       a += 3 * nl;
-      p[l] = pl; t[l] = tl;
-      int64_t cnt = (int64_t)hs[l] * ws[l] * C;
-      if (cnt > 0) {
-        k_pool2<<<gs_div_up(cnt, 256), 256, 0, st>>>(hs[l], ws[l], C, ws[l - 1], p[l - 1], l == 1, t[l - 1],
-                                                     l == 1 ? target_u8 : nullptr, pl, tl);
-        GS_LAUNCH_CHECK();
-      }
     }
   }
   GS_CUDA(cudaMemsetAsync(ssim_sums, 0, (size_t)levels * sizeof(float), st));
-  for (int l = 0; l < levels; ++l) {
-    if (hs[l] <= 0 || ws[l] <= 0) continue;
+  // (running the coarse levels on a helper stream beside level 0 was measured: no gain — every kernel here is issue-bound
+  // and fills the machine on its own, and the fork / join events cost what the overlap of the tails saves)
+  cudaStream_t sc = st;
+  auto fwd = [&](int l, cudaStream_t s_) -> int {
+    if (hs[l] <= 0 || ws[l] <= 0) return GS_OK;
     dim3 grid((ws[l] + ST - 1) / ST, (hs[l] + ST - 1) / ST);
-    k_ssim_fwd<C><<<grid, ST * ST, fwd_smem, st>>>(win, hs[l], ws[l], p[l], l == 0, t[l], l == 0 ? target_u8 : nullptr, dm[l][0],
-                                            dm[l][1], dm[l][2], ssim_sums + l);
+    const bool lm = l == 0 && lm_sums != nullptr;
+    k_ssim_fwd<C><<<grid, ST * ST, fwd_smem, s_>>>(win, hs[l], ws[l], p[l], l == 0, t[l], l == 0 ? target_u8 : nullptr, dm[l][0],
+                                            dm[l][1], dm[l][2], ssim_sums + l, w_l1, w_mse,
+                                            1.0f / (float)((int64_t)H * W * C), lm ? d_pred : nullptr, lm ? lm_sums : nullptr);
     GS_LAUNCH_CHECK();
-  }
-  if (!d_pred) return GS_OK;
-  for (int l = levels - 1; l >= 0; --l) {  // coarse to fine: level l adds the upsampled gradient of level l + 1
-    if (hs[l] <= 0 || ws[l] <= 0) continue;
+    return GS_OK;
+  };
+  auto bwd = [&](int l, cudaStream_t s_) -> int {
+    if (hs[l] <= 0 || ws[l] <= 0) return GS_OK;
     dim3 grid((ws[l] + ST - 1) / ST, (hs[l] + ST - 1) / ST);
     double count = (hs[l] > 10 && ws[l] > 10) ? (double)(hs[l] - 10) * (ws[l] - 10) * C : 0.0;
     // loss = weight * mean_l (1 - ssim_l), ssim_l = sum_l / count_l
     float scale = count > 0 ? (float)(-(double)weight / ((double)levels * count)) : 0.f;
     bool has_coarse = l + 1 < levels && hs[l + 1] > 0 && ws[l + 1] > 0;
-    k_ssim_bwd<C><<<grid, ST * ST, bwd_smem, st>>>(win, hs[l], ws[l], p[l], l == 0, t[l], l == 0 ? target_u8 : nullptr, dm[l][0],
+    k_ssim_bwd<C><<<grid, ST * ST, bwd_smem, s_>>>(win, hs[l], ws[l], p[l], l == 0, t[l], l == 0 ? target_u8 : nullptr, dm[l][0],
                                             dm[l][1], dm[l][2], scale, d[l], l == 0, has_coarse ? d[l + 1] : nullptr,
                                             has_coarse ? hs[l + 1] : 0, has_coarse ? ws[l + 1] : 0);
     GS_LAUNCH_CHECK();
+    return GS_OK;
+  };
+  // coarse chain: pool 1..L-1, forward 1..L-1, backward L-1..1 (coarse to fine: level l adds the upsampled gradient of l+1)
+  for (int l = 1; l < levels; ++l) {
+    int64_t cnt = (int64_t)hs[l] * ws[l] * C;
+    if (cnt > 0) {
+      k_pool2<<<gs_div_up(cnt, 256), 256, 0, sc>>>(hs[l], ws[l], C, ws[l - 1], p[l - 1], l == 1, t[l - 1],
+                                                   l == 1 ? target_u8 : nullptr, (float *)p[l], (float *)t[l]);
+      GS_LAUNCH_CHECK();
+    }
   }
-  return GS_OK;
+  int rc;
+  if ((rc = fwd(0, st)) != GS_OK) return rc;
+  for (int l = 1; l < levels; ++l)
+    if ((rc = fwd(l, sc)) != GS_OK) return rc;
+  if (d_pred)
+    for (int l = levels - 1; l >= 1; --l)
+      if ((rc = bwd(l, sc)) != GS_OK) return rc;
+  if (!d_pred) return GS_OK;
+  return bwd(0, st);
+}
+
+static int loss_entry(const char *who, int height, int width, int channels, int levels, const float *pred, const float *target,
+                      const uint8_t *target_u8, float weight, float *d_pred, float *ssim_sums, void *workspace,
+                      size_t workspace_bytes, float w_l1, float w_mse, float *l1_mse_sums, cudaStream_t st) {
+  GS_REQUIRE(pred && (target || target_u8) && ssim_sums && workspace, "null argument");
+  GS_REQUIRE(height > 0 && width > 0, "bad image size");
+  GS_REQUIRE(levels >= 1 && levels <= 8, "levels must be 1..8");
+  if (workspace_bytes < gs_ssim_workspace_bytes(height, width, channels, levels)) {
+    gs_set_error("%s: workspace too small", who);
+    return GS_ERR_WORKSPACE;
+  }
+  if (l1_mse_sums) GS_CUDA(cudaMemsetAsync(l1_mse_sums, 0, 2 * sizeof(float), st));
+  switch (channels) {
+    case 1: return ssim_run<1>(height, width, levels, pred, target, target_u8, weight, d_pred, ssim_sums, workspace, st, w_l1, w_mse, l1_mse_sums);
+    case 3: return ssim_run<3>(height, width, levels, pred, target, target_u8, weight, d_pred, ssim_sums, workspace, st, w_l1, w_mse, l1_mse_sums);
+    case 4: return ssim_run<4>(height, width, levels, pred, target, target_u8, weight, d_pred, ssim_sums, workspace, st, w_l1, w_mse, l1_mse_sums);
+    default: gs_set_error("%s: channels must be 1, 3 or 4", who); return GS_ERR_UNSUPPORTED;
+  }
 }
 
 extern "C" int gs_ssim_loss(int height, int width, int channels, int levels, const float *pred, const float *target,
                             const uint8_t *target_u8, float weight, float *d_pred, float *ssim_sums, void *workspace,
                             size_t workspace_bytes, void *stream) {
-  GS_REQUIRE(pred && (target || target_u8) && ssim_sums && workspace, "null argument");
-  GS_REQUIRE(height > 0 && width > 0, "bad image size");
-  GS_REQUIRE(levels >= 1 && levels <= 8, "levels must be 1..8");
-  if (workspace_bytes < gs_ssim_workspace_bytes(height, width, channels, levels)) { gs_set_error("gs_ssim_loss: workspace too small"); return GS_ERR_WORKSPACE; }
-  cudaStream_t st = (cudaStream_t)stream;
-  switch (channels) {
-    case 1: return ssim_run<1>(height, width, levels, pred, target, target_u8, weight, d_pred, ssim_sums, workspace, st);
-    case 3: return ssim_run<3>(height, width, levels, pred, target, target_u8, weight, d_pred, ssim_sums, workspace, st);
-    case 4: return ssim_run<4>(height, width, levels, pred, target, target_u8, weight, d_pred, ssim_sums, workspace, st);
-    default: gs_set_error("gs_ssim_loss: channels must be 1, 3 or 4"); return GS_ERR_UNSUPPORTED;
-  }
+  return loss_entry("gs_ssim_loss", height, width, channels, levels, pred, target, target_u8, weight, d_pred, ssim_sums, workspace,
+                    workspace_bytes, 0.f, 0.f, nullptr, (cudaStream_t)stream);
+}
+
+extern "C" int gs_photometric_loss(int height, int width, int channels, int levels, const float *pred, const float *target,
+                                   const uint8_t *target_u8, float w_l1, float w_mse, float w_ssim, float *d_pred,
+                                   float *l1_mse_sums, float *ssim_sums, void *workspace, size_t workspace_bytes, void *stream) {
+  GS_REQUIRE(d_pred && l1_mse_sums, "null argument");
+  return loss_entry("gs_photometric_loss", height, width, channels, levels, pred, target, target_u8, w_ssim, d_pred, ssim_sums,
+                    workspace, workspace_bytes, w_l1, w_mse, l1_mse_sums, (cudaStream_t)stream);
 }

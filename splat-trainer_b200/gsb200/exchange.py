@@ -12,9 +12,16 @@ Transport (the records are written once and read in place):
   "nccl"  plain buffers + one all_gather_into_tensor of the fixed-capacity records, folded from the local copy.
   "local" world size 1 (or tests): records of several emulated ranks in one process.
 
-Every rank needs the summed gradients and `visible` in full (replicated optimiser), so those are folded for all rows by
-every rank; the controller statistics (split_score, prune_cost, points_in_view, visibility) are folded by each rank for
-its own row slice only and all-gathered when a densification reads them (Trainer.sync_statistics).
+Optimiser sharding (`shard`):
+  "replicated"  every rank folds the summed gradients and `visible` of ALL rows and steps all of them (the replicas
+                stay identical without a second exchange; cost grows with the world size).
+  "rows"        (peer transport) SURVEY 8(e)(1): rank r folds and steps only rows [r·N/W, (r+1)·N/W) and then writes the
+                parameter rows it touched into every peer's copy of the packed parameter buffer, which therefore lives
+                in symmetric memory; a second stream-ordered barrier ends the step.  The optimiser state of a row
+                (moments, running visibility, step count) exists only on its owner until Trainer.sync_statistics()
+                all-gathers it (before a densification, a checkpoint or a replica comparison).
+In both modes the controller statistics (split_score, prune_cost, points_in_view, visibility) are folded by each rank
+for its own row slice only and all-gathered when a densification reads them (Trainer.sync_statistics).
 """
 import torch
 import torch.distributed as dist
@@ -26,7 +33,7 @@ ATTRS = ("position", "log_scaling", "rotation", "alpha_logit", "sh")
 
 
 class ImageExchange:
-  def __init__(self, scene, world=1, rank=0, cap=0, images_per_rank=1, transport="auto", group=None):
+  def __init__(self, scene, world=1, rank=0, cap=0, images_per_rank=1, transport="auto", group=None, shard="auto"):
     self.scene, self.world, self.rank, self.k = scene, world, rank, images_per_rank
     self.group = group
     self.n = scene.n
@@ -65,6 +72,41 @@ class ImageExchange:
     b = min(rank * self.slice_len, self.n)
     self.stats_rows = (b, min(b + self.slice_len, self.n)) if world > 1 else (0, self.n)
     self._grads_ptr = scene.grads.data_ptr()
+    # row-sharded optimiser: needs peer memory (the updated rows are pushed into the peers' parameter planes)
+    if shard == "rows" and (self.transport != "peer" or world <= 1):
+      raise L.GsError(f"shard='rows' needs the peer transport and world > 1 (transport {self.transport!r}, world {world})")
+    self.shard = "rows" if (shard in ("auto", "rows") and self.transport == "peer" and world > 1) else "replicated"
+    self.grad_rows = self.stats_rows if self.shard == "rows" else (0, self.n)
+    if self.shard == "rows":
+      self._param_buf, self._param_handle = self._symmetric_params()
+      self.param_groups, _ = ops.exchange_groups([scene.p[a] for a in ATTRS])
+      self.param_peers = [int(p) for q, p in enumerate(self._param_handle.buffer_ptrs) if q != rank]
+
+  def _symmetric_params(self):
+    """the scene's packed parameter buffer in symmetric memory (moved there once per buffer: start-up, and each side of
+    the densification ping-pong); every rank runs this at the same point of its program."""
+    import torch.distributed._symmetric_memory as symm
+    scene = self.scene
+    reg = scene.__dict__.setdefault("_symm_params", {})
+    spare = getattr(scene, "_spare", None)
+    live = {scene.params.data_ptr()} | ({spare[0].data_ptr()} if spare else set())
+    for key in [k for k in reg if k not in live]:
+      del reg[key]
+    if scene.params.data_ptr() not in reg:
+      buf = symm.empty((scene.params.numel(),), dtype=torch.float32, device=scene.device)
+      handle = symm.rendezvous(buf, self.group or dist.group.WORLD)
+      buf.copy_(scene.params)
+      scene.params = buf
+      scene._view(scene.n)
+      reg[buf.data_ptr()] = (buf, handle)
+    return reg[scene.params.data_ptr()]
+
+  def publish(self):
+    """rows mode, after scene.step(rows=self.grad_rows): push the slice's touched parameter rows to the peers and close
+    the step with a barrier (the next forward on any rank reads all rows)."""
+    scene = self.scene
+    ops.exchange_publish(scene._vis_idx, self.grad_rows[0], self.param_groups, self._param_buf.data_ptr(), self.param_peers)
+    dist.all_reduce(self._token, group=self.group)
 
   def stale(self):
     """True once the scene re-allocated its packed buffers (densification): build a new ImageExchange."""
@@ -111,7 +153,7 @@ class ImageExchange:
     scene._mark("exchange_wait")  # barrier / all-gather, including the wait for the slowest rank's image
     ptrs = extra_ptrs if extra_ptrs is not None else self.record_ptrs()
     ops.exchange_fold(self.n, ptrs, self.cap, self.groups, c.split_alpha, c.prune_alpha, scene.stats,
-                      scene_visible=scene.visible, stats_rows=self.stats_rows)
+                      scene_visible=scene.visible, stats_rows=self.stats_rows, grad_rows=self.grad_rows)
     if self.transport == "peer":
       self.parity ^= 1
 

@@ -129,9 +129,11 @@ SIGNATURES = {
   "gs_exchange_pack": (_I, [_L, _P, _P, _I, _P, _I, _P, _P, _I, _P, _XG, _P, _L, _P, _Z, _P]),
   "gs_ssim_workspace_bytes": (_Z, [_I, _I, _I, _I]),
   "gs_ssim_loss": (_I, [_I, _I, _I, _I, _P, _P, _P, _F, _P, _P, _P, _Z, _P]),
+  "gs_photometric_loss": (_I, [_I, _I, _I, _I, _P, _P, _P, _F, _F, _F, _P, _P, _P, _P, _Z, _P]),
   "gs_mcmc_noise": (_I, [_L, _P, _P, _P, _P, _I, _F, _F, _P, _P, _P]),
   "gs_reg_loss": (_I, [_L, _F, _F, _F, _P, _P, _P, _P, _I, _P, _I, _P, _I, _P, _P, _P]),
-  "gs_exchange_fold": (_I, [_L, _I, C.POINTER(C.c_void_p), _L, _XG, _F, _F, _P, _P, _P, _P, _L, _L, _P, _P]),
+  "gs_exchange_fold": (_I, [_L, _I, C.POINTER(C.c_void_p), _L, _XG, _F, _F, _P, _P, _P, _P, _L, _L, _L, _L, _P, _P]),
+  "gs_exchange_publish": (_I, [_P, _P, _L, _L, _XG, _P, _I, C.POINTER(C.c_void_p), _P]),
 }
 
 _lib = None

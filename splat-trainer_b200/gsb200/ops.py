@@ -437,15 +437,26 @@ def exchange_pack(g2d, vis, heur, max_scale_px, groups, record, cap, workspace, 
                                     workspace.numel(), L.stream()))
 
 
-def exchange_fold(n, record_ptrs, cap, groups, split_alpha, prune_alpha, state, scene_visible=None, stats_rows=None):
+def exchange_fold(n, record_ptrs, cap, groups, split_alpha, prune_alpha, state, scene_visible=None, stats_rows=None,
+                  grad_rows=None):
   """record_ptrs: device (or peer-mapped) addresses of the step's records in image order.  stats_rows: (begin, end) of
-  the rows whose controller statistics this call folds (default: all)."""
+  the rows whose controller statistics this call folds (default: all); grad_rows: likewise for the gradient rows and
+  `visible` (the row-sharded optimiser folds its own slice only)."""
   arr = (C.c_void_p * len(record_ptrs))(*[int(p) for p in record_ptrs])
   b, e = (0, n) if stats_rows is None else stats_rows
+  gb, ge = (0, n) if grad_rows is None else grad_rows
   L.check(L.load().gs_exchange_fold(n, len(record_ptrs), arr, int(cap), C.byref(groups), split_alpha, prune_alpha,
                                     L.ptr(state["prune_cost"]), L.ptr(state["split_score"]),
-                                    L.ptr(state["points_in_view"]), L.ptr(state["visibility"]), int(b), int(e),
+                                    L.ptr(state["points_in_view"]), L.ptr(state["visibility"]), int(b), int(e), int(gb), int(ge),
                                     L.ptr(scene_visible), L.stream()))
+
+
+def exchange_publish(indexes, row_begin, param_groups, local_base, peer_bases):
+  """gs_exchange_publish: the parameter rows `indexes` (a VisibleIndexes over the slice starting at row_begin) go to
+  every peer's copy of the packed parameter buffer.  param_groups: exchange_groups() over the PARAMETER planes."""
+  arr = (C.c_void_p * max(len(peer_bases), 1))(*[int(p) for p in peer_bases])
+  L.check(L.load().gs_exchange_publish(L.ptr(indexes.indexes), L.ptr(indexes.count), indexes.n, int(row_begin),
+                                       C.byref(param_groups), int(local_base), len(peer_bases), arr, L.stream()))
 
 
 # ---- per-step controller / scene passes (include/gsb200.h section 7) -----------------------------------------------
@@ -503,6 +514,19 @@ def ssim_loss(pred, target, levels=3, weight=1.0, d_pred=None, sums=None, worksp
   L.check(L.load().gs_ssim_loss(H, W, C_, int(levels), L.ptr(_f32(pred)), L.ptr(tf), L.ptr(tu), float(weight), L.ptr(d_pred),
                                 L.ptr(sums), L.ptr(workspace), workspace.numel(), L.stream()))
   return sums
+
+
+def photometric_loss(pred, target, w_l1, w_mse, w_ssim, levels, d_pred, loss_sums, ssim_sums, workspace):
+  """gs_photometric_loss: loss_l1_mse + ssim_loss in one call (reference trainer/trainer.py:465-498); d_pred WRITTEN,
+  loss_sums (2,) and ssim_sums (levels,) zeroed and filled on the device."""
+  H, W, C_ = pred.shape
+  tf = target if target.dtype == torch.float32 else None
+  tu = target if target.dtype == torch.uint8 else None
+  assert tf is not None or tu is not None, "target must be float32 or uint8"
+  L.check(L.load().gs_photometric_loss(H, W, C_, int(levels), L.ptr(_f32(pred)), L.ptr(tf), L.ptr(tu), float(w_l1), float(w_mse),
+                                       float(w_ssim), L.ptr(d_pred), L.ptr(loss_sums), L.ptr(ssim_sums), L.ptr(workspace),
+                                       workspace.numel(), L.stream()))
+  return loss_sums, ssim_sums
 
 
 # ---- colour MLP path (include/gsb200.h section 9) -------------------------------------------------------------------

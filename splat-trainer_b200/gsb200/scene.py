@@ -293,9 +293,13 @@ class SplatScene:
   # ---- MCMC controller (reference controller/mcmc_controller.py:69-100) ---------------------------------------------
   stats_partial = None  # set by the Trainer under data parallelism while each rank holds only a slice of the statistics
 
+  state_partial = None  # likewise for the optimiser state under the row-sharded optimiser
+
   def _require_full_stats(self):
     if self.stats_partial:
       raise L.GsError(f"scene statistics are incomplete on this rank: {self.stats_partial}")
+    if self.state_partial:
+      raise L.GsError(f"optimiser state is incomplete on this rank: {self.state_partial}")
 
   def mcmc_noise(self, noise_level, min_views=5, opacity_threshold=0.1, randn=None):
     """noise branch (:91-100).  randn: (N,3) N(0,1) draws (None: torch's CUDA generator; seed it identically on every
@@ -332,11 +336,12 @@ class SplatScene:
     c = self.config
     if target_ready is not None:
       torch.cuda.current_stream().wait_event(target_ready)
-    w["loss_sums"].zero_()
-    ops.loss_l1_mse(w["image"], target, c.w_l1, c.w_mse, d_pred=w["d_image"], sums=w["loss_sums"])
-    if c.w_ssim != 0.0:  # multi-scale SSIM (reference trainer/trainer.py:450-462); its gradient joins d_image
-      ops.ssim_loss(w["image"], target, c.ssim_levels, c.w_ssim, d_pred=w["d_image"], sums=w["ssim_sums"],
-                    workspace=w["ssim_ws"])
+    if c.w_ssim != 0.0:  # L1/MSE + multi-scale SSIM (reference trainer/trainer.py:450-498), one fused call
+      ops.photometric_loss(w["image"], target, c.w_l1, c.w_mse, c.w_ssim, c.ssim_levels, w["d_image"], w["loss_sums"],
+                           w["ssim_sums"], w["ssim_ws"])
+    else:
+      w["loss_sums"].zero_()
+      ops.loss_l1_mse(w["image"], target, c.w_l1, c.w_mse, d_pred=w["d_image"], sums=w["loss_sums"])
     self._mark("loss")
     acc = w["acc"]
     ops.raster_bwd(self.raster_cfg, w["g2d"], w["rgb"], tb.overlap_to_point, tb.tile_ranges, cam.width, cam.height,
@@ -375,25 +380,33 @@ class SplatScene:
     return w["loss_sums"]
 
   # ---- optimiser step (reference scene/mlp_scene.py:214-239) -----------------------------------------------------
-  def step(self):
+  def step(self, rows=None):
+    """rows = (begin, end): step only that row slice (row-sharded optimiser under DP, begin a multiple of 128; the
+    other rows' state on this rank is then stale until Trainer.sync_statistics gathers it)."""
     c, o = self.config, self.ocfg
     vis, rv, st = self.visible, self.running_vis, self.opt_step
+    p, g, m1, m2 = self.p, self.g, self.m1, self.m2
+    n = self.n
+    if rows is not None and rows != (0, self.n):
+      b, e = rows
+      n = e - b
+      vis, rv, st = vis[b:e], rv[b:e], st[b:e]
+      p, g, m1, m2 = ({k: v[b:e] for k, v in d.items()} for d in (p, g, m1, m2))
     self._mark("optim_begin")
-    if self._vis_idx is None or self._vis_idx.n != self.n:
-      self._vis_idx = ops.VisibleIndexes(self.n, self.device)
+    if self._vis_idx is None or self._vis_idx.n != n:
+      self._vis_idx = ops.VisibleIndexes(n, self.device)
     # visibility state + device-side visible.nonzero() (reference mlp_scene.py:217) in one kernel, no host sync
     ix = self._vis_idx.begin(o, vis, rv, st)
-    p, g, m1, m2 = self.p, self.g, self.m1, self.m2
     # two launches instead of five: position's local basis is built from log_scaling / rotation BEFORE their update
     # (mlp_scene.py:219), so those two groups go in the second launch; groups within a launch are independent
     G = ops.optim_group
-    ops.optim_step_groups(o, self.n, [
+    ops.optim_step_groups(o, n, [
       G(L.GS_GROUP_LOCAL_VECTOR, c.lr_position, p["position"], g["position"], m1["position"], m2["position"],
         basis_ls=p["log_scaling"], basis_q=p["rotation"]),
       G(L.GS_GROUP_SCALAR, c.lr_alpha_logit, p["alpha_logit"], g["alpha_logit"], m1["alpha_logit"], m2["alpha_logit"]),
       G(L.GS_GROUP_VECTOR, c.lr_feature if self.color is not None else c.lr_sh, p["sh"], g["sh"], m1["sh"], m2["sh"])],
       vis, rv, st, indexes=ix)
-    ops.optim_step_groups(o, self.n, [
+    ops.optim_step_groups(o, n, [
       G(L.GS_GROUP_SCALAR, c.lr_log_scaling, p["log_scaling"], g["log_scaling"], m1["log_scaling"], m2["log_scaling"],
         post=L.GS_POST_CLAMP, post_lo=-8.0, post_hi=8.0),
       G(L.GS_GROUP_VECTOR, c.lr_rotation, p["rotation"], g["rotation"], m1["rotation"], m2["rotation"],

@@ -37,10 +37,12 @@ class StageTimer:
 
 class Trainer:
   def __init__(self, scene, world_size=1, rank=0, exchange="auto", exchange_cap=0, images_per_rank=1, controller=None,
-               check_every=50, strict_overflow=False):
+               check_every=50, strict_overflow=False, shard="auto"):
     """exchange: "auto" (sparse per-image records over peer memory when world_size > 1), "peer", "nccl" (records
     all-gathered with NCCL), "dense" (SUM all-reduce of the whole packed gradient buffer; statistics stay per rank:
     a bench arm only, densification raises) or an ImageExchange instance.
+    shard: "rows" (each rank folds and steps its own row slice and pushes the updated rows to its peers; needs the peer
+    transport), "replicated" (every rank steps every row) or "auto" (rows whenever the transport is peer memory).
     controller: a gsb200.controller.TargetController stepped after every optimiser step (reference
     trainer/trainer.py:672-689).  check_every: the two device-side overflow flags (tile list, exchange record) are read
     every that many steps and right after a densification — one 8-byte read; on overflow the buffer is regrown for the
@@ -64,9 +66,14 @@ class Trainer:
         from .exchange import ImageExchange
         scene.zero_grad()
         self.exchange = ImageExchange(scene, world_size, rank, cap=exchange_cap, images_per_rank=images_per_rank,
-                                      transport=exchange)
+                                      transport=exchange, shard=shard)
     else:
       self.exchange = exchange
+
+  @property
+  def sharded(self):
+    """True when the optimiser is sharded by row slice (ImageExchange shard="rows")."""
+    return getattr(self.exchange, "shard", "replicated") == "rows"
 
   def _to_device(self, image):
     """host (pinned) uint8/float image -> one of two reusable device buffers, copied on a side stream so the transfer
@@ -120,7 +127,7 @@ class Trainer:
     cap = min(self.scene.n, int(rows * margin) + 4096)
     self.scene.zero_grad()
     self.exchange = ImageExchange(self.scene, ex.world, ex.rank, cap=cap, images_per_rank=ex.k, transport=ex.transport,
-                                  group=ex.group)
+                                  group=ex.group, shard=getattr(ex, "shard", "auto"))
     return rows
 
   def sync_statistics(self):
@@ -137,20 +144,36 @@ class Trainer:
       # the scene was resized by a densification since the last fold: its statistics are the fresh all-zero PointState on
       # every rank (reference controller/target_controller.py:122), nothing to gather
       self.scene.stats_partial = None
+      self.scene.state_partial = None
       return
     dist.all_reduce(st["max_scale_px"], op=dist.ReduceOp.MAX)
     self.scene.stats_partial = None
     if ex is None or ex.stats_rows == (0, self.scene.n):
       return
-    b, e = ex.stats_rows
     for k in ("prune_cost", "split_score", "visibility", "points_in_view"):
-      t = st[k]
-      dt = torch.int32 if t.dtype == torch.int16 else t.dtype  # NCCL has no int16
-      send = torch.zeros((ex.slice_len,), device=t.device, dtype=dt)
-      send[:e - b] = t[b:e].to(dt)
-      out = torch.empty((self.world_size * ex.slice_len,), device=t.device, dtype=dt)
-      dist.all_gather_into_tensor(out, send, group=ex.group)
-      t.copy_(out[:self.scene.n].to(t.dtype))
+      self._gather_rows(st[k])
+    if self.sharded and getattr(self.scene, "state_partial", None):
+      # row-sharded optimiser: moments, running visibility and step counts live on the slice's owner
+      sc = self.scene
+      for name in sc.m1:
+        self._gather_rows(sc.m1[name])
+        self._gather_rows(sc.m2[name])
+      self._gather_rows(sc.running_vis)
+      self._gather_rows(sc.opt_step)
+      sc.state_partial = None
+
+  def _gather_rows(self, t):
+    """t: (n, ...) contiguous view whose rows [b, e) of this rank's slice are current -> all rows current (all-gather of
+    the equal-length, zero-padded slices, in place)."""
+    ex, n = self.exchange, self.scene.n
+    b, e = ex.stats_rows
+    flat = t.view(n, -1)
+    dt = torch.int32 if t.dtype == torch.int16 else t.dtype  # NCCL has no int16
+    send = torch.zeros((ex.slice_len, flat.shape[1]), device=t.device, dtype=dt)
+    send[:e - b] = flat[b:e].to(dt)
+    out = torch.empty((self.world_size * ex.slice_len, flat.shape[1]), device=t.device, dtype=dt)
+    dist.all_gather_into_tensor(out, send, group=ex.group)
+    flat.copy_(out[:n].to(t.dtype))
 
   def check_overflow(self):
     """read the device-side overflow flags of the last step (tile-overlap list; exchange record) — one small host read,
@@ -171,7 +194,7 @@ class Trainer:
         from .exchange import ImageExchange
         scene.zero_grad()  # rows a full record dropped are still in the dense buffer
         self.exchange = ImageExchange(scene, ex.world, ex.rank, cap=min(scene.n, 2 * ex.cap), images_per_rank=ex.k,
-                                      transport=ex.transport, group=ex.group)
+                                      transport=ex.transport, group=ex.group, shard=getattr(ex, "shard", "auto"))
         grew.append("exchange_record")
     if grew:
       self.overflow_events.append((self.steps_done, grew))
@@ -181,7 +204,10 @@ class Trainer:
     return grew
 
   def state_dict(self):
-    """the reference's checkpoint layout (trainer/trainer.py:188-194): dict(step, scene, controller)."""
+    """the reference's checkpoint layout (trainer/trainer.py:188-194): dict(step, scene, controller).  Under DP every
+    rank must call it (the row slices of the statistics / optimiser state are gathered first)."""
+    if self.world_size > 1 and not self.dense:
+      self.sync_statistics()
     ctrl = self.controller.state_dict() if self.controller is not None else dict(
         points={k: v.clone() for k, v in self.scene.stats.items()}, start_points=self.scene.num_points)
     return dict(step=int(self.step_count), scene=self.scene.state_dict(), controller=ctrl)
@@ -213,7 +239,8 @@ class Trainer:
       from .exchange import ImageExchange
       e = self.exchange
       scene.zero_grad()
-      self.exchange = ImageExchange(scene, e.world, e.rank, cap=e.cap, images_per_rank=e.k, transport=e.transport, group=e.group)
+      self.exchange = ImageExchange(scene, e.world, e.rank, cap=e.cap, images_per_rank=e.k, transport=e.transport, group=e.group,
+                                    shard=getattr(e, "shard", "auto"))
     if self.exchange is not None and len(mine) != self.exchange.k:
       raise L.GsError(f"the exchange was sized for {self.exchange.k} image(s) per rank, got {len(mine)}")
     for k, item in enumerate(mine):
@@ -229,7 +256,13 @@ class Trainer:
       total = sums.clone() if total is None else total + sums
     self.step_count += len(batch)  # the reference counts images, trainer/trainer.py:532
     self.exchange_gradients()
-    scene.step()
+    if self.sharded:
+      scene.step(rows=self.exchange.grad_rows)
+      self.exchange.publish()
+      scene.state_partial = "each rank holds the optimiser state of its own row slice: call Trainer.sync_statistics() first"
+      scene._mark("publish")
+    else:
+      scene.step()
     self._grads_clean = True  # scene.step() cleared every gradient row it consumed
     self.steps_done += 1
     if self._check_now or (self.check_every > 0 and self.steps_done % self.check_every == 0):

@@ -19,7 +19,7 @@ def _port():
     return s.getsockname()[1]
 
 
-@pytest.mark.parametrize("transport", ["auto", "nccl", "dense"])
+@pytest.mark.parametrize("transport", ["auto", "peer-replicated", "nccl", "dense"])
 def test_two_gpu_dp_equals_sequential(transport):
   if torch.cuda.device_count() < 2:
     pytest.skip("needs 2 GPUs")

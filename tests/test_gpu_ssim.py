@@ -64,3 +64,30 @@ def test_ssim_identical_images():
   counts = ops.ssim_counts(64, 64, 3, 2)
   assert all(abs(float(s) / c - 1.0) < 1e-5 for s, c in zip(npy(sums), counts))
   assert d.abs().max().item() < 1e-4
+
+
+@pytest.mark.parametrize("size,levels,C,u8", [((70, 90), 3, 3, True), ((97, 64), 2, 4, False), ((48, 48), 1, 1, False),
+                                              ((240, 323), 3, 3, True)])
+def test_photometric_loss_is_l1_mse_then_ssim(size, levels, C, u8):
+  """gs_photometric_loss (the fused call of the training path, reference trainer/trainer.py:465-498) against the two
+  separate entry points and against the oracle's gso_loss_l1_mse + gso_ssim_loss on an over-shooting render."""
+  H, W = size
+  pred, target = _images(H, W, C, H + 7, overshoot=1.0)
+  tu8 = np.round(target * 255).astype(np.uint8)
+  tgt = cu(tu8) if u8 else cu(target)
+  tref = tu8.astype(np.float32) / np.float32(255.0) if u8 else target
+  ws = ops.ssim_workspace(H, W, C, levels)
+  d = torch.full((H, W, C), 7.0, device="cuda")  # WRITTEN, whatever was there
+  ls = torch.full((2,), 3.0, device="cuda"); ss = torch.full((levels,), 3.0, device="cuda")
+  ops.photometric_loss(cu(pred), tgt, 0.3, 10.0, 0.7, levels, d, ls, ss, ws)
+  d2 = torch.zeros((H, W, C), device="cuda")
+  _, ls2 = ops.loss_l1_mse(cu(pred), tgt, 0.3, 10.0, d_pred=d2)
+  ss2 = ops.ssim_loss(cu(pred), tgt, levels, 0.7, d_pred=d2)
+  assert np.allclose(npy(ls), npy(ls2), rtol=2e-6) and np.allclose(npy(ss), npy(ss2), rtol=2e-6)
+  assert np.abs(npy(d) - npy(d2)).max() <= 1e-7 * max(1.0, float(d2.abs().max()))
+  o = oracle()
+  d_lm, sums_ref = o.loss_l1_mse(pred, None if u8 else target, 0.3, 10.0, target_u8=tu8 if u8 else None)
+  _, d_ss, _ = o.ssim_loss(np.clip(pred, 0, 1), tref, levels=levels, weight=0.7)
+  d_ref = d_lm + np.where((pred >= 0) & (pred <= 1), d_ss, 0)
+  assert np.allclose(npy(ls), sums_ref, rtol=1e-4)
+  assert np.abs(npy(d) - d_ref).max() / np.abs(d_ref).max() < 2e-3
