@@ -411,12 +411,20 @@ __global__ void __launch_bounds__(PB_THREADS) k_project_bwd(CamDev cam, CfgDev c
   if (threadIdx.x == 0) s_count = 0;
   __syncthreads();
   int64_t base = (int64_t)blockIdx.x * PB_ROWS;
+  // scan of the CTA's rows: all loads of the "blended by some pixel" plane are issued before the first test (this sweep of
+  // n rows is all the kernel does for most CTAs; at the occupancy the row work below allows, dependent loads one after the
+  // other left it latency-bound); the flag of the forward culling is only read for the few rows that pass
+  float rv[PB_ITEMS];
 #pragma unroll
   for (int k = 0; k < PB_ITEMS; ++k) {
     int64_t i = base + k * PB_THREADS + threadIdx.x;
-    if (i >= n) continue;
-    if (row_vis && !(row_vis[(int64_t)row_vis_stride * i] > 0.f)) continue;  // blended by no pixel (contiguous plane: test first)
-    if (!(g2d[GS_G2D_STRIDE * i + 5] > 0.f)) continue;                       // culled in forward
+    rv[k] = (i < n) ? (row_vis ? row_vis[(int64_t)row_vis_stride * i] : 1.f) : 0.f;
+  }
+#pragma unroll
+  for (int k = 0; k < PB_ITEMS; ++k) {
+    if (!(rv[k] > 0.f)) continue;  // blended by no pixel
+    int64_t i = base + k * PB_THREADS + threadIdx.x;
+    if (!(g2d[GS_G2D_STRIDE * i + 5] > 0.f)) continue;  // culled in forward
     s_list[atomicAdd(&s_count, 1)] = (int)(i - base);
   }
   __syncthreads();

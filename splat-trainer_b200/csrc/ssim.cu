@@ -58,8 +58,7 @@ template <int C>
 __global__ void __launch_bounds__(ST * ST) k_ssim_fwd(Win win, int H, int W, const float *__restrict__ pred, int clamp_pred,
                                                       const float *__restrict__ target, const uint8_t *__restrict__ target_u8,
                                                       float *__restrict__ dm1, float *__restrict__ dm2, float *__restrict__ dm3,
-                                                      float *__restrict__ sum_out, float w_l1, float w_mse, float inv_n,
-                                                      float *__restrict__ lm_dpred, float *__restrict__ lm_sums) {
+                                                      float *__restrict__ sum_out, float *__restrict__ lm_sums) {
   extern __shared__ float ssim_smem[];
   float *sP = ssim_smem, *sT = sP + SH * SH * C, *sHz = sT + SH * SH * C;
   constexpr int HZ = SH * ST * C;  // one horizontally filtered plane
@@ -89,18 +88,15 @@ __global__ void __launch_bounds__(ST * ST) k_ssim_fwd(Win win, int H, int W, con
       if (i < SH * SH * C) {
         sP[i] = clamp_pred ? clamp01(pl[it]) : pl[it];
         sT[i] = target_u8 ? u8_unit(tl[it]) : tl[it];
-        // gs_loss_l1_mse's arithmetic for the 16x16 pixels this tile owns: the values are in registers anyway, so the
-        // separate loss kernel and its sweep of the image are gone
-        int c = i % C, rx = (i / C) % SH, ry = i / (C * SH);
+        // gs_loss_l1_mse's sums over the 16x16 pixels this tile owns: the values are in registers anyway, so the separate
+        // loss kernel and its sweep of the image are gone (its gradient is formed by the level-0 backward, which holds
+        // the same pixel again when it writes d pred)
+        int rx = (i / C) % SH, ry = i / (C * SH);
         int gx = tx0 - SR + rx, gy = ty0 - SR + ry;
         if (lm_sums && rx >= SR && rx < SR + ST && ry >= SR && ry < SR + ST && gx < W && gy < H) {
-          float pr = pl[it];
-          bool ins = (pr >= 0.f) && (pr <= 1.f);
-          float dd = clamp01(pr) - sT[i];
+          float dd = sP[i] - sT[i];  // (level 0: sP holds the clamped render)
           lm1 += fabsf(dd);
           lm2 += dd * dd;
-          float sg = dd > 0.f ? 1.f : (dd < 0.f ? -1.f : 0.f);
-          if (lm_dpred) lm_dpred[((int64_t)gy * W + gx) * C + c] = ins ? (w_l1 * sg + w_mse * 2.0f * dd) * inv_n : 0.f;
         }
       }
     }
@@ -205,7 +201,8 @@ __global__ void __launch_bounds__(ST * ST) k_ssim_bwd(Win win, int H, int W, con
                                                       const float *__restrict__ target, const uint8_t *__restrict__ target_u8,
                                                       const float *__restrict__ dm1, const float *__restrict__ dm2,
                                                       const float *__restrict__ dm3, float scale, float *__restrict__ d_out,
-                                                      int accumulate, const float *__restrict__ d_coarse, int hc, int wc) {
+                                                      int accumulate, const float *__restrict__ d_coarse, int hc, int wc,
+                                                      int lm, float w_l1, float w_mse, float inv_n) {
   extern __shared__ float ssim_smem[];
   constexpr int HM = SH * SH * C, HZ = SH * ST * C;
   float *sM = ssim_smem, *sHz = sM + 3 * HM;
@@ -269,6 +266,11 @@ __global__ void __launch_bounds__(ST * ST) k_ssim_bwd(Win win, int H, int W, con
       // transpose of the 2x2 average pooling: a quarter of the next coarser level's gradient (already complete: the
       // backward runs coarse to fine), for pixels inside the pooled area (floor sizes)
       if (d_coarse && (gy >> 1) < hc && (gx >> 1) < wc) d += 0.25f * d_coarse[((int64_t)(gy >> 1) * wc + (gx >> 1)) * C + c];
+      if (lm) {  // + the L1 / MSE gradient of gs_loss_l1_mse on the same pixel (gs_photometric_loss: d pred is written once)
+        float dd = p - t;
+        float sg = dd > 0.f ? 1.f : (dd < 0.f ? -1.f : 0.f);
+        d += (w_l1 * sg + w_mse * 2.0f * dd) * inv_n;
+      }
       if (clamp_pred && !(raw >= 0.f && raw <= 1.f)) d = 0.f;
       if (accumulate) d_out[gi] += d; else d_out[gi] = d;
     }
@@ -352,11 +354,11 @@ static int ssim_run(int H, int W, int levels, const float *pred, const float *ta
     dim3 grid((ws[l] + ST - 1) / ST, (hs[l] + ST - 1) / ST);
     const bool lm = l == 0 && lm_sums != nullptr;
     k_ssim_fwd<C><<<grid, ST * ST, fwd_smem, s_>>>(win, hs[l], ws[l], p[l], l == 0, t[l], l == 0 ? target_u8 : nullptr, dm[l][0],
-                                            dm[l][1], dm[l][2], ssim_sums + l, w_l1, w_mse,
-                                            1.0f / (float)((int64_t)H * W * C), lm ? d_pred : nullptr, lm ? lm_sums : nullptr);
+                                            dm[l][1], dm[l][2], ssim_sums + l, lm ? lm_sums : nullptr);
     GS_LAUNCH_CHECK();
     return GS_OK;
   };
+  const bool lm0 = lm_sums != nullptr;
   auto bwd = [&](int l, cudaStream_t s_) -> int {
     if (hs[l] <= 0 || ws[l] <= 0) return GS_OK;
     dim3 grid((ws[l] + ST - 1) / ST, (hs[l] + ST - 1) / ST);
@@ -365,8 +367,9 @@ static int ssim_run(int H, int W, int levels, const float *pred, const float *ta
     float scale = count > 0 ? (float)(-(double)weight / ((double)levels * count)) : 0.f;
     bool has_coarse = l + 1 < levels && hs[l + 1] > 0 && ws[l + 1] > 0;
     k_ssim_bwd<C><<<grid, ST * ST, bwd_smem, s_>>>(win, hs[l], ws[l], p[l], l == 0, t[l], l == 0 ? target_u8 : nullptr, dm[l][0],
-                                            dm[l][1], dm[l][2], scale, d[l], l == 0, has_coarse ? d[l + 1] : nullptr,
-                                            has_coarse ? hs[l + 1] : 0, has_coarse ? ws[l + 1] : 0);
+                                            dm[l][1], dm[l][2], scale, d[l], l == 0 && !lm0, has_coarse ? d[l + 1] : nullptr,
+                                            has_coarse ? hs[l + 1] : 0, has_coarse ? ws[l + 1] : 0, l == 0 && lm0, w_l1, w_mse,
+                                            1.0f / (float)((int64_t)H * W * C));
     GS_LAUNCH_CHECK();
     return GS_OK;
   };

@@ -127,6 +127,17 @@ __global__ void __launch_bounds__(LC_THREADS) k_live_compact(const int32_t *__re
 #pragma unroll
     for (int i = 0; i < LC_ITEMS; ++i) c[i] = (base + i < m) ? counts[base + i] : 0;
   }
+  // the depth keys of the thread's rows are fetched now, live or not (two 16-byte loads that run under the scan and the
+  // look-back), instead of one dependent 4-byte load per live row after the look-back
+  uint32_t dk[LC_ITEMS];
+  if (base + LC_ITEMS <= m) {
+    const uint4 *p = reinterpret_cast<const uint4 *>(depth + base);
+    uint4 a = p[0], b = p[1];
+    dk[0] = a.x; dk[1] = a.y; dk[2] = a.z; dk[3] = a.w; dk[4] = b.x; dk[5] = b.y; dk[6] = b.z; dk[7] = b.w;
+  } else {
+#pragma unroll
+    for (int i = 0; i < LC_ITEMS; ++i) dk[i] = (base + i < m) ? __float_as_uint(depth[base + i]) : 0u;
+  }
   int sum = 0;
 #pragma unroll
   for (int i = 0; i < LC_ITEMS; ++i) sum += c[i] > 0;
@@ -146,7 +157,7 @@ __global__ void __launch_bounds__(LC_THREADS) k_live_compact(const int32_t *__re
 #pragma unroll
   for (int i = 0; i < LC_ITEMS; ++i) {
     if (c[i] > 0) {
-      uint32_t key = __float_as_uint(depth[base + i]);
+      uint32_t key = dk[i];
       depth_keys[pos] = key;
       rows[pos] = (uint32_t)(base + i);
       ++pos;
