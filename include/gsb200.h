@@ -261,6 +261,18 @@ size_t gs_visible_indexes_workspace_bytes(int64_t n);
 int gs_visible_indexes(int64_t n, const float *visible, int32_t *indexes, int32_t *count_dev,
                        void *workspace, size_t workspace_bytes, void *stream);
 
+/* gs_visible_indexes for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  No counterpart in the reference.  Same outputs
+ * as gs_visible_indexes, no workspace argument: a single-pass chained-scan compaction whose scratch (one ticket and one
+ * status word per 2048-row tile, 33 KB) is a file-scope device array inside the library, held by every GPU that loads
+ * it until the process exits.  The call performs no cudaMalloc / cudaFree / allocating library call: one
+ * cudaMemsetAsync of the scratch it uses (the array keeps the last call's contents) and one kernel, on `stream`.
+ * Limit: 0 <= n <= GS_VISIBLE_INDEXES_STATIC_MAX_ROWS, beyond which it returns GS_ERR_INVALID with a message.
+ * Every call on a device shares the one array: calls that overlap on the GPU race — serialise them on one stream. */
+#define GS_VISIBLE_INDEXES_STATIC_MAX_ROWS ((int64_t)1 << 24)
+int64_t gs_visible_indexes_static_max_rows(void);
+int gs_visible_indexes_static(int64_t n, const float *visible, int32_t *indexes, int32_t *count_dev, void *stream);
+
 /* gs_optim_vis_update + gs_visible_indexes fused into one pass over `visible` (one kernel, no host sync). */
 size_t gs_optim_begin_workspace_bytes(int64_t n);
 int gs_optim_begin(const gs_optim_config *h_cfg, int64_t n, const float *visible, float *running_vis, float *step,

@@ -102,6 +102,8 @@ SIGNATURES = {
   "gs_optim_vis_update": (_I, [_OPT, _L, _P, _P, _P, _P]),
   "gs_visible_indexes_workspace_bytes": (_Z, [_L]),
   "gs_visible_indexes": (_I, [_L, _P, _P, _P, _P, _Z, _P]),
+  "gs_visible_indexes_static_max_rows": (_L, []),
+  "gs_visible_indexes_static": (_I, [_L, _P, _P, _P, _P]),
   "gs_color_mlp_fwd": (_I, [C.POINTER(ColorMLP), _L, _P, _I, _P, _P, C.POINTER(C.c_float), _P, _F, _P, _P, _P]),
   "gs_color_mlp_bwd": (_I, [C.POINTER(ColorMLP), C.POINTER(ColorMLP), _L, _P, _I, _P, _P, C.POINTER(C.c_float), _P, _F, _P, _I,
                              _F, _P, _P, _P, _I, _P]),
