@@ -23,6 +23,8 @@ Optimiser sharding (`shard`):
 In both modes the controller statistics (split_score, prune_cost, points_in_view, visibility) are folded by each rank
 for its own row slice only and all-gathered when a densification reads them (Trainer.sync_statistics).
 """
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -65,6 +67,9 @@ class ImageExchange:
     elif self.transport == "local":
       self.buf = torch.zeros((slot_bytes,), device=dev, dtype=torch.uint8)
     self._token = torch.zeros((1,), device=dev)
+    # the step's barriers: "nccl" = a 4-byte all-reduce; "symm" = the symmetric-memory signal-pad barrier of the record
+    # buffer's handle (one small kernel, no NCCL launch) — peer transport only
+    self.barrier_kind = os.environ.get("GSB200_BARRIER", "nccl") if self.transport == "peer" else "nccl"
     # controller statistics are only read at a densification: every rank folds them for its own slice of the rows
     # (Trainer.sync_statistics all-gathers the slices), so the statistics cost per rank does not grow with the world
     self.slice_len = (self.n + world - 1) // world
@@ -106,7 +111,15 @@ class ImageExchange:
     the step with a barrier (the next forward on any rank reads all rows)."""
     scene = self.scene
     ops.exchange_publish(scene._vis_idx, self.grad_rows[0], self.param_groups, self._param_buf.data_ptr(), self.param_peers)
-    dist.all_reduce(self._token, group=self.group)
+    self._barrier(1)
+
+  def _barrier(self, channel=0):
+    """stream-ordered barrier across the ranks: everything enqueued before it on any rank is complete (and its peer
+    writes visible) before anything enqueued after it on any rank starts."""
+    if self.barrier_kind == "symm":
+      self.handle.barrier(channel=channel, timeout_ms=20000)
+    else:
+      dist.all_reduce(self._token, group=self.group)
 
   def stale(self):
     """True once the scene re-allocated its packed buffers (densification): build a new ImageExchange."""
@@ -146,8 +159,8 @@ class ImageExchange:
     """make every rank's records visible, then fold them in image order into scene.g / scene.visible / scene.stats."""
     scene, c = self.scene, self.scene.config
     if self.transport == "peer":
-      # stream-ordered NCCL barrier: every rank's pack kernels have completed before any rank's fold starts
-      dist.all_reduce(self._token, group=self.group)
+      # stream-ordered barrier: every rank's pack kernels have completed before any rank's fold starts
+      self._barrier(0)
     elif self.transport == "nccl":
       dist.all_gather_into_tensor(self.gathered, self.buf, group=self.group)
     scene._mark("exchange_wait")  # barrier / all-gather, including the wait for the slowest rank's image
