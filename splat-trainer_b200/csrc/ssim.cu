@@ -9,8 +9,8 @@
 // forward: per-pixel partial derivatives of the map (w.r.t. mu1, E[pp], E[pt]; zero outside the valid crop) + the
 //          sum of the map over the valid crop;
 // backward: the three partial maps blurred with the same window, combined into d pred.
-// Coarser levels: 2x2 average pooling forward; its transpose is folded into the next finer level's backward kernel
-// (the backward runs coarse to fine).  HBM traffic ~ 40 B per pixel-channel per level.
+// Coarser levels: 2x2 average pooling (F.avg_pool2d(2), floor sizes) done by the finer level's forward kernel from the tile
+// it has staged; its transpose is folded into the next finer level's backward kernel (the backward runs coarse to fine).  HBM traffic ~ 40 B per pixel-channel per level.
 #include <math.h>
 
 #include "common.cuh"
@@ -58,7 +58,8 @@ template <int C>
 __global__ void __launch_bounds__(ST * ST) k_ssim_fwd(Win win, int H, int W, const float *__restrict__ pred, int clamp_pred,
                                                       const float *__restrict__ target, const uint8_t *__restrict__ target_u8,
                                                       float *__restrict__ dm1, float *__restrict__ dm2, float *__restrict__ dm3,
-                                                      float *__restrict__ sum_out, float *__restrict__ lm_sums) {
+                                                      float *__restrict__ sum_out, float *__restrict__ lm_sums,
+                                                      float *__restrict__ pool_p, float *__restrict__ pool_t, int hc, int wc) {
   extern __shared__ float ssim_smem[];
   float *sP = ssim_smem, *sT = sP + SH * SH * C, *sHz = sT + SH * SH * C;
   constexpr int HZ = SH * ST * C;  // one horizontally filtered plane
@@ -102,6 +103,26 @@ __global__ void __launch_bounds__(ST * ST) k_ssim_fwd(Win win, int H, int W, con
     }
   }
   __syncthreads();
+  // next coarser level's input (F.avg_pool2d(2), floor sizes) of the tile's own 16x16 pixels: the staged tile holds them, so
+  // the pooling kernel and its sweep of both images are gone.  Same order of additions as the oracle's pooling loop.
+  if (pool_p && tid < (ST / 2) * (ST / 2) * C) {
+    const int c = tid % C, x = (tid / C) % (ST / 2), y = tid / (C * (ST / 2));
+    const int ox = (tx0 >> 1) + x, oy = (ty0 >> 1) + y;
+    if (ox < wc && oy < hc) {
+      float ps = 0.f, ts = 0.f;
+#pragma unroll
+      for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+        for (int dx = 0; dx < 2; ++dx) {
+          const int j = ((SR + 2 * y + dy) * SH + SR + 2 * x + dx) * C + c;
+          ps += sP[j];
+          ts += sT[j];
+        }
+      const int64_t o = ((int64_t)oy * wc + ox) * C + c;
+      pool_p[o] = 0.25f * ps;
+      pool_t[o] = 0.25f * ts;
+    }
+  }
   // horizontal pass: a thread filters 4 consecutive x of one (halo row, channel) for the 5 quantities p, t, pp, tt, pt
   for (int i = tid; i < SH * (ST / SG) * C; i += ST * ST) {
     int c = i % C, xg = (i / C) % (ST / SG), ry = i / (C * (ST / SG));
@@ -277,28 +298,6 @@ __global__ void __launch_bounds__(ST * ST) k_ssim_bwd(Win win, int H, int W, con
   }
 }
 
-// F.avg_pool2d(kernel 2, stride 2) of prediction and target together (floor sizes)
-__global__ void __launch_bounds__(256) k_pool2(int h, int w, int C, int Wf, const float *__restrict__ p_in, int clamp_pred,
-                                               const float *__restrict__ t_in, const uint8_t *__restrict__ t_u8,
-                                               float *__restrict__ p_out, float *__restrict__ t_out) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= (int64_t)h * w * C) return;
-  int c = (int)(i % C);
-  int x = (int)((i / C) % w), y = (int)(i / ((int64_t)C * w));
-  float ps = 0.f, ts = 0.f;
-#pragma unroll
-  for (int dy = 0; dy < 2; ++dy)
-#pragma unroll
-    for (int dx = 0; dx < 2; ++dx) {
-      int64_t j = ((int64_t)(2 * y + dy) * Wf + 2 * x + dx) * C + c;
-      float p = p_in[j];
-      ps += clamp_pred ? clamp01(p) : p;
-      ts += t_u8 ? u8_unit((float)t_u8[j]) : t_in[j];
-    }
-  p_out[i] = 0.25f * ps;
-  t_out[i] = 0.25f * ts;
-}
-
 Win make_window() {
   Win w;
   double t[11], s = 0;
@@ -353,8 +352,11 @@ static int ssim_run(int H, int W, int levels, const float *pred, const float *ta
     if (hs[l] <= 0 || ws[l] <= 0) return GS_OK;
     dim3 grid((ws[l] + ST - 1) / ST, (hs[l] + ST - 1) / ST);
     const bool lm = l == 0 && lm_sums != nullptr;
+    const bool pool = l + 1 < levels && hs[l + 1] > 0 && ws[l + 1] > 0;  // this level's forward also pools for the next
     k_ssim_fwd<C><<<grid, ST * ST, fwd_smem, s_>>>(win, hs[l], ws[l], p[l], l == 0, t[l], l == 0 ? target_u8 : nullptr, dm[l][0],
-                                            dm[l][1], dm[l][2], ssim_sums + l, lm ? lm_sums : nullptr);
+                                            dm[l][1], dm[l][2], ssim_sums + l, lm ? lm_sums : nullptr,
+                                            pool ? (float *)p[l + 1] : nullptr, pool ? (float *)t[l + 1] : nullptr,
+                                            pool ? hs[l + 1] : 0, pool ? ws[l + 1] : 0);
     GS_LAUNCH_CHECK();
     return GS_OK;
   };
@@ -373,19 +375,11 @@ static int ssim_run(int H, int W, int levels, const float *pred, const float *ta
     GS_LAUNCH_CHECK();
     return GS_OK;
   };
-  // coarse chain: pool 1..L-1, forward 1..L-1, backward L-1..1 (coarse to fine: level l adds the upsampled gradient of l+1)
-  for (int l = 1; l < levels; ++l) {
-    int64_t cnt = (int64_t)hs[l] * ws[l] * C;
-    if (cnt > 0) {
-      k_pool2<<<gs_div_up(cnt, 256), 256, 0, sc>>>(hs[l], ws[l], C, ws[l - 1], p[l - 1], l == 1, t[l - 1],
-                                                   l == 1 ? target_u8 : nullptr, (float *)p[l], (float *)t[l]);
-      GS_LAUNCH_CHECK();
-    }
-  }
+  // forward fine to coarse (level l writes level l + 1's pooled inputs), backward coarse to fine (level l adds the
+  // upsampled gradient of l + 1)
   int rc;
-  if ((rc = fwd(0, st)) != GS_OK) return rc;
-  for (int l = 1; l < levels; ++l)
-    if ((rc = fwd(l, sc)) != GS_OK) return rc;
+  for (int l = 0; l < levels; ++l)
+    if ((rc = fwd(l, st)) != GS_OK) return rc;
   if (d_pred)
     for (int l = levels - 1; l >= 1; --l)
       if ((rc = bwd(l, sc)) != GS_OK) return rc;

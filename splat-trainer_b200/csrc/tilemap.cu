@@ -402,6 +402,9 @@ __global__ void __launch_bounds__(EX_THREADS) k_expand(const float *__restrict__
   __shared__ uint32_t sCnt[EX_WARPS][64];
   // persistent CTAs: the grid is sized for the machine, not for the list capacity (a launch with one CTA per POSSIBLE chunk
   // spent most of its time starting CTAs that found nothing to do); the chunk table is staged once per CTA
+  // (the write pass is launched with one CTA per POSSIBLE chunk of the list's capacity: the ones past the real count leave
+  // before staging the table — on C2 that is 48 k of 58 k CTAs)
+  if (WRITE && (int)blockIdx.x >= stab[2 * NS + 1]) return;
   chunk_table(stab, NS, ex_smem);
   const int total_chunks = ex_smem[NS];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;

@@ -20,7 +20,7 @@ COLS = ["Kernel Name", "Grid Size", "Block Size", "gpu__time_duration.sum", "dra
 # stage of the bench's stages_ms each kernel belongs to
 STAGES = [("project_fwd", r"k_project_fwd"), ("tile_map", r"k_live_compact|k_os_|k_super_emit|k_seg_tables|k_expand|k_chunk_prefix"),
           ("raster_bwd", r"k_raster_bwd"), ("raster_fwd", r"k_raster_fwd|k_raster_records"), ("tile_order", r"k_tile_order"),
-          ("loss", r"k_loss_l1_mse|k_pool2|k_ssim_"),
+          ("loss", r"k_loss_l1_mse|k_ssim_"),
           ("reg", r"k_reg_"), ("project_bwd", r"k_project_bwd"), ("stats", r"k_accumulate_stats|k_pack_|k_fold_"),
           ("optim", r"k_optim_")]
 
