@@ -53,6 +53,7 @@ def parse():
   ap.add_argument("--shard", default="auto", choices=["auto", "rows", "replicated"],
                   help="N>1: optimiser sharded by row slice (each rank steps N/W rows and pushes them to its peers) or replicated")
   ap.add_argument("--raster", default="async", choices=["async", "gather"])
+  ap.add_argument("--exchange-cap", type=int, default=0, help="testing: initial rows per exchange record (0 = a quarter of the scene)")
   ap.add_argument("--c5-steps", type=int, default=2000, help="c5: optimiser steps of the whole 500k -> 5M run")
   return ap.parse_args()
 
@@ -268,6 +269,40 @@ def replicas_identical(scene, world, trainer=None):
   dist.all_reduce(lo, op=dist.ReduceOp.MIN)
   dist.all_reduce(hi, op=dist.ReduceOp.MAX)
   return bool(torch.equal(lo, hi))
+
+
+def replica_diagnosis(scene, trainer, rank, step):
+  """GS_C5_DIAG=1 (debugging aid, not a bench mode): after every step gather the row slices and compare every state tensor
+  across the ranks; prints the first divergence (tensor, differing elements, first row) and returns True."""
+  import torch
+  import torch.distributed as dist
+  if trainer.exchange is not None and trainer.exchange.stale():
+    return False  # right after a densification: compared after the next step
+  trainer.sync_statistics()
+  named = dict(params=scene.params[:scene._total], exp_avg=scene.exp_avg[:scene._total], exp_avg_sq=scene.exp_avg_sq_flat,
+               running_vis=scene.running_vis, opt_step=scene.opt_step, grads=scene.grads,
+               **{"stats." + k: v.float() for k, v in scene.stats.items()})
+  for k in ATTR_NAMES:
+    named["p." + k] = scene.p[k].reshape(scene.n, -1)
+    named["m1." + k] = scene.m1[k].reshape(scene.n, -1)
+    named["m2." + k] = scene.m2[k].reshape(scene.n, -1)
+  bad = []
+  for name, t in named.items():
+    lo, hi = t.clone(), t.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    diff = (lo != hi)
+    cnt = int(diff.sum().item())
+    if cnt:
+      first = int(diff.reshape(diff.shape[0], -1).any(dim=1).nonzero()[0].item()) if diff.dim() > 1 else int(diff.nonzero()[0].item())
+      bad.append((name, cnt, first, tuple(t.shape)))
+  if bad and rank == 0:
+    ex = trainer.exchange
+    print(f"[diag] step {step}: n={scene.n} slice_len={ex.slice_len} rows={ex.grad_rows} densified={len(trainer.controller.history) if trainer.controller else 0} "
+          f"overflow_events={trainer.overflow_events} diverged: {bad}", file=sys.stderr, flush=True)
+  return bool(bad)
+
+
+ATTR_NAMES = ("position", "log_scaling", "rotation", "alpha_logit", "sh")
 
 
 def run_b200(args):
@@ -518,7 +553,7 @@ def run_c5(args):
   target_points = 10 * wl["n"]
   total_images = args.c5_steps * world  # the reference's schedule counts images (trainer/trainer.py:532)
   scene = SplatScene(wl["gaussians"], SceneConfig(sh_degree=wl["sh_degree"], raster=args.raster, capacity=int(1.02 * target_points)))
-  trainer = Trainer(scene, world, rank, exchange=args.exchange, check_every=25, shard=args.shard)
+  trainer = Trainer(scene, world, rank, exchange=args.exchange, check_every=25, shard=args.shard, exchange_cap=args.exchange_cap)
   controller = TargetController(TargetConfig(), scene, target_points, total_images, trainer=trainer, seed=0)
   controller.record_events = True
   trainer.controller = controller
@@ -540,6 +575,8 @@ def run_c5(args):
     t0 = time.perf_counter()
     for i in range(args.c5_steps):
       trainer.training_step(batch_for(i))
+      if world > 1 and os.environ.get("GS_C5_DIAG") and replica_diagnosis(scene, trainer, rank, i):
+        break
     e1.record()
     torch.cuda.synchronize()
     if world > 1:

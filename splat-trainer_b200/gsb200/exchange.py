@@ -86,6 +86,7 @@ class ImageExchange:
       self._param_buf, self._param_handle = self._symmetric_params()
       self.param_groups, _ = ops.exchange_groups([scene.p[a] for a in ATTRS])
       self.param_peers = [int(p) for q, p in enumerate(self._param_handle.buffer_ptrs) if q != rank]
+    self._params_ptr = scene.params.data_ptr()
 
   def _symmetric_params(self):
     """the scene's packed parameter buffer in symmetric memory (moved there once per buffer: start-up, and each side of
@@ -122,8 +123,11 @@ class ImageExchange:
       dist.all_reduce(self._token, group=self.group)
 
   def stale(self):
-    """True once the scene re-allocated its packed buffers (densification): build a new ImageExchange."""
-    return self.n != self.scene.n or self._grads_ptr != self.scene.grads.data_ptr()
+    """True once the scene resized or swapped its packed buffers (densification): build a new ImageExchange.  The
+    parameter buffer is compared too: a densification that prunes as many rows as it adds keeps n and the gradient buffer
+    but swaps the ping-pong parameter buffers, and the row-sharded publish holds their addresses."""
+    return (self.n != self.scene.n or self._grads_ptr != self.scene.grads.data_ptr()
+            or self._params_ptr != self.scene.params.data_ptr())
 
   # ---- this rank's side ----------------------------------------------------------------------------------
   def _local_offset(self, slot, parity=None):

@@ -116,6 +116,27 @@ def main():
           print(f"[{mode}] after densify: replicas identical {name}: {same}")
     elif rank == 0:
       print(f"[{mode}] after densify: point counts differ across ranks FAIL")
+  # 4. a densification that leaves the row count unchanged (prunes as many as it adds: the steady state of the target
+  #    schedule) only swaps the ping-pong parameter buffers; the exchange must notice and follow them
+  if mode != "dense":
+    tr.controller = None
+    tr.sync_statistics()
+    n0 = scene.num_points
+    scene.split_and_prune(torch.ones((n0,), device="cuda", dtype=torch.bool))
+    scene.stats = scene.new_point_state(scene.num_points)
+    for b in more[:2]:
+      tr.training_step(b)
+    tr.sync_statistics()
+    torch.cuda.synchronize()
+    same_all = scene.num_points == n0
+    for name, t in dict(params=scene.params[:scene._total], exp_avg=scene.exp_avg[:scene._total]).items():
+      lo, hi = t.clone(), t.clone()
+      dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+      same = bool(torch.equal(lo, hi))
+      same_all &= same
+      if rank == 0:
+        print(f"[{mode}] after a size-preserving densify: replicas identical {name}: {same}")
+    ok &= same_all
   flag = torch.tensor([0 if ok else 1], device="cuda")
   dist.all_reduce(flag)
   dist.destroy_process_group()
