@@ -35,7 +35,10 @@ ATTRS = ("position", "log_scaling", "rotation", "alpha_logit", "sh")
 
 
 class ImageExchange:
-  def __init__(self, scene, world=1, rank=0, cap=0, images_per_rank=1, transport="auto", group=None, shard="auto"):
+  def __init__(self, scene, world=1, rank=0, cap=0, images_per_rank=1, transport="auto", group=None, shard="auto", reuse=None):
+    """reuse: the ImageExchange this one replaces (after a densification): its symmetric record buffer is taken over when it
+    is large enough, so that a growing scene does not pay an allocation + rendezvous across the ranks per densification
+    (the buffer is laid out for the scene's row capacity the first time)."""
     self.scene, self.world, self.rank, self.k = scene, world, rank, images_per_rank
     self.group = group
     self.n = scene.n
@@ -53,10 +56,21 @@ class ImageExchange:
     if self.transport == "peer":
       try:
         import torch.distributed._symmetric_memory as symm
-        self.buf = symm.empty((2 * slot_bytes,), dtype=torch.uint8, device=dev)
-        self.handle = symm.rendezvous(self.buf, group or dist.group.WORLD)
-        self.peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]
-        self.buf.zero_()
+        if (reuse is not None and reuse.transport == "peer" and reuse.world == world and reuse.group is group
+            and reuse.buf.numel() >= 2 * slot_bytes):
+          # every rank is past the barrier that closed the last step: nobody reads these records any more
+          self.buf, self.handle, self.peer_ptrs = reuse.buf, reuse.handle, reuse.peer_ptrs
+          for parity in (0, 1):
+            for slot in range(self.k):
+              o = parity * slot_bytes + slot * self.rec_bytes
+              self.buf[o:o + 8].zero_()  # count / overflow header of the (now meaningless) old records
+        else:
+          rows = max(self.n, int(getattr(scene, "capacity", 0) or 0))
+          room = 2 * self.k * ops.exchange_record_bytes(rows, self.cap, self.row_floats)
+          self.buf = symm.empty((max(room, 2 * slot_bytes),), dtype=torch.uint8, device=dev)
+          self.handle = symm.rendezvous(self.buf, group or dist.group.WORLD)
+          self.peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]
+          self.buf.zero_()
       except Exception as e:  # symmetric memory unavailable on this box: NCCL all-gather transport (still GPU-only)
         if transport == "peer":
           raise
@@ -67,9 +81,12 @@ class ImageExchange:
     elif self.transport == "local":
       self.buf = torch.zeros((slot_bytes,), device=dev, dtype=torch.uint8)
     self._token = torch.zeros((1,), device=dev)
-    # the step's barriers: "nccl" = a 4-byte all-reduce; "symm" = the symmetric-memory signal-pad barrier of the record
-    # buffer's handle (one small kernel, no NCCL launch) — peer transport only
-    self.barrier_kind = os.environ.get("GSB200_BARRIER", "nccl") if self.transport == "peer" else "nccl"
+    # the step's two barriers: "symm" = the symmetric-memory signal-pad barrier of the record buffer's handle (one small
+    # kernel, no NCCL launch: 8 GPUs, c2-sparse 4556 -> 4631 it/s) — peer transport only; "nccl" = a 4-byte all-reduce
+    # (GSB200_BARRIER=nccl selects it)
+    self.barrier_kind = "nccl"
+    if self.transport == "peer" and hasattr(self.handle, "barrier"):
+      self.barrier_kind = os.environ.get("GSB200_BARRIER", "symm")
     # controller statistics are only read at a densification: every rank folds them for its own slice of the rows
     # (Trainer.sync_statistics all-gathers the slices), so the statistics cost per rank does not grow with the world
     self.slice_len = (self.n + world - 1) // world

@@ -127,7 +127,7 @@ class Trainer:
     cap = min(self.scene.n, int(rows * margin) + 4096)
     self.scene.zero_grad()
     self.exchange = ImageExchange(self.scene, ex.world, ex.rank, cap=cap, images_per_rank=ex.k, transport=ex.transport,
-                                  group=ex.group, shard=getattr(ex, "shard", "auto"))
+                                  group=ex.group, shard=getattr(ex, "shard", "auto"), reuse=ex)
     return rows
 
   def sync_statistics(self):
@@ -194,7 +194,7 @@ class Trainer:
         from .exchange import ImageExchange
         scene.zero_grad()  # rows a full record dropped are still in the dense buffer
         self.exchange = ImageExchange(scene, ex.world, ex.rank, cap=min(scene.n, 2 * ex.cap), images_per_rank=ex.k,
-                                      transport=ex.transport, group=ex.group, shard=getattr(ex, "shard", "auto"))
+                                      transport=ex.transport, group=ex.group, shard=getattr(ex, "shard", "auto"), reuse=ex)
         grew.append("exchange_record")
     if grew:
       self.overflow_events.append((self.steps_done, grew))
@@ -240,7 +240,7 @@ class Trainer:
       e = self.exchange
       scene.zero_grad()
       self.exchange = ImageExchange(scene, e.world, e.rank, cap=e.cap, images_per_rank=e.k, transport=e.transport, group=e.group,
-                                    shard=getattr(e, "shard", "auto"))
+                                    shard=getattr(e, "shard", "auto"), reuse=e)
     if self.exchange is not None and len(mine) != self.exchange.k:
       raise L.GsError(f"the exchange was sized for {self.exchange.k} image(s) per rank, got {len(mine)}")
     for k, item in enumerate(mine):
