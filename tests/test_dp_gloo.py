@@ -196,3 +196,119 @@ def test_replicated_colour_model_stays_identical_under_dp(tmp_path):
     cm.step()
   assert torch.allclose(r[0]["flat"], cm.flat, rtol=0, atol=1e-5) and torch.allclose(r[0]["glo"], cm.glo, rtol=0, atol=1e-5)
   assert r[0]["glo"][1].abs().max() > 0 and r[0]["glo"][2].abs().max() > 0 and not r[0]["glo"][0].any() and not r[0]["glo"][3].any()
+
+
+# ---- row-sharded optimiser: fold + step own row slice, publish the rows, gather the state ------------
+class RowsScene(StubScene):
+  """StubScene + per-row optimiser state and controller statistics, stepped by row slice like SplatScene.step(rows=)."""
+  n = N
+
+  def __init__(self):
+    super().__init__()
+    self.m1 = dict(w=torch.zeros(N, D))
+    self.m2 = dict(w=torch.zeros(N))
+    self.running_vis, self.opt_step = torch.zeros(N), torch.zeros(N)
+    self.stats = dict(max_scale_px=torch.zeros(N), prune_cost=torch.zeros(N), split_score=torch.zeros(N),
+                      visibility=torch.zeros(N), points_in_view=torch.zeros(N, dtype=torch.int16))
+    self.stats_partial = self.state_partial = None
+
+  def step(self, rows=None):
+    b, e = rows if rows is not None else (0, N)
+    g = self.grads[:N * D].view(N, D)
+    sel = torch.zeros(N, dtype=torch.bool)
+    sel[b:e] = self.visible[b:e] > 0
+    self.m1["w"][sel] = 0.9 * self.m1["w"][sel] + 0.1 * g[sel]
+    self.m2["w"][sel] += 1.0
+    self.opt_step[sel] += 1.0
+    self.running_vis[sel] = 0.5 * self.running_vis[sel] + 0.5 * self.visible[sel]
+    self.params[sel] -= 0.1 * self.m1["w"][sel]
+    self.touched = sel
+    self.grads.zero_()
+
+
+class RowsExchange(StubExchange):
+  """shard="rows" protocol: only the rank's slice of every record is folded; publish() sends the rows the rank stepped to
+  every replica (here one all_gather of the slices); the statistics are folded per slice too."""
+  shard, transport, group = "rows", "peer", None
+
+  def __init__(self, world, rank, k):
+    super().__init__(world, rank, k)
+    self.slice_len = (N + world - 1) // world
+    b = min(rank * self.slice_len, N)
+    self.grad_rows = self.stats_rows = (b, min(b + self.slice_len, N))
+    self.published = 0
+
+  def fold(self):
+    gathered = [torch.zeros_like(self.records) for _ in range(self.world)]
+    dist.all_gather(gathered, self.records)
+    b, e = self.grad_rows
+    g, vis = self.scene.grads[:N * D].view(N, D), self.scene.visible
+    for slot in range(self.k):
+      for r in range(self.world):
+        rec = gathered[r][slot]
+        g[b:e] += rec[:N * D].view(N, D)[b:e]
+        vis[b:e] += rec[N * D:][b:e]
+        seen = rec[N * D:][b:e] > 0
+        self.scene.stats["points_in_view"][b:e] += seen.to(torch.int16)
+        self.scene.stats["visibility"][b:e] += rec[N * D:][b:e]
+    self.folds += 1
+
+  def publish(self):
+    b, e = self.grad_rows
+    send = torch.zeros(self.slice_len, D)
+    send[:e - b] = self.scene.params[b:e]
+    out = torch.zeros(self.world * self.slice_len, D)
+    dist.all_gather_into_tensor(out, send)
+    self.scene.params.copy_(out[:N])
+    self.published += 1
+
+
+def rows_worker(rank, world, port, out):
+  os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+  dist.init_process_group("gloo", rank=rank, world_size=world)
+  from gsb200 import lib as L
+  from gsb200.trainer import Trainer
+  scene = RowsScene()
+  ex = RowsExchange(world, rank, 2)
+  ex.scene = scene
+  tr = Trainer(scene, world, rank, exchange=ex)
+  assert tr.sharded
+  for b in make_batches():
+    tr.training_step(b)
+  b, e = ex.grad_rows
+  others = torch.ones(N, dtype=torch.bool)
+  others[b:e] = False
+  partial = dict(stale_moments=bool((scene.m1["w"][others] == 0).all()), flagged=bool(scene.state_partial and scene.stats_partial))
+  tr.sync_statistics()
+  torch.save(dict(params=scene.params, m1=scene.m1["w"], m2=scene.m2["w"], opt_step=scene.opt_step, running_vis=scene.running_vis,
+                  piv=scene.stats["points_in_view"], visibility=scene.stats["visibility"], partial=partial,
+                  published=ex.published, cleared=scene.state_partial is None and scene.stats_partial is None),
+             os.path.join(out, f"rows{rank}.pt"))
+  dist.destroy_process_group()
+
+
+def test_row_sharded_optimiser_equals_sequential(tmp_path):
+  """Trainer with an exchange whose shard is "rows": every rank steps only its row slice (scene.step(rows=...)), publishes
+  it, and Trainer.sync_statistics() gathers the per-slice optimiser state and statistics: afterwards both replicas hold
+  what one process stepping every row holds."""
+  world = 2
+  mp.spawn(rows_worker, args=(world, free_port(), str(tmp_path)), nprocs=world, join=True)
+  r = [torch.load(os.path.join(tmp_path, f"rows{k}.pt")) for k in range(world)]
+  from gsb200.trainer import Trainer
+  seq = RowsScene()
+  seq_tr = Trainer(seq, 1, 0, exchange="dense")
+  piv, visib = torch.zeros(N, dtype=torch.int16), torch.zeros(N)
+  for b in make_batches():
+    seq_tr.training_step(b)
+  for k in range(8):  # the statistics the sharded fold accumulated per slice: every image's visibility of every row
+    rows = (torch.arange(N) + k) % 3 == 0
+    piv += rows.to(torch.int16)
+    visib += rows.float() * 0.25 * (k + 1)
+  for k in ("params", "m1", "m2", "opt_step", "running_vis"):
+    assert torch.equal(r[0][k], r[1][k]), k
+  assert torch.allclose(r[0]["params"], seq.params, rtol=0, atol=1e-5)
+  assert torch.allclose(r[0]["m1"], seq.m1["w"], rtol=0, atol=1e-6) and torch.equal(r[0]["opt_step"], seq.opt_step)
+  assert torch.equal(r[0]["piv"], piv) and torch.equal(r[1]["piv"], piv) and torch.allclose(r[0]["visibility"], visib)
+  for k in range(world):
+    assert r[k]["partial"] == dict(stale_moments=True, flagged=True)  # before the gather: other slices' state untouched
+    assert r[k]["published"] == 2 and r[k]["cleared"]
