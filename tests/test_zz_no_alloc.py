@@ -123,5 +123,5 @@ def test_no_device_allocation_during_the_call():
     L.check(_static(vis, indexes, count))
   torch.cuda.synchronize()
   free1, _ = torch.cuda.mem_get_info()
-  assert free1 == free0 and torch.cuda.memory_reserved() == reserved0
+  assert free1 >= free0 and torch.cuda.memory_reserved() == reserved0  # nothing was taken from the device
   assert int(count.item()) == int((vis > 0).sum().item())
