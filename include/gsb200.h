@@ -447,9 +447,10 @@ int gs_ssim_loss(int height, int width, int channels, int levels, const float *p
                  const uint8_t *target_u8, float weight, float *d_pred, float *ssim_sums, void *workspace,
                  size_t workspace_bytes, void *stream);
 /* The whole image loss of Trainer.compute_losses in one call (reference trainer/trainer.py:465-498: l1 / mse terms +
- * compute_ssim_loss): gs_loss_l1_mse followed by gs_ssim_loss, with the L1/MSE arithmetic done by the level-0 SSIM
- * forward on the pixels it already holds (no separate sweep of the image) and the pooled levels running on a helper
- * stream beside it.  d_pred is WRITTEN; l1_mse_sums[2] = Σ|d|, Σd² and ssim_sums[levels] are zeroed here. */
+ * compute_ssim_loss): the results of gs_loss_l1_mse followed by gs_ssim_loss, in 2 * levels launches: the L1/MSE sums are
+ * taken by the level-0 SSIM forward on the pixels it already holds, every level's forward also writes the 2x2-pooled
+ * inputs of the next level, and the level-0 backward adds the L1/MSE gradient when it writes d_pred — once, no separate
+ * sweep of the image.  d_pred is WRITTEN; l1_mse_sums[2] = Σ|d|, Σd² and ssim_sums[levels] are zeroed here. */
 int gs_photometric_loss(int height, int width, int channels, int levels, const float *pred, const float *target,
                         const uint8_t *target_u8, float w_l1, float w_mse, float w_ssim, float *d_pred,
                         float *l1_mse_sums, float *ssim_sums, void *workspace, size_t workspace_bytes, void *stream);
