@@ -135,7 +135,7 @@ class ImageExchange:
     """stream-ordered barrier across the ranks: everything enqueued before it on any rank is complete (and its peer
     writes visible) before anything enqueued after it on any rank starts."""
     if self.barrier_kind == "symm":
-      self.handle.barrier(channel=channel, timeout_ms=20000)
+      self.handle.barrier(channel=channel, timeout_ms=120000)  # a skewed start is not a hang
     else:
       dist.all_reduce(self._token, group=self.group)
 
